@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py -- cosine top-k queries/s of the exact scan over the BASELINE corpus.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step is one query (batch=1, top_k=10, every document requested, 0.7 floor) answered by one
+pass of the fused scan over the synthetic 10M x 3072 fp32 corpus, which is row-sharded over the
+N ranks (one process per GPU); each rank's local top-k is all-gathered with NCCL and merged.
+Total work is fixed as N grows => "scaling": "strong".
+
+`value`      K / (CUDA-event time of K back-to-back searches, inputs resident in HBM), max over ranks
+`e2e`        the same through the C-ABI call a user makes: host query in, host ids/scores out
+`roofline`   algorithmic bytes of one scan launch / its average CUDA-event duration vs measured HBM peak
+`cpu_baseline` the oracle's pgvector-flag build timed on this box's host cores (bounded sample)
+PyTorch is used only for the process group (barrier, max over ranks, broadcast of the NCCL id).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ROWS = int(os.environ.get("DA_BENCH_ROWS", 10_000_000))
+DIM = int(os.environ.get("DA_BENCH_DIM", 3072))
+TOP_K = 10
+MIN_SIM = 0.7
+METRIC = "cosine top-k queries/sec at 10M x 3072"
+UNIT = "queries/s"
+
+
+def workload_name(n_gpus: int) -> str:
+    return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch=1, top_k={TOP_K}, "
+            f"all documents requested, min_similarity={MIN_SIM}, local top-k + NCCL all-gather merge")
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic():
+    """dram bytes per scan launch from the committed ncu --set full capture, if there is one."""
+    p = os.path.join(ROOT, "profiles", "scan_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.lines: list[str] = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def shard_range(rank: int, world: int, n_rows: int, chunks_per_doc: int):
+    """Rows [lo, hi) of `rank`: contiguous, split on document boundaries (a document stays on one GPU)."""
+    per = -(-n_rows // world)
+    if per % chunks_per_doc:
+        per += chunks_per_doc - per % chunks_per_doc
+    lo = min(n_rows, rank * per)
+    hi = n_rows if rank == world - 1 else min(n_rows, lo + per)
+    return lo, hi
+
+
+def merge_candidates(per_rank, k: int):
+    """Host statement of the device merge: per_rank = [(scores, global_rows)], best first each.
+    Order: score descending, then lower global row (the tie rule of DESIGN.md)."""
+    scores = np.concatenate([np.asarray(s, dtype=np.float32) for s, _ in per_rank])
+    rows = np.concatenate([np.asarray(r, dtype=np.int64) for _, r in per_rank])
+    order = np.lexsort((rows, -scores.astype(np.float64)))[:k]
+    return scores[order], rows[order]
+
+
+def cpu_reference_run(steps: int, warmup: int, want_seconds: float = 12.0):
+    """The reference path's CPU implementation (oracle, pgvector-flag build, all host threads) on a
+    bounded sample of the workload.  Returns (queries/s extrapolated to N_ROWS, info dict, ms_per_step)."""
+    import oracle
+    S = oracle.Synth()
+    threads = oracle.num_threads()
+    sample = int(os.environ.get("DA_CPU_SAMPLE_ROWS", min(N_ROWS, 400_000)))
+    mat = oracle.gen_rows(S, 0, sample, DIM)
+    qs = [oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(max(1, steps + warmup))]
+    one = None
+    for i in range(warmup):
+        t0 = time.perf_counter()
+        oracle.topk(mat, None, None, qs[i], TOP_K, MIN_SIM, fast=True, threads=threads)
+        one = time.perf_counter() - t0
+    if one is None:
+        t0 = time.perf_counter()
+        oracle.topk(mat, None, None, qs[0], TOP_K, MIN_SIM, fast=True, threads=threads)
+        one = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    for i in range(steps):
+        oracle.topk(mat, None, None, qs[warmup + i], TOP_K, MIN_SIM, fast=True, threads=threads)
+    dt = (time.perf_counter() - t0) / steps
+    qps_sample = 1.0 / dt
+    qps_full = qps_sample * sample / N_ROWS
+    info = {"value": qps_full, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": (f"{sample} of {N_ROWS} rows x {DIM} ({sample * DIM * 4 / 1e9:.2f} GB) scanned once per step by "
+                       f"oracle/oracle_fast.c (pgvector build flags, OpenMP, {threads} threads), {steps} steps; "
+                       f"{qps_sample:.2f} queries/s on the sample, linearly extrapolated to {N_ROWS} rows; "
+                       f"{sample * (DIM * 4 + 8) / dt / 1e9:.1f} GB/s effective"),
+            "gbs": sample * (DIM * 4 + 8) / dt / 1e9}
+    return qps_full, info, dt * 1e3 * N_ROWS / sample
+
+
+def run_reference_arm(args, rank: int):
+    if rank != 0:
+        return
+    steps = max(1, args.steps)
+    qps, info, ms = cpu_reference_run(steps, max(0, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.gpus), "note": "CPU path: pgvector semantics restated in C "
+                       "(the reference's Go + Postgres/pgvector cannot run on this box)"},
+            "cpu_baseline": info,
+            "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if world == 1 and args.gpus > 1:
+        raise SystemExit("launch N>1 with torch.distributed.run (one rank per GPU)")
+    warmup = max(3, args.warmup)
+    steps = max(1, args.steps)
+
+    import torch
+    import torch.distributed as dist
+    import oracle   # only for the synthetic-corpus parameters, the queries and the cpu_baseline leg
+    from doc_agents_b200 import GpuStore, build
+
+    build.build()
+    torch.cuda.set_device(local_rank)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.tensor(list(GpuStore.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().tolist())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    S = oracle.Synth()
+    lo, hi = shard_range(rank, world, N_ROWS, S.chunks_per_doc)
+    st = GpuStore(dim=DIM, capacity_rows=max(1, hi - lo), devices=(local_rank,), min_similarity=MIN_SIM,
+                  world_size=world, rank=rank, nccl_id=nccl_id)
+    st.generate_synthetic(S, lo, hi - lo)
+    queries = np.stack([oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(warmup + steps)])
+
+    # warm-up (untimed): W full searches through the public call
+    for i in range(warmup):
+        st.search(queries[i], TOP_K, all_docs=True)
+    st.bench_resident(queries[0], TOP_K, warmup, all_docs=True)
+
+    # ---- timed region 1: K steps, inputs resident in HBM, CUDA events on the launching stream
+    s_before = st.stats()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    ms_total = st.bench_resident(queries[warmup], TOP_K, steps, all_docs=True)
+    barrier()
+    clocks = sampler.stop()
+    s_after = st.stats()
+    ms_total = max_over_ranks(ms_total)
+    launches = int(s_after.kernel_launches - s_before.kernel_launches) - 1      # minus the query-norm kernel of staging
+    scan_launches = int(s_after.scan_launches - s_before.scan_launches)
+    scan_ms = (s_after.scan_ms_sum - s_before.scan_ms_sum) / max(1, scan_launches)
+    bytes_per_launch = int(s_after.last_bytes_algorithmic)
+    value = steps / (ms_total / 1e3)
+
+    # ---- timed region 2: K steps end to end through the C-ABI call (host buffers in and out)
+    barrier()
+    t0 = time.perf_counter()
+    last = None
+    for i in range(steps):
+        last = st.search(queries[warmup + i], TOP_K, all_docs=True)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = steps / e2e_s
+
+    peak, peak_src = measured_peak()
+    achieved = bytes_per_launch / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(world), "rows_per_gpu": hi - lo, "dim": DIM, "top_k": TOP_K,
+                   "batch": 1, "l2": "inputs larger than L2 (%.1f GB per GPU per step vs 126 MB)" % ((hi - lo) * DIM * 4 / 1e9),
+                   "seeds": {"data": hex(S.seed_data), "centroids": hex(S.seed_centroid), "queries": hex(S.seed_query)}},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": DIM * 4, "d2h_bytes_per_step": TOP_K * 24,
+                "ms_per_step": e2e_s * 1e3 / steps},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": recorded_traffic(), "kernel": "scan_topk_kernel", "peak_source": peak_src,
+                     "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,
+                     "frac_of_nominal_8000": achieved / 8000.0},
+        "result_check": {"hits": int(len(last[2][0])), "top_score": float(last[1][0][0]) if len(last[1][0]) else None},
+    }
+    st.close()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        _, info, _ = cpu_reference_run(steps=3, warmup=1)
+        line["cpu_baseline"] = info
+    if world > 1:
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,109 @@
+// Internal declarations shared by the .cu translation units of libdocagents_b200.so.
+// Not part of the C ABI (include/docagents_b200.h is).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+namespace da {
+
+// ---------------------------------------------------------------------------
+// Candidate key: one 64-bit integer orders (score desc, global row asc).
+//   hi 32 = order-preserving image of the fp32 similarity
+//   lo 32 = ~global_row                 (lower row => larger key)
+// 0 is "empty".  Ordering ties the way DESIGN.md "Tie rule" states.
+// ---------------------------------------------------------------------------
+typedef unsigned long long key_t64;
+
+__host__ __device__ inline uint32_t score_to_ordered(float f)
+{
+#ifdef __CUDA_ARCH__
+    uint32_t b = __float_as_uint(f);
+#else
+    union { float f; uint32_t u; } c; c.f = f; uint32_t b = c.u;
+#endif
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ inline float ordered_to_score(uint32_t o)
+{
+    uint32_t b = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    union { float f; uint32_t u; } c; c.u = b; return c.f;
+#endif
+}
+__host__ __device__ inline key_t64 make_key(float score, uint32_t global_row)
+{
+    return ((key_t64)score_to_ordered(score) << 32) | (key_t64)(~global_row);
+}
+__host__ __device__ inline uint32_t key_row(key_t64 k) { return ~(uint32_t)(k & 0xFFFFFFFFull); }
+__host__ __device__ inline float key_score(key_t64 k) { return ordered_to_score((uint32_t)(k >> 32)); }
+
+// ---------------------------------------------------------------------------
+// Exact scan
+// ---------------------------------------------------------------------------
+constexpr int kScanThreads = 512;
+constexpr int kScanWarps = kScanThreads / 32;
+constexpr int kMaxNQ = 8;          // queries served by one pass of the SIMT scan
+
+struct ScanArgs {
+    const float *mat;              // n_rows x dim, row-major, 16-byte aligned rows
+    const float *inv_norm;         // 1/|row| (0 for a zero row)
+    const uint32_t *doc_slot;      // document slot of each row
+    const uint8_t *chunk_ids;      // 16 bytes per row
+    const uint32_t *doc_bitmap;    // bit per document slot; nullptr = every document
+    const float *queries;          // nq x dim (device)
+    const float *q_inv_norm;       // nq
+    const uint32_t *row_list;      // optional: scan only these rows (IVF probe lists); nullptr = [0,n_rows)
+    uint32_t n_rows;               // rows (or entries of row_list) to visit
+    uint32_t row_base;             // global row of local row 0
+    int dim;
+    int nq;                        // <= kMaxNQ
+    int k;
+    int P;                         // pow2 >= kScanWarps * k   (smem sort width)
+    float min_sim;
+    int read_all;                  // 1: doc mask applied after reading the row
+    key_t64 *cta_out;              // gridDim.x x nq x k   scratch
+    unsigned int *counter;         // scratch: last-block ticket (left at 0)
+    key_t64 *out_keys;             // nq x k, best first, 0-padded
+    uint8_t *out_ids;              // nq x k x 16
+    unsigned long long *rows_read; // optional statistics counter
+};
+
+size_t scan_smem_bytes(int dim, int nq, int k, int *P_out);
+int scan_pick_nq(int dim, int k, int batch);   // how many queries one pass may carry
+// Launches the fused scan on `stream`; grid is chosen inside (persistent, multiple of SM count).
+cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t stream, int *grid_out);
+int scan_grid_for(int sm_count);
+
+// Merge of G gathered candidate blocks (one block per rank, layout: batch*k keys then batch*k*16 ids).
+cudaError_t launch_merge(const uint8_t *gathered, int G, int batch, int k, key_t64 *out_keys,
+                         uint8_t *out_ids, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------
+// Row maintenance
+// ---------------------------------------------------------------------------
+// inv_norm / doc_slot / chunk id of the rows listed in `rows`.
+cudaError_t launch_finalize_rows(const float *mat, int dim, const uint32_t *rows, const uint32_t *slots,
+                                 const uint8_t *ids, uint32_t n, float *inv_norm, uint32_t *doc_slot,
+                                 uint8_t *chunk_ids, cudaStream_t stream);
+cudaError_t launch_query_inv_norm(const float *queries, int dim, int nq, float *out, cudaStream_t stream);
+
+struct SynthArgs {
+    uint64_t seed_data, seed_centroid, seed_ids;
+    uint32_t chunks_per_doc, n_clusters;
+    int32_t cmul, nmul;
+    uint64_t row_lo;               // global row of local row 0
+    uint32_t n_rows;
+    uint32_t doc_slot_base;        // global doc index mapped to slot 0
+    int dim;
+};
+cudaError_t launch_synth(const SynthArgs &a, float *mat, float *inv_norm, uint32_t *doc_slot,
+                         uint8_t *chunk_ids, cudaStream_t stream);
+
+// Host restatement of the id hash of the synthetic corpus (spec: DESIGN.md).
+void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);
+
+}  // namespace da

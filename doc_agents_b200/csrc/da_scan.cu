@@ -1,0 +1,357 @@
+// Fused exact scan for sm_100a: cosine score + document mask + similarity floor + top-k
+// in one pass over the resident embedding matrix.
+//
+// Replaces the per-row `e.vector <=> $1` loop, the `document_id = ANY($2)` filter, the
+// `>= 0.7` floor, ORDER BY and LIMIT of the reference's one SQL statement
+// (internal/store/postgres.go:225-243).  HBM-bound: 4*dim + 8 bytes per row, 2*dim flops.
+//
+// Shape of the kernel
+//   - persistent grid (multiple of the SM count), 16 warps per CTA;
+//   - a warp owns R consecutive rows at a time and streams them with 128-bit
+//     ld.global.nc.L1::no_allocate loads, R*U of them in flight per lane;
+//   - queries live in shared memory (up to 8 per pass, so a small batch re-uses every
+//     row fetched from HBM);
+//   - each warp keeps its own top-k (unsorted, with a cached minimum) in shared memory;
+//     inserts are rare once the list is warm, so bookkeeping stays off the load path;
+//   - CTA epilogue: bitonic sort of the warps' lists, k keys per query to global scratch;
+//   - the last CTA to finish (ticket counter) merges all CTAs' keys, gathers the chunk
+//     ids and writes the final records: one launch per pass, no host round trip.
+#include "da_internal.h"
+
+namespace da {
+
+namespace {
+
+__device__ __forceinline__ float4 ldg_stream(const float4 *p)
+{
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ key_t64 warp_min_key(key_t64 v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        key_t64 t = __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        v = t < v ? t : v;
+    }
+    return v;
+}
+
+// Unsorted bounded list with cached minimum.  All lanes call with identical arguments.
+__device__ __forceinline__ void warp_list_insert(key_t64 *list, int K, int &cnt, key_t64 &wmin,
+                                                 key_t64 key, int lane)
+{
+    if (cnt < K) {
+        if (lane == 0) list[cnt] = key;
+        cnt++;
+        __syncwarp();
+        if (cnt == K) {
+            key_t64 m = ~0ull;
+            for (int i = lane; i < K; i += 32) { key_t64 t = list[i]; m = t < m ? t : m; }
+            wmin = warp_min_key(m);
+        }
+        return;
+    }
+    if (key <= wmin) return;
+    // keys are unique (they embed the row), so exactly one slot holds wmin
+    for (int i = lane; i < K; i += 32)
+        if (list[i] == wmin) list[i] = key;
+    __syncwarp();
+    key_t64 m = ~0ull;
+    for (int i = lane; i < K; i += 32) { key_t64 t = list[i]; m = t < m ? t : m; }
+    wmin = warp_min_key(m);
+}
+
+// In-place descending bitonic sort of P (power of two) keys in shared memory by the whole CTA.
+__device__ void cta_bitonic_desc(key_t64 *buf, int P)
+{
+    for (int size = 2; size <= P; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
+                int lo = 2 * t - (t & (stride - 1));
+                int hi = lo + stride;
+                bool desc = ((lo & size) == 0);
+                key_t64 a = buf[lo], b = buf[hi];
+                if ((a < b) == desc) { buf[lo] = b; buf[hi] = a; }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+template <int NQ, int R, int U, bool FULL_TILES>
+__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int D4 = a.dim >> 2;
+    float4 *q_s = reinterpret_cast<float4 *>(smem_raw);                       // NQ x D4
+    key_t64 *lists = reinterpret_cast<key_t64 *>(smem_raw + (size_t)NQ * D4 * sizeof(float4));  // NQ x P
+    __shared__ float q_inv_s[NQ];
+    __shared__ unsigned int is_last_s;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int K = a.k, P = a.P;
+
+    // stage queries (rows beyond a.nq are zero so they never qualify) and clear the lists
+    for (int i = tid; i < NQ * D4; i += kScanThreads) {
+        int q = i / D4;
+        q_s[i] = (q < a.nq) ? reinterpret_cast<const float4 *>(a.queries)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int i = tid; i < NQ * P; i += kScanThreads) lists[i] = 0ull;
+    if (tid < NQ) q_inv_s[tid] = (tid < a.nq) ? a.q_inv_norm[tid] : 0.f;
+    __syncthreads();
+
+    int cnt[NQ];
+    key_t64 wmin[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; q++) { cnt[q] = 0; wmin[q] = 0ull; }
+
+    const uint32_t n_groups = (a.n_rows + R - 1) / R;
+    const uint32_t gstride = gridDim.x * kScanWarps;
+    unsigned int my_rows_read = 0;
+
+    for (uint32_t g = blockIdx.x * kScanWarps + warp; g < n_groups; g += gstride) {
+        const uint32_t row0 = g * R;
+        // lane r (< R) looks at row0 + r: document mask and 1/|row|
+        uint32_t my_row = row0 + lane;
+        bool valid = (lane < R) && (my_row < a.n_rows);
+        bool wanted = valid;
+        float my_inv = 0.f;
+        if (valid) {
+            my_inv = a.inv_norm[my_row];
+            if (a.doc_bitmap) {
+                uint32_t slot = a.doc_slot[my_row];
+                wanted = (a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u;
+            }
+        }
+        const uint32_t valid_mask = __ballot_sync(0xFFFFFFFFu, valid);
+        const uint32_t want_mask = __ballot_sync(0xFFFFFFFFu, wanted);
+        const uint32_t load_mask = a.read_all ? valid_mask : want_mask;
+        if (load_mask == 0) continue;
+        my_rows_read += __popc(load_mask);
+
+        float acc[R][NQ];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+#pragma unroll
+            for (int q = 0; q < NQ; q++) acc[r][q] = 0.f;
+
+        const float4 *rp = reinterpret_cast<const float4 *>(a.mat) + (size_t)row0 * D4;
+
+        for (int c0 = 0; c0 < D4; c0 += 32 * U) {
+            float4 v[R][U];
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    int c = c0 + u * 32 + lane;
+                    bool ok = ((load_mask >> r) & 1u) && (FULL_TILES || c < D4);
+                    v[r][u] = ok ? ldg_stream(rp + (size_t)r * D4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                int c = c0 + u * 32 + lane;
+                if (!FULL_TILES && c >= D4) c = 0;   // v is zero there; any in-range q slot will do
+#pragma unroll
+                for (int q = 0; q < NQ; q++) {
+                    float4 qv = q_s[q * D4 + c];
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        acc[r][q] = fmaf(v[r][u].x, qv.x, acc[r][q]);
+                        acc[r][q] = fmaf(v[r][u].y, qv.y, acc[r][q]);
+                        acc[r][q] = fmaf(v[r][u].z, qv.z, acc[r][q]);
+                        acc[r][q] = fmaf(v[r][u].w, qv.w, acc[r][q]);
+                    }
+                }
+            }
+        }
+
+#pragma unroll
+        for (int r = 0; r < R; r++)
+#pragma unroll
+            for (int q = 0; q < NQ; q++) {
+                float s = acc[r][q];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+                acc[r][q] = s;
+            }
+
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const float inv = __shfl_sync(0xFFFFFFFFu, my_inv, r);
+            if (!((want_mask >> r) & 1u) || !(inv > 0.f)) continue;     // zero-norm rows never match
+#pragma unroll
+            for (int q = 0; q < NQ; q++) {
+                float sim = acc[r][q] * inv * q_inv_s[q];
+                sim = fminf(1.f, fmaxf(-1.f, sim));                     // pgvector clamps to [-1, 1]
+                if (!(sim >= a.min_sim)) continue;                      // also drops NaN
+                key_t64 key = make_key(sim, a.row_base + row0 + r);
+                warp_list_insert(lists + (size_t)q * P + warp * K, K, cnt[q], wmin[q], key, lane);
+            }
+        }
+    }
+
+    if (a.rows_read) {
+        unsigned int tot = my_rows_read;   // identical in every lane of the warp
+        if (lane == 0 && tot) atomicAdd(a.rows_read, (unsigned long long)tot);
+    }
+
+    // ---- CTA epilogue: k best of this CTA per query -> global scratch
+    for (int q = 0; q < a.nq; q++) {
+        cta_bitonic_desc(lists + (size_t)q * P, P);
+        for (int i = tid; i < K; i += kScanThreads)
+            a.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        unsigned int t = atomicAdd(a.counter, 1u);
+        is_last_s = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last_s) return;
+    __threadfence();
+
+    // ---- last CTA: merge gridDim.x * K keys per query, then write the records
+    for (int q = 0; q < a.nq; q++) {
+        key_t64 *buf = lists + (size_t)q * P;
+        const uint32_t total = gridDim.x * (uint32_t)K;
+        for (int i = tid; i < K; i += kScanThreads) buf[i] = 0ull;
+        uint32_t done = 0;
+        while (done < total) {
+            __syncthreads();
+            const uint32_t room = (uint32_t)(P - K);
+            for (uint32_t i = tid; i < room; i += kScanThreads) {
+                uint32_t j = done + i;
+                key_t64 v = 0ull;
+                if (j < total) {
+                    uint32_t cta = j / K, idx = j % K;
+                    v = __ldcg(&a.cta_out[((size_t)cta * a.nq + q) * K + idx]);
+                }
+                buf[K + i] = v;
+            }
+            cta_bitonic_desc(buf, P);
+            done += room;
+        }
+        for (int i = tid; i < K; i += kScanThreads) {
+            key_t64 key = buf[i];
+            a.out_keys[(size_t)q * K + i] = key;
+            uint4 id = make_uint4(0, 0, 0, 0);
+            if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
+            reinterpret_cast<uint4 *>(a.out_ids)[(size_t)q * K + i] = id;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *a.counter = 0u;
+}
+
+int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+template <int NQ, int R, int U>
+cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t stream)
+{
+    const bool full = ((a.dim >> 2) % (32 * U)) == 0;
+    auto kern = full ? scan_topk_kernel<NQ, R, U, true> : scan_topk_kernel<NQ, R, U, false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, kScanThreads, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+constexpr size_t kSmemBudget = 220 * 1024;
+
+}  // namespace
+
+size_t scan_smem_bytes(int dim, int nq_tmpl, int k, int *P_out)
+{
+    int P = next_pow2(kScanWarps * k);
+    if (P < 2 * k) P = next_pow2(2 * k);
+    if (P_out) *P_out = P;
+    return (size_t)nq_tmpl * dim * sizeof(float) + (size_t)nq_tmpl * P * sizeof(key_t64);
+}
+
+static int nq_template_for(int nq) { return nq <= 1 ? 1 : nq <= 2 ? 2 : nq <= 4 ? 4 : 8; }
+
+int scan_pick_nq(int dim, int k, int batch)
+{
+    int nq = batch < kMaxNQ ? batch : kMaxNQ;
+    while (nq > 1 && scan_smem_bytes(dim, nq_template_for(nq), k, nullptr) > kSmemBudget) nq >>= 1;
+    return nq;
+}
+
+int scan_grid_for(int sm_count) { return sm_count; }
+
+cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream, int *grid_out)
+{
+    ScanArgs a = a_in;
+    const int nqt = nq_template_for(a.nq);
+    size_t smem = scan_smem_bytes(a.dim, nqt, a.k, &a.P);
+    if (smem > kSmemBudget || (a.dim & 3) || a.nq < 1 || a.nq > kMaxNQ) return cudaErrorInvalidValue;
+    int grid = scan_grid_for(sm_count);
+    if (grid_out) *grid_out = grid;
+    switch (nqt) {
+        case 1: return launch_one<1, 4, 4>(a, grid, smem, stream);
+        case 2: return launch_one<2, 4, 4>(a, grid, smem, stream);
+        case 4: return launch_one<4, 4, 2>(a, grid, smem, stream);
+        default: return launch_one<8, 2, 2>(a, grid, smem, stream);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Merge of the all-gathered candidates: one CTA per query.
+// gathered: G blocks of [batch*k keys][batch*k*16 id bytes]
+// ---------------------------------------------------------------------------
+namespace {
+constexpr int kMergeThreads = 256;
+
+__global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gathered, int G, int batch, int k,
+                                                              int P, key_t64 *out_keys, uint8_t *out_ids)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    key_t64 *keys = reinterpret_cast<key_t64 *>(smem_raw);        // P
+    const int q = blockIdx.x;
+    const size_t block_bytes = (size_t)batch * k * 24;
+    const int total = G * k;
+    for (int i = threadIdx.x; i < P; i += kMergeThreads) {
+        key_t64 v = 0ull;
+        if (i < total) {
+            int g = i / k, j = i % k;
+            v = reinterpret_cast<const key_t64 *>(gathered + (size_t)g * block_bytes)[(size_t)q * k + j];
+        }
+        keys[i] = v;
+    }
+    cta_bitonic_desc(keys, P);
+    // keys are unique across ranks (global rows), so the id of a winner is found by
+    // looking its key up again in the owner's block.
+    for (int i = threadIdx.x; i < k; i += kMergeThreads) {
+        key_t64 key = keys[i];
+        uint4 id = make_uint4(0, 0, 0, 0);
+        if (key) {
+            for (int g = 0; g < G; g++) {
+                const key_t64 *kb = reinterpret_cast<const key_t64 *>(gathered + (size_t)g * block_bytes) + (size_t)q * k;
+                const uint4 *ib = reinterpret_cast<const uint4 *>(gathered + (size_t)g * block_bytes + (size_t)batch * k * 8) + (size_t)q * k;
+                for (int j = 0; j < k; j++)
+                    if (kb[j] == key) id = ib[j];
+            }
+        }
+        out_keys[(size_t)q * k + i] = key;
+        reinterpret_cast<uint4 *>(out_ids)[(size_t)q * k + i] = id;
+    }
+}
+}  // namespace
+
+cudaError_t launch_merge(const uint8_t *gathered, int G, int batch, int k, key_t64 *out_keys,
+                         uint8_t *out_ids, cudaStream_t stream)
+{
+    int P = next_pow2(G * k);
+    if (P < 2) P = 2;
+    merge_kernel<<<batch, kMergeThreads, (size_t)P * sizeof(key_t64), stream>>>(gathered, G, batch, k, P, out_keys, out_ids);
+    return cudaGetLastError();
+}
+
+}  // namespace da

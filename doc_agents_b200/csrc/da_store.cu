@@ -1,0 +1,740 @@
+// Host side of libdocagents_b200.so: the device-resident embedding store and the C ABI
+// declared in include/docagents_b200.h.  Mirrors, for one path only, what
+// internal/store/postgres.go does for the reference: SaveChunks (:142-164, chunk -> document),
+// SaveEmbeddings (:176-201, upsert by chunk id) and TopK (:218-285).
+//
+// There is no CPU fallback anywhere in this file: every search is the CUDA scan, and a
+// missing device, a failed allocation or a failed launch is an error to the caller.
+#include "../../include/docagents_b200.h"
+#include "da_internal.h"
+
+#include <nccl.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(expr)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (expr);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(DA_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+#define NC(expr)                                                                                   \
+    do {                                                                                           \
+        ncclResult_t r_ = (expr);                                                                  \
+        if (r_ != ncclSuccess)                                                                     \
+            return fail(DA_ERR_NCCL, "%s failed: %s (%s:%d)", #expr, ncclGetErrorString(r_), __FILE__, __LINE__); \
+    } while (0)
+
+struct Id16 {
+    uint64_t a, b;
+    bool operator==(const Id16 &o) const { return a == o.a && b == o.b; }
+};
+struct Id16Hash {
+    size_t operator()(const Id16 &k) const
+    {
+        uint64_t z = k.a ^ (k.b * 0x9E3779B97F4A7C15ull);
+        z ^= z >> 32; z *= 0xD6E8FEB86659FD93ull; z ^= z >> 32;
+        return (size_t)z;
+    }
+};
+inline Id16 load_id(const uint8_t *p) { Id16 k; memcpy(&k, p, 16); return k; }
+
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+
+struct ChunkInfo { uint32_t slot; int32_t shard; uint32_t row; };
+struct DocInfo { Id16 id; int32_t shard; };
+
+template <typename T>
+struct DevBuf {   // grow-only device buffer
+    T *p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void **)&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template <typename T>
+struct PinBuf {   // grow-only pinned host buffer
+    T *p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMallocHost((void **)&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+struct Shard {
+    int device = 0, sm_count = 148;
+    uint64_t cap_rows = 0;
+    uint32_t n_rows = 0, row_base = 0;
+    float *mat = nullptr, *inv_norm = nullptr;
+    uint32_t *doc_slot = nullptr;
+    uint8_t *chunk_ids = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr, ev_all0 = nullptr, ev_all1 = nullptr;
+    std::vector<cudaEvent_t> ev_pool;   // extra pairs for per-launch timing inside a bench loop
+    ncclComm_t comm = nullptr;
+    // search state
+    DevBuf<float> d_queries, d_qinv;
+    DevBuf<uint32_t> d_bitmap;
+    DevBuf<uint8_t> d_out, d_gather, d_final;
+    da::key_t64 *d_cta = nullptr;
+    unsigned int *d_counter = nullptr;
+    unsigned long long *d_rows_read = nullptr;
+    PinBuf<float> h_queries;
+    PinBuf<uint32_t> h_bitmap;
+    PinBuf<uint8_t> h_result;
+    // upsert staging
+    DevBuf<uint32_t> d_up_rows, d_up_slots;
+    DevBuf<uint8_t> d_up_ids;
+    PinBuf<uint32_t> h_up_rows, h_up_slots;
+    PinBuf<uint8_t> h_up_ids;
+    uint64_t hbm_bytes = 0;
+};
+
+}  // namespace
+
+struct da_store {
+    std::mutex mu;
+    int dim = 0;
+    float min_sim = DA_DEFAULT_MIN_SIMILARITY;
+    int world = 1, rank = 0, total_ranks = 1;
+    std::vector<Shard> shards;
+    std::unordered_map<Id16, uint32_t, Id16Hash> doc_slot_of;
+    std::vector<DocInfo> docs;                 // slot -> document
+    std::unordered_map<Id16, ChunkInfo, Id16Hash> chunks;
+    // statistics
+    float last_scan_ms = 0, last_search_ms = 0;
+    uint64_t last_rows_read = 0, last_bytes = 0, launches = 0, scan_launches = 0;
+    double scan_ms_sum = 0;
+    int scan_grid = 0;
+};
+
+namespace {
+
+void free_shard(Shard &s)
+{
+    cudaSetDevice(s.device);
+    if (s.comm) ncclCommDestroy(s.comm);
+    if (s.stream) cudaStreamSynchronize(s.stream);
+    cudaFree(s.mat); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
+    cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
+    s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
+    s.d_out.release(); s.d_gather.release(); s.d_final.release();
+    s.h_queries.release(); s.h_bitmap.release(); s.h_result.release();
+    s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
+    s.h_up_rows.release(); s.h_up_slots.release(); s.h_up_ids.release();
+    if (s.ev_scan0) cudaEventDestroy(s.ev_scan0);
+    if (s.ev_scan1) cudaEventDestroy(s.ev_scan1);
+    if (s.ev_all0) cudaEventDestroy(s.ev_all0);
+    if (s.ev_all1) cudaEventDestroy(s.ev_all1);
+    for (cudaEvent_t e : s.ev_pool) cudaEventDestroy(e);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Shard();
+}
+
+int init_shard(Shard &s, int device, int dim, uint64_t cap_rows)
+{
+    s.device = device;
+    s.cap_rows = cap_rows;
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(DA_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    s.sm_count = prop.multiProcessorCount;
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    const uint64_t need = cap_rows * ((uint64_t)dim * 4 + 4 + 4 + 16);
+    if (need + (512ull << 20) > free_b)
+        return fail(DA_ERR_CAPACITY, "capacity_rows=%llu x dim=%d needs %.2f GB on device %d, %.2f GB free (no CPU fallback)",
+                    (unsigned long long)cap_rows, dim, need / 1e9, device, free_b / 1e9);
+    CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&s.ev_scan0)); CU(cudaEventCreate(&s.ev_scan1));
+    CU(cudaEventCreate(&s.ev_all0)); CU(cudaEventCreate(&s.ev_all1));
+    CU(cudaMalloc((void **)&s.mat, cap_rows * (uint64_t)dim * 4));
+    CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
+    CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
+    CU(cudaMalloc((void **)&s.chunk_ids, cap_rows * 16));
+    const size_t cta_keys = (size_t)da::scan_grid_for(s.sm_count) * da::kMaxNQ * DA_MAX_K;
+    CU(cudaMalloc((void **)&s.d_cta, cta_keys * sizeof(da::key_t64)));
+    CU(cudaMalloc((void **)&s.d_counter, sizeof(unsigned int)));
+    CU(cudaMalloc((void **)&s.d_rows_read, sizeof(unsigned long long)));
+    CU(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
+    CU(cudaMemsetAsync(s.d_rows_read, 0, sizeof(unsigned long long), s.stream));
+    CU(cudaStreamSynchronize(s.stream));
+    s.hbm_bytes = need + cta_keys * sizeof(da::key_t64);
+    return DA_OK;
+}
+
+struct SearchPlan {
+    int batch, k;
+    float min_sim;
+    bool all_docs, read_all;
+    size_t bitmap_words;
+};
+
+// Enqueue one complete search on every local shard: scan passes, collective, merge.
+// Queries, query norms and bitmap are already on the devices.
+int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr, cudaEvent_t e1 = nullptr)
+{
+    const int dim = st->dim;
+    const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
+    for (Shard &s : st->shards) {
+        CU(cudaSetDevice(s.device));
+        const bool first = (&s == &st->shards[0]);
+        CU(cudaEventRecord(first && e0 ? e0 : s.ev_scan0, s.stream));
+        da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(s.d_out.p);
+        uint8_t *out_ids = s.d_out.p + (size_t)pl.batch * pl.k * 8;
+        const int nq_max = da::scan_pick_nq(dim, pl.k, pl.batch);
+        for (int q0 = 0; q0 < pl.batch; q0 += nq_max) {
+            da::ScanArgs a{};
+            a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
+            a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p;
+            a.queries = s.d_queries.p + (size_t)q0 * dim;
+            a.q_inv_norm = s.d_qinv.p + q0;
+            a.row_list = nullptr;
+            a.n_rows = s.n_rows; a.row_base = s.row_base;
+            a.dim = dim; a.nq = std::min(nq_max, pl.batch - q0); a.k = pl.k;
+            a.min_sim = pl.min_sim; a.read_all = pl.read_all ? 1 : 0;
+            a.cta_out = s.d_cta; a.counter = s.d_counter;
+            a.out_keys = out_keys + (size_t)q0 * pl.k;
+            a.out_ids = out_ids + (size_t)q0 * pl.k * 16;
+            a.rows_read = s.d_rows_read;
+            int grid = 0;
+            CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
+            st->launches++;
+            if (first) { st->scan_grid = grid; st->scan_launches++; }
+        }
+        CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+    }
+    if (st->total_ranks > 1) {
+        NC(ncclGroupStart());
+        for (Shard &s : st->shards)
+            NC(ncclAllGather(s.d_out.p, s.d_gather.p, rec_bytes, ncclChar, s.comm, s.stream));
+        NC(ncclGroupEnd());
+        Shard &s0 = st->shards[0];
+        CU(cudaSetDevice(s0.device));
+        CU(da::launch_merge(s0.d_gather.p, st->total_ranks, pl.batch, pl.k,
+                            reinterpret_cast<da::key_t64 *>(s0.d_final.p),
+                            s0.d_final.p + (size_t)pl.batch * pl.k * 8, s0.stream));
+        st->launches++;
+    }
+    return DA_OK;
+}
+
+// Validate + stage the inputs of a search on every local shard.
+int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
+{
+    if (!p) return fail(DA_ERR_INVALID, "search params are NULL");
+    if (p->dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, p->dim);
+    if (p->k < 0) return fail(DA_ERR_INVALID, "LIMIT must not be negative (k=%d)", p->k);
+    if (p->k > DA_MAX_K) return fail(DA_ERR_INVALID, "k=%d exceeds DA_MAX_K=%d", p->k, DA_MAX_K);
+    if (p->batch < 1 || p->batch > DA_MAX_BATCH) return fail(DA_ERR_INVALID, "batch=%d out of range [1,%d]", p->batch, DA_MAX_BATCH);
+    if (!p->queries) return fail(DA_ERR_INVALID, "query vector is NULL");
+    if (p->flags & DA_SEARCH_IVF) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store");
+    const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
+    if (!all_docs && p->n_docs && !p->doc_ids) return fail(DA_ERR_INVALID, "doc_ids is NULL with n_docs=%zu", p->n_docs);
+    const size_t nq_elems = (size_t)p->batch * st->dim;
+    for (size_t i = 0; i < nq_elems; i++)
+        if (!std::isfinite(p->queries[i])) return fail(DA_ERR_NONFINITE, "query element %zu is not finite", i);
+
+    pl.batch = p->batch; pl.k = p->k; pl.min_sim = p->min_similarity;
+    pl.all_docs = all_docs; pl.read_all = (p->flags & DA_SEARCH_READ_ALL_ROWS) != 0;
+    pl.bitmap_words = (st->docs.size() + 31) / 32 + 1;
+
+    // document filter -> bit per slot (document_id = ANY($2): postgres.go:239); unknown ids match nothing
+    std::vector<uint32_t> bitmap;
+    if (!all_docs) {
+        bitmap.assign(pl.bitmap_words, 0u);
+        for (size_t i = 0; i < p->n_docs; i++) {
+            auto it = st->doc_slot_of.find(load_id(p->doc_ids + 16 * i));
+            if (it != st->doc_slot_of.end()) bitmap[it->second >> 5] |= 1u << (it->second & 31);
+        }
+    }
+    if (pl.k == 0) return DA_OK;
+    const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
+    for (Shard &s : st->shards) {
+        CU(cudaSetDevice(s.device));
+        CU(s.d_queries.ensure(nq_elems)); CU(s.d_qinv.ensure(p->batch));
+        CU(s.h_queries.ensure(nq_elems));
+        CU(s.d_out.ensure(rec_bytes)); CU(s.h_result.ensure(rec_bytes));
+        if (st->total_ranks > 1) { CU(s.d_gather.ensure(rec_bytes * st->total_ranks)); CU(s.d_final.ensure(rec_bytes)); }
+        memcpy(s.h_queries.p, p->queries, nq_elems * sizeof(float));
+        CU(cudaMemcpyAsync(s.d_queries.p, s.h_queries.p, nq_elems * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+        if (!all_docs) {
+            CU(s.d_bitmap.ensure(pl.bitmap_words)); CU(s.h_bitmap.ensure(pl.bitmap_words));
+            memcpy(s.h_bitmap.p, bitmap.data(), pl.bitmap_words * 4);
+            CU(cudaMemcpyAsync(s.d_bitmap.p, s.h_bitmap.p, pl.bitmap_words * 4, cudaMemcpyHostToDevice, s.stream));
+        }
+        CU(da::launch_query_inv_norm(s.d_queries.p, st->dim, p->batch, s.d_qinv.p, s.stream));
+        st->launches++;
+    }
+    return DA_OK;
+}
+
+int collect_stats(da_store *st, const SearchPlan &pl)
+{
+    Shard &s0 = st->shards[0];
+    CU(cudaSetDevice(s0.device));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, s0.ev_scan0, s0.ev_scan1));
+    st->last_scan_ms = ms;
+    uint64_t rows_read = 0, rows_scanned = 0;
+    for (Shard &s : st->shards) {
+        CU(cudaSetDevice(s.device));
+        unsigned long long rr = 0;
+        CU(cudaMemcpyAsync(&rr, s.d_rows_read, sizeof rr, cudaMemcpyDeviceToHost, s.stream));
+        CU(cudaMemsetAsync(s.d_rows_read, 0, sizeof rr, s.stream));
+        CU(cudaStreamSynchronize(s.stream));
+        rows_read += rr;
+        rows_scanned += s.n_rows;
+    }
+    const int passes = (pl.batch + da::scan_pick_nq(st->dim, pl.k, pl.batch) - 1) / da::scan_pick_nq(st->dim, pl.k, pl.batch);
+    st->last_rows_read = rows_read;
+    // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
+    // + doc_slot (4 B) of every row visited when a document filter is present.
+    st->last_bytes = rows_read * (uint64_t)st->dim * 4 +
+                     rows_scanned * (uint64_t)passes * (pl.all_docs ? 4 : 8);
+    return DA_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+extern "C" {
+
+const char *da_last_error(void) { return g_err.c_str(); }
+int da_abi_version(void) { return DA_ABI_VERSION; }
+
+int da_nccl_unique_id(uint8_t out[DA_NCCL_ID_BYTES])
+{
+    static_assert(sizeof(ncclUniqueId) == DA_NCCL_ID_BYTES, "ncclUniqueId size");
+    if (!out) return fail(DA_ERR_INVALID, "out is NULL");
+    ncclUniqueId id;
+    NC(ncclGetUniqueId(&id));
+    memcpy(out, &id, sizeof id);
+    return DA_OK;
+}
+
+int da_store_create(const da_config *cfg, da_store **out)
+{
+    if (!cfg || !out) return fail(DA_ERR_INVALID, "cfg/out is NULL");
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(da_config)) return fail(DA_ERR_INVALID, "da_config.struct_size=%u, expected %zu", cfg->struct_size, sizeof(da_config));
+    if (cfg->dim <= 0 || (cfg->dim & 3)) return fail(DA_ERR_DIM, "dim=%d must be a positive multiple of 4", cfg->dim);
+    if (cfg->dim > 16384) return fail(DA_ERR_DIM, "dim=%d exceeds 16384", cfg->dim);
+    if (cfg->n_devices < 1 || cfg->n_devices > DA_MAX_DEVICES) return fail(DA_ERR_INVALID, "n_devices=%d out of range", cfg->n_devices);
+    if (cfg->capacity_rows == 0) return fail(DA_ERR_INVALID, "capacity_rows is 0");
+    const int world = cfg->world_size > 1 ? cfg->world_size : 1;
+    const int rank = world > 1 ? cfg->rank : 0;
+    if (rank < 0 || rank >= world) return fail(DA_ERR_INVALID, "rank=%d outside world_size=%d", rank, world);
+    const uint64_t total = (uint64_t)world * cfg->n_devices;
+    if (total * cfg->capacity_rows > 0xFFFFFFF0ull) return fail(DA_ERR_CAPACITY, "total capacity exceeds 2^32 rows");
+    int n_dev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&n_dev);
+    if (ce != cudaSuccess || n_dev == 0)
+        return fail(DA_ERR_CUDA, "no CUDA device: %s (this library has no CPU fallback)", cudaGetErrorString(ce));
+    for (int i = 0; i < cfg->n_devices; i++)
+        if (cfg->device_ids[i] < 0 || cfg->device_ids[i] >= n_dev) return fail(DA_ERR_INVALID, "device id %d not present (%d devices)", cfg->device_ids[i], n_dev);
+
+    da_store *st = new da_store();
+    st->dim = cfg->dim;
+    st->min_sim = cfg->min_similarity;
+    st->world = world; st->rank = rank; st->total_ranks = (int)total;
+    st->shards.resize(cfg->n_devices);
+    for (int i = 0; i < cfg->n_devices; i++) {
+        int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows);
+        if (rc != DA_OK) { da_store_destroy(st); return rc; }
+        st->shards[i].row_base = (uint32_t)(((uint64_t)rank * cfg->n_devices + i) * cfg->capacity_rows);
+    }
+    if (total > 1) {
+        int rc = DA_OK;
+        if (world == 1) {
+            std::vector<ncclComm_t> comms(cfg->n_devices);
+            std::vector<int> devs(cfg->device_ids, cfg->device_ids + cfg->n_devices);
+            ncclResult_t r = ncclCommInitAll(comms.data(), cfg->n_devices, devs.data());
+            if (r != ncclSuccess) rc = fail(DA_ERR_NCCL, "ncclCommInitAll failed: %s", ncclGetErrorString(r));
+            else for (int i = 0; i < cfg->n_devices; i++) st->shards[i].comm = comms[i];
+        } else {
+            ncclUniqueId id;
+            memcpy(&id, cfg->nccl_id, sizeof id);
+            ncclResult_t r = ncclGroupStart();
+            for (int i = 0; i < cfg->n_devices && r == ncclSuccess; i++) {
+                cudaSetDevice(cfg->device_ids[i]);
+                r = ncclCommInitRank(&st->shards[i].comm, (int)total, id, rank * cfg->n_devices + i);
+            }
+            ncclResult_t r2 = ncclGroupEnd();
+            if (r == ncclSuccess) r = r2;
+            if (r != ncclSuccess) rc = fail(DA_ERR_NCCL, "ncclCommInitRank failed: %s", ncclGetErrorString(r));
+        }
+        if (rc != DA_OK) { da_store_destroy(st); return rc; }
+    }
+    *out = st;
+    return DA_OK;
+}
+
+void da_store_destroy(da_store *st)
+{
+    if (!st) return;
+    for (Shard &s : st->shards) free_shard(s);
+    delete st;
+}
+
+int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *chunk_ids, size_t n)
+{
+    if (!st || !doc_id) return fail(DA_ERR_INVALID, "store/doc_id is NULL");
+    if (n && !chunk_ids) return fail(DA_ERR_INVALID, "chunk_ids is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    const Id16 did = load_id(doc_id);
+    uint32_t slot;
+    auto it = st->doc_slot_of.find(did);
+    if (it == st->doc_slot_of.end()) {
+        slot = (uint32_t)st->docs.size();
+        st->docs.push_back(DocInfo{did, -1});
+        st->doc_slot_of.emplace(did, slot);
+    } else slot = it->second;
+    for (size_t i = 0; i < n; i++) {
+        const Id16 cid = load_id(chunk_ids + 16 * i);
+        auto c = st->chunks.find(cid);
+        if (c == st->chunks.end()) { st->chunks.emplace(cid, ChunkInfo{slot, -1, kNoRow}); continue; }
+        if (c->second.slot == slot) continue;
+        c->second.slot = slot;
+        if (c->second.row != kNoRow) {   // the chunk already has a vector: move its row to the new document
+            Shard &s = st->shards[c->second.shard];
+            CU(cudaSetDevice(s.device));
+            CU(cudaMemcpyAsync(s.doc_slot + c->second.row, &slot, 4, cudaMemcpyHostToDevice, s.stream));
+            CU(cudaStreamSynchronize(s.stream));
+        }
+    }
+    return DA_OK;
+}
+
+int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float *vecs, size_t n, int32_t dim)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    if (n == 0) return DA_OK;                                   // postgres.go:177-179
+    if (!chunk_ids || !vecs) return fail(DA_ERR_INVALID, "chunk_ids/vecs is NULL");
+    if (dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, dim);
+    std::lock_guard<std::mutex> lock(st->mu);
+
+    // Validate everything before touching the device: the reference's statement is atomic.
+    const size_t total = n * (size_t)dim;
+    for (size_t i = 0; i < total; i++)
+        if (!std::isfinite(vecs[i])) return fail(DA_ERR_NONFINITE, "element %zu of embedding %zu is not finite", i % dim, i / dim);
+    std::vector<ChunkInfo *> info(n);
+    {
+        std::unordered_map<Id16, size_t, Id16Hash> seen;
+        seen.reserve(n * 2);
+        for (size_t i = 0; i < n; i++) {
+            const Id16 cid = load_id(chunk_ids + 16 * i);
+            if (!seen.emplace(cid, i).second)
+                return fail(DA_ERR_INVALID, "ON CONFLICT DO UPDATE command cannot affect row a second time (embedding %zu repeats a chunk id)", i);
+            auto c = st->chunks.find(cid);
+            if (c == st->chunks.end())
+                return fail(DA_ERR_UNKNOWN_CHUNK, "embedding %zu violates foreign key: chunk not announced by save_chunks", i);
+            info[i] = &c->second;
+        }
+    }
+    // Placement: a document lives on one shard (keeps its rows together); new documents go to
+    // the emptiest shard.
+    const int S = (int)st->shards.size();
+    std::vector<uint32_t> pending(S, 0);
+    std::vector<int32_t> tgt_shard(n);
+    std::vector<uint32_t> tgt_row(n);
+    std::vector<std::pair<uint32_t, int32_t>> doc_assign;       // undo log if capacity check fails
+    for (size_t i = 0; i < n; i++) {
+        ChunkInfo &ci = *info[i];
+        if (ci.row != kNoRow) { tgt_shard[i] = ci.shard; tgt_row[i] = ci.row; continue; }
+        DocInfo &d = st->docs[ci.slot];
+        if (d.shard < 0) {
+            int best = 0;
+            for (int s = 1; s < S; s++)
+                if (st->shards[s].n_rows + pending[s] < st->shards[best].n_rows + pending[best]) best = s;
+            d.shard = best;
+            doc_assign.emplace_back(ci.slot, -1);
+        }
+        tgt_shard[i] = d.shard;
+        tgt_row[i] = st->shards[d.shard].n_rows + pending[d.shard]++;
+    }
+    for (int s = 0; s < S; s++)
+        if ((uint64_t)st->shards[s].n_rows + pending[s] > st->shards[s].cap_rows) {
+            for (auto &u : doc_assign) st->docs[u.first].shard = u.second;
+            return fail(DA_ERR_CAPACITY, "shard %d is full (%llu rows); raise capacity_rows (no CPU fallback)", s,
+                        (unsigned long long)st->shards[s].cap_rows);
+        }
+
+    for (int s = 0; s < S; s++) {
+        Shard &sh = st->shards[s];
+        size_t cnt = 0;
+        for (size_t i = 0; i < n; i++) cnt += (tgt_shard[i] == s);
+        if (!cnt) continue;
+        CU(cudaSetDevice(sh.device));
+        CU(sh.d_up_rows.ensure(cnt)); CU(sh.d_up_slots.ensure(cnt)); CU(sh.d_up_ids.ensure(cnt * 16));
+        CU(sh.h_up_rows.ensure(cnt)); CU(sh.h_up_slots.ensure(cnt)); CU(sh.h_up_ids.ensure(cnt * 16));
+        size_t j = 0;
+        for (size_t i = 0; i < n;) {
+            if (tgt_shard[i] != s) { i++; continue; }
+            // run of inputs that land on consecutive rows -> one copy
+            size_t e = i + 1;
+            while (e < n && tgt_shard[e] == s && tgt_row[e] == tgt_row[e - 1] + 1) e++;
+            CU(cudaMemcpyAsync(sh.mat + (size_t)tgt_row[i] * dim, vecs + i * (size_t)dim, (e - i) * (size_t)dim * 4,
+                               cudaMemcpyHostToDevice, sh.stream));
+            for (size_t t = i; t < e; t++, j++) {
+                sh.h_up_rows.p[j] = tgt_row[t];
+                sh.h_up_slots.p[j] = info[t]->slot;
+                memcpy(sh.h_up_ids.p + 16 * j, chunk_ids + 16 * t, 16);
+            }
+            i = e;
+        }
+        CU(cudaMemcpyAsync(sh.d_up_rows.p, sh.h_up_rows.p, cnt * 4, cudaMemcpyHostToDevice, sh.stream));
+        CU(cudaMemcpyAsync(sh.d_up_slots.p, sh.h_up_slots.p, cnt * 4, cudaMemcpyHostToDevice, sh.stream));
+        CU(cudaMemcpyAsync(sh.d_up_ids.p, sh.h_up_ids.p, cnt * 16, cudaMemcpyHostToDevice, sh.stream));
+        CU(da::launch_finalize_rows(sh.mat, dim, sh.d_up_rows.p, sh.d_up_slots.p, sh.d_up_ids.p, (uint32_t)cnt,
+                                    sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
+        st->launches++;
+    }
+    for (int s = 0; s < S; s++) {
+        Shard &sh = st->shards[s];
+        CU(cudaSetDevice(sh.device));
+        CU(cudaStreamSynchronize(sh.stream));
+        sh.n_rows += pending[s];
+    }
+    for (size_t i = 0; i < n; i++) { info[i]->shard = tgt_shard[i]; info[i]->row = tgt_row[i]; }
+    return DA_OK;
+}
+
+int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids, float *out_scores,
+                    uint32_t *out_rows, int32_t *out_n)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    if (!out_n) return fail(DA_ERR_INVALID, "out_n is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    Shard &s0 = st->shards[0];
+    SearchPlan pl{};
+    CU(cudaSetDevice(s0.device));
+    CU(cudaEventRecord(s0.ev_all0, s0.stream));
+    int rc = stage_search(st, p, pl);
+    if (rc != DA_OK) return rc;
+    for (int q = 0; q < pl.batch; q++) out_n[q] = 0;
+    if (pl.k == 0) return DA_OK;
+    if (!out_chunk_ids || !out_scores) return fail(DA_ERR_INVALID, "output buffers are NULL");
+    rc = enqueue_search(st, pl);
+    if (rc != DA_OK) return rc;
+    const size_t nk = (size_t)pl.batch * pl.k, rec_bytes = nk * 24;
+    CU(cudaSetDevice(s0.device));
+    const uint8_t *src = st->total_ranks > 1 ? s0.d_final.p : s0.d_out.p;
+    CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes, cudaMemcpyDeviceToHost, s0.stream));
+    CU(cudaEventRecord(s0.ev_all1, s0.stream));
+    for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p);
+    const uint8_t *ids = s0.h_result.p + nk * 8;
+    for (int q = 0; q < pl.batch; q++) {
+        int c = 0;
+        for (int i = 0; i < pl.k; i++) {
+            const da::key_t64 key = keys[(size_t)q * pl.k + i];
+            if (!key) break;
+            out_scores[(size_t)q * pl.k + c] = da::key_score(key);
+            if (out_rows) out_rows[(size_t)q * pl.k + c] = da::key_row(key);
+            memcpy(out_chunk_ids + ((size_t)q * pl.k + c) * 16, ids + ((size_t)q * pl.k + i) * 16, 16);
+            c++;
+        }
+        out_n[q] = c;
+    }
+    CU(cudaSetDevice(s0.device));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, s0.ev_all0, s0.ev_all1));
+    st->last_search_ms = ms;
+    rc = collect_stats(st, pl);
+    if (rc != DA_OK) return rc;
+    st->scan_ms_sum += st->last_scan_ms;
+    return DA_OK;
+}
+
+int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *query, int32_t dim,
+                  int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    da_search_params p{};
+    p.struct_size = sizeof p;
+    p.flags = 0;
+    p.doc_ids = doc_ids; p.n_docs = n_docs;
+    p.queries = query; p.batch = 1; p.dim = dim;
+    p.k = k;
+    p.min_similarity = st->min_sim;
+    return da_store_search(st, &p, out_chunk_ids, out_scores, nullptr, out_n);
+}
+
+int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t iters, float *out_total_ms)
+{
+    if (!st || !out_total_ms) return fail(DA_ERR_INVALID, "store/out is NULL");
+    if (iters < 1) return fail(DA_ERR_INVALID, "iters must be >= 1");
+    std::lock_guard<std::mutex> lock(st->mu);
+    SearchPlan pl{};
+    int rc = stage_search(st, p, pl);
+    if (rc != DA_OK) return rc;
+    if (pl.k == 0) return fail(DA_ERR_INVALID, "k must be > 0");
+    for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    Shard &s0 = st->shards[0];
+    CU(cudaSetDevice(s0.device));
+    while (s0.ev_pool.size() < 2 * (size_t)iters) {
+        cudaEvent_t e;
+        CU(cudaEventCreate(&e));
+        s0.ev_pool.push_back(e);
+    }
+    CU(cudaEventRecord(s0.ev_all0, s0.stream));
+    for (int i = 0; i < iters; i++) {
+        rc = enqueue_search(st, pl, s0.ev_pool[2 * i], s0.ev_pool[2 * i + 1]);
+        if (rc != DA_OK) return rc;
+    }
+    CU(cudaSetDevice(s0.device));
+    CU(cudaEventRecord(s0.ev_all1, s0.stream));
+    for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    CU(cudaSetDevice(s0.device));
+    CU(cudaEventElapsedTime(out_total_ms, s0.ev_all0, s0.ev_all1));
+    double scan_ms = 0;
+    for (int i = 0; i < iters; i++) {
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, s0.ev_pool[2 * i], s0.ev_pool[2 * i + 1]));
+        scan_ms += ms;
+        st->last_scan_ms = ms;
+    }
+    st->scan_ms_sum += scan_ms;
+    return collect_stats(st, pl);
+}
+
+int da_store_build_ivf(da_store *st, const da_ivf_params *p)
+{
+    (void)p;
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    return fail(DA_ERR_STATE, "IVFFlat build is not available in this build");
+}
+
+int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
+{
+    if (!st || !p) return fail(DA_ERR_INVALID, "store/params is NULL");
+    if (p->struct_size != sizeof(da_synth_params)) return fail(DA_ERR_INVALID, "da_synth_params.struct_size mismatch");
+    if (!p->chunks_per_doc || !p->n_clusters) return fail(DA_ERR_INVALID, "chunks_per_doc/n_clusters must be > 0");
+    if (p->row_lo + p->n_rows > 0xFFFFFFF0ull) return fail(DA_ERR_CAPACITY, "rows exceed 2^32");
+    std::lock_guard<std::mutex> lock(st->mu);
+    const int S = (int)st->shards.size();
+    for (Shard &s : st->shards)
+        if (s.n_rows) return fail(DA_ERR_STATE, "generate_synthetic needs an empty store");
+    if (!st->docs.empty()) return fail(DA_ERR_STATE, "generate_synthetic needs an empty store");
+    // documents [doc_lo, doc_hi] -> slots 0..
+    const uint64_t doc_lo = p->row_lo / p->chunks_per_doc;
+    const uint64_t doc_hi = p->n_rows ? (p->row_lo + p->n_rows - 1) / p->chunks_per_doc : doc_lo;
+    // split rows over shards on document boundaries where possible
+    uint64_t per = (p->n_rows + S - 1) / S;
+    if (per % p->chunks_per_doc) per += p->chunks_per_doc - per % p->chunks_per_doc;
+    uint64_t lo = p->row_lo, end = p->row_lo + p->n_rows;
+    for (int i = 0; i < S; i++) {
+        Shard &s = st->shards[i];
+        uint64_t hi = std::min(end, lo + per);
+        if (i == S - 1) hi = end;
+        if (hi - lo > s.cap_rows) return fail(DA_ERR_CAPACITY, "shard %d: %llu rows exceed capacity_rows=%llu", i,
+                                              (unsigned long long)(hi - lo), (unsigned long long)s.cap_rows);
+        da::SynthArgs a{};
+        a.seed_data = p->seed_data; a.seed_centroid = p->seed_centroid; a.seed_ids = p->seed_ids;
+        a.chunks_per_doc = p->chunks_per_doc; a.n_clusters = p->n_clusters;
+        a.cmul = p->cmul; a.nmul = p->nmul;
+        a.row_lo = lo; a.n_rows = (uint32_t)(hi - lo); a.doc_slot_base = (uint32_t)doc_lo; a.dim = st->dim;
+        CU(cudaSetDevice(s.device));
+        CU(da::launch_synth(a, s.mat, s.inv_norm, s.doc_slot, s.chunk_ids, s.stream));
+        st->launches++;
+        s.row_base = (uint32_t)lo;
+        s.n_rows = (uint32_t)(hi - lo);
+        lo = hi;
+    }
+    if (p->n_rows) {
+        st->docs.reserve(doc_hi - doc_lo + 1);
+        st->doc_slot_of.reserve((doc_hi - doc_lo + 1) * 2);
+        for (uint64_t d = doc_lo; d <= doc_hi; d++) {
+            uint8_t id[16];
+            da::synth_doc_id(p->seed_ids, d, id);
+            const Id16 k = load_id(id);
+            st->doc_slot_of.emplace(k, (uint32_t)(d - doc_lo));
+            st->docs.push_back(DocInfo{k, 0});
+        }
+    }
+    for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    return DA_OK;
+}
+
+int da_store_stats(da_store *st, da_stats *out)
+{
+    if (!st || !out) return fail(DA_ERR_INVALID, "store/out is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    memset(out, 0, sizeof *out);
+    out->struct_size = sizeof *out;
+    out->dim = st->dim; out->n_devices = (int)st->shards.size();
+    out->world_size = st->world; out->rank = st->rank;
+    for (size_t i = 0; i < st->shards.size(); i++) {
+        out->rows += st->shards[i].n_rows;
+        out->rows_per_device[i] = st->shards[i].n_rows;
+        out->hbm_bytes += st->shards[i].hbm_bytes;
+    }
+    out->n_docs = st->docs.size();
+    out->last_scan_ms = st->last_scan_ms; out->last_search_ms = st->last_search_ms;
+    out->last_rows_read = st->last_rows_read; out->last_bytes_algorithmic = st->last_bytes;
+    out->kernel_launches = st->launches;
+    out->ivf_lists = 0;
+    out->scan_grid = st->scan_grid;
+    out->scan_ms_sum = st->scan_ms_sum; out->scan_launches = st->scan_launches;
+    return DA_OK;
+}
+
+int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo, uint64_t n, float *out_vecs,
+                             float *out_inv_norm, uint32_t *out_doc_slot, uint8_t *out_chunk_ids)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
+    Shard &s = st->shards[device_index];
+    if (row_lo + n > s.n_rows) return fail(DA_ERR_INVALID, "rows [%llu,%llu) outside the %u resident rows",
+                                           (unsigned long long)row_lo, (unsigned long long)(row_lo + n), s.n_rows);
+    CU(cudaSetDevice(s.device));
+    if (out_vecs) CU(cudaMemcpy(out_vecs, s.mat + row_lo * st->dim, n * st->dim * 4, cudaMemcpyDeviceToHost));
+    if (out_inv_norm) CU(cudaMemcpy(out_inv_norm, s.inv_norm + row_lo, n * 4, cudaMemcpyDeviceToHost));
+    if (out_doc_slot) CU(cudaMemcpy(out_doc_slot, s.doc_slot + row_lo, n * 4, cudaMemcpyDeviceToHost));
+    if (out_chunk_ids) CU(cudaMemcpy(out_chunk_ids, s.chunk_ids + row_lo * 16, n * 16, cudaMemcpyDeviceToHost));
+    return DA_OK;
+}
+
+}  // extern "C"

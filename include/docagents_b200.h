@@ -1,0 +1,185 @@
+/*
+ * docagents_b200.h -- C ABI of the B200-native semantic-search store.
+ *
+ * One shared library (libdocagents_b200.so: CUDA runtime + NCCL, no PyTorch,
+ * no CPU fallback) replaces ONE path of tomerlieber/doc-agents: the Query
+ * Agent's `Store.TopK` and its write side `Store.SaveEmbeddings`.  Each entry
+ * point below names the reference interface it stands in for (paths relative
+ * to the reference tree).  The cgo binding a maintainer adds on the Go side is
+ * in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative da_status; the message
+ *     for the calling thread's most recent failure is da_last_error().  This is
+ *     the channel that becomes a Go `error` (TopK errors surface as HTTP 500:
+ *     cmd/query/main.go:102-105).
+ *   - the caller owns every in/out buffer; nothing is retained after return
+ *     (cgo pointer rules); the library owns all device memory.
+ *   - thread-safe: any OS thread may call any function on a store at any time
+ *     (one goroutine per request: cmd/query/main.go:34); calls on one store
+ *     are serialised internally.  The CUDA device is selected per call.
+ *   - ids are 16 raw bytes (google/uuid's [16]byte: internal/store/store.go:23-48).
+ */
+#ifndef DOCAGENTS_B200_H
+#define DOCAGENTS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DA_ABI_VERSION 1
+#define DA_MAX_DEVICES 8
+#define DA_MAX_K 128            /* reference API caps top_k at 20 (cmd/query/main.go:23) */
+#define DA_MAX_BATCH 4096
+#define DA_NCCL_ID_BYTES 128
+#define DA_DEFAULT_MIN_SIMILARITY 0.7f   /* internal/store/postgres.go:223 */
+
+typedef enum {
+    DA_OK = 0,
+    DA_ERR_INVALID = -1,        /* bad argument (NULL, k<0, ...) */
+    DA_ERR_DIM = -2,            /* vector length != store dimension (pgvector: "expected N dimensions") */
+    DA_ERR_UNKNOWN_CHUNK = -3,  /* embedding for a chunk never announced by save_chunks
+                                   (the FK embeddings.chunk_id -> chunks.id: postgres.go:82-83) */
+    DA_ERR_CAPACITY = -4,       /* store full / not enough HBM; there is no CPU fallback */
+    DA_ERR_CUDA = -5,
+    DA_ERR_NCCL = -6,
+    DA_ERR_STATE = -7,          /* e.g. IVF search before the index was built */
+    DA_ERR_NONFINITE = -8       /* NaN/Inf element (pgvector rejects them) */
+} da_status;
+
+typedef struct da_store da_store;
+
+/* Provider configuration: what `buildStore` (internal/app/deps.go:179-202) would pass for
+ * STORE_PROVIDER=gpu, from env knobs in the style of internal/config/config.go:11-42. */
+typedef struct {
+    uint32_t struct_size;           /* sizeof(da_config) */
+    int32_t  dim;                   /* 3072 (vector(3072): postgres.go:84) or 1536 */
+    int32_t  n_devices;             /* GPUs driven by THIS process (1..8) */
+    int32_t  device_ids[DA_MAX_DEVICES];
+    uint64_t capacity_rows;         /* per device; HBM is reserved up front */
+    float    min_similarity;        /* floor used by da_store_topk; 0.7 for reference parity */
+    /* Multi-process row sharding (one process per GPU, e.g. under torchrun):
+     * world_size processes, each with n_devices local shards.  world_size<=1 => single process. */
+    int32_t  world_size;
+    int32_t  rank;
+    uint8_t  nccl_id[DA_NCCL_ID_BYTES];   /* from da_nccl_unique_id on rank 0, same on all ranks */
+    uint32_t flags;                 /* reserved, 0 */
+} da_config;
+
+/* Fills `out` with a fresh ncclUniqueId to hand to every rank's da_config. */
+int da_nccl_unique_id(uint8_t out[DA_NCCL_ID_BYTES]);
+
+/* store.NewPostgres (internal/store/postgres.go:23-33): open the provider. */
+int da_store_create(const da_config *cfg, da_store **out);
+void da_store_destroy(da_store *st);
+
+/* Store.SaveChunks (internal/store/store.go:61; postgres.go:142-164) as seen by the device
+ * store: it only needs chunk -> document, because store.Embedding carries no document id
+ * (store.go:44-48) and TopK filters on chunks.document_id (postgres.go:237-239).
+ * chunk_ids: n x 16 bytes.  Re-announcing a chunk under another document moves it. */
+int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *chunk_ids, size_t n);
+
+/* Store.SaveEmbeddings (store.go:64; postgres.go:176-201): upsert keyed by chunk_id
+ * (ON CONFLICT (chunk_id) DO UPDATE, :197).  n == 0 is a no-op (:177-179).
+ * vecs: n x dim row-major float32, the exact bits of embeddings.Vector
+ * (vectorToString is lossless: postgres.go:321-330). */
+int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float *vecs,
+                             size_t n, int32_t dim);
+
+/* Store.TopK (store.go:66; postgres.go:218-285).  Rows whose chunk belongs to one of
+ * doc_ids (n_docs x 16 bytes; n_docs == 0 matches nothing, :239), cosine similarity
+ * 1 - (vector <=> query) >= the store's min_similarity (:223,:240), best first (:241),
+ * at most k (:242).  out_chunk_ids: k x 16 bytes, out_scores: k floats (Score float32,
+ * :259), *out_n: rows returned (0 <=> the reference's nil slice, :250). */
+int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *query,
+                  int32_t dim, int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n);
+
+/* Flags of da_search_params. */
+#define DA_SEARCH_ALL_DOCS      0x1u  /* ignore doc_ids: every document is requested (bench roofline runs) */
+#define DA_SEARCH_READ_ALL_ROWS 0x2u  /* doc mask as a predicate: read every row even if its document is
+                                         not requested (configs[1] "HBM-bound" measurement); default skips them */
+#define DA_SEARCH_IVF           0x4u  /* probe the IVFFlat lists instead of the exact scan */
+
+/* Same query as da_store_topk with every knob exposed, batched: `batch` queries share one
+ * doc filter (one /api/query has one document set: cmd/query/main.go:20-24). */
+typedef struct {
+    uint32_t struct_size;
+    uint32_t flags;
+    const uint8_t *doc_ids;  size_t n_docs;
+    const float *queries;    int32_t batch;   int32_t dim;    /* batch x dim */
+    int32_t k;
+    float   min_similarity;  /* use -INFINITY for "no floor" */
+    int32_t ivf_probes;      /* DA_SEARCH_IVF only; 0 = store default */
+} da_search_params;
+
+/* Outputs are batch x k (row-major); out_n is batch counts; out_rows (optional, may be NULL)
+ * receives the global insertion row of each hit. */
+int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids,
+                    float *out_scores, uint32_t *out_rows, int32_t *out_n);
+
+/* The IVFFlat index of the reference DDL (postgres.go:95-99: lists = 100, vector_cosine_ops):
+ * spherical k-means on a sample, every row assigned to its nearest centroid, rows regrouped
+ * by list.  Searches with DA_SEARCH_IVF rank the centroids and scan `probes` lists. */
+typedef struct {
+    uint32_t struct_size;
+    int32_t  lists;          /* 100 in the reference DDL; 4096 in BASELINE configs[4] */
+    int32_t  iters;          /* k-means iterations (<= 20) */
+    uint64_t sample_rows;    /* 0 = max(lists*50, 10000), pgvector's rule */
+    uint64_t seed;
+    int32_t  default_probes; /* pgvector default is 1 (ivfflat.probes) */
+} da_ivf_params;
+int da_store_build_ivf(da_store *st, const da_ivf_params *p);
+
+/* Device-side synthetic corpus (bench/tests only; SURVEY.md section 8d, DESIGN.md
+ * "Synthetic corpus").  Fills global rows [row_lo, row_lo + n) -- split evenly over this
+ * store's shards -- bit-identically to the CPU oracle's generator, and registers their
+ * documents.  No counterpart in the reference (its data comes from OpenAI embeddings). */
+typedef struct {
+    uint32_t struct_size;
+    uint64_t seed_data, seed_centroid, seed_ids;
+    uint32_t chunks_per_doc, n_clusters;
+    int32_t  cmul, nmul;
+    uint64_t row_lo, n_rows;
+} da_synth_params;
+int da_store_generate_synthetic(da_store *st, const da_synth_params *p);
+
+typedef struct {
+    uint32_t struct_size;
+    int32_t  dim, n_devices, world_size, rank;
+    uint64_t rows;                  /* resident on this process's shards */
+    uint64_t rows_per_device[DA_MAX_DEVICES];
+    uint64_t hbm_bytes;             /* reserved by this store */
+    uint64_t n_docs;
+    /* last search, this process: */
+    float    last_scan_ms;          /* CUDA-event time of the scan kernel(s) on shard 0's stream */
+    float    last_search_ms;        /* events around H2D + kernels + collective + D2H */
+    uint64_t last_rows_read;        /* rows whose vectors were actually read */
+    uint64_t last_bytes_algorithmic;/* rows_scanned*(4*dim+8) or rows_read*(4*dim+4)+4*rows: DESIGN.md */
+    uint64_t kernel_launches;       /* cumulative count of this library's kernel launches */
+    int32_t  ivf_lists;             /* 0 = no index */
+    int32_t  scan_grid;             /* CTAs of the last scan launch */
+    double   scan_ms_sum;           /* cumulative CUDA-event time of scan launches on shard 0 */
+    uint64_t scan_launches;         /* how many launches scan_ms_sum covers */
+} da_stats;
+int da_store_stats(da_store *st, da_stats *out);
+
+/* Bench helper, no counterpart in the reference: uploads the queries of `p` once, then runs
+ * `iters` complete searches (scan, collective, merge) back to back with inputs and results
+ * resident in HBM, timed by CUDA events on shard 0's stream.  *out_total_ms covers all iters. */
+int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t iters, float *out_total_ms);
+
+/* Raw device views for the test harness (row-major matrix, 1/|row| vector, doc slots). */
+int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo, uint64_t n,
+                             float *out_vecs, float *out_inv_norm, uint32_t *out_doc_slot,
+                             uint8_t *out_chunk_ids);
+
+const char *da_last_error(void);
+int da_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DOCAGENTS_B200_H */

@@ -1,0 +1,104 @@
+"""CPU suite: the C-ABI library builds for sm_100a, loads, and exports every symbol that
+include/docagents_b200.h declares.  No compute calls here (no GPU in the build container)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from doc_agents_b200 import _lib as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "docagents_b200.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(da_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_the_path_entry_points():
+    syms = declared_symbols()
+    for must in ("da_store_create", "da_store_destroy", "da_store_save_chunks", "da_store_save_embeddings",
+                 "da_store_topk", "da_store_search", "da_last_error"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    lib = C.CDLL(built_lib)
+    for s in declared_symbols():
+        assert hasattr(lib, s), f"{s} is declared in the header but not exported"
+    out = subprocess.run(["nm", "-D", "--defined-only", built_lib], capture_output=True, text=True, check=True).stdout
+    exported = set(re.findall(r" T (da_[a-z0-9_]+)", out))
+    assert exported == set(declared_symbols()), exported ^ set(declared_symbols())
+    assert set(L.SIGNATURES) == set(declared_symbols())       # the ctypes twin binds exactly the header
+
+
+def test_header_compiles_as_c_and_struct_sizes_match(built_lib, tmp_path):
+    """The header is plain C (cgo includes it as C) and the ctypes structs have the C layout."""
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "docagents_b200.h"\n'
+                   'int main(void){printf("%zu %zu %zu %zu %zu\\n", sizeof(da_config), sizeof(da_search_params),'
+                   'sizeof(da_ivf_params), sizeof(da_synth_params), sizeof(da_stats));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.run(["/usr/bin/gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.dirname(HEADER), str(src), "-o", str(exe)],
+                   check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert sizes == [C.sizeof(L.da_config), C.sizeof(L.da_search_params), C.sizeof(L.da_ivf_params),
+                     C.sizeof(L.da_synth_params), C.sizeof(L.da_stats)]
+
+
+def test_library_is_sm100a_and_has_no_torch_dependency(built_lib):
+    needed = subprocess.run(["readelf", "-d", built_lib], capture_output=True, text=True, check=True).stdout
+    assert "libnccl" in needed                                  # cudart is linked statically
+    assert "torch" not in needed and "libc10" not in needed
+    sass = subprocess.run(["cuobjdump", "-lelf", built_lib], capture_output=True, text=True)
+    if sass.returncode == 0:
+        assert "sm_100a" in sass.stdout
+
+
+def test_abi_version_and_error_channel(built_lib):
+    lib = L.load()
+    assert lib.da_abi_version() == 1
+    # argument errors are reported without touching a device
+    assert lib.da_store_create(None, None) == L.DA_ERR_INVALID
+    assert "NULL" in L.last_error()
+    cfg = L.da_config()
+    cfg.struct_size = 3
+    h = C.c_void_p()
+    assert lib.da_store_create(C.byref(cfg), C.byref(h)) == L.DA_ERR_INVALID
+    cfg.struct_size = C.sizeof(L.da_config)
+    cfg.dim = 3070
+    cfg.n_devices = 1
+    cfg.capacity_rows = 10
+    assert lib.da_store_create(C.byref(cfg), C.byref(h)) == L.DA_ERR_DIM
+    assert lib.da_store_save_embeddings(None, None, None, 0, 0) == L.DA_ERR_INVALID
+
+
+def test_no_silent_fallback_without_a_gpu(built_lib):
+    """Without a CUDA device the product path must fail loudly (no CPU fallback, north_star)."""
+    import doc_agents_b200
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = os.path.exists("/dev/nvidia0")
+    if has_gpu:
+        pytest.skip("a GPU is present; the loud-failure path is exercised in the CPU container")
+    with pytest.raises(doc_agents_b200.StoreError) as ei:
+        doc_agents_b200.GpuStore(dim=3072, capacity_rows=16)
+    assert ei.value.code == L.DA_ERR_CUDA
+    assert "no CPU fallback" in ei.value.message
+
+
+def test_product_never_touches_the_oracle():
+    """oracle/ is test infrastructure: nothing under doc_agents_b200/ may import or link it."""
+    pkg = os.path.join(ROOT, "doc_agents_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h", ".cuh", ".cpp")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f
+                assert "liboracle" not in text and '#include "oracle' not in text, f

@@ -1,0 +1,242 @@
+"""GPU parity suite (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on
+the same seeded inputs, against the committed golden fixtures, and -- at BASELINE.json's full
+sizes -- through checks that stay cheap for the oracle (a document filter or the similarity floor
+restricts the rows that can qualify to a few thousand)."""
+import json
+import os
+import uuid
+
+import numpy as np
+import pytest
+
+import oracle
+from cases import ABS_TOL, REL_TOL, bits_f32, build_cases, check_against_oracle
+from doc_agents_b200 import Chunk, Embedding, GpuStore, StoreError, Summary, calculate_avg_similarity
+from doc_agents_b200 import _lib as L
+from gpu_util import S0, device_count, doc_filter, ids_for, load_case
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "topk_cases.json")))
+CASES = build_cases()
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: c.name)
+def test_case_matches_oracle_and_golden(case):
+    n, dim = case.mat.shape
+    with GpuStore(dim=dim, capacity_rows=n + 8) as st:
+        chunk, docs = load_case(st, case)
+        ids, scores, rows = st.search(case.q, case.k, doc_filter(case, docs), min_similarity=case.min_sim)
+        check_against_oracle(case, rows[0], scores[0])
+        assert np.array_equal(ids[0], chunk[rows[0]])                   # chunk ids gathered on the device
+        g = GOLDEN["cases"][case.name]
+        assert len(rows[0]) == len(g["f32"]["rows"])
+        assert np.allclose(scores[0], bits_f32(g["f32"]["score_bits"]), rtol=REL_TOL, atol=ABS_TOL)
+        assert np.allclose(scores[0], bits_f32(g["f64"]["score_bits"]), rtol=REL_TOL, atol=ABS_TOL)
+        if case.name not in ("no_floor_negative_scores",):             # near-zero scores may reorder within tol
+            assert [int(r) for r in rows[0]] == g["f64"]["rows"]
+        # the mask-as-predicate scan (reads every row) returns the same thing
+        ids2, scores2, rows2 = st.search(case.q, case.k, doc_filter(case, docs), min_similarity=case.min_sim,
+                                         read_all_rows=True)
+        assert np.array_equal(rows2[0], rows[0]) and np.array_equal(scores2[0], scores[0])
+        assert st.stats().last_rows_read == n
+
+
+def test_store_interface_mirrors_the_reference_contract():
+    """Replays what the reference's tests pin about TopK/SaveEmbeddings (cmd/query/main_test.go:72-79,
+    :226-254; cmd/analysis/main_test.go:76-78,:231) against the real C ABI."""
+    case = CASES[0]
+    n, dim = case.mat.shape
+    doc = uuid.UUID(bytes=bytes(oracle.doc_ids(S0, 0, 1)[0]))
+    other = uuid.uuid4()
+    with GpuStore(dim=dim, capacity_rows=512) as st:
+        saved = st.SaveChunks(doc, [Chunk(uuid.UUID(int=0), Text=f"chunk {i}", TokenCount=3) for i in range(n)])
+        assert len(saved) == n and all(c.DocumentID == doc for c in saved) and len({c.ID for c in saved}) == n
+        st.SaveSummary(doc, Summary(doc, "a summary", ["p1", "p2"]))
+        st.SaveEmbeddings([])                                            # empty slice: no-op, no error
+        assert st.TopK([doc], case.q, 5) is None                         # nothing stored yet -> nil slice
+        st.SaveEmbeddings([Embedding(c.ID, case.mat[i], "text-embedding-3-large") for i, c in enumerate(saved)])
+        res = st.TopK([doc], case.q, 5)                                  # top_k default of the handler is 5
+        o_rows, o_scores, _ = oracle.topk(case.mat, case.row_doc, case.allowed(), case.q, 5)
+        assert [r.Chunk.ID for r in res] == [saved[i].ID for i in o_rows]
+        assert np.allclose([r.Score for r in res], o_scores, rtol=REL_TOL)
+        assert all(isinstance(r.Score, np.float32) for r in res)         # Score float32 (store.go:52)
+        assert res[0].Chunk.Text == f"chunk {o_rows[0]}" and res[0].Chunk.DocumentID == doc
+        assert res[0].Summary.Summary == "a summary" and res[0].Summary.KeyPoints == ["p1", "p2"]
+        assert st.TopK([other], case.q, 5) is None                       # unknown document: nil, no error
+        assert st.TopK([], case.q, 5) is None                            # ANY('{}')
+        assert st.TopK([doc], case.q, 0) is None                         # LIMIT 0
+        assert len(st.TopK([other, doc, doc], case.q, 20)) == 20         # API cap 20, duplicates harmless
+        avg = calculate_avg_similarity(res)
+        assert avg == np.float32(oracle.avg_similarity([r.Score for r in res]))
+        assert calculate_avg_similarity(None) == 0.0
+        with pytest.raises(StoreError) as e:                             # dimension mismatch is an error (-> HTTP 500)
+            st.TopK([doc], case.q[:1536], 5)
+        assert e.value.code == L.DA_ERR_DIM
+        with pytest.raises(StoreError) as e:
+            st.TopK([doc], case.q, -1)
+        assert e.value.code == L.DA_ERR_INVALID
+
+
+def test_save_embeddings_upsert_semantics():
+    S = oracle.Synth(n_clusters=1)
+    dim, n = 1536, 300
+    mat = oracle.gen_rows(S, 0, n, dim)
+    q = oracle.gen_query(S, 0, 0, dim)
+    chunk, docs = ids_for(n, 2)
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        with pytest.raises(StoreError) as e:                             # FK: chunk never announced
+            st.save_embeddings_raw(chunk[:3], mat[:3])
+        assert e.value.code == L.DA_ERR_UNKNOWN_CHUNK
+        st.save_chunks_raw(docs[0], chunk[:200])
+        st.save_chunks_raw(docs[1], chunk[200:])
+        st.save_embeddings_raw(chunk[:200], mat[:200])
+        st.save_embeddings_raw(chunk[200:], mat[200:])
+        assert st.stats().rows == n
+        base_rows = st.search(q, 10, docs[:2])[2][0]
+        # overwrite 5 rows with copies of the best row's vector scaled: ON CONFLICT DO UPDATE keeps the row count
+        tgt = np.array([7, 250, 3, 299, 100])
+        newv = oracle.gen_rows(S, 5000, 5, dim)
+        st.save_embeddings_raw(chunk[tgt], newv)
+        assert st.stats().rows == n
+        mat2 = mat.copy()
+        mat2[tgt] = newv
+        got_v, got_inv, got_slot, got_ids = st.debug_rows(0, 0, n)
+        assert np.array_equal(got_v.view(np.uint32), mat2.view(np.uint32))      # lossless, like vectorToString
+        assert np.array_equal(got_ids, chunk)
+        assert np.array_equal(got_slot, (np.arange(n) >= 200).astype(np.uint32))
+        assert np.allclose(got_inv, 1.0 / np.linalg.norm(mat2.astype(np.float64), axis=1), rtol=1e-6)
+        rows = st.search(q, 10, docs[:2])[2][0]
+        o_rows, _, _ = oracle.topk(mat2, (np.arange(n) >= 200).astype(np.uint32), None, q, 10)
+        assert np.array_equal(rows, o_rows)
+        assert not np.array_equal(rows, base_rows) or not np.isin(tgt, base_rows).any()
+        # statement-level atomicity: a bad element / repeated id / wrong dim writes nothing
+        bad = newv.copy()
+        bad[2, 5] = np.nan
+        for ids_, vecs_, code in ((chunk[tgt], bad, L.DA_ERR_NONFINITE),
+                                  (chunk[[1, 2, 1]], newv[:3], L.DA_ERR_INVALID),
+                                  (chunk[:2], newv[:2, :512], L.DA_ERR_DIM)):
+            with pytest.raises(StoreError) as e:
+                st.save_embeddings_raw(ids_, vecs_)
+            assert e.value.code == code
+        assert np.array_equal(st.debug_rows(0, 0, n)[0].view(np.uint32), mat2.view(np.uint32))
+        # moving a chunk to another document changes which filter finds it
+        best = int(rows[0])
+        st.save_chunks_raw(docs[1 - int(best >= 200)], chunk[best:best + 1])
+        rows_moved = st.search(q, 10, docs[int(best >= 200):int(best >= 200) + 1])[2][0]
+        assert best not in rows_moved
+    with GpuStore(dim=dim, capacity_rows=4) as st:                       # full store: loud error, no fallback
+        st.save_chunks_raw(docs[0], chunk[:5])
+        with pytest.raises(StoreError) as e:
+            st.save_embeddings_raw(chunk[:5], mat[:5])
+        assert e.value.code == L.DA_ERR_CAPACITY
+        assert st.stats().rows == 0
+
+
+@pytest.mark.parametrize("dim,row_lo,n", [(3072, 0, 400), (1536, 123400, 257), (100, 5, 9)])
+def test_device_generator_is_bit_identical_to_the_oracle(dim, row_lo, n):
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S0, row_lo, n)
+        vecs, inv, slot, ids = st.debug_rows(0, 0, n)
+        ref = oracle.gen_rows(S0, row_lo, n, dim)
+        assert np.array_equal(vecs.view(np.uint32), ref.view(np.uint32))
+        assert np.array_equal(ids, oracle.chunk_ids(S0, row_lo, n))
+        assert np.array_equal(slot, oracle.row_docs(S0, row_lo, n) - row_lo // S0.chunks_per_doc)
+        assert np.allclose(inv, 1.0 / np.linalg.norm(ref.astype(np.float64), axis=1), rtol=1e-6)
+        assert st.stats().n_docs == (row_lo + n - 1) // 200 - row_lo // 200 + 1
+
+
+@pytest.mark.parametrize("batch", [1, 2, 3, 5, 8, 9, 17])
+def test_batched_queries_equal_single_queries(batch):
+    S = oracle.Synth(n_clusters=4)
+    n, dim, k = 3000, 1536, 10
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S, 0, n)
+        docs = oracle.doc_ids(S, 0, 15)
+        qs = np.stack([oracle.gen_query(S, i, i % 4, dim) for i in range(batch)])
+        ids_b, sc_b, rows_b = st.search(qs, k, docs[[0, 1, 2, 3, 5, 6, 8, 13]])
+        mat = oracle.gen_rows(S, 0, n, dim)
+        allowed = np.zeros(15, np.uint8)
+        allowed[[0, 1, 2, 3, 5, 6, 8, 13]] = 1
+        for i in range(batch):
+            ids_1, sc_1, rows_1 = st.search(qs[i], k, docs[[0, 1, 2, 3, 5, 6, 8, 13]])
+            assert np.array_equal(rows_b[i], rows_1[0]) and np.array_equal(ids_b[i], ids_1[0])
+            assert np.allclose(sc_b[i], sc_1[0], rtol=1e-6)
+            o_rows, o_sc, _ = oracle.topk(mat, oracle.row_docs(S, 0, n), allowed, qs[i], k)
+            assert np.array_equal(rows_b[i], o_rows)
+            assert np.allclose(sc_b[i], o_sc, rtol=REL_TOL)
+
+
+def _full_size_check(n_rows, dim, k, n_filter_docs):
+    """Parity at a BASELINE size: the document filter (or the 0.7 floor plus the cluster
+    structure) leaves only a few thousand rows that can qualify; the oracle scores exactly those."""
+    S = S0
+    n_docs = n_rows // S.chunks_per_doc
+    with GpuStore(dim=dim, capacity_rows=n_rows) as st:
+        st.generate_synthetic(S, 0, n_rows)
+        assert st.stats().rows == n_rows
+        for qi, cluster in ((0, 3), (1, 1000)):
+            q = oracle.gen_query(S, qi, cluster, dim)
+            # (i) filtered to n_filter_docs documents, half of them in the query's cluster
+            in_cl = [d for d in range(cluster, n_docs, S.n_clusters)][: n_filter_docs // 2]
+            others = [d for d in range(7, n_docs, max(1, n_docs // n_filter_docs)) if d % S.n_clusters != cluster]
+            chosen = sorted(in_cl + others[: n_filter_docs - len(in_cl)])
+            docs = oracle.doc_ids(S, 0, n_docs)[chosen] if n_docs <= 60000 else \
+                np.stack([oracle.doc_ids(S, d, 1)[0] for d in chosen])
+            ids, sc, rows = st.search(q, k, docs)
+            assert st.stats().last_rows_read == len(chosen) * S.chunks_per_doc      # rows of other docs skipped
+            sub_rows = np.concatenate([np.arange(d * 200, d * 200 + 200) for d in chosen])
+            sub = np.concatenate([oracle.gen_rows(S, d * 200, 200, dim) for d in chosen])
+            o_rows, o_sc, _ = oracle.topk(sub, None, None, q, k)
+            assert np.array_equal(rows[0], sub_rows[o_rows])
+            assert np.allclose(sc[0], o_sc, rtol=REL_TOL)
+            assert np.array_equal(ids[0], np.stack([oracle.chunk_ids(S, int(r), 1)[0] for r in rows[0]]))
+            # (ii) every document requested: only the query's cluster can clear the floor
+            ids_a, sc_a, rows_a = st.search(q, k, all_docs=True)
+            assert st.stats().last_rows_read == n_rows
+            cl_docs = list(range(cluster, n_docs, S.n_clusters))
+            sub_rows = np.concatenate([np.arange(d * 200, d * 200 + 200) for d in cl_docs])
+            sub = np.concatenate([oracle.gen_rows(S, d * 200, 200, dim) for d in cl_docs])
+            o_rows, o_sc, _ = oracle.topk(sub, None, None, q, k)
+            assert np.array_equal(rows_a[0], sub_rows[o_rows])
+            assert np.allclose(sc_a[0], o_sc, rtol=REL_TOL)
+            # (iii) size-independent properties: idempotence, LIMIT prefix, batch == single
+            again = st.search(q, k, all_docs=True)
+            assert np.array_equal(again[2][0], rows_a[0]) and np.array_equal(again[1][0], sc_a[0])
+            assert np.array_equal(st.search(q, k // 2, all_docs=True)[2][0], rows_a[0][: k // 2])
+        qs = np.stack([oracle.gen_query(S, i, (37 * i) % S.n_clusters, dim) for i in range(4)])
+        b = st.search(qs, k, all_docs=True)
+        for i in range(4):
+            one = st.search(qs[i], k, all_docs=True)
+            assert np.array_equal(b[2][i], one[2][0]) and np.allclose(b[1][i], one[1][0], rtol=1e-6)
+
+
+def test_config2_exact_scan_1m_x_3072_filtered_to_16_docs():
+    _full_size_check(1_000_000, 3072, 10, 16)
+
+
+def test_config3_exact_scan_10m_x_3072_single_gpu():
+    _full_size_check(10_000_000, 3072, 10, 16)
+
+
+def test_dim_1536_store():
+    _full_size_check(400_000, 1536, 20, 8)
+
+
+@pytest.mark.skipif(device_count() < 2, reason="needs 2 GPUs in one process")
+def test_two_shards_in_one_process_equal_one_shard():
+    S = oracle.Synth(n_clusters=8)
+    n, dim, k = 40_000, 3072, 10
+    with GpuStore(dim=dim, capacity_rows=n, devices=(0,)) as one, \
+            GpuStore(dim=dim, capacity_rows=n, devices=(0, 1)) as two:
+        one.generate_synthetic(S, 0, n)
+        two.generate_synthetic(S, 0, n)
+        assert list(two.stats().rows_per_device[:2]) == [20_000, 20_000]
+        docs = oracle.doc_ids(S, 0, 200)
+        qs = np.stack([oracle.gen_query(S, i, i % 8, dim) for i in range(5)])
+        for kw in (dict(all_docs=True), dict(doc_ids=docs[::3])):
+            a = one.search(qs, k, **kw)
+            b = two.search(qs, k, **kw)
+            for i in range(5):
+                assert np.array_equal(a[2][i], b[2][i]) and np.array_equal(a[0][i], b[0][i])
+                assert np.array_equal(a[1][i], b[1][i])

@@ -1,0 +1,174 @@
+"""CPU suite: the oracle against the committed golden fixtures, against the independent numpy
+restatement, and against the reference-visible semantics it restates.  No GPU, no product code."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import oracle_np
+from cases import ABS_TOL, REL_TOL, bits_f32, build_cases, f32_bits
+
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "topk_cases.json")))
+CASES = build_cases()
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: c.name)
+def test_oracle_matches_golden(case):
+    g = GOLDEN["cases"][case.name]
+    assert g["digest"] == case.digest(), "case inputs drifted from the ones the fixture was minted on"
+    for key, f64 in (("f32", False), ("f64", True)):
+        rows, scores, _ = oracle.topk(case.mat, case.row_doc, case.allowed(), case.q, case.k, case.min_sim, f64=f64)
+        assert [int(r) for r in rows] == g[key]["rows"]
+        assert f32_bits(scores) == g[key]["score_bits"]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: c.name)
+def test_numpy_restatement_agrees(case):
+    rows, scores, dist = oracle.topk(case.mat, case.row_doc, case.allowed(), case.q, case.k, case.min_sim, f64=True)
+    rn, sn, dn = oracle_np.topk(case.mat, case.row_doc, case.allowed(), case.q, case.k, case.min_sim, f64=True)
+    assert np.array_equal(rows, rn)
+    assert np.allclose(dist, dn, rtol=0, atol=1e-12)
+    # float accumulators (pgvector restated) stay within the parity tolerance of the truth
+    r32, s32, _ = oracle.topk(case.mat, case.row_doc, case.allowed(), case.q, case.k, case.min_sim)
+    assert len(r32) == len(rows)
+    assert np.allclose(s32, scores, rtol=REL_TOL, atol=ABS_TOL)
+
+
+@pytest.mark.parametrize("case", [c for c in CASES if c.mat.shape[0] <= 2000][:8], ids=lambda c: c.name)
+def test_fast_build_and_threads_agree(case):
+    """The vectorised/OpenMP build that bench.py times returns the same rows (ties aside)."""
+    r, s, _ = oracle.topk(case.mat, case.row_doc, case.allowed(), case.q, case.k, case.min_sim)
+    for threads in (1, 3):
+        rf, sf, _ = oracle.topk(case.mat, case.row_doc, case.allowed(), case.q, case.k, case.min_sim,
+                                fast=True, threads=threads)
+        assert len(rf) == len(r)
+        assert np.allclose(sf, s, rtol=REL_TOL, atol=ABS_TOL)
+        same = rf == r
+        full = oracle.all_scores(case.mat, case.q, f64=True)
+        for a, b in zip(rf[~same], r[~same]):
+            assert abs(full[a] - full[b]) <= REL_TOL * abs(full[b]) + ABS_TOL
+
+
+def test_synthetic_known_answers():
+    g = GOLDEN["synthetic"]
+    S = oracle.Synth()
+    rows = oracle.gen_rows(S, 0, 400, 3072)
+    assert hashlib.sha256(rows.tobytes()).hexdigest() == g["rows_0_400_dim3072_sha256"]
+    assert f32_bits(rows[0, :8]) == g["row0_first8_bits"]
+    assert f32_bits(rows[399, -4:]) == g["row399_last4_bits"]
+    assert f32_bits(oracle.gen_query(S, 0, 0, 3072)[:4]) == g["query0_cluster0_first4_bits"]
+    assert oracle.chunk_ids(S, 0, 1)[0].tolist() == g["chunk_id_row0"]
+    assert oracle.chunk_ids(S, 123456, 1)[0].tolist() == g["chunk_id_row123456"]
+    assert oracle.doc_ids(S, 0, 1)[0].tolist() == g["doc_id_0"]
+
+
+@pytest.mark.parametrize("dim,row_lo,n", [(3072, 0, 64), (1536, 12345, 33), (100, 7, 5), (4, 0, 3)])
+def test_generator_c_equals_numpy_bit_for_bit(dim, row_lo, n):
+    S = oracle.Synth()
+    a = oracle.gen_rows(S, row_lo, n, dim)
+    b = oracle_np.gen_rows(S, row_lo, n, dim)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    qa, qb = oracle.gen_query(S, 5, 17, dim), oracle_np.gen_query(S, 5, 17, dim)
+    assert np.array_equal(qa.view(np.uint32), qb.view(np.uint32))
+
+
+def test_generator_is_position_independent_and_unit_norm():
+    S = oracle.Synth()
+    whole = oracle.gen_rows(S, 1000, 50, 3072)
+    part = oracle.gen_rows(S, 1020, 10, 3072)
+    assert np.array_equal(whole[20:30], part)
+    norms = np.linalg.norm(whole.astype(np.float64), axis=1)
+    assert np.allclose(norms, 1.0, atol=2e-7)
+    # same-cluster cosine ~ 0.8 clears the 0.7 floor, cross-cluster ~ 0 does not
+    q = oracle.gen_query(S, 0, (1000 // 200) % 1024, 3072)
+    same = oracle.all_scores(oracle.gen_rows(S, 1000, 200, 3072), q)
+    other = oracle.all_scores(oracle.gen_rows(S, 1200, 200, 3072), q)
+    assert same.min() > 0.75 and same.max() < 0.85
+    assert np.abs(other).max() < 0.1
+
+
+def test_ids_are_uuid4_and_distinct():
+    import uuid
+    S = oracle.Synth()
+    ids = oracle.chunk_ids(S, 0, 500)
+    assert len({bytes(r) for r in ids}) == 500
+    for r in ids[:20]:
+        u = uuid.UUID(bytes=bytes(r))
+        assert u.version == 4 and u.variant == uuid.RFC_4122
+
+
+def test_normalize_follows_openai_go():
+    """internal/embeddings/openai.go:146-158: float64 sum of squares, float32 magnitude, float32 divide."""
+    rng = np.random.default_rng(3)
+    v = rng.standard_normal(3072).astype(np.float32) * np.float32(3.7)
+    mag = np.float32(np.sqrt((v.astype(np.float64) ** 2).sum()))
+    assert np.array_equal(oracle.normalize(v), v / mag)
+    assert np.array_equal(oracle_np.normalize(v), v / mag)
+    z = np.zeros(8, np.float32)
+    assert np.array_equal(oracle.normalize(z), z)          # zero vector left alone (:151-153)
+
+
+def test_cosine_distance_semantics():
+    rng = np.random.default_rng(5)
+    a = rng.standard_normal(3072).astype(np.float32)
+    b = rng.standard_normal(3072).astype(np.float32)
+    d32, d64 = oracle.cosine_distance(a, b), oracle.cosine_distance(a, b, f64=True)
+    ref = 1.0 - float(a.astype(np.float64) @ b.astype(np.float64)) / float(
+        np.linalg.norm(a.astype(np.float64)) * np.linalg.norm(b.astype(np.float64)))
+    assert abs(d64 - ref) < 1e-12
+    assert abs(d32 - ref) < 1e-5
+    assert abs(oracle_np.cosine_distance(a, b) - ref) < 1e-5
+    assert oracle.cosine_distance(a, a) == pytest.approx(0.0, abs=1e-6)
+    assert oracle.cosine_distance(a, -a) == pytest.approx(2.0, abs=1e-6)
+    assert oracle.cosine_distance(a, 2.5 * a) == pytest.approx(0.0, abs=1e-6)     # scale invariant
+    assert np.isnan(oracle.cosine_distance(a, np.zeros_like(a)))                   # zero norm => NaN
+    assert 0.0 <= oracle.cosine_distance(a, a) <= 2.0                              # clamp keeps [0, 2]
+
+
+def test_topk_properties():
+    S = oracle.Synth(n_clusters=4)
+    mat = oracle.gen_rows(S, 0, 1200, 256)
+    rd = oracle.row_docs(S, 0, 1200)
+    q = oracle.gen_query(S, 3, 1, 256)
+    r10, s10, d10 = oracle.topk(mat, rd, None, q, 10, -np.inf)
+    r5, s5, _ = oracle.topk(mat, rd, None, q, 5, -np.inf)
+    assert np.array_equal(r10[:5], r5)                       # prefix property of LIMIT
+    assert np.all(np.diff(d10) >= 0)                         # ORDER BY distance ascending
+    assert np.array_equal(s10, (1.0 - d10).astype(np.float32))
+    # restricting to the documents that hold the winners changes nothing
+    allowed = np.zeros(6, np.uint8)
+    allowed[np.unique(rd[r10])] = 1
+    r10f, _, _ = oracle.topk(mat, rd, allowed, q, 10, -np.inf)
+    assert np.array_equal(r10f, r10)
+    # k = 0 and an all-zero filter give the reference's nil slice
+    assert len(oracle.topk(mat, rd, None, q, 0, -np.inf)[0]) == 0
+    assert len(oracle.topk(mat, rd, np.zeros(6, np.uint8), q, 10, -np.inf)[0]) == 0
+    # scaling the query does not change the ranking (cosine divides by both norms)
+    r10s, s10s, _ = oracle.topk(mat, rd, None, q * np.float32(7.0), 10, -np.inf)
+    assert np.array_equal(r10s, r10) and np.allclose(s10s, s10, rtol=REL_TOL, atol=ABS_TOL)
+
+
+def test_avg_similarity_is_float32_running_sum():
+    s = np.array([0.81, 0.8, 0.79, 0.7000001, 0.75], np.float32)
+    t = np.float32(0)
+    for x in s:
+        t = np.float32(t + x)
+    assert oracle.avg_similarity(s) == np.float32(t / np.float32(5))
+    assert oracle.avg_similarity(np.zeros(0, np.float32)) == 0.0   # cmd/query/main.go:162-164
+
+
+def test_table_upsert_overwrites_by_chunk_id():
+    S = oracle.Synth()
+    t = oracle.Table(64)
+    ids = oracle.chunk_ids(S, 0, 5)
+    v1 = oracle.gen_rows(S, 0, 5, 64)
+    assert t.upsert(ids, v1) == 0 and t.rows == 5
+    v2 = oracle.gen_rows(S, 100, 2, 64)
+    assert t.upsert(ids[[3, 1]], v2) == 0 and t.rows == 5          # ON CONFLICT DO UPDATE (postgres.go:197)
+    got = t.vecs()
+    assert np.array_equal(got[3], v2[0]) and np.array_equal(got[1], v2[1]) and np.array_equal(got[0], v1[0])
+    assert t.upsert(ids[:0], v1[:0]) == 0                           # empty slice is a no-op (:177-179)
+    assert t.upsert(ids[:1], np.zeros((1, 32), np.float32)) == -1   # dimension mismatch is an error
