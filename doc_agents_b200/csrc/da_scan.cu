@@ -304,7 +304,7 @@ cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream,
 
 // ---------------------------------------------------------------------------
 // Merge of the all-gathered candidates: one CTA per query.
-// gathered: G blocks of [batch*k keys][batch*k*16 id bytes]
+// gathered: G blocks of [batch*k ids of 16 B][batch*k keys of 8 B]
 // ---------------------------------------------------------------------------
 namespace {
 constexpr int kMergeThreads = 256;
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gat
         key_t64 v = 0ull;
         if (i < total) {
             int g = i / k, j = i % k;
-            v = reinterpret_cast<const key_t64 *>(gathered + (size_t)g * block_bytes)[(size_t)q * k + j];
+            v = reinterpret_cast<const key_t64 *>(gathered + (size_t)g * block_bytes + (size_t)batch * k * 16)[(size_t)q * k + j];
         }
         keys[i] = v;
     }
@@ -333,8 +333,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gat
         uint4 id = make_uint4(0, 0, 0, 0);
         if (key) {
             for (int g = 0; g < G; g++) {
-                const key_t64 *kb = reinterpret_cast<const key_t64 *>(gathered + (size_t)g * block_bytes) + (size_t)q * k;
-                const uint4 *ib = reinterpret_cast<const uint4 *>(gathered + (size_t)g * block_bytes + (size_t)batch * k * 8) + (size_t)q * k;
+                const key_t64 *kb = reinterpret_cast<const key_t64 *>(gathered + (size_t)g * block_bytes + (size_t)batch * k * 16) + (size_t)q * k;
+                const uint4 *ib = reinterpret_cast<const uint4 *>(gathered + (size_t)g * block_bytes) + (size_t)q * k;
                 for (int j = 0; j < k; j++)
                     if (kb[j] == key) id = ib[j];
             }

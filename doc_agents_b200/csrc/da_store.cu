@@ -218,8 +218,9 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         CU(cudaSetDevice(s.device));
         const bool first = (&s == &st->shards[0]);
         CU(cudaEventRecord(first && e0 ? e0 : s.ev_scan0, s.stream));
-        da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(s.d_out.p);
-        uint8_t *out_ids = s.d_out.p + (size_t)pl.batch * pl.k * 8;
+        // record block: [batch*k ids of 16 B][batch*k keys of 8 B]  (ids first keeps them 16-byte aligned)
+        uint8_t *out_ids = s.d_out.p;
+        da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(s.d_out.p + (size_t)pl.batch * pl.k * 16);
         const int nq_max = da::scan_pick_nq(dim, pl.k, pl.batch);
         for (int q0 = 0; q0 < pl.batch; q0 += nq_max) {
             da::ScanArgs a{};
@@ -250,8 +251,8 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         Shard &s0 = st->shards[0];
         CU(cudaSetDevice(s0.device));
         CU(da::launch_merge(s0.d_gather.p, st->total_ranks, pl.batch, pl.k,
-                            reinterpret_cast<da::key_t64 *>(s0.d_final.p),
-                            s0.d_final.p + (size_t)pl.batch * pl.k * 8, s0.stream));
+                            reinterpret_cast<da::key_t64 *>(s0.d_final.p + (size_t)pl.batch * pl.k * 16),
+                            s0.d_final.p, s0.stream));
         st->launches++;
     }
     return DA_OK;
@@ -307,7 +308,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     return DA_OK;
 }
 
-int collect_stats(da_store *st, const SearchPlan &pl)
+int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
 {
     Shard &s0 = st->shards[0];
     CU(cudaSetDevice(s0.device));
@@ -325,6 +326,7 @@ int collect_stats(da_store *st, const SearchPlan &pl)
         rows_scanned += s.n_rows;
     }
     const int passes = (pl.batch + da::scan_pick_nq(st->dim, pl.k, pl.batch) - 1) / da::scan_pick_nq(st->dim, pl.k, pl.batch);
+    rows_read /= (uint64_t)searches;
     st->last_rows_read = rows_read;
     // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
     // + doc_slot (4 B) of every row visited when a document filter is present.
@@ -563,8 +565,8 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes, cudaMemcpyDeviceToHost, s0.stream));
     CU(cudaEventRecord(s0.ev_all1, s0.stream));
     for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
-    const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p);
-    const uint8_t *ids = s0.h_result.p + nk * 8;
+    const uint8_t *ids = s0.h_result.p;
+    const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p + nk * 16);
     for (int q = 0; q < pl.batch; q++) {
         int c = 0;
         for (int i = 0; i < pl.k; i++) {
@@ -636,7 +638,7 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
         st->last_scan_ms = ms;
     }
     st->scan_ms_sum += scan_ms;
-    return collect_stats(st, pl);
+    return collect_stats(st, pl, iters);
 }
 
 int da_store_build_ivf(da_store *st, const da_ivf_params *p)

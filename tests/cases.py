@@ -163,3 +163,21 @@ def check_against_oracle(case: Case, got_rows, got_scores, tol: float = REL_TOL)
         a, b = full[gr], full[orow]
         assert abs(a - b) <= tol * max(abs(a), abs(b)) + ABS_TOL, (case.name, i, gr, orow, a, b)
     assert np.allclose(got_scores, o_scores, rtol=tol, atol=ABS_TOL), (case.name, got_scores, o_scores)
+
+
+def same_rows_up_to_ties(got_rows, ref_rows, ref_scores, tol: float = REL_TOL) -> bool:
+    """True if got_rows equals ref_rows after collapsing runs of reference scores that tie within tol
+    (the acceptance rule: identical order except for ties within the tolerance)."""
+    got_rows, ref_rows = list(map(int, got_rows)), list(map(int, ref_rows))
+    if len(got_rows) != len(ref_rows):
+        return False
+    ref_scores = np.asarray(ref_scores, dtype=np.float64)
+    i = 0
+    while i < len(ref_rows):
+        j = i + 1
+        while j < len(ref_rows) and abs(ref_scores[j] - ref_scores[j - 1]) <= tol * abs(ref_scores[j - 1]) + ABS_TOL:
+            j += 1
+        if set(got_rows[i:j]) != set(ref_rows[i:j]):
+            return False
+        i = j
+    return True
