@@ -93,6 +93,23 @@ SIGNATURES = {
 _lib = None
 
 
+def _preload_newest_nccl() -> None:
+    """The library needs libnccl.so.2.  A Python process that later imports torch must end up with
+    ONE NCCL, and torch needs its own (newer) bundled build: load that one first when it exists, so
+    the loader does not bind the older system copy under the same SONAME.  (A Go host has no such
+    concern and simply uses the system libnccl.)"""
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+                return
+    except Exception:
+        pass
+
+
 def load() -> C.CDLL:
     """Load the in-tree shared library; raise if it has not been built."""
     global _lib
@@ -101,6 +118,7 @@ def load() -> C.CDLL:
             raise RuntimeError(
                 f"{LIB_PATH} is missing: build it with `python -m doc_agents_b200.build` "
                 "(there is no CPU or PyTorch fallback for this path)")
+        _preload_newest_nccl()
         lib = C.CDLL(LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)
