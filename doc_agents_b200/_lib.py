@@ -32,6 +32,9 @@ DA_SEARCH_ALL_DOCS = 0x1
 DA_SEARCH_READ_ALL_ROWS = 0x2
 DA_SEARCH_IVF = 0x4
 
+DA_NOALLOC_MAX_K = 128
+DA_NOALLOC_MAX_CTAS = 256
+
 
 class da_config(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("dim", C.c_int32), ("n_devices", C.c_int32),
@@ -86,6 +89,9 @@ SIGNATURES = {
                                           C.POINTER(C.c_float)]),
     "da_store_debug_read_rows": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p]),
+    "da_scan_topk_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_float,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "da_last_error": (C.c_char_p, []),
     "da_abi_version": (C.c_int, []),
 }

@@ -337,6 +337,11 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
 
 }  // namespace
 
+namespace da {
+// Lets other translation units of the library report through da_last_error().
+void set_last_error(const std::string &msg) { g_err = msg; }
+}  // namespace da
+
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------

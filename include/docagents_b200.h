@@ -176,6 +176,34 @@ int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo
                              float *out_vecs, float *out_inv_norm, uint32_t *out_doc_slot,
                              uint8_t *out_chunk_ids);
 
+/* No counterpart in the reference.  The exact scan of da_store_search for hosts that must not
+ * allocate: a serving loop that cannot afford cudaMalloc's device-wide synchronisation, a process
+ * whose HBM is already fully committed (a late cudaMalloc would fail), or code running where its
+ * framework forbids the CUDA allocator.  The caller owns every buffer (all DEVICE pointers, on
+ * `device`); the kernel's scratch (a ticket counter, 1/|q| and k candidate keys per CTA) lives
+ * in a fixed __device__ array inside the library (about 258 KB per GPU, held until exit), so this
+ * call never runs cudaMalloc, cudaFree or any allocating routine.
+ *   d_mat n_rows x dim row-major; d_inv_norm 1/|row| (0 for a zero row); d_chunk_ids 16 B per row;
+ *   d_doc_bitmap (bit per document slot) with d_doc_slot (slot per row), or both NULL for "every
+ *   document"; d_query dim floats.  d_mat, d_query, d_chunk_ids, d_out_chunk_ids 16-byte aligned.
+ *   Outputs, best first: d_out_scores[k], d_out_rows[k] (row_base + row; may be NULL),
+ *   d_out_chunk_ids[k x 16], *d_out_n = hits.  `stream` is a cudaStream_t (NULL = default stream).
+ * Limits: one query, 1 <= k <= DA_NOALLOC_MAX_K, a GPU of at most DA_NOALLOC_MAX_CTAS SMs; larger
+ * requests fail with DA_ERR_CAPACITY and launch nothing.
+ * The first call on a device resolves the scratch array's device address and loads the kernels:
+ * make it at start-up, before any stream capture on that device.  Asynchronous: outputs are valid
+ * when `stream` reaches this point.  All calls on a device share the one scratch array (each call
+ * clears the parts that must start at zero); calls that can overlap on the same GPU race on it --
+ * serialise them, e.g. on one stream. */
+#define DA_NOALLOC_MAX_K 128
+#define DA_NOALLOC_MAX_CTAS 256
+int da_scan_topk_noalloc(int32_t device, const float *d_mat, const float *d_inv_norm,
+                         const uint32_t *d_doc_slot, const uint8_t *d_chunk_ids,
+                         const uint32_t *d_doc_bitmap, const float *d_query, uint64_t n_rows,
+                         uint32_t row_base, int32_t dim, int32_t k, float min_similarity, void *stream,
+                         float *d_out_scores, uint32_t *d_out_rows, uint8_t *d_out_chunk_ids,
+                         int32_t *d_out_n);
+
 const char *da_last_error(void);
 int da_abi_version(void);
 
