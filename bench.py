@@ -51,65 +51,84 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def recorded_traffic():
-    """dram bytes per scan launch from the committed ncu --set full capture, if there is one."""
+def recorded_traffic(bytes_per_launch: int):
+    """dram bytes per scan launch from the committed ncu --set full capture (taken at 10M rows on one
+    GPU), scaled by this run's algorithmic bytes per launch when the shard size differs."""
     p = os.path.join(ROOT, "profiles", "scan_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("dram_bytes_per_launch")
+            d = json.load(open(p))
+            return d["dram_bytes_per_launch"] * bytes_per_launch / d["algorithmic_bytes_per_launch"]
         except Exception:
             return None
     return None
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons sampled DURING the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clocks and throttle reasons sampled DURING the timed region (NVML polled every ~2 ms from a
+    thread; the timed region of an 8-GPU run is only tens of milliseconds, too short for nvidia-smi -lms)."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.lines: list[str] = []
-        self.proc = None
+        self.samples: list[tuple[float, float, int]] = []
+        self.ok = False
+        self._stop = threading.Event()
+        self.t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(gpu_index))
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:       # noqa: BLE001
+            self.err = repr(e)
+
+    @staticmethod
+    def _physical_index(i: int) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        if vis:
+            try:
+                return int(vis.split(",")[i])
+            except (ValueError, IndexError):
+                return i
+        return i
+
+    def _poll(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                try:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:    # noqa: BLE001
+                    rs = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((sm, pw, rs))
+            except Exception:        # noqa: BLE001
+                pass
+            time.sleep(0.002)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+        if self.ok:
+            self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
-        except OSError:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
 
     def stop(self) -> dict:
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        sm, mx, reasons, power = [], [], set(), []
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "err", "?")]}
+        self._stop.set()
+        self.t.join(timeout=2)
+        sm = [s[0] for s in self.samples]
+        bits = 0
+        for s in self.samples:
+            bits |= s[2]
+        reasons = sorted(name for bit, name in self.REASONS.items() if bits & bit)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_sm,
+                "power_w_max": max((s[1] for s in self.samples), default=None), "samples": len(sm),
+                "reasons": reasons}
 
 
 def shard_range(rank: int, world: int, n_rows: int, chunks_per_doc: int):
@@ -284,7 +303,7 @@ def main():
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": recorded_traffic(), "kernel": "scan_topk_kernel", "peak_source": peak_src,
+                     "traffic": recorded_traffic(bytes_per_launch), "kernel": "scan_topk_kernel", "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,
                      "frac_of_nominal_8000": achieved / 8000.0},
         "result_check": {"hits": int(len(last[2][0])), "top_score": float(last[1][0][0]) if len(last[1][0]) else None},

@@ -115,6 +115,7 @@ struct Shard {
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
     unsigned long long *d_rows_read = nullptr;
+    PinBuf<unsigned long long> h_rows_read;
     PinBuf<float> h_queries;
     PinBuf<uint32_t> h_bitmap;
     PinBuf<uint8_t> h_result;
@@ -155,7 +156,7 @@ void free_shard(Shard &s)
     cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
-    s.h_queries.release(); s.h_bitmap.release(); s.h_result.release();
+    s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
     s.h_up_rows.release(); s.h_up_slots.release(); s.h_up_ids.release();
     if (s.ev_scan0) cudaEventDestroy(s.ev_scan0);
@@ -194,6 +195,7 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows)
     CU(cudaMalloc((void **)&s.d_cta, cta_keys * sizeof(da::key_t64)));
     CU(cudaMalloc((void **)&s.d_counter, sizeof(unsigned int)));
     CU(cudaMalloc((void **)&s.d_rows_read, sizeof(unsigned long long)));
+    CU(s.h_rows_read.ensure(1));
     CU(cudaMemsetAsync(s.d_counter, 0, sizeof(unsigned int), s.stream));
     CU(cudaMemsetAsync(s.d_rows_read, 0, sizeof(unsigned long long), s.stream));
     CU(cudaStreamSynchronize(s.stream));
@@ -308,24 +310,29 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     return DA_OK;
 }
 
+// Queue the read-back (and reset) of the rows-read counters behind the search on every stream.
+int enqueue_stats_readback(da_store *st)
+{
+    for (Shard &s : st->shards) {
+        CU(cudaSetDevice(s.device));
+        CU(cudaMemcpyAsync(s.h_rows_read.p, s.d_rows_read, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s.stream));
+        CU(cudaMemsetAsync(s.d_rows_read, 0, sizeof(unsigned long long), s.stream));
+    }
+    return DA_OK;
+}
+
+// After the streams were synchronised: fold the counters into the statistics.
 int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
 {
     Shard &s0 = st->shards[0];
     CU(cudaSetDevice(s0.device));
-    float ms = 0;
-    CU(cudaEventElapsedTime(&ms, s0.ev_scan0, s0.ev_scan1));
-    st->last_scan_ms = ms;
     uint64_t rows_read = 0, rows_scanned = 0;
     for (Shard &s : st->shards) {
-        CU(cudaSetDevice(s.device));
-        unsigned long long rr = 0;
-        CU(cudaMemcpyAsync(&rr, s.d_rows_read, sizeof rr, cudaMemcpyDeviceToHost, s.stream));
-        CU(cudaMemsetAsync(s.d_rows_read, 0, sizeof rr, s.stream));
-        CU(cudaStreamSynchronize(s.stream));
-        rows_read += rr;
+        rows_read += *s.h_rows_read.p;
         rows_scanned += s.n_rows;
     }
-    const int passes = (pl.batch + da::scan_pick_nq(st->dim, pl.k, pl.batch) - 1) / da::scan_pick_nq(st->dim, pl.k, pl.batch);
+    const int nq = da::scan_pick_nq(st->dim, pl.k, pl.batch);
+    const int passes = (pl.batch + nq - 1) / nq;
     rows_read /= (uint64_t)searches;
     st->last_rows_read = rows_read;
     // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
@@ -569,6 +576,8 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     const uint8_t *src = st->total_ranks > 1 ? s0.d_final.p : s0.d_out.p;
     CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes, cudaMemcpyDeviceToHost, s0.stream));
     CU(cudaEventRecord(s0.ev_all1, s0.stream));
+    rc = enqueue_stats_readback(st);
+    if (rc != DA_OK) return rc;
     for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
     const uint8_t *ids = s0.h_result.p;
     const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p + nk * 16);
@@ -588,6 +597,8 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, s0.ev_all0, s0.ev_all1));
     st->last_search_ms = ms;
+    CU(cudaEventElapsedTime(&ms, s0.ev_scan0, s0.ev_scan1));
+    st->last_scan_ms = ms;
     rc = collect_stats(st, pl);
     if (rc != DA_OK) return rc;
     st->scan_ms_sum += st->last_scan_ms;
@@ -632,6 +643,8 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
     }
     CU(cudaSetDevice(s0.device));
     CU(cudaEventRecord(s0.ev_all1, s0.stream));
+    rc = enqueue_stats_readback(st);
+    if (rc != DA_OK) return rc;
     for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
     CU(cudaSetDevice(s0.device));
     CU(cudaEventElapsedTime(out_total_ms, s0.ev_all0, s0.ev_all1));
