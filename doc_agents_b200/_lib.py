@@ -89,6 +89,7 @@ SIGNATURES = {
                                           C.POINTER(C.c_float)]),
     "da_store_debug_read_rows": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p]),
+    "da_store_debug_read_ivf": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "da_scan_topk_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_float,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

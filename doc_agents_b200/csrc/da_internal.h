@@ -57,7 +57,8 @@ struct ScanArgs {
     const float *queries;          // nq x dim (device)
     const float *q_inv_norm;       // nq
     const uint32_t *row_list;      // optional: scan only these rows (IVF probe lists); nullptr = [0,n_rows)
-    uint32_t n_rows;               // rows (or entries of row_list) to visit
+    const uint32_t *n_rows_dev;    // with row_list: device-resident count of entries
+    uint32_t n_rows;               // rows to visit when row_list is null
     uint32_t row_base;             // global row of local row 0
     int dim;
     int nq;                        // <= kMaxNQ
@@ -68,7 +69,7 @@ struct ScanArgs {
     key_t64 *cta_out;              // gridDim.x x nq x k   scratch
     unsigned int *counter;         // scratch: last-block ticket (left at 0)
     key_t64 *out_keys;             // nq x k, best first, 0-padded
-    uint8_t *out_ids;              // nq x k x 16
+    uint8_t *out_ids;              // nq x k x 16; nullptr = do not gather ids
     unsigned long long *rows_read; // optional statistics counter
 };
 
@@ -102,6 +103,24 @@ struct SynthArgs {
 };
 cudaError_t launch_synth(const SynthArgs &a, float *mat, float *inv_norm, uint32_t *doc_slot,
                          uint8_t *chunk_ids, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------
+// IVFFlat (da_ivf.cu)
+// ---------------------------------------------------------------------------
+#define DA_IVF_MAX_PROBES 128      // = DA_MAX_K: the centroid ranking is a top-k of the fused scan
+cudaError_t ivf_launch_assign(const float *mat, int D, const uint32_t *row_idx, uint32_t n, const float *cent, int L,
+                              uint32_t *out_assign, int out_by_row, cudaStream_t stream);
+cudaError_t ivf_launch_sample(uint32_t n_rows, uint32_t n_sample, uint64_t seed, uint32_t *out, cudaStream_t stream);
+cudaError_t ivf_launch_init_centroids(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
+                                      uint32_t n_sample, int L, float *cent, float *cent_inv, cudaStream_t stream);
+cudaError_t ivf_launch_accumulate(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
+                                  uint32_t n_sample, const uint32_t *assign, float *sums, float *counts,
+                                  cudaStream_t stream);
+cudaError_t ivf_launch_finalize(const float *sums, const float *counts, int L, int D, float *cent, cudaStream_t stream);
+cudaError_t ivf_launch_build_lists(const uint32_t *assign, uint32_t n, int L, uint32_t *counts, uint32_t *offsets,
+                                   uint32_t *cursor, uint32_t *list_rows, cudaStream_t stream);
+cudaError_t ivf_launch_expand(const key_t64 *probe_keys, int probes, const uint32_t *offsets, const uint32_t *list_rows,
+                              uint32_t *out_rows, uint32_t *out_n, cudaStream_t stream);
 
 // Host restatement of the id hash of the synthetic corpus (spec: DESIGN.md).
 void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);

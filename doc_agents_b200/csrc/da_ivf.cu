@@ -1,0 +1,315 @@
+// IVFFlat kernels: the index the reference asks Postgres for with
+//   CREATE INDEX ... USING ivfflat (vector vector_cosine_ops) WITH (lists = 100)
+// (internal/store/postgres.go:95-99).  pgvector builds it by k-means on a sample and then
+// assigns every row to its nearest centroid; a query ranks the centroids and scans the
+// `probes` nearest lists.  Here:
+//   - k-means is spherical (centroids kept at unit length, nearest = largest dot product);
+//   - "assign rows to centroids" is a GEMM (rows x centroids^T) fused with a per-row argmax:
+//     the score matrix is never written;
+//   - a list is an array of row numbers -- rows stay where they are in HBM (a 12 KB row is
+//     read contiguously anyway), so building or refreshing the index moves no vectors;
+//   - a query = the fused scan over the centroid matrix (top `probes`), an expansion of the
+//     chosen lists into one row list, and the fused scan again over that row list.
+#include "da_internal.h"
+
+namespace da {
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 16, TM = 8, TN = 8;
+constexpr int kAssignThreads = 256;
+
+__host__ __device__ inline unsigned long long ivf_mix64(unsigned long long z)
+{
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 27; z *= 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return z;
+}
+
+// SIMT fp32 GEMM + row argmax.  out[i] = argmax_j  <row_i, centroid_j>.
+// rows are mat[row_idx[i]] when row_idx != nullptr, else mat[i].  The result for item i is written
+// to out_assign[out_by_row ? source row : i].
+__global__ void __launch_bounds__(kAssignThreads) assign_simt_kernel(const float *__restrict__ mat, int D,
+                                                                     const uint32_t *__restrict__ row_idx, uint32_t n,
+                                                                     const float *__restrict__ cent, int L,
+                                                                     uint32_t *__restrict__ out_assign, int out_by_row)
+{
+    __shared__ __align__(16) float As[BK][BM + 4];
+    __shared__ __align__(16) float Bs[BK][BN + 4];
+    __shared__ float red_val[BM][17];
+    __shared__ int red_idx[BM][17];
+
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const uint32_t m0 = blockIdx.x * BM;
+    const int lr = tid >> 2, kq = tid & 3;     // loader: rows lr and lr + 64, float4 number kq of the BK slice
+
+    const float *a_src[2];
+    bool a_ok[2];
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        uint32_t g = m0 + lr + 64 * i;
+        a_ok[i] = g < n;
+        uint32_t src = a_ok[i] ? (row_idx ? row_idx[g] : g) : 0u;
+        a_src[i] = mat + (size_t)src * D;
+    }
+
+    float best_val[TM];
+    int best_idx[TM];
+#pragma unroll
+    for (int i = 0; i < TM; i++) { best_val[i] = -3.0e38f; best_idx[i] = 0; }
+
+    for (int n0 = 0; n0 < L; n0 += BN) {
+        float acc[TM][TN];
+#pragma unroll
+        for (int i = 0; i < TM; i++)
+#pragma unroll
+            for (int j = 0; j < TN; j++) acc[i][j] = 0.f;
+
+        const float *b_src[2];
+        bool b_ok[2];
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            int c = n0 + lr + 64 * i;
+            b_ok[i] = c < L;
+            b_src[i] = cent + (size_t)(b_ok[i] ? c : 0) * D;
+        }
+
+        for (int k0 = 0; k0 < D; k0 += BK) {
+            const int k = k0 + kq * 4;
+            const bool kin = k < D;
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                float4 va = (a_ok[i] && kin) ? *reinterpret_cast<const float4 *>(a_src[i] + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                float4 vb = (b_ok[i] && kin) ? *reinterpret_cast<const float4 *>(b_src[i] + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const int r = lr + 64 * i;
+                As[kq * 4 + 0][r] = va.x; As[kq * 4 + 1][r] = va.y; As[kq * 4 + 2][r] = va.z; As[kq * 4 + 3][r] = va.w;
+                Bs[kq * 4 + 0][r] = vb.x; Bs[kq * 4 + 1][r] = vb.y; Bs[kq * 4 + 2][r] = vb.z; Bs[kq * 4 + 3][r] = vb.w;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int kk = 0; kk < BK; kk++) {
+                float a[TM], b[TN];
+                const float4 a0 = *reinterpret_cast<const float4 *>(&As[kk][ty * TM]);
+                const float4 a1 = *reinterpret_cast<const float4 *>(&As[kk][ty * TM + 4]);
+                const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[kk][tx * TN]);
+                const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[kk][tx * TN + 4]);
+                a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+                b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+#pragma unroll
+                for (int i = 0; i < TM; i++)
+#pragma unroll
+                    for (int j = 0; j < TN; j++) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int i = 0; i < TM; i++)
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                const int c = n0 + tx * TN + j;
+                if (c < L && acc[i][j] > best_val[i]) { best_val[i] = acc[i][j]; best_idx[i] = c; }
+            }
+    }
+
+    // reduce over the 16 threads (tx) that share a row; ties go to the lower centroid index
+#pragma unroll
+    for (int i = 0; i < TM; i++) { red_val[ty * TM + i][tx] = best_val[i]; red_idx[ty * TM + i][tx] = best_idx[i]; }
+    __syncthreads();
+    if (tid < BM) {
+        const uint32_t g = m0 + tid;
+        if (g < n) {
+            float bv = red_val[tid][0];
+            int bi = red_idx[tid][0];
+            for (int t = 1; t < 16; t++) {
+                float v = red_val[tid][t];
+                int ix = red_idx[tid][t];
+                if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; }
+            }
+            const uint32_t dst = out_by_row ? (row_idx ? row_idx[g] : g) : g;
+            out_assign[dst] = (uint32_t)bi;
+        }
+    }
+}
+
+// sample row numbers: evenly spaced with a hashed offset inside each stride (distinct rows)
+__global__ void sample_rows_kernel(uint32_t n_rows, uint32_t n_sample, unsigned long long seed, uint32_t *out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_sample) return;
+    const unsigned long long step = n_rows / n_sample;          // >= 1
+    const unsigned long long off = step > 1 ? ivf_mix64(seed ^ (i + 1) * 0x9E3779B97F4A7C15ull) % step : 0;
+    out[i] = (uint32_t)(i * step + off);
+}
+
+// centroid l starts as the unit-length copy of the (l * n_sample / L)-th sample row
+__global__ void init_centroids_kernel(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
+                                      uint32_t n_sample, int L, float *cent)
+{
+    const int l = blockIdx.x;
+    const uint32_t row = sample[(unsigned long long)l * n_sample / L];
+    const float inv = inv_norm[row];
+    for (int c = threadIdx.x; c < D; c += blockDim.x) cent[(size_t)l * D + c] = mat[(size_t)row * D + c] * inv;
+}
+
+// sums[assign[i]] += unit(row_i); counts[assign[i]] += 1      (one warp per sample row)
+__global__ void kmeans_accumulate_kernel(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
+                                         uint32_t n_sample, const uint32_t *assign, float *sums, float *counts)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = w; i < n_sample; i += nw) {
+        const uint32_t row = sample[i];
+        const uint32_t a = assign[i];
+        const float inv = inv_norm[row];
+        const float *src = mat + (size_t)row * D;
+        float *dst = sums + (size_t)a * D;
+        for (int c = lane; c < D; c += 32) atomicAdd(dst + c, src[c] * inv);
+        if (lane == 0) atomicAdd(counts + a, 1.0f);
+    }
+}
+
+// centroid = sums / |sums| (spherical k-means); an empty or degenerate cluster keeps its centroid
+__global__ void kmeans_finalize_kernel(const float *sums, const float *counts, int D, float *cent)
+{
+    const int l = blockIdx.x;
+    __shared__ float red[32];
+    __shared__ float inv_s;
+    float ss = 0.f;
+    for (int c = threadIdx.x; c < D; c += blockDim.x) { float v = sums[(size_t)l * D + c]; ss += v * v; }
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xFFFFFFFFu, ss, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int i = 0; i < (int)(blockDim.x >> 5); i++) t += red[i];
+        inv_s = (counts[l] > 0.f && t > 0.f) ? rsqrtf(t) : 0.f;
+    }
+    __syncthreads();
+    if (inv_s == 0.f) return;
+    for (int c = threadIdx.x; c < D; c += blockDim.x) cent[(size_t)l * D + c] = sums[(size_t)l * D + c] * inv_s;
+}
+
+__global__ void fill_ones_kernel(float *p, int n)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = 1.0f;
+}
+
+__global__ void list_hist_kernel(const uint32_t *assign, uint32_t n, uint32_t *counts)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) atomicAdd(counts + assign[i], 1u);
+}
+
+// exclusive prefix sum of counts[0..L) into offsets[0..L]; cursor = copy of offsets.  One CTA.
+__global__ void list_scan_kernel(const uint32_t *counts, int L, uint32_t *offsets, uint32_t *cursor)
+{
+    __shared__ uint32_t part[1024];
+    const int t = threadIdx.x, T = blockDim.x;
+    const int per = (L + T - 1) / T;
+    uint32_t s = 0;
+    for (int i = t * per; i < min(L, (t + 1) * per); i++) s += counts[i];
+    part[t] = s;
+    __syncthreads();
+    if (t == 0) {
+        uint32_t run = 0;
+        for (int i = 0; i < T; i++) { uint32_t v = part[i]; part[i] = run; run += v; }
+        offsets[L] = run;
+    }
+    __syncthreads();
+    uint32_t run = part[t];
+    for (int i = t * per; i < min(L, (t + 1) * per); i++) { offsets[i] = run; cursor[i] = run; run += counts[i]; }
+}
+
+__global__ void list_scatter_kernel(const uint32_t *assign, uint32_t n, uint32_t *cursor, uint32_t *list_rows)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        list_rows[atomicAdd(cursor + assign[i], 1u)] = i;
+}
+
+// Concatenate the rows of the probed lists.  probe_keys: the centroid scan's result (row = list id).
+__global__ void expand_probes_kernel(const key_t64 *probe_keys, int probes, const uint32_t *offsets,
+                                     const uint32_t *list_rows, uint32_t *out_rows, uint32_t *out_n)
+{
+    __shared__ uint32_t start[DA_IVF_MAX_PROBES + 1];
+    __shared__ uint32_t src[DA_IVF_MAX_PROBES];
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int p = 0; p < probes; p++) {
+            const key_t64 key = probe_keys[p];
+            uint32_t len = 0, off = 0;
+            if (key) { const uint32_t l = key_row(key); off = offsets[l]; len = offsets[l + 1] - off; }
+            start[p] = run; src[p] = off; run += len;
+        }
+        start[probes] = run;
+        *out_n = run;
+    }
+    __syncthreads();
+    for (int p = 0; p < probes; p++) {
+        const uint32_t len = start[p + 1] - start[p];
+        for (uint32_t i = threadIdx.x; i < len; i += blockDim.x) out_rows[start[p] + i] = list_rows[src[p] + i];
+    }
+}
+
+}  // namespace
+
+cudaError_t ivf_launch_assign(const float *mat, int D, const uint32_t *row_idx, uint32_t n, const float *cent, int L,
+                              uint32_t *out_assign, int out_by_row, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    assign_simt_kernel<<<(n + BM - 1) / BM, kAssignThreads, 0, stream>>>(mat, D, row_idx, n, cent, L, out_assign, out_by_row);
+    return cudaGetLastError();
+}
+
+cudaError_t ivf_launch_sample(uint32_t n_rows, uint32_t n_sample, uint64_t seed, uint32_t *out, cudaStream_t stream)
+{
+    if (n_sample == 0) return cudaSuccess;
+    sample_rows_kernel<<<(n_sample + 255) / 256, 256, 0, stream>>>(n_rows, n_sample, seed, out);
+    return cudaGetLastError();
+}
+
+cudaError_t ivf_launch_init_centroids(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
+                                      uint32_t n_sample, int L, float *cent, float *cent_inv, cudaStream_t stream)
+{
+    init_centroids_kernel<<<L, 256, 0, stream>>>(mat, D, inv_norm, sample, n_sample, L, cent);
+    fill_ones_kernel<<<(L + 255) / 256, 256, 0, stream>>>(cent_inv, L);
+    return cudaGetLastError();
+}
+
+cudaError_t ivf_launch_accumulate(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
+                                  uint32_t n_sample, const uint32_t *assign, float *sums, float *counts,
+                                  cudaStream_t stream)
+{
+    if (n_sample == 0) return cudaSuccess;
+    int blocks = (int)((n_sample + 7) / 8);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    kmeans_accumulate_kernel<<<blocks, 256, 0, stream>>>(mat, D, inv_norm, sample, n_sample, assign, sums, counts);
+    return cudaGetLastError();
+}
+
+cudaError_t ivf_launch_finalize(const float *sums, const float *counts, int L, int D, float *cent, cudaStream_t stream)
+{
+    kmeans_finalize_kernel<<<L, 256, 0, stream>>>(sums, counts, D, cent);
+    return cudaGetLastError();
+}
+
+cudaError_t ivf_launch_build_lists(const uint32_t *assign, uint32_t n, int L, uint32_t *counts, uint32_t *offsets,
+                                   uint32_t *cursor, uint32_t *list_rows, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(counts, 0, (size_t)L * 4, stream);
+    if (e != cudaSuccess) return e;
+    if (n) list_hist_kernel<<<148 * 4, 256, 0, stream>>>(assign, n, counts);
+    list_scan_kernel<<<1, 1024, 0, stream>>>(counts, L, offsets, cursor);
+    if (n) list_scatter_kernel<<<148 * 4, 256, 0, stream>>>(assign, n, cursor, list_rows);
+    return cudaGetLastError();
+}
+
+cudaError_t ivf_launch_expand(const key_t64 *probe_keys, int probes, const uint32_t *offsets, const uint32_t *list_rows,
+                              uint32_t *out_rows, uint32_t *out_n, cudaStream_t stream)
+{
+    expand_probes_kernel<<<1, 1024, 0, stream>>>(probe_keys, probes, offsets, list_rows, out_rows, out_n);
+    return cudaGetLastError();
+}
+
+}  // namespace da

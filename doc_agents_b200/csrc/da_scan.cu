@@ -83,7 +83,10 @@ __device__ void cta_bitonic_desc(key_t64 *buf, int P)
     __syncthreads();
 }
 
-template <int NQ, int R, int U, bool FULL_TILES>
+// INDIRECT: visit the rows listed in a.row_list (count in *a.n_rows_dev) instead of [0, n_rows):
+// the probed IVFFlat lists.  A 12 KB row is still read contiguously, so gathering by row costs
+// no bandwidth.
+template <int NQ, int R, int U, bool FULL_TILES, bool INDIRECT>
 __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -110,7 +113,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 #pragma unroll
     for (int q = 0; q < NQ; q++) { cnt[q] = 0; wmin[q] = 0ull; }
 
-    const uint32_t n_groups = (a.n_rows + R - 1) / R;
+    const uint32_t n_rows = INDIRECT ? *a.n_rows_dev : a.n_rows;
+    const uint32_t n_groups = (n_rows + R - 1) / R;
     const uint32_t gstride = gridDim.x * kScanWarps;
     unsigned int my_rows_read = 0;
 
@@ -118,7 +122,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         const uint32_t row0 = g * R;
         // lane r (< R) looks at row0 + r: document mask and 1/|row|
         uint32_t my_row = row0 + lane;
-        bool valid = (lane < R) && (my_row < a.n_rows);
+        bool valid = (lane < R) && (my_row < n_rows);
+        if (INDIRECT) my_row = valid ? a.row_list[my_row] : 0u;
         bool wanted = valid;
         float my_inv = 0.f;
         if (valid) {
@@ -141,6 +146,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             for (int q = 0; q < NQ; q++) acc[r][q] = 0.f;
 
         const float4 *rp = reinterpret_cast<const float4 *>(a.mat) + (size_t)row0 * D4;
+        const float4 *rpi[R];
+        if (INDIRECT) {
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                rpi[r] = reinterpret_cast<const float4 *>(a.mat) + (size_t)__shfl_sync(0xFFFFFFFFu, my_row, r) * D4;
+        }
 
         for (int c0 = 0; c0 < D4; c0 += 32 * U) {
             float4 v[R][U];
@@ -150,7 +161,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 for (int u = 0; u < U; u++) {
                     int c = c0 + u * 32 + lane;
                     bool ok = ((load_mask >> r) & 1u) && (FULL_TILES || c < D4);
-                    v[r][u] = ok ? ldg_stream(rp + (size_t)r * D4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float4 *src = INDIRECT ? rpi[r] + c : rp + (size_t)r * D4 + c;
+                    v[r][u] = ok ? ldg_stream(src) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
 #pragma unroll
@@ -184,13 +196,14 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 #pragma unroll
         for (int r = 0; r < R; r++) {
             const float inv = __shfl_sync(0xFFFFFFFFu, my_inv, r);
+            const uint32_t row = INDIRECT ? __shfl_sync(0xFFFFFFFFu, my_row, r) : row0 + r;
             if (!((want_mask >> r) & 1u) || !(inv > 0.f)) continue;     // zero-norm rows never match
 #pragma unroll
             for (int q = 0; q < NQ; q++) {
                 float sim = acc[r][q] * inv * q_inv_s[q];
                 sim = fminf(1.f, fmaxf(-1.f, sim));                     // pgvector clamps to [-1, 1]
                 if (!(sim >= a.min_sim)) continue;                      // also drops NaN
-                key_t64 key = make_key(sim, a.row_base + row0 + r);
+                key_t64 key = make_key(sim, a.row_base + row);
                 warp_list_insert(lists + (size_t)q * P + warp * K, K, cnt[q], wmin[q], key, lane);
             }
         }
@@ -241,9 +254,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         for (int i = tid; i < K; i += kScanThreads) {
             key_t64 key = buf[i];
             a.out_keys[(size_t)q * K + i] = key;
-            uint4 id = make_uint4(0, 0, 0, 0);
-            if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
-            reinterpret_cast<uint4 *>(a.out_ids)[(size_t)q * K + i] = id;
+            if (a.out_ids) {
+                uint4 id = make_uint4(0, 0, 0, 0);
+                if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
+                reinterpret_cast<uint4 *>(a.out_ids)[(size_t)q * K + i] = id;
+            }
         }
         __syncthreads();
     }
@@ -256,7 +271,11 @@ template <int NQ, int R, int U>
 cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t stream)
 {
     const bool full = ((a.dim >> 2) % (32 * U)) == 0;
-    auto kern = full ? scan_topk_kernel<NQ, R, U, true> : scan_topk_kernel<NQ, R, U, false>;
+    auto kern = full ? scan_topk_kernel<NQ, R, U, true, false> : scan_topk_kernel<NQ, R, U, false, false>;
+    if (a.row_list) {
+        if constexpr (NQ == 1) kern = full ? scan_topk_kernel<1, R, U, true, true> : scan_topk_kernel<1, R, U, false, true>;
+        else return cudaErrorInvalidValue;
+    }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<grid, kScanThreads, smem, stream>>>(a);

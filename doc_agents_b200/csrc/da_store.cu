@@ -15,6 +15,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -125,7 +126,28 @@ struct Shard {
     PinBuf<uint32_t> h_up_rows, h_up_slots;
     PinBuf<uint8_t> h_up_ids;
     uint64_t hbm_bytes = 0;
+    // IVFFlat index over this shard's rows (centroids are identical on every shard)
+    struct Ivf {
+        float *cent = nullptr, *cent_inv = nullptr, *sums = nullptr, *counts_f = nullptr;
+        uint32_t *assign = nullptr, *offsets = nullptr, *cursor = nullptr, *counts = nullptr;
+        uint32_t *list_rows = nullptr, *probe_rows = nullptr, *n_probe = nullptr;
+        uint32_t *sample = nullptr, *sample_assign = nullptr;
+        da::key_t64 *probe_keys = nullptr;
+        uint32_t n_sample = 0;
+        uint64_t bytes = 0;
+    } ivf;
 };
+
+void free_ivf(Shard &s)
+{
+    Shard::Ivf &v = s.ivf;
+    cudaFree(v.cent); cudaFree(v.cent_inv); cudaFree(v.sums); cudaFree(v.counts_f);
+    cudaFree(v.assign); cudaFree(v.offsets); cudaFree(v.cursor); cudaFree(v.counts);
+    cudaFree(v.list_rows); cudaFree(v.probe_rows); cudaFree(v.n_probe);
+    cudaFree(v.sample); cudaFree(v.sample_assign); cudaFree(v.probe_keys);
+    s.hbm_bytes -= v.bytes;
+    v = Shard::Ivf();
+}
 
 }  // namespace
 
@@ -143,6 +165,7 @@ struct da_store {
     uint64_t last_rows_read = 0, last_bytes = 0, launches = 0, scan_launches = 0;
     double scan_ms_sum = 0;
     int scan_grid = 0;
+    int ivf_lists = 0, ivf_default_probes = 1;
 };
 
 namespace {
@@ -150,6 +173,7 @@ namespace {
 void free_shard(Shard &s)
 {
     cudaSetDevice(s.device);
+    free_ivf(s);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
     cudaFree(s.mat); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
@@ -208,6 +232,8 @@ struct SearchPlan {
     float min_sim;
     bool all_docs, read_all;
     size_t bitmap_words;
+    bool ivf;
+    int probes;
 };
 
 // Enqueue one complete search on every local shard: scan passes, collective, merge.
@@ -223,6 +249,37 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         // record block: [batch*k ids of 16 B][batch*k keys of 8 B]  (ids first keeps them 16-byte aligned)
         uint8_t *out_ids = s.d_out.p;
         da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(s.d_out.p + (size_t)pl.batch * pl.k * 16);
+        if (pl.ivf) {
+            // per query: rank the centroids (the fused scan over the L x dim centroid matrix, top `probes`),
+            // expand the chosen lists into one row list, run the fused scan over that row list.
+            const float ninf = -std::numeric_limits<float>::infinity();
+            for (int q = 0; q < pl.batch; q++) {
+                da::ScanArgs c{};
+                c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
+                c.queries = s.d_queries.p + (size_t)q * dim; c.q_inv_norm = s.d_qinv.p + q;
+                c.n_rows = (uint32_t)st->ivf_lists; c.row_base = 0;
+                c.dim = dim; c.nq = 1; c.k = pl.probes; c.min_sim = ninf;
+                c.cta_out = s.d_cta; c.counter = s.d_counter; c.out_keys = s.ivf.probe_keys;
+                CU(da::launch_scan(c, s.sm_count, s.stream, nullptr));
+                CU(da::ivf_launch_expand(s.ivf.probe_keys, pl.probes, s.ivf.offsets, s.ivf.list_rows, s.ivf.probe_rows,
+                                         s.ivf.n_probe, s.stream));
+                da::ScanArgs a{};
+                a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
+                a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p;
+                a.queries = c.queries; a.q_inv_norm = c.q_inv_norm;
+                a.row_list = s.ivf.probe_rows; a.n_rows_dev = s.ivf.n_probe; a.n_rows = 0; a.row_base = s.row_base;
+                a.dim = dim; a.nq = 1; a.k = pl.k; a.min_sim = pl.min_sim; a.read_all = pl.read_all ? 1 : 0;
+                a.cta_out = s.d_cta; a.counter = s.d_counter;
+                a.out_keys = out_keys + (size_t)q * pl.k; a.out_ids = out_ids + (size_t)q * pl.k * 16;
+                a.rows_read = s.d_rows_read;
+                int grid = 0;
+                CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
+                st->launches += 3;
+                if (first) { st->scan_grid = grid; st->scan_launches++; }
+            }
+            CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            continue;
+        }
         const int nq_max = da::scan_pick_nq(dim, pl.k, pl.batch);
         for (int q0 = 0; q0 < pl.batch; q0 += nq_max) {
             da::ScanArgs a{};
@@ -269,7 +326,8 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (p->k > DA_MAX_K) return fail(DA_ERR_INVALID, "k=%d exceeds DA_MAX_K=%d", p->k, DA_MAX_K);
     if (p->batch < 1 || p->batch > DA_MAX_BATCH) return fail(DA_ERR_INVALID, "batch=%d out of range [1,%d]", p->batch, DA_MAX_BATCH);
     if (!p->queries) return fail(DA_ERR_INVALID, "query vector is NULL");
-    if (p->flags & DA_SEARCH_IVF) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store");
+    const bool ivf = (p->flags & DA_SEARCH_IVF) != 0;
+    if (ivf && st->ivf_lists == 0) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store (da_store_build_ivf)");
     const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
     if (!all_docs && p->n_docs && !p->doc_ids) return fail(DA_ERR_INVALID, "doc_ids is NULL with n_docs=%zu", p->n_docs);
     const size_t nq_elems = (size_t)p->batch * st->dim;
@@ -279,6 +337,12 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     pl.batch = p->batch; pl.k = p->k; pl.min_sim = p->min_similarity;
     pl.all_docs = all_docs; pl.read_all = (p->flags & DA_SEARCH_READ_ALL_ROWS) != 0;
     pl.bitmap_words = (st->docs.size() + 31) / 32 + 1;
+    pl.ivf = ivf;
+    pl.probes = 0;
+    if (ivf) {
+        int probes = p->ivf_probes > 0 ? p->ivf_probes : st->ivf_default_probes;
+        pl.probes = std::max(1, std::min(probes, std::min(st->ivf_lists, DA_IVF_MAX_PROBES)));
+    }
 
     // document filter -> bit per slot (document_id = ANY($2): postgres.go:239); unknown ids match nothing
     std::vector<uint32_t> bitmap;
@@ -337,8 +401,12 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     st->last_rows_read = rows_read;
     // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
     // + doc_slot (4 B) of every row visited when a document filter is present.
-    st->last_bytes = rows_read * (uint64_t)st->dim * 4 +
-                     rows_scanned * (uint64_t)passes * (pl.all_docs ? 4 : 8);
+    if (pl.ivf)   // centroid matrix per query + the probed rows (vector, inv_norm, doc slot if filtered, row number)
+        st->last_bytes = (uint64_t)pl.batch * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
+                         rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
+    else
+        st->last_bytes = rows_read * (uint64_t)st->dim * 4 +
+                         rows_scanned * (uint64_t)passes * (pl.all_docs ? 4 : 8);
     return DA_OK;
 }
 
@@ -543,6 +611,12 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
         CU(da::launch_finalize_rows(sh.mat, dim, sh.d_up_rows.p, sh.d_up_slots.p, sh.d_up_ids.p, (uint32_t)cnt,
                                     sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
         st->launches++;
+        if (st->ivf_lists) {   // keep the index current, as pgvector does on insert: nearest list for the touched rows
+            CU(da::ivf_launch_assign(sh.mat, dim, sh.d_up_rows.p, (uint32_t)cnt, sh.ivf.cent, st->ivf_lists, sh.ivf.assign, 1, sh.stream));
+            CU(da::ivf_launch_build_lists(sh.ivf.assign, sh.n_rows + pending[s], st->ivf_lists, sh.ivf.counts, sh.ivf.offsets,
+                                          sh.ivf.cursor, sh.ivf.list_rows, sh.stream));
+            st->launches += 4;
+        }
     }
     for (int s = 0; s < S; s++) {
         Shard &sh = st->shards[s];
@@ -661,9 +735,92 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
 
 int da_store_build_ivf(da_store *st, const da_ivf_params *p)
 {
-    (void)p;
-    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
-    return fail(DA_ERR_STATE, "IVFFlat build is not available in this build");
+    if (!st || !p) return fail(DA_ERR_INVALID, "store/params is NULL");
+    if (p->struct_size != sizeof(da_ivf_params)) return fail(DA_ERR_INVALID, "da_ivf_params.struct_size mismatch");
+    if (p->lists < 1 || p->lists > 65536) return fail(DA_ERR_INVALID, "lists=%d out of range [1, 65536]", p->lists);
+    std::lock_guard<std::mutex> lock(st->mu);
+    const int L = p->lists, D = st->dim;
+    const int iters = p->iters <= 0 ? 10 : std::min(p->iters, 20);
+    for (Shard &s : st->shards)
+        if (s.n_rows == 0) return fail(DA_ERR_STATE, "build_ivf: a shard holds no rows");
+    if ((uint64_t)L > st->shards[0].n_rows) return fail(DA_ERR_INVALID, "lists=%d exceeds the %u rows of the first shard", L, st->shards[0].n_rows);
+    const uint64_t sample_total = p->sample_rows ? p->sample_rows : std::max<uint64_t>((uint64_t)L * 50, 10000);   // pgvector's rule
+    const uint64_t per_shard = (sample_total + st->total_ranks - 1) / st->total_ranks;
+    st->ivf_lists = 0;
+    for (Shard &s : st->shards) {
+        CU(cudaSetDevice(s.device));
+        free_ivf(s);
+        Shard::Ivf &v = s.ivf;
+        v.n_sample = (uint32_t)std::min<uint64_t>(s.n_rows, std::max<uint64_t>(per_shard, (uint64_t)L));
+        const size_t cd = (size_t)L * D * 4;
+        CU(cudaMalloc((void **)&v.cent, cd)); CU(cudaMalloc((void **)&v.sums, cd));
+        CU(cudaMalloc((void **)&v.cent_inv, (size_t)L * 4)); CU(cudaMalloc((void **)&v.counts_f, (size_t)L * 4));
+        CU(cudaMalloc((void **)&v.assign, s.cap_rows * 4)); CU(cudaMalloc((void **)&v.list_rows, s.cap_rows * 4));
+        CU(cudaMalloc((void **)&v.probe_rows, s.cap_rows * 4)); CU(cudaMalloc((void **)&v.n_probe, 4));
+        CU(cudaMalloc((void **)&v.offsets, (size_t)(L + 1) * 4)); CU(cudaMalloc((void **)&v.cursor, (size_t)L * 4));
+        CU(cudaMalloc((void **)&v.counts, (size_t)L * 4));
+        CU(cudaMalloc((void **)&v.sample, (size_t)v.n_sample * 4)); CU(cudaMalloc((void **)&v.sample_assign, (size_t)v.n_sample * 4));
+        CU(cudaMalloc((void **)&v.probe_keys, DA_IVF_MAX_PROBES * sizeof(da::key_t64)));
+        v.bytes = 2 * cd + (size_t)L * 20 + s.cap_rows * 12 + (size_t)v.n_sample * 8 + 4096;
+        s.hbm_bytes += v.bytes;
+        CU(da::ivf_launch_sample(s.n_rows, v.n_sample, p->seed + 0x51ED * (uint64_t)(&s - &st->shards[0] + 1 + st->rank * st->shards.size()),
+                                 v.sample, s.stream));
+        st->launches++;
+    }
+    // initial centroids: sample rows of global rank 0, then the same on every shard
+    {
+        Shard &s0 = st->shards[0];
+        CU(cudaSetDevice(s0.device));
+        if (st->rank == 0) {
+            CU(da::ivf_launch_init_centroids(s0.mat, D, s0.inv_norm, s0.ivf.sample, s0.ivf.n_sample, L, s0.ivf.cent,
+                                             s0.ivf.cent_inv, s0.stream));
+            st->launches += 2;
+        }
+        if (st->total_ranks > 1) {
+            NC(ncclGroupStart());
+            for (Shard &s : st->shards) NC(ncclBroadcast(s.ivf.cent, s.ivf.cent, (size_t)L * D, ncclFloat, 0, s.comm, s.stream));
+            NC(ncclGroupEnd());
+            NC(ncclGroupStart());
+            for (Shard &s : st->shards) NC(ncclBroadcast(s.ivf.cent_inv, s.ivf.cent_inv, (size_t)L, ncclFloat, 0, s.comm, s.stream));
+            NC(ncclGroupEnd());
+        }
+    }
+    for (int it = 0; it < iters; it++) {
+        for (Shard &s : st->shards) {
+            Shard::Ivf &v = s.ivf;
+            CU(cudaSetDevice(s.device));
+            CU(cudaMemsetAsync(v.sums, 0, (size_t)L * D * 4, s.stream));
+            CU(cudaMemsetAsync(v.counts_f, 0, (size_t)L * 4, s.stream));
+            CU(da::ivf_launch_assign(s.mat, D, v.sample, v.n_sample, v.cent, L, v.sample_assign, 0, s.stream));
+            CU(da::ivf_launch_accumulate(s.mat, D, s.inv_norm, v.sample, v.n_sample, v.sample_assign, v.sums, v.counts_f, s.stream));
+            st->launches += 2;
+        }
+        if (st->total_ranks > 1) {   // data-parallel k-means: partial sums and counts meet here
+            NC(ncclGroupStart());
+            for (Shard &s : st->shards) {
+                NC(ncclAllReduce(s.ivf.sums, s.ivf.sums, (size_t)L * D, ncclFloat, ncclSum, s.comm, s.stream));
+                NC(ncclAllReduce(s.ivf.counts_f, s.ivf.counts_f, (size_t)L, ncclFloat, ncclSum, s.comm, s.stream));
+            }
+            NC(ncclGroupEnd());
+        }
+        for (Shard &s : st->shards) {
+            CU(cudaSetDevice(s.device));
+            CU(da::ivf_launch_finalize(s.ivf.sums, s.ivf.counts_f, L, D, s.ivf.cent, s.stream));
+            st->launches++;
+        }
+    }
+    // every resident row joins the list of its nearest centroid
+    for (Shard &s : st->shards) {
+        Shard::Ivf &v = s.ivf;
+        CU(cudaSetDevice(s.device));
+        CU(da::ivf_launch_assign(s.mat, D, nullptr, s.n_rows, v.cent, L, v.assign, 0, s.stream));
+        CU(da::ivf_launch_build_lists(v.assign, s.n_rows, L, v.counts, v.offsets, v.cursor, v.list_rows, s.stream));
+        st->launches += 4;
+    }
+    for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    st->ivf_lists = L;
+    st->ivf_default_probes = p->default_probes > 0 ? p->default_probes : 1;
+    return DA_OK;
 }
 
 int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
@@ -734,7 +891,7 @@ int da_store_stats(da_store *st, da_stats *out)
     out->last_scan_ms = st->last_scan_ms; out->last_search_ms = st->last_search_ms;
     out->last_rows_read = st->last_rows_read; out->last_bytes_algorithmic = st->last_bytes;
     out->kernel_launches = st->launches;
-    out->ivf_lists = 0;
+    out->ivf_lists = st->ivf_lists;
     out->scan_grid = st->scan_grid;
     out->scan_ms_sum = st->scan_ms_sum; out->scan_launches = st->scan_launches;
     return DA_OK;
@@ -754,6 +911,22 @@ int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo
     if (out_inv_norm) CU(cudaMemcpy(out_inv_norm, s.inv_norm + row_lo, n * 4, cudaMemcpyDeviceToHost));
     if (out_doc_slot) CU(cudaMemcpy(out_doc_slot, s.doc_slot + row_lo, n * 4, cudaMemcpyDeviceToHost));
     if (out_chunk_ids) CU(cudaMemcpy(out_chunk_ids, s.chunk_ids + row_lo * 16, n * 16, cudaMemcpyDeviceToHost));
+    return DA_OK;
+}
+
+int da_store_debug_read_ivf(da_store *st, int32_t device_index, uint32_t *out_offsets, uint32_t *out_list_rows,
+                            float *out_centroids)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
+    if (!st->ivf_lists) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store");
+    Shard &s = st->shards[device_index];
+    const int L = st->ivf_lists;
+    CU(cudaSetDevice(s.device));
+    if (out_offsets) CU(cudaMemcpy(out_offsets, s.ivf.offsets, (size_t)(L + 1) * 4, cudaMemcpyDeviceToHost));
+    if (out_list_rows) CU(cudaMemcpy(out_list_rows, s.ivf.list_rows, (size_t)s.n_rows * 4, cudaMemcpyDeviceToHost));
+    if (out_centroids) CU(cudaMemcpy(out_centroids, s.ivf.cent, (size_t)L * st->dim * 4, cudaMemcpyDeviceToHost));
     return DA_OK;
 }
 

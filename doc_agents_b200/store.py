@@ -276,6 +276,18 @@ class GpuStore:
         return vecs, inv, slot, ids
 
 
+    def debug_ivf(self, device_index: int = 0):
+        """(list offsets, row numbers grouped by list, centroids) of the IVFFlat index on one shard."""
+        st = self.stats()
+        L, n = st.ivf_lists, int(st.rows_per_device[device_index])
+        off = np.empty(L + 1, dtype=np.uint32)
+        rows = np.empty(n, dtype=np.uint32)
+        cent = np.empty((L, self.dim), dtype=np.float32)
+        _check(self._lib.da_store_debug_read_ivf(self._h, device_index, off.ctypes.data, rows.ctypes.data,
+                                                 cent.ctypes.data))
+        return off, rows, cent
+
+
 def calculate_avg_similarity(results) -> np.float32:
     """cmd/query/main.go:161-170: float32 running sum over the results, divided by n."""
     if not results:

@@ -176,6 +176,11 @@ int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo
                              float *out_vecs, float *out_inv_norm, uint32_t *out_doc_slot,
                              uint8_t *out_chunk_ids);
 
+/* Test-harness view of the IVFFlat index on one shard: out_offsets lists+1 entries, out_list_rows
+ * one entry per resident row (rows grouped by list), out_centroids lists x dim.  Any may be NULL. */
+int da_store_debug_read_ivf(da_store *st, int32_t device_index, uint32_t *out_offsets,
+                            uint32_t *out_list_rows, float *out_centroids);
+
 /* No counterpart in the reference.  The exact scan of da_store_search for hosts that must not
  * allocate: a serving loop that cannot afford cudaMalloc's device-wide synchronisation, a process
  * whose HBM is already fully committed (a late cudaMalloc would fail), or code running where its
