@@ -32,6 +32,8 @@ DA_SEARCH_ALL_DOCS = 0x1
 DA_SEARCH_READ_ALL_ROWS = 0x2
 DA_SEARCH_IVF = 0x4
 
+DA_IVF_SIMT_ASSIGN = 0x1
+
 DA_NOALLOC_MAX_K = 128
 DA_NOALLOC_MAX_CTAS = 256
 
@@ -52,7 +54,8 @@ class da_search_params(C.Structure):
 
 class da_ivf_params(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("lists", C.c_int32), ("iters", C.c_int32),
-                ("sample_rows", C.c_uint64), ("seed", C.c_uint64), ("default_probes", C.c_int32)]
+                ("sample_rows", C.c_uint64), ("seed", C.c_uint64), ("default_probes", C.c_int32),
+                ("flags", C.c_uint32)]
 
 
 class da_synth_params(C.Structure):

@@ -122,6 +122,12 @@ cudaError_t ivf_launch_build_lists(const uint32_t *assign, uint32_t n, int L, ui
 cudaError_t ivf_launch_expand(const key_t64 *probe_keys, int probes, const uint32_t *offsets, const uint32_t *list_rows,
                               uint32_t *out_rows, uint32_t *out_n, cudaStream_t stream);
 
+// Tensor-core assignment (da_tc.cu): out_assign[m] = argmax_l <mat[m], cent[l]>, tcgen05 kind::tf32.
+size_t tc_assign_scratch_bytes(uint32_t M);
+cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *cent, int L,
+                             unsigned long long *packed_scratch, uint32_t *out_assign, cudaStream_t stream);
+cudaError_t tc_launch_gather_rows(const float *mat, int D, const uint32_t *rows, uint32_t n, float *out, cudaStream_t stream);
+
 // Host restatement of the id hash of the synthetic corpus (spec: DESIGN.md).
 void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);
 

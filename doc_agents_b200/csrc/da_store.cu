@@ -133,6 +133,8 @@ struct Shard {
         uint32_t *list_rows = nullptr, *probe_rows = nullptr, *n_probe = nullptr;
         uint32_t *sample = nullptr, *sample_assign = nullptr;
         da::key_t64 *probe_keys = nullptr;
+        float *sample_mat = nullptr;              // the k-means sample, gathered once (tensor-core path)
+        unsigned long long *packed = nullptr;     // per-row packed (score, list) for the tensor-core argmax
         uint32_t n_sample = 0;
         uint64_t bytes = 0;
     } ivf;
@@ -145,6 +147,7 @@ void free_ivf(Shard &s)
     cudaFree(v.assign); cudaFree(v.offsets); cudaFree(v.cursor); cudaFree(v.counts);
     cudaFree(v.list_rows); cudaFree(v.probe_rows); cudaFree(v.n_probe);
     cudaFree(v.sample); cudaFree(v.sample_assign); cudaFree(v.probe_keys);
+    cudaFree(v.sample_mat); cudaFree(v.packed);
     s.hbm_bytes -= v.bytes;
     v = Shard::Ivf();
 }
@@ -741,6 +744,7 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     std::lock_guard<std::mutex> lock(st->mu);
     const int L = p->lists, D = st->dim;
     const int iters = p->iters <= 0 ? 10 : std::min(p->iters, 20);
+    const bool use_tc = !(p->flags & DA_IVF_SIMT_ASSIGN);
     for (Shard &s : st->shards)
         if (s.n_rows == 0) return fail(DA_ERR_STATE, "build_ivf: a shard holds no rows");
     if ((uint64_t)L > st->shards[0].n_rows) return fail(DA_ERR_INVALID, "lists=%d exceeds the %u rows of the first shard", L, st->shards[0].n_rows);
@@ -762,10 +766,19 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
         CU(cudaMalloc((void **)&v.sample, (size_t)v.n_sample * 4)); CU(cudaMalloc((void **)&v.sample_assign, (size_t)v.n_sample * 4));
         CU(cudaMalloc((void **)&v.probe_keys, DA_IVF_MAX_PROBES * sizeof(da::key_t64)));
         v.bytes = 2 * cd + (size_t)L * 20 + s.cap_rows * 12 + (size_t)v.n_sample * 8 + 4096;
+        if (use_tc) {
+            CU(cudaMalloc((void **)&v.sample_mat, (size_t)v.n_sample * D * 4));
+            CU(cudaMalloc((void **)&v.packed, da::tc_assign_scratch_bytes((uint32_t)s.cap_rows)));
+            v.bytes += (size_t)v.n_sample * D * 4 + s.cap_rows * 8;
+        }
         s.hbm_bytes += v.bytes;
         CU(da::ivf_launch_sample(s.n_rows, v.n_sample, p->seed + 0x51ED * (uint64_t)(&s - &st->shards[0] + 1 + st->rank * st->shards.size()),
                                  v.sample, s.stream));
         st->launches++;
+        if (use_tc) {
+            CU(da::tc_launch_gather_rows(s.mat, D, v.sample, v.n_sample, v.sample_mat, s.stream));
+            st->launches++;
+        }
     }
     // initial centroids: sample rows of global rank 0, then the same on every shard
     {
@@ -791,7 +804,8 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
             CU(cudaSetDevice(s.device));
             CU(cudaMemsetAsync(v.sums, 0, (size_t)L * D * 4, s.stream));
             CU(cudaMemsetAsync(v.counts_f, 0, (size_t)L * 4, s.stream));
-            CU(da::ivf_launch_assign(s.mat, D, v.sample, v.n_sample, v.cent, L, v.sample_assign, 0, s.stream));
+            if (use_tc) CU(da::tc_launch_assign(v.sample_mat, v.n_sample, D, v.cent, L, v.packed, v.sample_assign, s.stream));
+            else CU(da::ivf_launch_assign(s.mat, D, v.sample, v.n_sample, v.cent, L, v.sample_assign, 0, s.stream));
             CU(da::ivf_launch_accumulate(s.mat, D, s.inv_norm, v.sample, v.n_sample, v.sample_assign, v.sums, v.counts_f, s.stream));
             st->launches += 2;
         }
@@ -813,7 +827,8 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     for (Shard &s : st->shards) {
         Shard::Ivf &v = s.ivf;
         CU(cudaSetDevice(s.device));
-        CU(da::ivf_launch_assign(s.mat, D, nullptr, s.n_rows, v.cent, L, v.assign, 0, s.stream));
+        if (use_tc) CU(da::tc_launch_assign(s.mat, s.n_rows, D, v.cent, L, v.packed, v.assign, s.stream));
+        else CU(da::ivf_launch_assign(s.mat, D, nullptr, s.n_rows, v.cent, L, v.assign, 0, s.stream));
         CU(da::ivf_launch_build_lists(v.assign, s.n_rows, L, v.counts, v.offsets, v.cursor, v.list_rows, s.stream));
         st->launches += 4;
     }

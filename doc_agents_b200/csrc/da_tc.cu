@@ -1,0 +1,297 @@
+// Tensor-core GEMM with a fused per-row reduction for sm_100a (tcgen05 + TMEM + TMA).
+//
+//   scores = A (M x K, fp32, K contiguous) . B^T (N x K, fp32, K contiguous)     as kind::tf32
+//   out[m] = argmax_n scores[m][n]                       (the score matrix is never written)
+//
+// Used for the IVFFlat build (internal/store/postgres.go:95-99 asks Postgres for that index):
+// A = embedding rows (or the k-means sample), B = centroids.  TF32 reads the fp32 words as they
+// sit in HBM (TMA -> 128B-swizzled shared memory -> tcgen05.mma), so no conversion pass and no
+// second copy of the corpus exist.  Assignment only steers recall; scores returned to the caller
+// always come from the fp32 scan.
+//
+// CTA = 192 threads:  warp 0 TMA producer | warp 1 TMEM owner + MMA issuer | warps 2-5 epilogue.
+// Tile 128 (M) x 256 (N) x 32 (K, = one 128-byte swizzle row), 4-stage smem ring (48 KB/stage),
+// two 256-column accumulators in TMEM so the epilogue of tile t overlaps the MMAs of tile t+1.
+// Epilogue thread r owns accumulator lane r = one row of A, streams the 256 columns through
+// registers with tcgen05.ld and keeps a running (max, argmax): no cross-thread reduction.
+// Grid = M tiles x N partitions; sibling CTAs (same M tile) run together so the A tile is read
+// from HBM once and from L2 afterwards; partitions meet through one 64-bit atomicMax per row.
+#include "da_internal.h"
+
+#include <cuda.h>
+
+namespace da {
+
+namespace {
+
+constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32, TC_STAGES = 4, TC_UMMA_K = 8;
+constexpr int TC_THREADS = 192;
+constexpr uint32_t TC_A_BYTES = TC_BM * TC_BK * 4;            // 16 KB
+constexpr uint32_t TC_B_BYTES = TC_BN * TC_BK * 4;            // 32 KB
+constexpr uint32_t TC_STAGE_BYTES = TC_A_BYTES + TC_B_BYTES;  // 48 KB
+constexpr uint32_t TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t TC_TMEM_COLS = 512;
+
+// instruction descriptor: D=f32, A=B=tf32, both K-major, N=256, M=128
+constexpr uint32_t TC_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+// K-major, 128-byte swizzle: 8-row groups are 1024 B apart (SBO), LBO unused (=1), descriptor version 1
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr)
+{
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+           ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da_, uint64_t db_, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+                 "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_rowargmax_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    uint32_t M, uint32_t N, int K, int n_parts, unsigned long long *__restrict__ out_packed)
+{
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;          // SW128 tiles need 1024-byte alignment
+    const uint32_t bars = base + TC_STAGES * TC_STAGE_BYTES;
+    // barrier slots (8 B each): full[4] | empty[4] | tmem_full[2] | tmem_empty[2] | tmem base address
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * TC_STAGES;
+    const uint32_t bar_tfull = bars + 16 * TC_STAGES, bar_tempty = bar_tfull + 16;
+    const uint32_t tmem_slot = bar_tempty + 16;
+    volatile uint32_t *tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t m_tile = blockIdx.x / n_parts, part = blockIdx.x % n_parts;
+    const uint32_t m0 = m_tile * TC_BM;
+    const int n_tiles_total = (int)((N + TC_BN - 1) / TC_BN);
+    const int per_part = (n_tiles_total + n_parts - 1) / n_parts;
+    const int t_begin = (int)part * per_part;
+    const int t_end = min(n_tiles_total, t_begin + per_part);
+    const int kb_count = (K + TC_BK - 1) / TC_BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = t_begin; t < t_end; t++) {
+                for (int kb = 0; kb < kb_count; kb++) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                    mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
+                    tma_load_2d(sa, &map_a, bar_full + 8 * stage, kb * TC_BK, (int)m0);
+                    tma_load_2d(sb, &map_b, bar_full + 8 * stage, kb * TC_BK, t * TC_BN);
+                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one elected lane) =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = t_begin; t < t_end; t++, it++) {
+                const int as = it & 1;
+                const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+                mbar_wait(bar_tempty + 8 * as, aphase ^ 1);            // epilogue drained this accumulator
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + (uint32_t)as * TC_BN;
+                for (int kb = 0; kb < kb_count; kb++) {
+                    mbar_wait(bar_full + 8 * stage, phase);              // TMA bytes have landed
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                    const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
+#pragma unroll
+                    for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
+                        // advancing K inside the 128-byte swizzle row: +32 bytes = +2 in the >>4 start address
+                        umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
+                    }
+                    umma_commit(bar_empty + 8 * stage);                  // frees the smem slot when the MMAs retire
+                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(bar_tfull + 8 * as);                         // accumulator complete -> epilogue
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+        const uint32_t quad = (uint32_t)warp & 3u;
+        const uint32_t row = m0 + quad * 32 + (uint32_t)lane;
+        float best = -3.0e38f;
+        uint32_t best_n = 0;
+        int it = 0;
+        for (int t = t_begin; t < t_end; t++, it++) {
+            const int as = it & 1;
+            const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+            mbar_wait(bar_tfull + 8 * as, aphase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * TC_BN;
+#pragma unroll 1
+            for (int c = 0; c < TC_BN / 32; c++) {
+                uint32_t r[32];
+                tmem_ld32(taddr + (uint32_t)c * 32u, r);
+                const uint32_t n0 = (uint32_t)t * TC_BN + (uint32_t)c * 32u;
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    const float v = __uint_as_float(r[j]);
+                    if (n0 + j < N && v > best) { best = v; best_n = n0 + j; }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+        }
+        if (row < M && t_begin < t_end) {
+            const unsigned long long packed = ((unsigned long long)score_to_ordered(best) << 32) | (unsigned long long)(~best_n);
+            atomicMax(out_packed + row, packed);
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
+    }
+}
+
+__global__ void unpack_assign_kernel(const unsigned long long *packed, uint32_t n, uint32_t *assign)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        assign[i] = ~(uint32_t)(packed[i] & 0xFFFFFFFFull);
+}
+
+__global__ void gather_rows_kernel(const float *mat, int D, const uint32_t *rows, uint32_t n, float *out)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = w; i < n; i += nw) {
+        const float4 *src = reinterpret_cast<const float4 *>(mat + (size_t)rows[i] * D);
+        float4 *dst = reinterpret_cast<float4 *>(out + (size_t)i * D);
+        for (int c = lane; c < (D >> 2); c += 32) dst[c] = src[c];
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// rows x K fp32 row-major -> boxes of [box_rows][32 floats], 128-byte swizzle, zero fill out of bounds
+bool make_map(CUtensorMap *map, const float *ptr, uint64_t rows, uint64_t K, uint32_t box_rows)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {K, rows};
+    cuuint64_t strides[1] = {K * 4};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(ptr), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+size_t tc_assign_scratch_bytes(uint32_t M) { return (size_t)M * sizeof(unsigned long long); }
+
+cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *cent, int L,
+                             unsigned long long *packed_scratch, uint32_t *out_assign, cudaStream_t stream)
+{
+    if (M == 0) return cudaSuccess;
+    if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(cent) & 15) || (D & 3)) return cudaErrorInvalidValue;
+    CUtensorMap map_a, map_b;
+    if (!make_map(&map_a, mat, M, (uint64_t)D, TC_BM) || !make_map(&map_b, cent, (uint64_t)L, (uint64_t)D, TC_BN))
+        return cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(packed_scratch, 0, tc_assign_scratch_bytes(M), stream);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tc_rowargmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    const int n_tiles = (L + TC_BN - 1) / TC_BN;
+    // N partitions: sibling CTAs share one A tile through L2 and each sweeps at most 4 B tiles
+    int n_parts = (n_tiles + 3) / 4;
+    if (n_parts < 1) n_parts = 1;
+    const uint32_t m_tiles = (M + TC_BM - 1) / TC_BM;
+    tc_rowargmax_kernel<<<m_tiles * (uint32_t)n_parts, TC_THREADS, TC_SMEM_BYTES, stream>>>(map_a, map_b, M, (uint32_t)L, D, n_parts, packed_scratch);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    unpack_assign_kernel<<<148 * 4, 256, 0, stream>>>(packed_scratch, M, out_assign);
+    return cudaGetLastError();
+}
+
+cudaError_t tc_launch_gather_rows(const float *mat, int D, const uint32_t *rows, uint32_t n, float *out, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    gather_rows_kernel<<<148 * 4, 256, 0, stream>>>(mat, D, rows, n, out);
+    return cudaGetLastError();
+}
+
+}  // namespace da

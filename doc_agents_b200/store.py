@@ -255,10 +255,11 @@ class GpuStore:
         _check(self._lib.da_store_generate_synthetic(self._h, C.byref(p)))
 
     def build_ivf(self, lists: int = 100, iters: int = 10, sample_rows: int = 0, seed: int = 1,
-                  default_probes: int = 1) -> None:
+                  default_probes: int = 1, simt_assign: bool = False) -> None:
         p = L.da_ivf_params()
         p.struct_size = C.sizeof(L.da_ivf_params)
         p.lists, p.iters, p.sample_rows, p.seed, p.default_probes = lists, iters, sample_rows, seed, default_probes
+        p.flags = L.DA_IVF_SIMT_ASSIGN if simt_assign else 0
         _check(self._lib.da_store_build_ivf(self._h, C.byref(p)))
 
     def stats(self) -> L.da_stats:

@@ -130,7 +130,9 @@ typedef struct {
     uint64_t sample_rows;    /* 0 = max(lists*50, 10000), pgvector's rule */
     uint64_t seed;
     int32_t  default_probes; /* pgvector default is 1 (ivfflat.probes) */
+    uint32_t flags;          /* DA_IVF_SIMT_ASSIGN: assign with the fp32 SIMT GEMM instead of tcgen05 TF32 */
 } da_ivf_params;
+#define DA_IVF_SIMT_ASSIGN 0x1u
 int da_store_build_ivf(da_store *st, const da_ivf_params *p);
 
 /* Device-side synthetic corpus (bench/tests only; SURVEY.md section 8d, DESIGN.md

@@ -48,7 +48,9 @@ def test_ivf_structure_and_exactness(n, dim, lists, clusters):
             list_of_row[rows[off[l]:off[l + 1]]] = l
         best = dots.max(axis=1)
         got = dots[np.arange(n), list_of_row]
-        assert np.all(best - got <= 1e-5), "a row is not in the list of its nearest centroid"
+        # tensor-core (TF32) assignment may pick a centroid that is nearest only up to TF32 rounding
+        assert np.all(best - got <= 2e-3), "a row is not in the list of a nearest centroid"
+        assert np.mean(best - got <= 1e-6) > 0.99
 
         docs = oracle.doc_ids(S, 0, n // 200)
         rd = oracle.row_docs(S, 0, n)
@@ -121,3 +123,29 @@ def test_ivf_stays_current_after_upserts():
         got = st.search(q, 5, all_docs=True, ivf=True, probes=1)
         assert list(got[2][0][:3]) == [n, n + 1, n + 2] and np.allclose(got[1][0][:3], 1.0, atol=1e-6)
         assert np.array_equal(got[0][0][:3], chunk)
+
+
+@pytest.mark.parametrize("n,dim,lists", [(5000, 3072, 300), (4100, 1536, 64), (777, 100, 9)])
+def test_tensor_core_assignment_agrees_with_fp32_simt(n, dim, lists):
+    """The tcgen05 TF32 GEMM+argmax against the fp32 SIMT GEMM+argmax on the same centroids
+    (iters=0 -> k-means keeps the seeded centroids, so both builds assign against identical ones)."""
+    S = oracle.Synth(n_clusters=32)
+    results = {}
+    for simt in (True, False):
+        with GpuStore(dim=dim, capacity_rows=n) as st:
+            st.generate_synthetic(S, 0, n)
+            st.build_ivf(lists=lists, iters=1, seed=5, simt_assign=simt)
+            off, rows, cent = st.debug_ivf()
+            lor = np.empty(n, dtype=np.int64)
+            for l in range(lists):
+                lor[rows[off[l]:off[l + 1]]] = l
+            results[simt] = (lor, cent)
+    (l_simt, c_simt), (l_tc, c_tc) = results[True], results[False]
+    mat = oracle.gen_rows(S, 0, n, dim).astype(np.float64)
+    # after one k-means step the two centroid sets differ only where TF32 flipped a near-tie
+    d_tc = mat @ c_tc.astype(np.float64).T
+    best = d_tc.max(axis=1)
+    got = d_tc[np.arange(n), l_tc]
+    assert np.all(best - got <= 2e-3)
+    assert np.mean(best - got <= 1e-6) > 0.99
+    assert np.mean(l_simt == l_tc) > 0.97
