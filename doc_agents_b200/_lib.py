@@ -71,7 +71,9 @@ class da_stats(C.Structure):
                 ("n_docs", C.c_uint64), ("last_scan_ms", C.c_float), ("last_search_ms", C.c_float),
                 ("last_rows_read", C.c_uint64), ("last_bytes_algorithmic", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("ivf_lists", C.c_int32), ("scan_grid", C.c_int32),
-                ("scan_ms_sum", C.c_double), ("scan_launches", C.c_uint64)]
+                ("scan_ms_sum", C.c_double), ("scan_launches", C.c_uint64),
+                ("ivf_build_ms", C.c_float), ("ivf_kmeans_ms", C.c_float), ("ivf_assign_ms", C.c_float),
+                ("ivf_assign_tflops", C.c_float)]
 
 
 # Every symbol include/docagents_b200.h declares, with its signature.

@@ -169,6 +169,7 @@ struct da_store {
     double scan_ms_sum = 0;
     int scan_grid = 0;
     int ivf_lists = 0, ivf_default_probes = 1;
+    float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
 
 namespace {
@@ -751,6 +752,14 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     const uint64_t sample_total = p->sample_rows ? p->sample_rows : std::max<uint64_t>((uint64_t)L * 50, 10000);   // pgvector's rule
     const uint64_t per_shard = (sample_total + st->total_ranks - 1) / st->total_ranks;
     st->ivf_lists = 0;
+    cudaEvent_t ev[4];
+    {
+        Shard &s0 = st->shards[0];
+        CU(cudaSetDevice(s0.device));
+        while (s0.ev_pool.size() < 4) { cudaEvent_t e; CU(cudaEventCreate(&e)); s0.ev_pool.push_back(e); }
+        for (int i = 0; i < 4; i++) ev[i] = s0.ev_pool[i];
+        CU(cudaEventRecord(ev[0], s0.stream));
+    }
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
         free_ivf(s);
@@ -798,6 +807,7 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
             NC(ncclGroupEnd());
         }
     }
+    { Shard &s0 = st->shards[0]; CU(cudaSetDevice(s0.device)); CU(cudaEventRecord(ev[1], s0.stream)); }
     for (int it = 0; it < iters; it++) {
         for (Shard &s : st->shards) {
             Shard::Ivf &v = s.ivf;
@@ -827,12 +837,26 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     for (Shard &s : st->shards) {
         Shard::Ivf &v = s.ivf;
         CU(cudaSetDevice(s.device));
+        if (&s == &st->shards[0]) CU(cudaEventRecord(ev[2], s.stream));
         if (use_tc) CU(da::tc_launch_assign(s.mat, s.n_rows, D, v.cent, L, v.packed, v.assign, s.stream));
         else CU(da::ivf_launch_assign(s.mat, D, nullptr, s.n_rows, v.cent, L, v.assign, 0, s.stream));
+        if (&s == &st->shards[0]) CU(cudaEventRecord(ev[3], s.stream));
         CU(da::ivf_launch_build_lists(v.assign, s.n_rows, L, v.counts, v.offsets, v.cursor, v.list_rows, s.stream));
         st->launches += 4;
     }
     for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    {
+        Shard &s0 = st->shards[0];
+        CU(cudaSetDevice(s0.device));
+        cudaEvent_t done = s0.ev_all1;
+        CU(cudaEventRecord(done, s0.stream));
+        CU(cudaEventSynchronize(done));
+        CU(cudaEventElapsedTime(&st->ivf_build_ms, ev[0], done));
+        CU(cudaEventElapsedTime(&st->ivf_kmeans_ms, ev[1], ev[2]));
+        CU(cudaEventElapsedTime(&st->ivf_assign_ms, ev[2], ev[3]));
+        st->ivf_assign_tflops = st->ivf_assign_ms > 0
+            ? (float)(2.0 * s0.n_rows * (double)L * D / (st->ivf_assign_ms * 1e-3) / 1e12) : 0.f;
+    }
     st->ivf_lists = L;
     st->ivf_default_probes = p->default_probes > 0 ? p->default_probes : 1;
     return DA_OK;
@@ -909,6 +933,8 @@ int da_store_stats(da_store *st, da_stats *out)
     out->ivf_lists = st->ivf_lists;
     out->scan_grid = st->scan_grid;
     out->scan_ms_sum = st->scan_ms_sum; out->scan_launches = st->scan_launches;
+    out->ivf_build_ms = st->ivf_build_ms; out->ivf_kmeans_ms = st->ivf_kmeans_ms;
+    out->ivf_assign_ms = st->ivf_assign_ms; out->ivf_assign_tflops = st->ivf_assign_tflops;
     return DA_OK;
 }
 

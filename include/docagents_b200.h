@@ -165,6 +165,11 @@ typedef struct {
     int32_t  scan_grid;             /* CTAs of the last scan launch */
     double   scan_ms_sum;           /* cumulative CUDA-event time of scan launches on shard 0 */
     uint64_t scan_launches;         /* how many launches scan_ms_sum covers */
+    /* last da_store_build_ivf, CUDA events on shard 0's stream: */
+    float    ivf_build_ms;          /* whole build */
+    float    ivf_kmeans_ms;         /* all k-means iterations (assignment GEMM + accumulate + finalize + all-reduce) */
+    float    ivf_assign_ms;         /* final assignment GEMM over every resident row of shard 0 */
+    float    ivf_assign_tflops;     /* 2 * rows * lists * dim / ivf_assign_ms */
 } da_stats;
 int da_store_stats(da_store *st, da_stats *out);
 
