@@ -31,6 +31,7 @@ DA_ERR_NONFINITE = -8
 DA_SEARCH_ALL_DOCS = 0x1
 DA_SEARCH_READ_ALL_ROWS = 0x2
 DA_SEARCH_IVF = 0x4
+DA_SEARCH_NO_TENSOR = 0x10
 
 DA_IVF_SIMT_ASSIGN = 0x1
 

@@ -364,6 +364,104 @@ __global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gat
 }
 }  // namespace
 
+// ---------------------------------------------------------------------------
+// Second and third stage of the batched tensor-core path (da_tc.cu produces the candidates).
+// ---------------------------------------------------------------------------
+namespace {
+
+// Exact fp32 score of every candidate, with the scan kernel's own arithmetic (lane owns float4
+// slots lane + 32 j, x-y-z-w FMA order, xor-shuffle tree, then * 1/|row| * 1/|q|), so a batched
+// search returns bit-identical scores to a single one.  The entry is overwritten by its final key.
+__global__ void __launch_bounds__(128) rescore_candidates_kernel(key_t64 *cand, const uint32_t *cand_count, int cap,
+                                                                 int n_splits, int batch, const float *mat, int dim,
+                                                                 const float *inv_norm, const float *queries,
+                                                                 const float *q_inv, uint32_t row_base, float min_sim)
+{
+    const size_t list_id = blockIdx.x;
+    const uint32_t cnt = cand_count[list_id];
+    if (cnt == 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t qlocal = (uint32_t)(list_id % 128);
+    const uint32_t m_tile = (uint32_t)(list_id / ((size_t)n_splits * 128));
+    const uint32_t q = m_tile * 128 + qlocal;
+    if (q >= (uint32_t)batch) return;
+    const int D4 = dim >> 2;
+    const float4 *qv = reinterpret_cast<const float4 *>(queries + (size_t)q * dim);
+    const float qi = q_inv[q];
+    key_t64 *lst = cand + list_id * (size_t)cap;
+    for (uint32_t i = warp; i < cnt; i += 4) {
+        const uint32_t row = (uint32_t)(lst[i] & 0xFFFFFFFFull);
+        const float4 *rp = reinterpret_cast<const float4 *>(mat) + (size_t)row * D4;
+        float acc = 0.f;
+        for (int c = lane; c < D4; c += 32) {
+            const float4 v = ldg_stream(rp + c), w = qv[c];
+            acc = fmaf(v.x, w.x, acc); acc = fmaf(v.y, w.y, acc); acc = fmaf(v.z, w.z, acc); acc = fmaf(v.w, w.w, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+        float sim = acc * inv_norm[row] * qi;
+        sim = fminf(1.f, fmaxf(-1.f, sim));
+        if (lane == 0) lst[i] = (sim >= min_sim) ? make_key(sim, row_base + row) : 0ull;
+    }
+}
+
+// One CTA per query: top-k of all its re-scored candidates, then the chunk-id gather.
+__global__ void __launch_bounds__(256) select_candidates_kernel(const key_t64 *cand, const uint32_t *cand_count, int cap,
+                                                                int n_splits, int k, int P, const uint8_t *chunk_ids,
+                                                                uint32_t row_base, key_t64 *out_keys, uint8_t *out_ids)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    key_t64 *buf = reinterpret_cast<key_t64 *>(smem_raw);       // P keys: [0,k) kept, [k,P) incoming
+    const uint32_t q = blockIdx.x, m_tile = q / 128, qlocal = q % 128;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < P; i += blockDim.x) buf[i] = 0ull;
+    __syncthreads();
+    int fill = 0;
+    const int room = P - k;
+    for (int sp = 0; sp < n_splits; sp++) {
+        const size_t list_id = ((size_t)m_tile * n_splits + sp) * 128 + qlocal;
+        const int c = (int)cand_count[list_id];
+        if (c == 0) continue;
+        if (fill + c > room) {
+            cta_bitonic_desc(buf, P);
+            for (int i = k + tid; i < P; i += blockDim.x) buf[i] = 0ull;
+            __syncthreads();
+            fill = 0;
+        }
+        const key_t64 *lst = cand + list_id * (size_t)cap;
+        for (int i = tid; i < c; i += blockDim.x) buf[k + fill + i] = lst[i];
+        fill += c;
+        __syncthreads();
+    }
+    cta_bitonic_desc(buf, P);
+    for (int i = tid; i < k; i += blockDim.x) {
+        const key_t64 key = buf[i];
+        out_keys[(size_t)q * k + i] = key;
+        uint4 id = make_uint4(0, 0, 0, 0);
+        if (key) id = reinterpret_cast<const uint4 *>(chunk_ids)[key_row(key) - row_base];
+        reinterpret_cast<uint4 *>(out_ids)[(size_t)q * k + i] = id;
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_rescore_select(key_t64 *cand, const uint32_t *cand_count, int cap, int n_splits, int batch,
+                                  const float *mat, int dim, const float *inv_norm, const float *queries,
+                                  const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
+                                  int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream)
+{
+    const size_t lists = (size_t)((batch + 127) / 128) * n_splits * 128;
+    rescore_candidates_kernel<<<(unsigned)lists, 128, 0, stream>>>(cand, cand_count, cap, n_splits, batch, mat, dim,
+                                                                   inv_norm, queries, q_inv, row_base, min_sim);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    int P = next_pow2(cap + k);
+    if (P < 2048) P = 2048;
+    select_candidates_kernel<<<batch, 256, (size_t)P * sizeof(key_t64), stream>>>(cand, cand_count, cap, n_splits, k, P,
+                                                                                  chunk_ids, row_base, out_keys, out_ids);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_merge(const uint8_t *gathered, int G, int batch, int k, key_t64 *out_keys,
                          uint8_t *out_ids, cudaStream_t stream)
 {

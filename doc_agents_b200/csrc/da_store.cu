@@ -113,6 +113,9 @@ struct Shard {
     DevBuf<float> d_queries, d_qinv;
     DevBuf<uint32_t> d_bitmap;
     DevBuf<uint8_t> d_out, d_gather, d_final;
+    DevBuf<unsigned long long> d_cand;          // batched tensor-core path: candidate lists
+    DevBuf<uint32_t> d_cand_count, d_overflow;
+    PinBuf<uint32_t> h_overflow;
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
     unsigned long long *d_rows_read = nullptr;
@@ -169,6 +172,7 @@ struct da_store {
     double scan_ms_sum = 0;
     int scan_grid = 0;
     int ivf_lists = 0, ivf_default_probes = 1;
+    uint64_t tc_overflows = 0;
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
 
@@ -184,6 +188,7 @@ void free_shard(Shard &s)
     cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
+    s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
     s.h_up_rows.release(); s.h_up_slots.release(); s.h_up_ids.release();
@@ -238,6 +243,7 @@ struct SearchPlan {
     size_t bitmap_words;
     bool ivf;
     int probes;
+    bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
 };
 
 // Enqueue one complete search on every local shard: scan passes, collective, merge.
@@ -281,6 +287,19 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 st->launches += 3;
                 if (first) { st->scan_grid = grid; st->scan_launches++; }
             }
+            CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            continue;
+        }
+        if (pl.use_tc) {
+            const int n_splits = s.sm_count;
+            CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_qinv.p, s.mat, s.n_rows, dim, s.inv_norm,
+                                              s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.k, pl.min_sim,
+                                              da::kTf32Eps, n_splits, s.d_cand.p, s.d_cand_count.p, s.d_overflow.p, s.stream));
+            CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), n_splits, pl.batch, s.mat, dim,
+                                         s.inv_norm, s.d_queries.p, s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k,
+                                         out_keys, out_ids, s.stream));
+            st->launches += 3;
+            if (first) { st->scan_grid = n_splits * da::tc_batch_m_tiles(pl.batch); st->scan_launches++; }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             continue;
         }
@@ -342,6 +361,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     pl.all_docs = all_docs; pl.read_all = (p->flags & DA_SEARCH_READ_ALL_ROWS) != 0;
     pl.bitmap_words = (st->docs.size() + 31) / 32 + 1;
     pl.ivf = ivf;
+    pl.use_tc = false;
     pl.probes = 0;
     if (ivf) {
         int probes = p->ivf_probes > 0 ? p->ivf_probes : st->ivf_default_probes;
@@ -358,9 +378,27 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
     }
     if (pl.k == 0) return DA_OK;
+    // Batches of 16+ queries become a dense contraction: tensor cores generate the candidates, fp32 re-scores
+    // them.  Not for narrow document filters, where the SIMT scan skips the rows it does not need.
+    if (!ivf && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16) {
+        size_t selected = st->docs.size();
+        if (!all_docs) {
+            selected = 0;
+            for (uint32_t w : bitmap) selected += (size_t)__builtin_popcount(w);
+        }
+        pl.use_tc = selected * 4 >= st->docs.size() && selected > 0;
+    }
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
+        if (pl.use_tc) {
+            const size_t lists = da::tc_batch_lists(p->batch, s.sm_count);
+            CU(s.d_cand.ensure(lists * (size_t)da::tc_batch_cap(pl.k)));
+            CU(s.d_cand_count.ensure(lists));
+            CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));
+            CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
+            *s.h_overflow.p = 0;
+        }
         CU(s.d_queries.ensure(nq_elems)); CU(s.d_qinv.ensure(p->batch));
         CU(s.h_queries.ensure(nq_elems));
         CU(s.d_out.ensure(rec_bytes)); CU(s.h_result.ensure(rec_bytes));
@@ -385,6 +423,8 @@ int enqueue_stats_readback(da_store *st)
         CU(cudaSetDevice(s.device));
         CU(cudaMemcpyAsync(s.h_rows_read.p, s.d_rows_read, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s.stream));
         CU(cudaMemsetAsync(s.d_rows_read, 0, sizeof(unsigned long long), s.stream));
+        if (s.d_overflow.p && s.h_overflow.p)
+            CU(cudaMemcpyAsync(s.h_overflow.p, s.d_overflow.p, 4, cudaMemcpyDeviceToHost, s.stream));
     }
     return DA_OK;
 }
@@ -402,12 +442,15 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     const int nq = da::scan_pick_nq(st->dim, pl.k, pl.batch);
     const int passes = (pl.batch + nq - 1) / nq;
     rows_read /= (uint64_t)searches;
+    if (pl.use_tc) rows_read = rows_scanned;        // the contraction reads every resident row once per 128 queries
     st->last_rows_read = rows_read;
     // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
     // + doc_slot (4 B) of every row visited when a document filter is present.
     if (pl.ivf)   // centroid matrix per query + the probed rows (vector, inv_norm, doc slot if filtered, row number)
         st->last_bytes = (uint64_t)pl.batch * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
                          rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
+    else if (pl.use_tc)
+        st->last_bytes = (uint64_t)da::tc_batch_m_tiles(pl.batch) * rows_scanned * ((uint64_t)st->dim * 4 + (pl.all_docs ? 4 : 8));
     else
         st->last_bytes = rows_read * (uint64_t)st->dim * 4 +
                          rows_scanned * (uint64_t)passes * (pl.all_docs ? 4 : 8);
@@ -647,16 +690,28 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     for (int q = 0; q < pl.batch; q++) out_n[q] = 0;
     if (pl.k == 0) return DA_OK;
     if (!out_chunk_ids || !out_scores) return fail(DA_ERR_INVALID, "output buffers are NULL");
-    rc = enqueue_search(st, pl);
-    if (rc != DA_OK) return rc;
     const size_t nk = (size_t)pl.batch * pl.k, rec_bytes = nk * 24;
-    CU(cudaSetDevice(s0.device));
-    const uint8_t *src = st->total_ranks > 1 ? s0.d_final.p : s0.d_out.p;
-    CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes, cudaMemcpyDeviceToHost, s0.stream));
-    CU(cudaEventRecord(s0.ev_all1, s0.stream));
-    rc = enqueue_stats_readback(st);
-    if (rc != DA_OK) return rc;
-    for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    for (int attempt = 0; attempt < 2; attempt++) {
+        rc = enqueue_search(st, pl);
+        if (rc != DA_OK) return rc;
+        CU(cudaSetDevice(s0.device));
+        const uint8_t *src = st->total_ranks > 1 ? s0.d_final.p : s0.d_out.p;
+        CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes, cudaMemcpyDeviceToHost, s0.stream));
+        CU(cudaEventRecord(s0.ev_all1, s0.stream));
+        rc = enqueue_stats_readback(st);
+        if (rc != DA_OK) return rc;
+        for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+        bool overflow = false;
+        if (pl.use_tc)
+            for (Shard &s : st->shards) overflow = overflow || (*s.h_overflow.p != 0);
+        if (!overflow) break;
+        // A candidate list stayed full after pruning (a mass of scores within the TF32 slack of the k-th
+        // best).  Every rank sees its own lists only, so in a multi-rank store this stays an error.
+        if (st->total_ranks > 1 && st->world > 1)
+            return fail(DA_ERR_STATE, "tensor-core candidate list overflow; retry with DA_SEARCH_NO_TENSOR");
+        st->tc_overflows++;
+        pl.use_tc = false;                 // answer this batch with the fp32 SIMT scan instead
+    }
     const uint8_t *ids = s0.h_result.p;
     const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p + nk * 16);
     for (int q = 0; q < pl.batch; q++) {

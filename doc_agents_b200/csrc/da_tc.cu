@@ -228,6 +228,235 @@ __global__ void gather_rows_kernel(const float *mat, int D, const uint32_t *rows
     }
 }
 
+// ---------------------------------------------------------------------------
+// Batched queries: scores = Q (batch x K) . X^T (N rows x K) on the tensor cores, fused with a
+// per-query candidate filter, so the batch x N score matrix never leaves the SM.
+//
+// Roles swap relative to the assignment kernel: A = queries (an M tile = 128 queries), B = corpus
+// rows (N tiles of 256 rows).  Epilogue thread r owns query r of the tile and walks the 256 row
+// scores of each accumulator tile.  TF32 scores are only a candidate generator: with
+//     eps >= |cos_tf32 - cos_fp32|
+// a row can be in the exact top-k only if  cos_tf32 >= T_k - 2*eps  (T_k = k-th best TF32 score
+// seen so far by this thread) and  cos_tf32 >= floor - eps.  Survivors go to a per-(CTA, query)
+// list in global memory; a second kernel re-scores them in fp32 with the scan kernel's exact
+// arithmetic and a third selects the top-k -- so results are identical to the fp32 scan.
+// ---------------------------------------------------------------------------
+constexpr uint32_t TCB_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 + 256 + 2 * TC_BN * 4;
+
+struct BatchArgs {
+    uint32_t n_rows;            // rows resident on this shard
+    int K, batch, k;
+    int n_splits;               // CTAs per M tile; each sweeps a contiguous range of N tiles
+    int cap;                    // entries per candidate list
+    float floor_eps;            // min_similarity - eps
+    float two_eps;
+    const float *inv_norm;      // per row
+    const uint32_t *doc_slot;   // per row (with doc_bitmap)
+    const uint32_t *doc_bitmap; // nullptr = every document
+    const float *q_inv;         // per query
+    unsigned long long *cand;   // [m_tile][split][128][cap]   ordered(score) << 32 | local row
+    uint32_t *cand_count;       // [m_tile][split][128]
+    uint32_t *overflow;         // set to 1 if a list could not be pruned below its capacity
+};
+
+// k-th largest of the n (<= 1024) entries of one list, found cooperatively by a warp through a
+// bisection on the ordered score bits; entries below (that - two_eps) are dropped in place.
+__device__ uint32_t warp_prune_list(unsigned long long *lst, uint32_t n, int k, float two_eps, int lane, float *thr_out)
+{
+    uint32_t sc[32];
+    unsigned long long ent[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        const uint32_t idx = (uint32_t)i * 32u + (uint32_t)lane;
+        ent[i] = idx < n ? lst[idx] : 0ull;
+        sc[i] = (uint32_t)(ent[i] >> 32);
+    }
+    uint32_t lo = 0u, hi = 0xFFFFFFFFu;          // largest t with count(score >= t) >= k
+    while (lo < hi) {
+        const uint32_t mid = lo + (uint32_t)(((unsigned long long)hi - lo + 1ull) >> 1);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < 32; i++) c += (sc[i] >= mid && ent[i] != 0ull);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+        if (c >= k) lo = mid; else hi = mid - 1u;
+    }
+    const float kth = ordered_to_score(lo);
+    const float thr = kth - two_eps;
+    const uint32_t thr_o = score_to_ordered(thr);
+    uint32_t out = 0;
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        const bool keep = ent[i] != 0ull && sc[i] >= thr_o;
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+        if (keep) lst[out + __popc(m & ((1u << lane) - 1u))] = ent[i];
+        out += __popc(m);
+    }
+    __syncwarp();
+    *thr_out = thr;
+    return out;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
+                           const BatchArgs a)
+{
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = base + TC_STAGES * TC_STAGE_BYTES;
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * TC_STAGES;
+    const uint32_t bar_tfull = bars + 16 * TC_STAGES, bar_tempty = bar_tfull + 16;
+    const uint32_t tmem_slot = bar_tempty + 16;
+    volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    float *s_inv = reinterpret_cast<float *>(smem_raw + (bars + 256 - smem_u32(smem_raw)));   // [2][TC_BN]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tiles = (a.batch + TC_BM - 1) / TC_BM;
+    const uint32_t split = blockIdx.x / m_tiles, m_tile = blockIdx.x % m_tiles;   // siblings (same rows) are adjacent
+    const int n_tiles_total = (int)((a.n_rows + TC_BN - 1) / TC_BN);
+    const int per_split = (n_tiles_total + a.n_splits - 1) / a.n_splits;
+    const int t_begin = (int)split * per_split;
+    const int t_end = min(n_tiles_total, t_begin + per_split);
+    const int kb_count = (a.K + TC_BK - 1) / TC_BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = t_begin; t < t_end; t++) {
+                for (int kb = 0; kb < kb_count; kb++) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                    mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
+                    tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * TC_BK, (int)(m_tile * TC_BM));
+                    tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * TC_BK, t * TC_BN);
+                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = t_begin; t < t_end; t++, it++) {
+                const int as = it & 1;
+                const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+                mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + (uint32_t)as * TC_BN;
+                for (int kb = 0; kb < kb_count; kb++) {
+                    mbar_wait(bar_full + 8 * stage, phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                    const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
+#pragma unroll
+                    for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
+                        umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
+                    umma_commit(bar_empty + 8 * stage);
+                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(bar_tfull + 8 * as);
+            }
+        }
+    } else {
+        // ===== epilogue warps 2..5: thread = one query of this M tile =====
+        const uint32_t quad = (uint32_t)warp & 3u;
+        const int etid = (int)threadIdx.x - 64;                       // 0..127 among the epilogue threads
+        const uint32_t qlocal = quad * 32u + (uint32_t)lane;
+        const uint32_t q = m_tile * TC_BM + qlocal;
+        const bool q_valid = q < (uint32_t)a.batch;
+        const float qinv = q_valid ? a.q_inv[q] : 0.f;
+        const size_t list_id = ((size_t)m_tile * a.n_splits + split) * TC_BM + qlocal;
+        unsigned long long *lst = a.cand + list_id * (size_t)a.cap;
+        uint32_t cnt = 0;
+        float thr = -3.0e38f;                                           // T_k - 2 eps once k candidates exist
+        int it = 0;
+        for (int t = t_begin; t < t_end; t++, it++) {
+            const int as = it & 1;
+            const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+            const uint32_t n0 = (uint32_t)t * TC_BN;
+            // per-row factor for this tile: 1/|row|, or 0 when the row is absent, zero or filtered out
+            float *inv_t = s_inv + as * TC_BN;
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int j = etid + h * 128;
+                const uint32_t row = n0 + (uint32_t)j;
+                float f = 0.f;
+                if (row < a.n_rows) {
+                    f = a.inv_norm[row];
+                    if (a.doc_bitmap) {
+                        const uint32_t slot = a.doc_slot[row];
+                        if (!((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u)) f = 0.f;
+                    }
+                }
+                inv_t[j] = f;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            // make room: a tile adds at most 256 entries to a list
+            {
+                const uint32_t need = __ballot_sync(0xFFFFFFFFu, cnt + TC_BN > (uint32_t)a.cap);
+                uint32_t m = need;
+                while (m) {
+                    const int src = __ffs(m) - 1;
+                    m &= m - 1;
+                    unsigned long long *l2 = reinterpret_cast<unsigned long long *>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)lst, src));
+                    const uint32_t n2 = __shfl_sync(0xFFFFFFFFu, cnt, src);
+                    float new_thr;
+                    const uint32_t kept = warp_prune_list(l2, n2, a.k, a.two_eps, lane, &new_thr);
+                    if (lane == src) {
+                        cnt = kept;
+                        thr = fmaxf(thr, new_thr);
+                        if (kept + TC_BN > (uint32_t)a.cap) *a.overflow = 1u;
+                    }
+                }
+            }
+            mbar_wait(bar_tfull + 8 * as, aphase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * TC_BN;
+            const float gate = fmaxf(thr, a.floor_eps);
+#pragma unroll 1
+            for (int c = 0; c < TC_BN / 32; c++) {
+                uint32_t r[32];
+                tmem_ld32(taddr + (uint32_t)c * 32u, r);
+                if (q_valid) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const float f = inv_t[c * 32 + j];
+                        const float v = __uint_as_float(r[j]) * f * qinv;
+                        if (f > 0.f && v >= gate && cnt < (uint32_t)a.cap) {
+                            lst[cnt++] = ((unsigned long long)score_to_ordered(v) << 32) | (unsigned long long)(n0 + c * 32 + j);
+                        }
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+        }
+        a.cand_count[list_id] = q_valid ? cnt : 0u;
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
+    }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -284,6 +513,32 @@ cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *c
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     unpack_assign_kernel<<<148 * 4, 256, 0, stream>>>(packed_scratch, M, out_assign);
+    return cudaGetLastError();
+}
+
+int tc_batch_cap(int k) { int c = 4 * k; if (c < 512) c = 512; if (c > 1024) c = 1024; return c; }
+int tc_batch_m_tiles(int batch) { return (batch + TC_BM - 1) / TC_BM; }
+size_t tc_batch_lists(int batch, int n_splits) { return (size_t)tc_batch_m_tiles(batch) * n_splits * TC_BM; }
+
+cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
+                                       uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
+                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int n_splits,
+                                       unsigned long long *cand, uint32_t *cand_count, uint32_t *overflow,
+                                       cudaStream_t stream)
+{
+    if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
+    CUtensorMap map_q, map_x;
+    if (!make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BN))
+        return cudaErrorInvalidValue;
+    BatchArgs a{};
+    a.n_rows = n_rows; a.K = D; a.batch = batch; a.k = k; a.n_splits = n_splits; a.cap = tc_batch_cap(k);
+    a.floor_eps = min_sim - eps; a.two_eps = 2.f * eps;
+    a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.q_inv = q_inv;
+    a.cand = cand; a.cand_count = cand_count; a.overflow = overflow;
+    cudaError_t e = cudaFuncSetAttribute(tc_batch_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    const uint32_t grid = (uint32_t)tc_batch_m_tiles(batch) * (uint32_t)n_splits;
+    tc_batch_candidates_kernel<<<grid, TC_THREADS, TCB_SMEM_BYTES, stream>>>(map_q, map_x, a);
     return cudaGetLastError();
 }
 

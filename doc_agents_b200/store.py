@@ -195,12 +195,12 @@ class GpuStore:
     # -- everything-exposed search on raw arrays -----------------------------------------
     def search(self, queries, k: int, doc_ids: np.ndarray | None = None, *, all_docs: bool = False,
                min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
-               probes: int = 0):
+               probes: int = 0, no_tensor: bool = False):
         """queries: dim or batch x dim.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor)
         b, kk = q.shape[0], max(int(k), 1)
         out_ids = np.zeros((b, kk, 16), dtype=np.uint8)
         out_scores = np.zeros((b, kk), dtype=np.float32)
@@ -213,11 +213,11 @@ class GpuStore:
                 [out_scores[i, :out_n[i]].copy() for i in range(b)],
                 [out_rows[i, :out_n[i]].copy() for i in range(b)])
 
-    def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes):
+    def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False):
         p = L.da_search_params()
         p.struct_size = C.sizeof(L.da_search_params)
         p.flags = (L.DA_SEARCH_ALL_DOCS if all_docs else 0) | (L.DA_SEARCH_READ_ALL_ROWS if read_all_rows else 0) \
-            | (L.DA_SEARCH_IVF if ivf else 0)
+            | (L.DA_SEARCH_IVF if ivf else 0) | (L.DA_SEARCH_NO_TENSOR if no_tensor else 0)
         d = None
         if doc_ids is not None:
             d = np.ascontiguousarray(doc_ids, dtype=np.uint8).reshape(-1, 16)
@@ -233,12 +233,12 @@ class GpuStore:
         return p, (q, d)
 
     def bench_resident(self, queries, k: int, iters: int, doc_ids=None, *, all_docs=False,
-                       min_similarity=None, read_all_rows=False, ivf=False, probes=0) -> float:
+                       min_similarity=None, read_all_rows=False, ivf=False, probes=0, no_tensor=False) -> float:
         """Total CUDA-event milliseconds of `iters` searches with inputs resident in HBM."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor)
         ms = C.c_float(0)
         _check(self._lib.da_store_bench_resident(self._h, C.byref(p), iters, C.byref(ms)))
         del keep

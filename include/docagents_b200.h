@@ -102,6 +102,8 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
 #define DA_SEARCH_READ_ALL_ROWS 0x2u  /* doc mask as a predicate: read every row even if its document is
                                          not requested (configs[1] "HBM-bound" measurement); default skips them */
 #define DA_SEARCH_IVF           0x4u  /* probe the IVFFlat lists instead of the exact scan */
+#define DA_SEARCH_NO_TENSOR     0x10u /* keep a batch of >= 16 queries on the fp32 SIMT scan (default: tcgen05 TF32
+                                         candidate generation + exact fp32 re-score; results are identical) */
 
 /* Same query as da_store_topk with every knob exposed, batched: `batch` queries share one
  * doc filter (one /api/query has one document set: cmd/query/main.go:20-24). */

@@ -1,0 +1,71 @@
+"""GPU suite for the batched path: tcgen05 TF32 candidate generation + exact fp32 re-score must
+return exactly what the fp32 SIMT scan returns (same rows, same order, bit-identical scores), and
+what the CPU oracle returns within the parity tolerance."""
+import numpy as np
+import pytest
+
+import oracle
+from cases import REL_TOL, same_rows_up_to_ties
+from doc_agents_b200 import GpuStore
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(st, qs, k, **kw):
+    tc = st.search(qs, k, **kw)
+    assert st.stats().last_rows_read == st.stats().rows               # the contraction visits every row
+    simt = st.search(qs, k, no_tensor=True, **kw)
+    for i in range(len(qs)):
+        assert np.array_equal(tc[2][i], simt[2][i]), (i, tc[2][i], simt[2][i])
+        assert np.array_equal(tc[1][i].view(np.uint32), simt[1][i].view(np.uint32)), i
+        assert np.array_equal(tc[0][i], simt[0][i]), i
+    return tc
+
+
+@pytest.mark.parametrize("batch", [16, 64, 130, 300])
+@pytest.mark.parametrize("dim", [1536, 3072])
+def test_tensor_batch_equals_simt_scan_and_oracle(batch, dim):
+    S = oracle.Synth(n_clusters=16)
+    n, k = 30_000, 10
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S, 0, n)
+        qs = np.stack([oracle.gen_query(S, i, i % 16, dim) for i in range(batch)])
+        tc = _compare(st, qs, k, all_docs=True)
+        mat = oracle.gen_rows(S, 0, n, dim)
+        for i in (0, batch // 2, batch - 1):
+            o_rows, o_sc, _ = oracle.topk(mat, None, None, qs[i], k)
+            assert same_rows_up_to_ties(tc[2][i], o_rows, o_sc)
+            assert np.allclose(tc[1][i], o_sc, rtol=REL_TOL)
+        # a wide document filter (2 of 3 documents) stays on the tensor path; a narrow one does not
+        docs = oracle.doc_ids(S, 0, n // 200)
+        wide = docs[[d for d in range(n // 200) if d % 3 != 1]]
+        _compare(st, qs, k, doc_ids=wide)
+        narrow = st.search(qs, k, doc_ids=docs[:5])
+        assert st.stats().last_rows_read == 5 * 200 * ((batch + 7) // 8)   # SIMT scan, rows of other documents skipped
+        assert all(len(r) <= k for r in narrow[2])
+
+
+def test_tensor_batch_no_floor_top100_exercises_pruning():
+    """No similarity floor, k = 100, ~2700 rows per CTA: every candidate list fills and is pruned several times."""
+    S = oracle.Synth(n_clusters=64)
+    n, dim, k, batch = 400_000, 256, 100, 40
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S, 0, n)
+        qs = np.stack([oracle.gen_query(S, i, (5 * i) % 64, dim) for i in range(batch)])
+        tc = _compare(st, qs, k, all_docs=True, min_similarity=-np.inf)
+        assert all(len(r) == k for r in tc[2])
+        mat = oracle.gen_rows(S, 0, n, dim)
+        for i in (0, 17, 39):
+            o_rows, o_sc, _ = oracle.topk(mat, None, None, qs[i], k, -np.inf)
+            assert np.allclose(tc[1][i], o_sc, rtol=REL_TOL, atol=5e-7)
+            assert len(np.intersect1d(tc[2][i], o_rows)) >= k - 1         # a tie at the k-th place may swap one row
+
+
+def test_tensor_batch_small_corpus_and_padding_queries():
+    S = oracle.Synth(n_clusters=2)
+    n, dim = 700, 100                                                    # fewer rows than one 256-row tile per CTA, ragged K
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S, 0, n)
+        qs = np.stack([oracle.gen_query(S, i, i % 2, dim) for i in range(17)])
+        _compare(st, qs, 5, all_docs=True)
+        _compare(st, qs, 128, all_docs=True, min_similarity=-np.inf)
