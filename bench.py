@@ -35,13 +35,30 @@ N_ROWS = int(os.environ.get("DA_BENCH_ROWS", 10_000_000))
 DIM = int(os.environ.get("DA_BENCH_DIM", 3072))
 TOP_K = 10
 MIN_SIM = 0.7
+BATCH = 1
+FILTER_DOCS = 0          # 0 = every document requested
+READ_ALL = False
+NO_TENSOR = False
 METRIC = "cosine top-k queries/sec at 10M x 3072"
 UNIT = "queries/s"
 
+# Other BASELINE configs, selectable with --workload (the driver's default run is configs[2] at batch=1).
+WORKLOADS = {
+    "cfg3_b1": {},
+    "cfg3_b64": {"BATCH": 64},
+    "cfg3_b64_simt": {"BATCH": 64, "NO_TENSOR": True},
+    "cfg2": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16},
+    "cfg2_predicate": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16, "READ_ALL": True},
+    "cfg4": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf")},
+}
+
 
 def workload_name(n_gpus: int) -> str:
-    return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch=1, top_k={TOP_K}, "
-            f"all documents requested, min_similarity={MIN_SIM}, local top-k + NCCL all-gather merge")
+    flt = "all documents requested" if not FILTER_DOCS else \
+        f"filtered to {FILTER_DOCS} doc IDs ({'mask as predicate, every row read' if READ_ALL else 'rows of other documents skipped'})"
+    path = "fused SIMT scan" if (BATCH < 16 or NO_TENSOR or FILTER_DOCS) else "tcgen05 TF32 candidates + exact fp32 re-score"
+    return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch={BATCH}, top_k={TOP_K}, "
+            f"{flt}, min_similarity={MIN_SIM}, {path}, local top-k + NCCL all-gather merge")
 
 
 def measured_peak():
@@ -205,7 +222,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="cfg3_b1", choices=sorted(WORKLOADS))
     args = ap.parse_args()
+    globals().update(WORKLOADS[args.workload])
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -219,7 +238,7 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     if world == 1 and args.gpus > 1:
         raise SystemExit("launch N>1 with torch.distributed.run (one rank per GPU)")
-    warmup = max(3, args.warmup)
+    warmup = max(3, args.warmup) if args.workload == "cfg3_b1" else max(1, args.warmup)
     steps = max(1, args.steps)
 
     import torch
@@ -255,19 +274,32 @@ def main():
     st = GpuStore(dim=DIM, capacity_rows=max(1, hi - lo), devices=(local_rank,), min_similarity=MIN_SIM,
                   world_size=world, rank=rank, nccl_id=nccl_id)
     st.generate_synthetic(S, lo, hi - lo)
-    queries = np.stack([oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(warmup + steps)])
+    n_q = (warmup + steps) * BATCH if BATCH <= 64 else 2 * BATCH
+    queries = np.stack([oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(n_q)])
+
+    def qbatch(i):
+        lo_ = (i * BATCH) % (n_q - BATCH + 1) if n_q > BATCH else 0
+        return queries[lo_:lo_ + BATCH]
+
+    n_docs = N_ROWS // S.chunks_per_doc
+    skw = dict(all_docs=True) if not FILTER_DOCS else dict(
+        doc_ids=np.stack([oracle.doc_ids(S, d, 1)[0] for d in
+                          ([(0 * 37) % S.n_clusters + j * S.n_clusters for j in range(FILTER_DOCS // 2)] +
+                           [7 + j * (n_docs // FILTER_DOCS) for j in range(FILTER_DOCS - FILTER_DOCS // 2)])]),
+        read_all_rows=READ_ALL)
+    skw.update(min_similarity=MIN_SIM, no_tensor=NO_TENSOR)
 
     # warm-up (untimed): W full searches through the public call
     for i in range(warmup):
-        st.search(queries[i], TOP_K, all_docs=True)
-    st.bench_resident(queries[0], TOP_K, warmup, all_docs=True)
+        st.search(qbatch(i), TOP_K, **skw)
+    st.bench_resident(qbatch(0), TOP_K, warmup, **skw)
 
     # ---- timed region 1: K steps, inputs resident in HBM, CUDA events on the launching stream
     s_before = st.stats()
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
-    ms_total = st.bench_resident(queries[warmup], TOP_K, steps, all_docs=True)
+    ms_total = st.bench_resident(qbatch(warmup), TOP_K, steps, **skw)
     barrier()
     clocks = sampler.stop()
     s_after = st.stats()
@@ -276,18 +308,18 @@ def main():
     scan_launches = int(s_after.scan_launches - s_before.scan_launches)
     scan_ms = (s_after.scan_ms_sum - s_before.scan_ms_sum) / max(1, scan_launches)
     bytes_per_launch = int(s_after.last_bytes_algorithmic)
-    value = steps / (ms_total / 1e3)
+    value = steps * BATCH / (ms_total / 1e3)
 
     # ---- timed region 2: K steps end to end through the C-ABI call (host buffers in and out)
     barrier()
     t0 = time.perf_counter()
     last = None
     for i in range(steps):
-        last = st.search(queries[warmup + i], TOP_K, all_docs=True)
+        last = st.search(qbatch(warmup + i), TOP_K, **skw)
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
-    e2e_value = steps / e2e_s
+    e2e_value = steps * BATCH / e2e_s
 
     peak, peak_src = measured_peak()
     achieved = bytes_per_launch / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
@@ -296,20 +328,22 @@ def main():
         "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(world), "rows_per_gpu": hi - lo, "dim": DIM, "top_k": TOP_K,
-                   "batch": 1, "l2": "inputs larger than L2 (%.1f GB per GPU per step vs 126 MB)" % ((hi - lo) * DIM * 4 / 1e9),
+                   "batch": BATCH, "workload_key": args.workload, "l2": "inputs larger than L2 (%.1f GB per GPU per step vs 126 MB)" % ((hi - lo) * DIM * 4 / 1e9),
                    "seeds": {"data": hex(S.seed_data), "centroids": hex(S.seed_centroid), "queries": hex(S.seed_query)}},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": DIM * 4, "d2h_bytes_per_step": TOP_K * 24,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * DIM * 4 + (0 if not FILTER_DOCS else (n_docs + 31) // 32 * 4),
+                "d2h_bytes_per_step": BATCH * TOP_K * 24,
                 "ms_per_step": e2e_s * 1e3 / steps},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": recorded_traffic(bytes_per_launch), "kernel": "scan_topk_kernel", "peak_source": peak_src,
+                     "traffic": recorded_traffic(bytes_per_launch) if args.workload == "cfg3_b1" else None,
+                     "kernel": "scan_topk_kernel" if "SIMT" in workload_name(world) else "tc_batch_candidates_kernel + rescore + select", "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,
                      "frac_of_nominal_8000": achieved / 8000.0},
         "result_check": {"hits": int(len(last[2][0])), "top_score": float(last[1][0][0]) if len(last[1][0]) else None},
     }
     st.close()
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "cfg3_b1":
         _, info, _ = cpu_reference_run(steps=3, warmup=1)
         line["cpu_baseline"] = info
     if world > 1:

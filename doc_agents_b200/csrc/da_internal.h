@@ -133,6 +133,7 @@ cudaError_t tc_launch_gather_rows(const float *mat, int D, const uint32_t *rows,
 constexpr float kTf32Eps = 2.5e-3f;
 int tc_batch_cap(int k);
 int tc_batch_m_tiles(int batch);
+int tc_batch_splits(int batch, int sm_count);
 size_t tc_batch_lists(int batch, int n_splits);
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,

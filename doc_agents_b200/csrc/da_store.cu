@@ -291,7 +291,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             continue;
         }
         if (pl.use_tc) {
-            const int n_splits = s.sm_count;
+            const int n_splits = da::tc_batch_splits(pl.batch, s.sm_count);
             CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_qinv.p, s.mat, s.n_rows, dim, s.inv_norm,
                                               s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.k, pl.min_sim,
                                               da::kTf32Eps, n_splits, s.d_cand.p, s.d_cand_count.p, s.d_overflow.p, s.stream));
@@ -392,7 +392,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
         if (pl.use_tc) {
-            const size_t lists = da::tc_batch_lists(p->batch, s.sm_count);
+            const size_t lists = da::tc_batch_lists(p->batch, da::tc_batch_splits(p->batch, s.sm_count));
             CU(s.d_cand.ensure(lists * (size_t)da::tc_batch_cap(pl.k)));
             CU(s.d_cand_count.ensure(lists));
             CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));

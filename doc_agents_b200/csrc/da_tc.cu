@@ -516,8 +516,20 @@ cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *c
     return cudaGetLastError();
 }
 
-int tc_batch_cap(int k) { int c = 4 * k; if (c < 512) c = 512; if (c > 1024) c = 1024; return c; }
+// Entries per candidate list: the most warp_prune_list handles (32 lanes x 32).  A list is pruned when fewer
+// than 256 slots are free, so up to 768 entries may sit within the TF32 slack of the k-th best before the
+// overflow flag is raised.
+int tc_batch_cap(int k) { (void)k; return 1024; }
 int tc_batch_m_tiles(int batch) { return (batch + TC_BM - 1) / TC_BM; }
+// CTAs per M tile.  One M tile: one CTA per SM.  Many M tiles already fill the machine, so fewer, longer row
+// ranges per CTA: a thread's k-th best over a longer range is a tighter gate, and fewer lists hold candidates.
+int tc_batch_splits(int batch, int sm_count)
+{
+    const int mt = tc_batch_m_tiles(batch);
+    if (mt == 1) return sm_count;
+    const int s = (2 * sm_count) / mt;
+    return s < 1 ? 1 : s;
+}
 size_t tc_batch_lists(int batch, int n_splits) { return (size_t)tc_batch_m_tiles(batch) * n_splits * TC_BM; }
 
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
