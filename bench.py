@@ -200,7 +200,7 @@ def cpu_reference_run(steps: int, warmup: int, want_seconds: float = 12.0):
     return qps_full, info, dt * 1e3 * N_ROWS / sample
 
 
-def run_reference_arm(args, rank: int):
+def run_reference_arm(args, rank: int, emit):
     if rank != 0:
         return
     steps = max(1, args.steps)
@@ -212,7 +212,7 @@ def run_reference_arm(args, rank: int):
                        "(the reference's Go + Postgres/pgvector cannot run on this box)"},
             "cpu_baseline": info,
             "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -225,13 +225,23 @@ def main():
     ap.add_argument("--workload", default="cfg3_b1", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     globals().update(WORKLOADS[args.workload])
+    # The contract is ONE JSON line on stdout: park fd 1 on stderr while libraries (NCCL prints its version
+    # banner on stdout) are active, and restore it for the final print.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(obj), flush=True)
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
 
     if args.impl == "reference":
-        run_reference_arm(args, rank)
+        run_reference_arm(args, rank, emit)
         return
 
     if world != args.gpus and world > 1:
@@ -349,7 +359,7 @@ def main():
     if world > 1:
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 if __name__ == "__main__":
