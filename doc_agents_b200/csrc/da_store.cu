@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <mutex>
@@ -108,6 +109,7 @@ struct Shard {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr, ev_all0 = nullptr, ev_all1 = nullptr;
     std::vector<cudaEvent_t> ev_pool;   // extra pairs for per-launch timing inside a bench loop
+    cudaEvent_t ev_done = nullptr;      // peer-gather mode: this shard's records have been written
     ncclComm_t comm = nullptr;
     // search state
     DevBuf<float> d_queries, d_qinv;
@@ -173,6 +175,7 @@ struct da_store {
     int scan_grid = 0;
     int ivf_lists = 0, ivf_default_probes = 1;
     uint64_t tc_overflows = 0;
+    bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
 
@@ -197,6 +200,7 @@ void free_shard(Shard &s)
     if (s.ev_all0) cudaEventDestroy(s.ev_all0);
     if (s.ev_all1) cudaEventDestroy(s.ev_all1);
     for (cudaEvent_t e : s.ev_pool) cudaEventDestroy(e);
+    if (s.ev_done) cudaEventDestroy(s.ev_done);
     if (s.stream) cudaStreamDestroy(s.stream);
     s = Shard();
 }
@@ -220,6 +224,7 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows)
     CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&s.ev_scan0)); CU(cudaEventCreate(&s.ev_scan1));
     CU(cudaEventCreate(&s.ev_all0)); CU(cudaEventCreate(&s.ev_all1));
+    CU(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
     CU(cudaMalloc((void **)&s.mat, cap_rows * (uint64_t)dim * 4));
     CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
     CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
@@ -256,9 +261,15 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         CU(cudaSetDevice(s.device));
         const bool first = (&s == &st->shards[0]);
         CU(cudaEventRecord(first && e0 ? e0 : s.ev_scan0, s.stream));
-        // record block: [batch*k ids of 16 B][batch*k keys of 8 B]  (ids first keeps them 16-byte aligned)
-        uint8_t *out_ids = s.d_out.p;
-        da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(s.d_out.p + (size_t)pl.batch * pl.k * 16);
+        // record block: [batch*k ids of 16 B][batch*k keys of 8 B]  (ids first keeps them 16-byte aligned).
+        // Peer-gather mode: the scan's last CTA stores the block straight into shard 0's gather buffer over
+        // NVLink -- compute and "all-to-one gather" are the same kernel, no collective is launched.
+        const size_t shard_index = (size_t)(&s - &st->shards[0]);
+        uint8_t *rec_base = st->p2p_gather ? st->shards[0].d_gather.p + shard_index * rec_bytes : s.d_out.p;
+        if (st->p2p_gather && !first)      // block `shard_index` is free again once shard 0 merged the previous search
+            CU(cudaStreamWaitEvent(s.stream, st->shards[0].ev_done, 0));
+        uint8_t *out_ids = rec_base;
+        da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(rec_base + (size_t)pl.batch * pl.k * 16);
         if (pl.ivf) {
             // per query: rank the centroids (the fused scan over the L x dim centroid matrix, top `probes`),
             // expand the chosen lists into one row list, run the fused scan over that row list.
@@ -288,6 +299,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 if (first) { st->scan_grid = grid; st->scan_launches++; }
             }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
         }
         if (pl.use_tc) {
@@ -301,6 +313,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             st->launches += 3;
             if (first) { st->scan_grid = n_splits * da::tc_batch_m_tiles(pl.batch); st->scan_launches++; }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
         }
         const int nq_max = da::scan_pick_nq(dim, pl.k, pl.batch);
@@ -324,18 +337,25 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             if (first) { st->scan_grid = grid; st->scan_launches++; }
         }
         CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+        if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
     }
     if (st->total_ranks > 1) {
-        NC(ncclGroupStart());
-        for (Shard &s : st->shards)
-            NC(ncclAllGather(s.d_out.p, s.d_gather.p, rec_bytes, ncclChar, s.comm, s.stream));
-        NC(ncclGroupEnd());
         Shard &s0 = st->shards[0];
+        if (st->p2p_gather) {
+            CU(cudaSetDevice(s0.device));
+            for (size_t g = 1; g < st->shards.size(); g++) CU(cudaStreamWaitEvent(s0.stream, st->shards[g].ev_done, 0));
+        } else {
+            NC(ncclGroupStart());
+            for (Shard &s : st->shards)
+                NC(ncclAllGather(s.d_out.p, s.d_gather.p, rec_bytes, ncclChar, s.comm, s.stream));
+            NC(ncclGroupEnd());
+        }
         CU(cudaSetDevice(s0.device));
         CU(da::launch_merge(s0.d_gather.p, st->total_ranks, pl.batch, pl.k,
                             reinterpret_cast<da::key_t64 *>(s0.d_final.p + (size_t)pl.batch * pl.k * 16),
                             s0.d_final.p, s0.stream));
         st->launches++;
+        if (st->p2p_gather) CU(cudaEventRecord(s0.ev_done, s0.stream));   // gather blocks may be overwritten after this
     }
     return DA_OK;
 }
@@ -512,6 +532,22 @@ int da_store_create(const da_config *cfg, da_store **out)
         int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows);
         if (rc != DA_OK) { da_store_destroy(st); return rc; }
         st->shards[i].row_base = (uint32_t)(((uint64_t)rank * cfg->n_devices + i) * cfg->capacity_rows);
+    }
+    if (world == 1 && cfg->n_devices > 1 && !getenv("DA_DISABLE_P2P")) {
+        // One process driving several GPUs (what the Go query agent does): if every shard can store into
+        // shard 0's memory, the scan epilogue delivers its records there directly and no collective is needed.
+        bool ok = true;
+        const int d0 = cfg->device_ids[0];
+        for (int i = 1; i < cfg->n_devices && ok; i++) {
+            int can = 0;
+            ok = cudaDeviceCanAccessPeer(&can, cfg->device_ids[i], d0) == cudaSuccess && can;
+            if (!ok) break;
+            cudaSetDevice(cfg->device_ids[i]);
+            cudaError_t e = cudaDeviceEnablePeerAccess(d0, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+            ok = (e == cudaSuccess);
+        }
+        st->p2p_gather = ok;
     }
     if (total > 1) {
         int rc = DA_OK;
@@ -990,6 +1026,7 @@ int da_store_stats(da_store *st, da_stats *out)
     out->scan_ms_sum = st->scan_ms_sum; out->scan_launches = st->scan_launches;
     out->ivf_build_ms = st->ivf_build_ms; out->ivf_kmeans_ms = st->ivf_kmeans_ms;
     out->ivf_assign_ms = st->ivf_assign_ms; out->ivf_assign_tflops = st->ivf_assign_tflops;
+    out->peer_gather = st->p2p_gather ? 1 : 0; out->tensor_overflows = st->tc_overflows;
     return DA_OK;
 }
 

@@ -172,6 +172,8 @@ typedef struct {
     float    ivf_kmeans_ms;         /* all k-means iterations (assignment GEMM + accumulate + finalize + all-reduce) */
     float    ivf_assign_ms;         /* final assignment GEMM over every resident row of shard 0 */
     float    ivf_assign_tflops;     /* 2 * rows * lists * dim / ivf_assign_ms */
+    int32_t  peer_gather;           /* 1: shards deliver their records into shard 0 over NVLink (no collective) */
+    uint64_t tensor_overflows;      /* batches answered by the SIMT scan because a candidate list overflowed */
 } da_stats;
 int da_store_stats(da_store *st, da_stats *out);
 

@@ -1,0 +1,68 @@
+"""GPU suite for one process driving several GPUs (what the Go query agent does): the peer-gather
+path (scan epilogue stores its records into shard 0 over NVLink) and the NCCL path must both equal
+a single-GPU store; IVFFlat and the batched tensor path on two shards."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from doc_agents_b200 import GpuStore
+from gpu_util import device_count
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(device_count() < 2, reason="needs 2 GPUs in one process")]
+
+S = oracle.Synth(n_clusters=8)
+N, DIM, K = 40_000, 1536, 10
+
+
+def _two(p2p: bool):
+    if p2p:
+        os.environ.pop("DA_DISABLE_P2P", None)
+    else:
+        os.environ["DA_DISABLE_P2P"] = "1"
+    try:
+        st = GpuStore(dim=DIM, capacity_rows=N, devices=(0, 1))
+    finally:
+        os.environ.pop("DA_DISABLE_P2P", None)
+    st.generate_synthetic(S, 0, N)
+    assert st.stats().peer_gather == (1 if p2p else 0)
+    return st
+
+
+@pytest.mark.parametrize("p2p", [True, False], ids=["peer_gather", "nccl_allgather"])
+def test_two_shards_equal_one_shard(p2p):
+    docs = oracle.doc_ids(S, 0, N // 200)
+    with GpuStore(dim=DIM, capacity_rows=N) as one, _two(p2p) as two:
+        one.generate_synthetic(S, 0, N)
+        qs = np.stack([oracle.gen_query(S, i, i % 8, DIM) for i in range(40)])
+        for batch in (1, 5, 9, 40):                      # 1 pass, 1 pass of 5, 2 passes, tensor path
+            for kw in (dict(all_docs=True), dict(doc_ids=docs[::3])):
+                a = one.search(qs[:batch], K, **kw)
+                b = two.search(qs[:batch], K, **kw)
+                b2 = two.search(qs[:batch], K, **kw)     # back to back: gather blocks are reused
+                for i in range(batch):
+                    assert np.array_equal(a[2][i], b[2][i]) and np.array_equal(a[0][i], b[0][i])
+                    assert np.array_equal(a[1][i].view(np.uint32), b[1][i].view(np.uint32))
+                    assert np.array_equal(b[2][i], b2[2][i])
+        ms = two.bench_resident(qs[0], K, 20, all_docs=True)      # 20 searches in flight without host syncs
+        assert ms > 0
+        again = two.search(qs[:5], K, all_docs=True)
+        ref = one.search(qs[:5], K, all_docs=True)
+        assert all(np.array_equal(again[2][i], ref[2][i]) for i in range(5))
+
+
+def test_ivf_on_two_shards_shares_centroids_and_probes_exactly():
+    with _two(True) as two:
+        two.build_ivf(lists=32, iters=6, seed=2)
+        off0, rows0, cent0 = two.debug_ivf(0)
+        off1, rows1, cent1 = two.debug_ivf(1)
+        assert np.array_equal(cent0.view(np.uint32), cent1.view(np.uint32))      # data-parallel k-means: same centroids
+        assert off0[-1] == N // 2 and off1[-1] == N // 2
+        for qi in range(8):
+            q = oracle.gen_query(S, qi, qi % 8, DIM)
+            exact = two.search(q, K, all_docs=True)
+            full = two.search(q, K, all_docs=True, ivf=True, probes=32)
+            assert np.array_equal(exact[2][0], full[2][0]) and np.array_equal(exact[0][0], full[0][0])
+            some = two.search(q, K, all_docs=True, ivf=True, probes=4)
+            assert len(np.intersect1d(some[2][0], exact[2][0])) >= K - 1
