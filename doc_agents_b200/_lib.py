@@ -43,7 +43,8 @@ class da_config(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("dim", C.c_int32), ("n_devices", C.c_int32),
                 ("device_ids", C.c_int32 * DA_MAX_DEVICES), ("capacity_rows", C.c_uint64),
                 ("min_similarity", C.c_float), ("world_size", C.c_int32), ("rank", C.c_int32),
-                ("nccl_id", C.c_uint8 * DA_NCCL_ID_BYTES), ("flags", C.c_uint32)]
+                ("nccl_id", C.c_uint8 * DA_NCCL_ID_BYTES), ("flags", C.c_uint32),
+                ("batch_window_us", C.c_uint32), ("batch_max", C.c_uint32)]
 
 
 class da_search_params(C.Structure):
@@ -74,7 +75,8 @@ class da_stats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("ivf_lists", C.c_int32), ("scan_grid", C.c_int32),
                 ("scan_ms_sum", C.c_double), ("scan_launches", C.c_uint64),
                 ("ivf_build_ms", C.c_float), ("ivf_kmeans_ms", C.c_float), ("ivf_assign_ms", C.c_float),
-                ("ivf_assign_tflops", C.c_float), ("peer_gather", C.c_int32), ("tensor_overflows", C.c_uint64)]
+                ("ivf_assign_tflops", C.c_float), ("peer_gather", C.c_int32), ("tensor_overflows", C.c_uint64),
+                ("topk_calls", C.c_uint64), ("topk_passes", C.c_uint64)]
 
 
 # Every symbol include/docagents_b200.h declares, with its signature.

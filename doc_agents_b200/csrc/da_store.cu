@@ -11,7 +11,9 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -175,6 +177,18 @@ struct da_store {
     int scan_grid = 0;
     int ivf_lists = 0, ivf_default_probes = 1;
     uint64_t tc_overflows = 0;
+    // request batching for da_store_topk
+    struct Pending {
+        const uint8_t *doc_ids; size_t n_docs; const float *query; int k;
+        uint8_t *out_ids; float *out_scores; int32_t *out_n;
+        int rc = 0; std::string err; bool done = false;
+    };
+    uint32_t batch_window_us = 0, batch_max = 64;
+    std::mutex bmu;
+    std::condition_variable bcv;
+    std::vector<Pending *> bqueue;
+    bool bleader = false;
+    uint64_t topk_calls = 0, topk_passes = 0;
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
@@ -527,6 +541,8 @@ int da_store_create(const da_config *cfg, da_store **out)
     st->dim = cfg->dim;
     st->min_sim = cfg->min_similarity;
     st->world = world; st->rank = rank; st->total_ranks = (int)total;
+    st->batch_window_us = cfg->batch_window_us;
+    st->batch_max = cfg->batch_max ? std::min<uint32_t>(cfg->batch_max, DA_MAX_BATCH) : 64;
     st->shards.resize(cfg->n_devices);
     for (int i = 0; i < cfg->n_devices; i++) {
         int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows);
@@ -774,18 +790,81 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     return DA_OK;
 }
 
-int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *query, int32_t dim,
-                  int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n)
+static int topk_direct(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *queries, int32_t batch,
+                       int32_t dim, int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n)
 {
-    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
     da_search_params p{};
     p.struct_size = sizeof p;
     p.flags = 0;
     p.doc_ids = doc_ids; p.n_docs = n_docs;
-    p.queries = query; p.batch = 1; p.dim = dim;
+    p.queries = queries; p.batch = batch; p.dim = dim;
     p.k = k;
     p.min_similarity = st->min_sim;
     return da_store_search(st, &p, out_chunk_ids, out_scores, nullptr, out_n);
+}
+
+int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *query, int32_t dim,
+                  int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    if (st->batch_window_us == 0 || k <= 0 || k > DA_MAX_K || dim != st->dim || !query || !out_n ||
+        !out_chunk_ids || !out_scores || (n_docs && !doc_ids)) {
+        {
+            std::lock_guard<std::mutex> lk(st->bmu);
+            st->topk_calls++; st->topk_passes++;
+        }
+        return topk_direct(st, doc_ids, n_docs, query, 1, dim, k, out_chunk_ids, out_scores, out_n);
+    }
+    // Request batching: the first caller to find no leader becomes one, waits for the window (or a full
+    // batch), then answers every queued call that asks for the same document set with one batched pass.
+    da_store::Pending me{doc_ids, n_docs, query, k, out_chunk_ids, out_scores, out_n};
+    std::unique_lock<std::mutex> lk(st->bmu);
+    st->bqueue.push_back(&me);
+    st->topk_calls++;
+    st->bcv.notify_all();
+    while (!me.done) {
+        if (st->bleader) { st->bcv.wait(lk); continue; }
+        st->bleader = true;
+        const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(st->batch_window_us);
+        while (st->bqueue.size() < st->batch_max && st->bcv.wait_until(lk, deadline) != std::cv_status::timeout) {}
+        // group = queued calls with the same document list as the oldest one
+        da_store::Pending *head = st->bqueue.front();
+        std::vector<da_store::Pending *> group, rest;
+        for (da_store::Pending *r : st->bqueue) {
+            const bool same = r->n_docs == head->n_docs &&
+                              (r->n_docs == 0 || r->doc_ids == head->doc_ids ||
+                               memcmp(r->doc_ids, head->doc_ids, 16 * r->n_docs) == 0);
+            if (same && group.size() < st->batch_max) group.push_back(r); else rest.push_back(r);
+        }
+        st->bqueue.swap(rest);
+        st->topk_passes++;
+        lk.unlock();
+        int kmax = 0;
+        for (da_store::Pending *r : group) kmax = std::max(kmax, r->k);
+        const size_t g = group.size();
+        std::vector<float> qs(g * (size_t)dim), sc(g * (size_t)kmax);
+        std::vector<uint8_t> ids(g * (size_t)kmax * 16);
+        std::vector<int32_t> cnt(g);
+        for (size_t i = 0; i < g; i++) memcpy(&qs[i * dim], group[i]->query, (size_t)dim * 4);
+        const int rc = topk_direct(st, head->doc_ids, head->n_docs, qs.data(), (int32_t)g, dim, kmax, ids.data(), sc.data(), cnt.data());
+        const std::string err = rc == DA_OK ? std::string() : g_err;
+        for (size_t i = 0; i < g; i++) {            // a smaller k is a prefix of the batch's top-kmax
+            da_store::Pending *r = group[i];
+            r->rc = rc; r->err = err;
+            if (rc == DA_OK) {
+                const int n = std::min(cnt[i], r->k);
+                memcpy(r->out_ids, &ids[i * (size_t)kmax * 16], (size_t)n * 16);
+                memcpy(r->out_scores, &sc[i * (size_t)kmax], (size_t)n * 4);
+                *r->out_n = n;
+            }
+        }
+        lk.lock();
+        for (da_store::Pending *r : group) r->done = true;
+        st->bleader = false;
+        st->bcv.notify_all();
+    }
+    if (me.rc != DA_OK) g_err = me.err;
+    return me.rc;
 }
 
 int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t iters, float *out_total_ms)
@@ -1027,6 +1106,7 @@ int da_store_stats(da_store *st, da_stats *out)
     out->ivf_build_ms = st->ivf_build_ms; out->ivf_kmeans_ms = st->ivf_kmeans_ms;
     out->ivf_assign_ms = st->ivf_assign_ms; out->ivf_assign_tflops = st->ivf_assign_tflops;
     out->peer_gather = st->p2p_gather ? 1 : 0; out->tensor_overflows = st->tc_overflows;
+    { std::lock_guard<std::mutex> bl(st->bmu); out->topk_calls = st->topk_calls; out->topk_passes = st->topk_passes; }
     return DA_OK;
 }
 

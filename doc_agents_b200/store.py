@@ -81,7 +81,7 @@ class GpuStore:
 
     def __init__(self, dim: int = 3072, capacity_rows: int = 1 << 16, devices: Sequence[int] = (0,),
                  min_similarity: float = L.DA_DEFAULT_MIN_SIMILARITY, world_size: int = 1, rank: int = 0,
-                 nccl_id: bytes | None = None):
+                 nccl_id: bytes | None = None, batch_window_us: int = 0, batch_max: int = 0):
         lib = L.load()
         cfg = L.da_config()
         cfg.struct_size = C.sizeof(L.da_config)
@@ -93,6 +93,8 @@ class GpuStore:
         cfg.min_similarity = min_similarity
         cfg.world_size = world_size
         cfg.rank = rank
+        cfg.batch_window_us = batch_window_us
+        cfg.batch_max = batch_max
         if nccl_id is not None:
             assert len(nccl_id) == L.DA_NCCL_ID_BYTES
             C.memmove(cfg.nccl_id, nccl_id, L.DA_NCCL_ID_BYTES)

@@ -67,6 +67,11 @@ typedef struct {
     int32_t  rank;
     uint8_t  nccl_id[DA_NCCL_ID_BYTES];   /* from da_nccl_unique_id on rank 0, same on all ranks */
     uint32_t flags;                 /* reserved, 0 */
+    /* Request batching for da_store_topk (0 = off).  Concurrent calls -- one goroutine per
+     * /api/query, cmd/query/main.go:34 -- that arrive within batch_window_us of each other and ask for the same
+     * document set are answered by ONE batched pass over the corpus (at most batch_max, default 64, calls). */
+    uint32_t batch_window_us;
+    uint32_t batch_max;
 } da_config;
 
 /* Fills `out` with a fresh ncclUniqueId to hand to every rank's da_config. */
@@ -174,6 +179,8 @@ typedef struct {
     float    ivf_assign_tflops;     /* 2 * rows * lists * dim / ivf_assign_ms */
     int32_t  peer_gather;           /* 1: shards deliver their records into shard 0 over NVLink (no collective) */
     uint64_t tensor_overflows;      /* batches answered by the SIMT scan because a candidate list overflowed */
+    uint64_t topk_calls;            /* da_store_topk calls answered */
+    uint64_t topk_passes;           /* searches run for them (== topk_calls unless request batching merged some) */
 } da_stats;
 int da_store_stats(da_store *st, da_stats *out);
 
