@@ -47,6 +47,7 @@ WORKLOADS = {
     "cfg3_b1": {},
     "cfg3_b64": {"BATCH": 64},
     "cfg3_b64_simt": {"BATCH": 64, "NO_TENSOR": True},
+    "cfg1": {"N_ROWS": 200, "TOP_K": 5, "FILTER_DOCS": 1},
     "cfg2": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16},
     "cfg2_predicate": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16, "READ_ALL": True},
     "cfg4": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf")},

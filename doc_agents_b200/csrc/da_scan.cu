@@ -332,6 +332,12 @@ cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream,
     size_t smem = scan_smem_bytes(a.dim, nqt, a.k, &a.P);
     if (smem > kSmemBudget || (a.dim & 3) || a.nq < 1 || a.nq > kMaxNQ) return cudaErrorInvalidValue;
     int grid = scan_grid_for(sm_count);
+    if (!a.row_list) {   // small stores (the reference's own scale) and centroid scans: no more CTAs than row groups need
+        const int r = 2;                                            // smallest R of any variant below
+        const long long groups = ((long long)a.n_rows + r - 1) / r;
+        const long long need = (groups + kScanWarps - 1) / kScanWarps;
+        if (need < grid) grid = need < 1 ? 1 : (int)need;
+    }
     if (grid_out) *grid_out = grid;
     // 256-bit loads need 32-byte aligned rows; other dimensions keep the 128-bit path
     const bool v8 = (a.dim % 8) == 0 && (reinterpret_cast<uintptr_t>(a.mat) & 31) == 0;

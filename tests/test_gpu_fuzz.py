@@ -1,0 +1,76 @@
+"""Randomised differential test: many small random configurations (rows, dimension, k, batch, document
+filter, floor, upsert order) through the C ABI against the CPU oracle.  Seeds are fixed; every
+configuration prints its parameters on failure."""
+import numpy as np
+import pytest
+
+import oracle
+from cases import ABS_TOL, REL_TOL, Case, check_against_oracle
+from doc_agents_b200 import GpuStore
+
+pytestmark = pytest.mark.gpu
+
+
+def _random_case(rng, idx):
+    dim = int(rng.choice([4, 8, 12, 64, 100, 128, 256, 772, 1024, 1536, 3072]))
+    n = int(rng.choice([1, 2, 3, 5, 31, 32, 33, 100, 255, 256, 257, 1000, 2049]))
+    n_docs = int(rng.integers(1, min(n, 9) + 1))
+    k = int(rng.choice([1, 2, 5, 10, 20, 33, 128]))
+    centers = oracle.normalize(rng.standard_normal(dim).astype(np.float32))
+    # rows: a mix of near-query rows and random rows, not normalised on purpose for some
+    q = centers
+    rows = []
+    for i in range(n):
+        mode = rng.integers(0, 4)
+        noise = rng.standard_normal(dim).astype(np.float32)
+        if mode == 0:
+            v = q + np.float32(0.3 / np.sqrt(dim)) * noise * np.float32(rng.uniform(0.2, 3.0))
+        elif mode == 1:
+            v = noise
+        elif mode == 2:
+            v = (q * np.float32(rng.uniform(0.1, 5.0))).astype(np.float32)      # exact multiples: ties after normalisation
+        else:
+            v = -q + np.float32(0.5 / np.sqrt(dim)) * noise
+        rows.append(v.astype(np.float32))
+    mat = np.stack(rows)
+    norm_mask = rng.random(n) < 0.7
+    for i in np.nonzero(norm_mask)[0]:
+        mat[i] = oracle.normalize(mat[i])
+    row_doc = rng.integers(0, n_docs, size=n).astype(np.uint32)
+    docs = None if rng.random() < 0.3 else sorted(set(int(d) for d in rng.integers(0, n_docs + 2, size=rng.integers(0, n_docs + 2))))
+    min_sim = float(rng.choice([0.7, 0.7, 0.0, -np.inf, 0.95, -0.5]))
+    return Case(f"fuzz{idx}", mat, row_doc, n_docs, q * np.float32(rng.uniform(0.5, 2.0)), k, min_sim, docs)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_configurations_match_the_oracle(seed):
+    rng = np.random.default_rng(1000 + seed)
+    S0 = oracle.Synth()
+    for idx in range(12):
+        c = _random_case(rng, seed * 100 + idx)
+        n, dim = c.mat.shape
+        chunk = oracle.chunk_ids(S0, 0, n)
+        docs = oracle.doc_ids(S0, 0, c.n_docs + 8)
+        info = dict(name=c.name, n=n, dim=dim, k=c.k, docs=c.docs, min_sim=c.min_sim, n_docs=c.n_docs)
+        with GpuStore(dim=dim, capacity_rows=n + 4) as st:
+            for d in range(c.n_docs):
+                st.save_chunks_raw(docs[d], chunk[c.row_doc == d])
+            # insert in two pieces, the second first half-overwritten later, to exercise the upsert path
+            half = n // 2
+            st.save_embeddings_raw(chunk[:half], c.mat[:half] * np.float32(0.5) if half else c.mat[:0])
+            st.save_embeddings_raw(chunk[half:], c.mat[half:])
+            if half:
+                st.save_embeddings_raw(chunk[:half], c.mat[:half])
+            filt = docs[: c.n_docs] if c.docs is None else (docs[np.asarray(c.docs, dtype=np.int64)] if len(c.docs) else docs[:0])
+            try:
+                ids, scores, rows = st.search(c.q, c.k, filt, min_similarity=c.min_sim)
+                check_against_oracle(c, rows[0], scores[0])
+                assert np.array_equal(ids[0], chunk[rows[0]])
+                # a small batch of scaled copies of the query returns the same rows for each
+                qs = np.stack([c.q, c.q * np.float32(2.0), c.q * np.float32(0.25)])
+                b = st.search(qs, c.k, filt, min_similarity=c.min_sim)
+                for i in range(3):
+                    assert len(b[2][i]) == len(rows[0]), info
+                    assert np.allclose(b[1][i], scores[0], rtol=REL_TOL, atol=ABS_TOL), info
+            except AssertionError as e:
+                raise AssertionError(f"{info}: {e}") from e
