@@ -226,6 +226,8 @@ def main():
     ap.add_argument("--workload", default="cfg3_b1", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     globals().update(WORKLOADS[args.workload])
+    if os.environ.get("DA_BENCH_MIN_SIM"):
+        globals()["MIN_SIM"] = float(os.environ["DA_BENCH_MIN_SIM"])
     # The contract is ONE JSON line on stdout: park fd 1 on stderr while libraries (NCCL prints its version
     # banner on stdout) are active, and restore it for the final print.
     sys.stdout.flush()

@@ -128,19 +128,21 @@ cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *c
                              unsigned long long *packed_scratch, uint32_t *out_assign, cudaStream_t stream);
 cudaError_t tc_launch_gather_rows(const float *mat, int D, const uint32_t *rows, uint32_t n, float *out, cudaStream_t stream);
 
-// Batched queries on the tensor cores (da_tc.cu): TF32 candidate generation, then exact fp32 re-score and
-// per-query selection (da_scan.cu).  eps bounds |cos_tf32 - cos_fp32|.
+// Batched queries on the tensor cores (da_tc.cu): TF32 candidate generation behind a global per-query gate,
+// then exact fp32 re-score and per-query selection (da_scan.cu).  eps bounds |cos_tf32 - cos_fp32|.
 constexpr float kTf32Eps = 2.5e-3f;
+#define DA_TC_MAX_BATCH 4096
+constexpr int kSurvivorCap = 4096;        // re-scored survivors kept per query
 int tc_batch_cap(int k);
 int tc_batch_m_tiles(int batch);
-int tc_batch_splits(int batch, int sm_count);
-size_t tc_batch_lists(int batch, int n_splits);
+size_t tc_batch_hist_words(int batch);
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
-                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int n_splits,
-                                       unsigned long long *cand, uint32_t *cand_count, uint32_t *overflow,
-                                       cudaStream_t stream);
-cudaError_t launch_rescore_select(key_t64 *cand, const uint32_t *cand_count, int cap, int n_splits, int batch,
+                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int sm_count,
+                                       unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
+                                       uint32_t *gate_ordered, uint32_t *overflow, cudaStream_t stream);
+cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_count, int cap, const uint32_t *gate_ordered,
+                                  key_t64 *surv, uint32_t *surv_count, uint32_t *overflow, int batch,
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
                                   int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream);

@@ -399,82 +399,86 @@ __global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gat
 // ---------------------------------------------------------------------------
 namespace {
 
-// Exact fp32 score of every candidate, with the scan kernel's own arithmetic (lane owns float4
-// slots lane + 32 j, x-y-z-w FMA order, xor-shuffle tree, then * 1/|row| * 1/|q|), so a batched
-// search returns bit-identical scores to a single one.  The entry is overwritten by its final key.
-__global__ void __launch_bounds__(128) rescore_candidates_kernel(key_t64 *cand, const uint32_t *cand_count, int cap,
-                                                                 int n_splits, int batch, const float *mat, int dim,
-                                                                 const float *inv_norm, const float *queries,
+constexpr int kRescoreBlocksPerQuery = 4;
+
+// Candidates below the query's final gate are dropped without touching their rows; the others get their
+// exact fp32 score with the scan kernel's own arithmetic (same lane ownership, x-y-z-w FMA order, xor-shuffle
+// tree, then * 1/|row| * 1/|q|), so a batched search returns bit-identical scores to a single one.
+__global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *cand, const uint32_t *cand_count, int cap,
+                                                                 const uint32_t *gate_ordered, key_t64 *surv,
+                                                                 uint32_t *surv_count, uint32_t *overflow, const float *mat,
+                                                                 int dim, const float *inv_norm, const float *queries,
                                                                  const float *q_inv, uint32_t row_base, float min_sim)
 {
-    const size_t list_id = blockIdx.x;
-    const uint32_t cnt = cand_count[list_id];
-    if (cnt == 0) return;
+    const uint32_t q = blockIdx.x / kRescoreBlocksPerQuery, part = blockIdx.x % kRescoreBlocksPerQuery;
+    const uint32_t cnt = min(cand_count[q], (uint32_t)cap);
+    const uint32_t per = (cnt + kRescoreBlocksPerQuery - 1) / kRescoreBlocksPerQuery;
+    const uint32_t lo = part * per, hi = min(cnt, lo + per);
+    if (lo >= hi) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t qlocal = (uint32_t)(list_id % 128);
-    const uint32_t m_tile = (uint32_t)(list_id / ((size_t)n_splits * 128));
-    const uint32_t q = m_tile * 128 + qlocal;
-    if (q >= (uint32_t)batch) return;
     const int D4 = dim >> 2;
     const bool vec8 = (dim % 8) == 0 && (reinterpret_cast<uintptr_t>(mat) & 31) == 0;
     const float4 *qv = reinterpret_cast<const float4 *>(queries + (size_t)q * dim);
     const float qi = q_inv[q];
-    key_t64 *lst = cand + list_id * (size_t)cap;
-    for (uint32_t i = warp; i < cnt; i += 4) {
-        const uint32_t row = (uint32_t)(lst[i] & 0xFFFFFFFFull);
-        const float4 *rp = reinterpret_cast<const float4 *>(mat) + (size_t)row * D4;
-        float acc = 0.f;
-        if (vec8) {          // the scan's 256-bit path: a lane owns 8 consecutive floats
-            for (int c = lane; c < (D4 >> 1); c += 32) {
+    const uint32_t gate = gate_ordered[q];
+    const key_t64 *lst = cand + (size_t)q * cap;
+    for (uint32_t i0 = lo + (uint32_t)warp * 32u; i0 < hi; i0 += 8u * 32u) {
+        const uint32_t i = i0 + (uint32_t)lane;
+        const key_t64 e = i < hi ? lst[i] : 0ull;
+        uint32_t m = __ballot_sync(0xFFFFFFFFu, i < hi && (uint32_t)(e >> 32) >= gate);
+        while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const uint32_t row = (uint32_t)(__shfl_sync(0xFFFFFFFFu, e, src) & 0xFFFFFFFFull);
+            const float4 *rp = reinterpret_cast<const float4 *>(mat) + (size_t)row * D4;
+            float acc = 0.f;
+            if (vec8) {          // the scan's 256-bit path: a lane owns 8 consecutive floats
+                for (int c = lane; c < (D4 >> 1); c += 32) {
 #pragma unroll
-                for (int i = 0; i < 2; i++) {
-                    const float4 v = ldg_stream(rp + 2 * c + i), w = qv[2 * c + i];
+                    for (int h = 0; h < 2; h++) {
+                        const float4 v = ldg_stream(rp + 2 * c + h), w = qv[2 * c + h];
+                        acc = fmaf(v.x, w.x, acc); acc = fmaf(v.y, w.y, acc); acc = fmaf(v.z, w.z, acc); acc = fmaf(v.w, w.w, acc);
+                    }
+                }
+            } else {
+                for (int c = lane; c < D4; c += 32) {
+                    const float4 v = ldg_stream(rp + c), w = qv[c];
                     acc = fmaf(v.x, w.x, acc); acc = fmaf(v.y, w.y, acc); acc = fmaf(v.z, w.z, acc); acc = fmaf(v.w, w.w, acc);
                 }
             }
-        } else {
-            for (int c = lane; c < D4; c += 32) {
-                const float4 v = ldg_stream(rp + c), w = qv[c];
-                acc = fmaf(v.x, w.x, acc); acc = fmaf(v.y, w.y, acc); acc = fmaf(v.z, w.z, acc); acc = fmaf(v.w, w.w, acc);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+            float sim = acc * inv_norm[row] * qi;
+            sim = fminf(1.f, fmaxf(-1.f, sim));
+            if (lane == 0 && sim >= min_sim) {
+                const uint32_t pos = atomicAdd(surv_count + q, 1u);
+                if (pos < (uint32_t)kSurvivorCap) surv[(size_t)q * kSurvivorCap + pos] = make_key(sim, row_base + row);
+                else *overflow = 1u;
             }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
-        float sim = acc * inv_norm[row] * qi;
-        sim = fminf(1.f, fmaxf(-1.f, sim));
-        if (lane == 0) lst[i] = (sim >= min_sim) ? make_key(sim, row_base + row) : 0ull;
     }
 }
 
-// One CTA per query: top-k of all its re-scored candidates, then the chunk-id gather.
-__global__ void __launch_bounds__(256) select_candidates_kernel(const key_t64 *cand, const uint32_t *cand_count, int cap,
-                                                                int n_splits, int k, int P, const uint8_t *chunk_ids,
-                                                                uint32_t row_base, key_t64 *out_keys, uint8_t *out_ids)
+// One CTA per query: top-k of its re-scored survivors, then the chunk-id gather.
+__global__ void __launch_bounds__(256) select_candidates_kernel(const key_t64 *surv, const uint32_t *surv_count, int k, int P,
+                                                                const uint8_t *chunk_ids, uint32_t row_base,
+                                                                key_t64 *out_keys, uint8_t *out_ids)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     key_t64 *buf = reinterpret_cast<key_t64 *>(smem_raw);       // P keys: [0,k) kept, [k,P) incoming
-    const uint32_t q = blockIdx.x, m_tile = q / 128, qlocal = q % 128;
+    const uint32_t q = blockIdx.x;
     const int tid = threadIdx.x;
-    for (int i = tid; i < P; i += blockDim.x) buf[i] = 0ull;
-    __syncthreads();
-    int fill = 0;
+    const int n = (int)min(surv_count[q], (uint32_t)kSurvivorCap);
+    const key_t64 *lst = surv + (size_t)q * kSurvivorCap;
+    for (int i = tid; i < k; i += blockDim.x) buf[i] = 0ull;
     const int room = P - k;
-    for (int sp = 0; sp < n_splits; sp++) {
-        const size_t list_id = ((size_t)m_tile * n_splits + sp) * 128 + qlocal;
-        const int c = (int)cand_count[list_id];
-        if (c == 0) continue;
-        if (fill + c > room) {
-            cta_bitonic_desc(buf, P);
-            for (int i = k + tid; i < P; i += blockDim.x) buf[i] = 0ull;
-            __syncthreads();
-            fill = 0;
-        }
-        const key_t64 *lst = cand + list_id * (size_t)cap;
-        for (int i = tid; i < c; i += blockDim.x) buf[k + fill + i] = lst[i];
-        fill += c;
+    int done = 0;
+    do {
         __syncthreads();
-    }
-    cta_bitonic_desc(buf, P);
+        for (int i = tid; i < room; i += blockDim.x) buf[k + i] = (done + i < n) ? lst[done + i] : 0ull;
+        cta_bitonic_desc(buf, P);
+        done += room;
+    } while (done < n);
     for (int i = tid; i < k; i += blockDim.x) {
         const key_t64 key = buf[i];
         out_keys[(size_t)q * k + i] = key;
@@ -486,20 +490,22 @@ __global__ void __launch_bounds__(256) select_candidates_kernel(const key_t64 *c
 
 }  // namespace
 
-cudaError_t launch_rescore_select(key_t64 *cand, const uint32_t *cand_count, int cap, int n_splits, int batch,
+cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_count, int cap, const uint32_t *gate_ordered,
+                                  key_t64 *surv, uint32_t *surv_count, uint32_t *overflow, int batch,
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
                                   int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream)
 {
-    const size_t lists = (size_t)((batch + 127) / 128) * n_splits * 128;
-    rescore_candidates_kernel<<<(unsigned)lists, 128, 0, stream>>>(cand, cand_count, cap, n_splits, batch, mat, dim,
-                                                                   inv_norm, queries, q_inv, row_base, min_sim);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = cudaMemsetAsync(surv_count, 0, (size_t)batch * 4, stream);
     if (e != cudaSuccess) return e;
-    int P = next_pow2(cap + k);
-    if (P < 2048) P = 2048;
-    select_candidates_kernel<<<batch, 256, (size_t)P * sizeof(key_t64), stream>>>(cand, cand_count, cap, n_splits, k, P,
-                                                                                  chunk_ids, row_base, out_keys, out_ids);
+    rescore_candidates_kernel<<<(unsigned)batch * kRescoreBlocksPerQuery, 256, 0, stream>>>(
+        cand, cand_count, cap, gate_ordered, surv, surv_count, overflow, mat, dim, inv_norm, queries, q_inv, row_base, min_sim);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    int P = next_pow2(2 * k);
+    if (P < 1024) P = 1024;
+    select_candidates_kernel<<<batch, 256, (size_t)P * sizeof(key_t64), stream>>>(surv, surv_count, k, P, chunk_ids, row_base,
+                                                                                  out_keys, out_ids);
     return cudaGetLastError();
 }
 

@@ -118,7 +118,8 @@ struct Shard {
     DevBuf<uint32_t> d_bitmap;
     DevBuf<uint8_t> d_out, d_gather, d_final;
     DevBuf<unsigned long long> d_cand;          // batched tensor-core path: candidate lists
-    DevBuf<uint32_t> d_cand_count, d_overflow;
+    DevBuf<uint32_t> d_cand_count, d_overflow, d_hist, d_gate, d_surv_count;
+    DevBuf<unsigned long long> d_surv;
     PinBuf<uint32_t> h_overflow;
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
@@ -206,6 +207,7 @@ void free_shard(Shard &s)
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
+    s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
     s.h_up_rows.release(); s.h_up_slots.release(); s.h_up_ids.release();
@@ -317,15 +319,15 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             continue;
         }
         if (pl.use_tc) {
-            const int n_splits = da::tc_batch_splits(pl.batch, s.sm_count);
             CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_qinv.p, s.mat, s.n_rows, dim, s.inv_norm,
                                               s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.k, pl.min_sim,
-                                              da::kTf32Eps, n_splits, s.d_cand.p, s.d_cand_count.p, s.d_overflow.p, s.stream));
-            CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), n_splits, pl.batch, s.mat, dim,
-                                         s.inv_norm, s.d_queries.p, s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k,
-                                         out_keys, out_ids, s.stream));
-            st->launches += 3;
-            if (first) { st->scan_grid = n_splits * da::tc_batch_m_tiles(pl.batch); st->scan_launches++; }
+                                              da::kTf32Eps, s.sm_count, s.d_cand.p, s.d_cand_count.p, s.d_hist.p,
+                                              s.d_gate.p, s.d_overflow.p, s.stream));
+            CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), s.d_gate.p, s.d_surv.p,
+                                         s.d_surv_count.p, s.d_overflow.p, pl.batch, s.mat, dim, s.inv_norm, s.d_queries.p,
+                                         s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream));
+            st->launches += 4;
+            if (first) { st->scan_grid = s.sm_count; st->scan_launches++; }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
@@ -426,9 +428,10 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
         if (pl.use_tc) {
-            const size_t lists = da::tc_batch_lists(p->batch, da::tc_batch_splits(p->batch, s.sm_count));
-            CU(s.d_cand.ensure(lists * (size_t)da::tc_batch_cap(pl.k)));
-            CU(s.d_cand_count.ensure(lists));
+            CU(s.d_cand.ensure((size_t)p->batch * da::tc_batch_cap(pl.k)));
+            CU(s.d_cand_count.ensure(p->batch)); CU(s.d_gate.ensure(p->batch)); CU(s.d_surv_count.ensure(p->batch));
+            CU(s.d_hist.ensure(da::tc_batch_hist_words(p->batch)));
+            CU(s.d_surv.ensure((size_t)p->batch * da::kSurvivorCap));
             CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));
             CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
             *s.h_overflow.p = 0;
@@ -484,7 +487,7 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
         st->last_bytes = (uint64_t)pl.batch * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
                          rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
     else if (pl.use_tc)
-        st->last_bytes = (uint64_t)da::tc_batch_m_tiles(pl.batch) * rows_scanned * ((uint64_t)st->dim * 4 + (pl.all_docs ? 4 : 8));
+        st->last_bytes = rows_scanned * ((uint64_t)st->dim * 4 + (pl.all_docs ? 4 : 8));   // every row once, whatever the batch
     else
         st->last_bytes = rows_read * (uint64_t)st->dim * 4 +
                          rows_scanned * (uint64_t)passes * (pl.all_docs ? 4 : 8);

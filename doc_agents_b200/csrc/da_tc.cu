@@ -233,68 +233,83 @@ __global__ void gather_rows_kernel(const float *mat, int D, const uint32_t *rows
 // per-query candidate filter, so the batch x N score matrix never leaves the SM.
 //
 // Roles swap relative to the assignment kernel: A = queries (an M tile = 128 queries), B = corpus
-// rows (N tiles of 256 rows).  Epilogue thread r owns query r of the tile and walks the 256 row
-// scores of each accumulator tile.  TF32 scores are only a candidate generator: with
-//     eps >= |cos_tf32 - cos_fp32|
-// a row can be in the exact top-k only if  cos_tf32 >= T_k - 2*eps  (T_k = k-th best TF32 score
-// seen so far by this thread) and  cos_tf32 >= floor - eps.  Survivors go to a per-(CTA, query)
-// list in global memory; a second kernel re-scores them in fp32 with the scan kernel's exact
-// arithmetic and a third selects the top-k -- so results are identical to the fp32 scan.
+// rows (N tiles of 256 rows).  A CTA owns a contiguous range of row tiles and, for each of them,
+// sweeps ALL query tiles back to back -- the row tile comes from HBM once and from L2 for the
+// other query tiles, so DRAM traffic is the corpus once per pass whatever the batch.  Epilogue
+// thread r owns query r of the current query tile and walks the 256 row scores of the accumulator.
+//
+// TF32 scores are only a candidate generator.  With eps >= |cos_tf32 - cos_fp32|, a row can be in
+// the exact top-k only if  cos_tf32 >= T_k - 2*eps  and  cos_tf32 >= floor - eps, where T_k is any
+// lower bound of the k-th best TF32 score.  T_k is GLOBAL here: every appended candidate is counted
+// in a per-query two-level histogram of scores (64 x 64 bins); scanning it from the top until k
+// entries are covered gives a bound that all CTAs share, lock-free (counters only grow).  Survivors
+// go to one list per query in global memory; a second kernel drops those below the final gate and
+// re-scores the rest in fp32 with the scan kernel's arithmetic; a third selects the top-k.
 // ---------------------------------------------------------------------------
-constexpr uint32_t TCB_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 + 256 + 2 * TC_BN * 4;
+constexpr int TCB_MAX_MTILES = DA_TC_MAX_BATCH / TC_BM;   // 32
+constexpr uint32_t TCB_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 + 256 + 2 * TC_BN * 4 + TCB_MAX_MTILES * TC_BM * 4;
 
 struct BatchArgs {
     uint32_t n_rows;            // rows resident on this shard
     int K, batch, k;
-    int n_splits;               // CTAs per M tile; each sweeps a contiguous range of N tiles
-    int cap;                    // entries per candidate list
+    int cap;                    // entries per query list
+    int group;                  // CTAs that share one range of row tiles and split the query tiles among them
     float floor_eps;            // min_similarity - eps
     float two_eps;
     const float *inv_norm;      // per row
     const uint32_t *doc_slot;   // per row (with doc_bitmap)
     const uint32_t *doc_bitmap; // nullptr = every document
     const float *q_inv;         // per query
-    unsigned long long *cand;   // [m_tile][split][128][cap]   ordered(score) << 32 | local row
-    uint32_t *cand_count;       // [m_tile][split][128]
-    uint32_t *overflow;         // set to 1 if a list could not be pruned below its capacity
+    unsigned long long *cand;   // [batch][cap]   ordered(score) << 32 | local row
+    uint32_t *cand_count;       // [batch]
+    uint32_t *hist;             // [batch][64 coarse + 4096 fine]
+    uint32_t *overflow;         // set to 1 if a query list ran out of room
 };
+constexpr int kHistWords = 64 + 64 * 64;
 
-// k-th largest of the n (<= 1024) entries of one list, found cooperatively by a warp through a
-// bisection on the ordered score bits; entries below (that - two_eps) are dropped in place.
-__device__ uint32_t warp_prune_list(unsigned long long *lst, uint32_t n, int k, float two_eps, int lane, float *thr_out)
+__device__ __forceinline__ void hist_bins(float v, int &c, int &f)
 {
-    uint32_t sc[32];
-    unsigned long long ent[32];
+    const float x = (v + 1.0f) * 32.0f;                 // [-1, 1] -> [0, 64]
+    c = min(63, max(0, (int)x));
+    f = min(63, max(0, (int)((x - (float)c) * 64.0f)));
+}
+__device__ __forceinline__ float hist_edge(int c, int f) { return ((float)c + (float)f * (1.0f / 64.0f)) * (1.0f / 32.0f) - 1.0f; }
+
+// A lower bound of the k-th best appended score of one query (-inf while fewer than k were appended).
+// Two rounds of 16 independent 128-bit loads (coarse row, then one fine row): latency of two L2 trips.
+__device__ float hist_kth_lower_bound(const uint32_t *h, int k)
+{
+    uint4 w[16];
 #pragma unroll
-    for (int i = 0; i < 32; i++) {
-        const uint32_t idx = (uint32_t)i * 32u + (uint32_t)lane;
-        ent[i] = idx < n ? lst[idx] : 0ull;
-        sc[i] = (uint32_t)(ent[i] >> 32);
+    for (int i = 0; i < 16; i++) w[i] = __ldcg(reinterpret_cast<const uint4 *>(h) + i);
+    uint32_t cum = 0;
+    int cbin = -1;
+#pragma unroll
+    for (int i = 15; i >= 0; i--) {
+        const uint32_t v[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+#pragma unroll
+        for (int j = 3; j >= 0; j--) {
+            if (cbin < 0) {
+                if (cum + v[j] >= (uint32_t)k) cbin = i * 4 + j; else cum += v[j];
+            }
+        }
     }
-    uint32_t lo = 0u, hi = 0xFFFFFFFFu;          // largest t with count(score >= t) >= k
-    while (lo < hi) {
-        const uint32_t mid = lo + (uint32_t)(((unsigned long long)hi - lo + 1ull) >> 1);
-        int c = 0;
+    if (cbin < 0) return -3.0e38f;
+    const uint4 *fine = reinterpret_cast<const uint4 *>(h + 64 + cbin * 64);
 #pragma unroll
-        for (int i = 0; i < 32; i++) c += (sc[i] >= mid && ent[i] != 0ull);
+    for (int i = 0; i < 16; i++) w[i] = __ldcg(fine + i);
+    int fbin = -1;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
-        if (c >= k) lo = mid; else hi = mid - 1u;
+    for (int i = 15; i >= 0; i--) {
+        const uint32_t v[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+#pragma unroll
+        for (int j = 3; j >= 0; j--) {
+            if (fbin < 0) {
+                if (cum + v[j] >= (uint32_t)k) fbin = i * 4 + j; else cum += v[j];
+            }
+        }
     }
-    const float kth = ordered_to_score(lo);
-    const float thr = kth - two_eps;
-    const uint32_t thr_o = score_to_ordered(thr);
-    uint32_t out = 0;
-#pragma unroll
-    for (int i = 0; i < 32; i++) {
-        const bool keep = ent[i] != 0ull && sc[i] >= thr_o;
-        const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
-        if (keep) lst[out + __popc(m & ((1u << lane) - 1u))] = ent[i];
-        out += __popc(m);
-    }
-    __syncwarp();
-    *thr_out = thr;
-    return out;
+    return hist_edge(cbin, fbin < 0 ? 0 : fbin);   // fine counters may lag the coarse one: its edge is still valid
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -309,14 +324,18 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const uint32_t tmem_slot = bar_tempty + 16;
     volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
     float *s_inv = reinterpret_cast<float *>(smem_raw + (bars + 256 - smem_u32(smem_raw)));   // [2][TC_BN]
+    float *gate_s = s_inv + 2 * TC_BN;                                                        // [m_tiles][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tiles = (a.batch + TC_BM - 1) / TC_BM;
-    const uint32_t split = blockIdx.x / m_tiles, m_tile = blockIdx.x % m_tiles;   // siblings (same rows) are adjacent
     const int n_tiles_total = (int)((a.n_rows + TC_BN - 1) / TC_BN);
-    const int per_split = (n_tiles_total + a.n_splits - 1) / a.n_splits;
-    const int t_begin = (int)split * per_split;
-    const int t_end = min(n_tiles_total, t_begin + per_split);
+    // `group` neighbouring CTAs share one range of row tiles (the tile reaches them through L2) and deal the
+    // query tiles out among themselves, so that the row tiles in flight across the chip stay L2-resident.
+    const int n_groups = (int)gridDim.x / a.group;
+    const int grp = (int)blockIdx.x / a.group, member = (int)blockIdx.x % a.group;
+    const int per_grp = (n_tiles_total + n_groups - 1) / n_groups;
+    const int t_begin = grp * per_grp;
+    const int t_end = min(n_tiles_total, t_begin + per_grp);
     const int kb_count = (a.K + TC_BK - 1) / TC_BK;
 
     if (threadIdx.x == 0) {
@@ -337,13 +356,15 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int t = t_begin; t < t_end; t++) {
-                for (int kb = 0; kb < kb_count; kb++) {
-                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                    const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
-                    mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
-                    tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * TC_BK, (int)(m_tile * TC_BM));
-                    tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * TC_BK, t * TC_BN);
-                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                for (int mt = member; mt < m_tiles; mt += a.group) {
+                    for (int kb = 0; kb < kb_count; kb++) {
+                        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                        const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                        mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
+                        tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * TC_BK, mt * TC_BM);
+                        tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * TC_BK, t * TC_BN);
+                        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                    }
                 }
             }
         }
@@ -351,45 +372,39 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             int it = 0;
-            for (int t = t_begin; t < t_end; t++, it++) {
-                const int as = it & 1;
-                const uint32_t aphase = (uint32_t)(it >> 1) & 1;
-                mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t tmem_d = tmem_base + (uint32_t)as * TC_BN;
-                for (int kb = 0; kb < kb_count; kb++) {
-                    mbar_wait(bar_full + 8 * stage, phase);
+            for (int t = t_begin; t < t_end; t++) {
+                for (int mt = member; mt < m_tiles; mt += a.group, it++) {
+                    const int as = it & 1;
+                    const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+                    mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
-                    const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
+                    const uint32_t tmem_d = tmem_base + (uint32_t)as * TC_BN;
+                    for (int kb = 0; kb < kb_count; kb++) {
+                        mbar_wait(bar_full + 8 * stage, phase);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                        const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
 #pragma unroll
-                    for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
-                        umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
-                    umma_commit(bar_empty + 8 * stage);
-                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                        for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
+                            umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
+                        umma_commit(bar_empty + 8 * stage);
+                        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                    }
+                    umma_commit(bar_tfull + 8 * as);
                 }
-                umma_commit(bar_tfull + 8 * as);
             }
         }
     } else {
-        // ===== epilogue warps 2..5: thread = one query of this M tile =====
+        // ===== epilogue warps 2..5: thread = query `qlocal` of every query tile =====
         const uint32_t quad = (uint32_t)warp & 3u;
         const int etid = (int)threadIdx.x - 64;                       // 0..127 among the epilogue threads
         const uint32_t qlocal = quad * 32u + (uint32_t)lane;
-        const uint32_t q = m_tile * TC_BM + qlocal;
-        const bool q_valid = q < (uint32_t)a.batch;
-        const float qinv = q_valid ? a.q_inv[q] : 0.f;
-        const size_t list_id = ((size_t)m_tile * a.n_splits + split) * TC_BM + qlocal;
-        unsigned long long *lst = a.cand + list_id * (size_t)a.cap;
-        uint32_t cnt = 0;
-        float thr = -3.0e38f;                                           // T_k - 2 eps once k candidates exist
-        int it = 0;
-        for (int t = t_begin; t < t_end; t++, it++) {
-            const int as = it & 1;
-            const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+        for (int mt = member; mt < m_tiles; mt += a.group) gate_s[mt * TC_BM + qlocal] = a.floor_eps;
+        int it = 0, visited = 0, next_refresh = 1;
+        for (int t = t_begin; t < t_end; t++, visited++) {
             const uint32_t n0 = (uint32_t)t * TC_BN;
-            // per-row factor for this tile: 1/|row|, or 0 when the row is absent, zero or filtered out
-            float *inv_t = s_inv + as * TC_BN;
+            // per-row factor for this row tile: 1/|row|, or 0 when the row is absent, zero or filtered out
+            float *inv_t = s_inv + (t & 1) * TC_BN;
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int j = etid + h * 128;
@@ -404,49 +419,78 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 }
                 inv_t[j] = f;
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            // make room: a tile adds at most 256 entries to a list
-            {
-                const uint32_t need = __ballot_sync(0xFFFFFFFFu, cnt + TC_BN > (uint32_t)a.cap);
-                uint32_t m = need;
-                while (m) {
-                    const int src = __ffs(m) - 1;
-                    m &= m - 1;
-                    unsigned long long *l2 = reinterpret_cast<unsigned long long *>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)lst, src));
-                    const uint32_t n2 = __shfl_sync(0xFFFFFFFFu, cnt, src);
-                    float new_thr;
-                    const uint32_t kept = warp_prune_list(l2, n2, a.k, a.two_eps, lane, &new_thr);
-                    if (lane == src) {
-                        cnt = kept;
-                        thr = fmaxf(thr, new_thr);
-                        if (kept + TC_BN > (uint32_t)a.cap) *a.overflow = 1u;
+            // tighten this thread's gates from the shared histograms: often at first, then every 16 row tiles
+            if (visited == next_refresh) {
+                next_refresh = visited < 4 ? visited + 1 : (visited < 16 ? visited + 2 : visited + 16);
+                for (int mt = member; mt < m_tiles; mt += a.group) {
+                    const uint32_t q = (uint32_t)mt * TC_BM + qlocal;
+                    if (q < (uint32_t)a.batch) {
+                        const float lb = hist_kth_lower_bound(a.hist + (size_t)q * kHistWords, a.k);
+                        gate_s[mt * TC_BM + qlocal] = fmaxf(a.floor_eps, lb - a.two_eps);
                     }
                 }
             }
-            mbar_wait(bar_tfull + 8 * as, aphase);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * TC_BN;
-            const float gate = fmaxf(thr, a.floor_eps);
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            for (int mt = member; mt < m_tiles; mt += a.group, it++) {
+                const int as = it & 1;
+                const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+                const uint32_t q = (uint32_t)mt * TC_BM + qlocal;
+                const bool q_valid = q < (uint32_t)a.batch;
+                const float qinv = q_valid ? a.q_inv[q] : 0.f;
+                const float gate = gate_s[mt * TC_BM + qlocal];
+                unsigned long long *lst = a.cand + (size_t)q * a.cap;
+                uint32_t *hq = a.hist + (size_t)q * kHistWords;
+                mbar_wait(bar_tfull + 8 * as, aphase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * TC_BN;
+                // pass 1: how many of the 256 rows pass this query's gate (no memory traffic at all)
+                uint32_t n_pass = 0;
 #pragma unroll 1
-            for (int c = 0; c < TC_BN / 32; c++) {
-                uint32_t r[32];
-                tmem_ld32(taddr + (uint32_t)c * 32u, r);
-                if (q_valid) {
+                for (int c = 0; c < TC_BN / 32; c++) {
+                    uint32_t r[32];
+                    tmem_ld32(taddr + (uint32_t)c * 32u, r);
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
                         const float f = inv_t[c * 32 + j];
                         const float v = __uint_as_float(r[j]) * f * qinv;
-                        if (f > 0.f && v >= gate && cnt < (uint32_t)a.cap) {
-                            lst[cnt++] = ((unsigned long long)score_to_ordered(v) << 32) | (unsigned long long)(n0 + c * 32 + j);
+                        n_pass += (f > 0.f && v >= gate) ? 1u : 0u;
+                    }
+                }
+                if (!q_valid) n_pass = 0;
+                // pass 2 (only if some query of this warp has survivors): one slot reservation per query, then
+                // plain stores and fire-and-forget histogram increments
+                if (__any_sync(0xFFFFFFFFu, n_pass != 0)) {
+                    uint32_t pos = n_pass ? atomicAdd(a.cand_count + q, n_pass) : 0u;
+#pragma unroll 1
+                    for (int c = 0; c < TC_BN / 32; c++) {
+                        uint32_t r[32];
+                        tmem_ld32(taddr + (uint32_t)c * 32u, r);
+                        if (n_pass) {
+#pragma unroll
+                            for (int j = 0; j < 32; j++) {
+                                const float f = inv_t[c * 32 + j];
+                                const float v = __uint_as_float(r[j]) * f * qinv;
+                                if (f > 0.f && v >= gate) {
+                                    if (pos < (uint32_t)a.cap) {
+                                        lst[pos] = ((unsigned long long)score_to_ordered(v) << 32) | (unsigned long long)(n0 + c * 32 + j);
+                                        int hc, hf;
+                                        hist_bins(fminf(1.f, fmaxf(-1.f, v)), hc, hf);
+                                        atomicAdd(hq + 64 + hc * 64 + hf, 1u);
+                                        atomicAdd(hq + hc, 1u);
+                                    } else {
+                                        *a.overflow = 1u;
+                                    }
+                                    pos++;
+                                }
+                            }
                         }
                     }
                 }
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
             }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
         }
-        a.cand_count[list_id] = q_valid ? cnt : 0u;
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -455,6 +499,15 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
     }
+}
+
+// Final gate per query, read by the re-score kernel.
+__global__ void batch_final_gate_kernel(const uint32_t *hist, int batch, int k, float floor_eps, float two_eps, uint32_t *gate_ordered)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= batch) return;
+    const float lb = hist_kth_lower_bound(hist + (size_t)q * kHistWords, k);
+    gate_ordered[q] = score_to_ordered(fmaxf(floor_eps, lb - two_eps));
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -516,41 +569,54 @@ cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *c
     return cudaGetLastError();
 }
 
-// Entries per candidate list: the most warp_prune_list handles (32 lanes x 32).  A list is pruned when fewer
-// than 256 slots are free, so up to 768 entries may sit within the TF32 slack of the k-th best before the
-// overflow flag is raised.
-int tc_batch_cap(int k) { (void)k; return 1024; }
+// Entries per query list.  The first row tile of every CTA is appended unfiltered (no gate exists yet), so a
+// list must hold at least grid x 256 entries; later appends pass the shared gate.
+int tc_batch_cap(int k) { (void)k; return 65536; }
 int tc_batch_m_tiles(int batch) { return (batch + TC_BM - 1) / TC_BM; }
-// CTAs per M tile.  One M tile: one CTA per SM.  Many M tiles already fill the machine, so fewer, longer row
-// ranges per CTA: a thread's k-th best over a longer range is a tighter gate, and fewer lists hold candidates.
-int tc_batch_splits(int batch, int sm_count)
-{
-    const int mt = tc_batch_m_tiles(batch);
-    if (mt == 1) return sm_count;
-    const int s = (2 * sm_count) / mt;
-    return s < 1 ? 1 : s;
-}
-size_t tc_batch_lists(int batch, int n_splits) { return (size_t)tc_batch_m_tiles(batch) * n_splits * TC_BM; }
+size_t tc_batch_hist_words(int batch) { return (size_t)batch * kHistWords; }
 
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
-                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int n_splits,
-                                       unsigned long long *cand, uint32_t *cand_count, uint32_t *overflow,
-                                       cudaStream_t stream)
+                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int sm_count,
+                                       unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
+                                       uint32_t *gate_ordered, uint32_t *overflow, cudaStream_t stream)
 {
     if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
+    if (batch > DA_TC_MAX_BATCH) return cudaErrorInvalidValue;
     CUtensorMap map_q, map_x;
     if (!make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BN))
         return cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(cand_count, 0, (size_t)batch * 4, stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(hist, 0, tc_batch_hist_words(batch) * 4, stream);
+    if (e != cudaSuccess) return e;
     BatchArgs a{};
-    a.n_rows = n_rows; a.K = D; a.batch = batch; a.k = k; a.n_splits = n_splits; a.cap = tc_batch_cap(k);
+    a.n_rows = n_rows; a.K = D; a.batch = batch; a.k = k; a.cap = tc_batch_cap(k);
     a.floor_eps = min_sim - eps; a.two_eps = 2.f * eps;
     a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.q_inv = q_inv;
-    a.cand = cand; a.cand_count = cand_count; a.overflow = overflow;
-    cudaError_t e = cudaFuncSetAttribute(tc_batch_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
+    a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
+    e = cudaFuncSetAttribute(tc_batch_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    const uint32_t grid = (uint32_t)tc_batch_m_tiles(batch) * (uint32_t)n_splits;
+    const uint32_t n_tiles = (n_rows + TC_BN - 1) / TC_BN;
+    // Row tiles in flight across the chip (one per group) plus the queries should sit in a fraction of the
+    // 126 MB L2; otherwise every query tile pulls its row tile from HBM again.  Measured on cfg4 (4096 queries,
+    // 1.25M x 1536 rows): group 1/4/16/32 -> 274/188/152/102 GB of DRAM reads for a 7.7 GB shard, 44/33/30/29 ms.
+    // Row-tile re-reads still miss L2 half of the time once the epilogue emits candidates (open issue, see
+    // profiles/README.md); with nothing emitted the kernel runs at 93 % tensor-pipe activity.
+    const int m_tiles = tc_batch_m_tiles(batch);
+    const double tile_mb = (double)TC_BN * D * 4 / 1e6, q_mb = (double)batch * D * 4 / 1e6;
+    int group = 1;
+    while (group < m_tiles && group < sm_count && (sm_count / group) * tile_mb + q_mb > 60.0) group++;
+    if (group > m_tiles) group = m_tiles;
+    int n_groups = sm_count / group;
+    if ((uint32_t)n_groups > n_tiles) n_groups = (int)n_tiles;
+    if (n_groups < 1) n_groups = 1;
+    a.group = group;
+    const uint32_t grid = (uint32_t)(n_groups * group);
     tc_batch_candidates_kernel<<<grid, TC_THREADS, TCB_SMEM_BYTES, stream>>>(map_q, map_x, a);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a.floor_eps, a.two_eps, gate_ordered);
     return cudaGetLastError();
 }
 
