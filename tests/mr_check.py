@@ -56,6 +56,27 @@ def main():
             assert np.array_equal(ids[i], chunk[o_rows]), (rank, i)
         one = st.search(qs[3], k, **kw)
         assert np.array_equal(one[2][0], rows[3])
+    # a batch large enough for the tensor-core path: candidates per rank, all-gather, merge
+    qs40 = np.stack([oracle.gen_query(S, 100 + i, i % 8, dim) for i in range(40)])
+    ids, sc, rows = st.search(qs40, k, all_docs=True)
+    for i in (0, 13, 39):
+        o_rows, o_sc, _ = oracle.topk(mat, rd, None, qs40[i], k)
+        assert np.array_equal(rows[i], o_rows), (rank, i, rows[i], o_rows)
+        assert np.allclose(sc[i], o_sc, rtol=1e-5), (rank, i)
+    # IVFFlat across ranks: k-means is data-parallel (NCCL broadcast of the seeds, all-reduce of the sums),
+    # so every rank holds the same centroids; probing every list equals the exact scan
+    st.build_ivf(lists=24, iters=5, seed=7)
+    _, _, cent = st.debug_ivf(0)
+    digest = torch.tensor([float(np.abs(cent).sum()), float(cent[3, 5])], dtype=torch.float64, device="cuda")
+    gathered = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(gathered, digest)
+    assert all(torch.equal(g, gathered[0]) for g in gathered), "centroids differ between ranks"
+    for i in range(4):
+        exact = st.search(qs[i], k, all_docs=True)
+        ivf_all = st.search(qs[i], k, all_docs=True, ivf=True, probes=24)
+        assert np.array_equal(exact[2][0], ivf_all[2][0]) and np.array_equal(exact[0][0], ivf_all[0][0])
+        ivf_some = st.search(qs[i], k, all_docs=True, ivf=True, probes=4)
+        assert len(np.intersect1d(ivf_some[2][0], exact[2][0])) >= k - 1
     # an unknown document everywhere => nil on every rank, collective still matched
     assert len(st.search(qs[0], k, doc_ids=oracle.doc_ids(S, 10_000, 1))[2][0]) == 0
     ms = st.bench_resident(qs[0], k, 5, all_docs=True)
