@@ -174,7 +174,12 @@ def cpu_reference_run(steps: int, warmup: int, want_seconds: float = 12.0):
     import oracle
     S = oracle.Synth()
     threads = oracle.num_threads()
-    sample = int(os.environ.get("DA_CPU_SAMPLE_ROWS", min(N_ROWS, 400_000)))
+    try:
+        avail_gb = next(int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")) / 1e6
+    except Exception:   # noqa: BLE001
+        avail_gb = 0.0
+    default_sample = 1_000_000 if avail_gb > 64 else 400_000      # 12.3 GB (= configs[1]) when the box has the RAM
+    sample = int(os.environ.get("DA_CPU_SAMPLE_ROWS", min(N_ROWS, default_sample)))
     mat = oracle.gen_rows(S, 0, sample, DIM)
     qs = [oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(max(1, steps + warmup))]
     one = None
@@ -256,8 +261,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    import oracle   # only for the synthetic-corpus parameters, the queries and the cpu_baseline leg
-    from doc_agents_b200 import GpuStore, build
+    from doc_agents_b200 import GpuStore, build, synth   # the GPU arm takes corpus, queries and ids from the product library
 
     build.build()
     torch.cuda.set_device(local_rank)
@@ -282,13 +286,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    S = oracle.Synth()
+    S = synth.Synth()
     lo, hi = shard_range(rank, world, N_ROWS, S.chunks_per_doc)
     st = GpuStore(dim=DIM, capacity_rows=max(1, hi - lo), devices=(local_rank,), min_similarity=MIN_SIM,
                   world_size=world, rank=rank, nccl_id=nccl_id)
     st.generate_synthetic(S, lo, hi - lo)
     n_q = (warmup + steps) * BATCH if BATCH <= 64 else 2 * BATCH
-    queries = np.stack([oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(n_q)])
+    queries = np.stack([synth.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(n_q)])
 
     def qbatch(i):
         lo_ = (i * BATCH) % (n_q - BATCH + 1) if n_q > BATCH else 0
@@ -296,7 +300,7 @@ def main():
 
     n_docs = N_ROWS // S.chunks_per_doc
     skw = dict(all_docs=True) if not FILTER_DOCS else dict(
-        doc_ids=np.stack([oracle.doc_ids(S, d, 1)[0] for d in
+        doc_ids=np.stack([synth.doc_ids(S, d, 1)[0] for d in
                           ([(0 * 37) % S.n_clusters + j * S.n_clusters for j in range(FILTER_DOCS // 2)] +
                            [7 + j * (n_docs // FILTER_DOCS) for j in range(FILTER_DOCS - FILTER_DOCS // 2)])]),
         read_all_rows=READ_ALL)
@@ -357,7 +361,7 @@ def main():
     }
     st.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "cfg3_b1":
-        _, info, _ = cpu_reference_run(steps=3, warmup=1)
+        _, info, _ = cpu_reference_run(steps=8, warmup=1)
         line["cpu_baseline"] = info
     if world > 1:
         dist.destroy_process_group()

@@ -92,6 +92,8 @@ SIGNATURES = {
                                   C.c_void_p, C.c_void_p]),
     "da_store_build_ivf": (C.c_int, [C.c_void_p, C.POINTER(da_ivf_params)]),
     "da_store_generate_synthetic": (C.c_int, [C.c_void_p, C.POINTER(da_synth_params)]),
+    "da_synth_query": (C.c_int, [C.POINTER(da_synth_params), C.c_uint64, C.c_uint64, C.c_uint32, C.c_int32, C.c_void_p]),
+    "da_synth_ids": (C.c_int, [C.POINTER(da_synth_params), C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p]),
     "da_store_stats": (C.c_int, [C.c_void_p, C.POINTER(da_stats)]),
     "da_store_bench_resident": (C.c_int, [C.c_void_p, C.POINTER(da_search_params), C.c_int32,
                                           C.POINTER(C.c_float)]),

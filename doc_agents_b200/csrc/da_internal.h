@@ -149,5 +149,8 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
 
 // Host restatement of the id hash of the synthetic corpus (spec: DESIGN.md).
 void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);
+void synth_vector_host(uint64_t seed_noise, uint64_t noise_index, uint64_t seed_centroid, uint64_t cluster,
+                       int cmul, int nmul, int dim, float *out);
+void synth_id_host(uint64_t seed_ids, int kind, uint64_t index, uint8_t out[16]);
 
 }  // namespace da

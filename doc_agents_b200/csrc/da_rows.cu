@@ -159,6 +159,33 @@ cudaError_t launch_synth(const SynthArgs &a, float *mat, float *inv_norm, uint32
     return cudaGetLastError();
 }
 
+// Host statement of one synthetic vector (queries for benches/tests): same integer-exact spec as synth_kernel.
+void synth_vector_host(uint64_t seed_noise, uint64_t noise_index, uint64_t seed_centroid, uint64_t cluster,
+                       int cmul, int nmul, int dim, float *out)
+{
+    const unsigned long long kn = stream_key(seed_noise, noise_index), kc = stream_key(seed_centroid, cluster);
+    long long ss = 0;
+    for (int c = 0; c < dim; c++) {
+        const unsigned long long hn = mix64(kn + (unsigned long long)((c >> 1) + 1) * kPair);
+        const unsigned long long hc = mix64(kc + (unsigned long long)((c >> 1) + 1) * kPair);
+        const uint32_t wn = (c & 1) ? (uint32_t)(hn >> 32) : (uint32_t)hn;
+        const uint32_t wc = (c & 1) ? (uint32_t)(hc >> 32) : (uint32_t)hc;
+        const int u = cmul * ih4(wc) + nmul * ih4(wn);
+        ss += (long long)u * u;
+        out[c] = (float)u;
+    }
+    if (ss == 0) return;
+    const float mag = (float)sqrt((double)ss);
+    for (int c = 0; c < dim; c++) out[c] /= mag;
+}
+
+void synth_id_host(uint64_t seed_ids, int kind, uint64_t index, uint8_t out[16])
+{
+    unsigned long long a, b;
+    id16(seed_ids, kind == 0 ? 0xC4A9000000000000ull : 0xD0C0000000000000ull, index, a, b);
+    for (int i = 0; i < 8; i++) { out[i] = (uint8_t)(a >> (8 * i)); out[8 + i] = (uint8_t)(b >> (8 * i)); }
+}
+
 void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16])
 {
     unsigned long long a, b;

@@ -1086,6 +1086,24 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
     return DA_OK;
 }
 
+int da_synth_query(const da_synth_params *p, uint64_t seed_query, uint64_t qi, uint32_t cluster, int32_t dim, float *out)
+{
+    if (!p || !out) return fail(DA_ERR_INVALID, "params/out is NULL");
+    if (p->struct_size != sizeof(da_synth_params)) return fail(DA_ERR_INVALID, "da_synth_params.struct_size mismatch");
+    if (dim <= 0) return fail(DA_ERR_DIM, "dim=%d", dim);
+    da::synth_vector_host(seed_query, qi, p->seed_centroid, cluster, p->cmul, p->nmul, dim, out);
+    return DA_OK;
+}
+
+int da_synth_ids(const da_synth_params *p, int32_t kind, uint64_t first, uint64_t n, uint8_t *out)
+{
+    if (!p || (n && !out)) return fail(DA_ERR_INVALID, "params/out is NULL");
+    if (p->struct_size != sizeof(da_synth_params)) return fail(DA_ERR_INVALID, "da_synth_params.struct_size mismatch");
+    if (kind != 0 && kind != 1) return fail(DA_ERR_INVALID, "kind must be 0 (chunk) or 1 (document)");
+    for (uint64_t i = 0; i < n; i++) da::synth_id_host(p->seed_ids, kind, first + i, out + 16 * i);
+    return DA_OK;
+}
+
 int da_store_stats(da_store *st, da_stats *out)
 {
     if (!st || !out) return fail(DA_ERR_INVALID, "store/out is NULL");

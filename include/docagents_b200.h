@@ -155,6 +155,12 @@ typedef struct {
 } da_synth_params;
 int da_store_generate_synthetic(da_store *st, const da_synth_params *p);
 
+/* Host-side pieces of the same synthetic corpus, so benches need nothing but this library: query number `qi`
+ * aimed at `cluster` (noise stream seeded by seed_query), and the 16-byte ids of chunks (kind 0, by global row)
+ * or documents (kind 1, by document index).  p->row_lo / n_rows are ignored.  No GPU involved. */
+int da_synth_query(const da_synth_params *p, uint64_t seed_query, uint64_t qi, uint32_t cluster, int32_t dim, float *out);
+int da_synth_ids(const da_synth_params *p, int32_t kind, uint64_t first, uint64_t n, uint8_t *out);
+
 typedef struct {
     uint32_t struct_size;
     int32_t  dim, n_devices, world_size, rank;

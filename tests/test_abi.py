@@ -102,3 +102,19 @@ def test_product_never_touches_the_oracle():
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f
                 assert "liboracle" not in text and '#include "oracle' not in text, f
+
+
+def test_library_synthetic_queries_and_ids_equal_the_oracle(built_lib):
+    """bench.py takes its queries and ids from the product library (it may not touch oracle/ outside the
+    cpu_baseline leg); they must be the oracle's, bit for bit.  Host-only code: runs without a GPU."""
+    import numpy as np
+    import oracle
+    from doc_agents_b200 import synth
+    for kw in ({}, {"n_clusters": 7, "cmul": 3, "nmul": 2, "seed_query": 99}):
+        so, sp = oracle.Synth(**kw), synth.Synth(**kw)
+        for dim in (3072, 1536, 100, 4):
+            for qi, cl in ((0, 0), (5, 3), (123456, 6)):
+                a, b = oracle.gen_query(so, qi, cl, dim), synth.gen_query(sp, qi, cl, dim)
+                assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        assert np.array_equal(oracle.chunk_ids(so, 12345, 50), synth.chunk_ids(sp, 12345, 50))
+        assert np.array_equal(oracle.doc_ids(so, 0, 50), synth.doc_ids(sp, 0, 50))

@@ -11,8 +11,7 @@ import time
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import oracle
-from doc_agents_b200 import GpuStore
+from doc_agents_b200 import GpuStore, synth as oracle   # corpus parameters and queries from the product library
 
 
 def main():
