@@ -140,7 +140,8 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
                                        const uint32_t *doc_bitmap, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
-                                       uint32_t *gate_ordered, uint32_t *overflow, cudaStream_t stream);
+                                       uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
+                                       cudaStream_t stream);
 cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_count, int cap, const uint32_t *gate_ordered,
                                   key_t64 *surv, uint32_t *surv_count, uint32_t *overflow, int batch,
                                   const float *mat, int dim, const float *inv_norm, const float *queries,

@@ -118,7 +118,7 @@ struct Shard {
     DevBuf<uint32_t> d_bitmap;
     DevBuf<uint8_t> d_out, d_gather, d_final;
     DevBuf<unsigned long long> d_cand;          // batched tensor-core path: candidate lists
-    DevBuf<uint32_t> d_cand_count, d_overflow, d_hist, d_gate, d_surv_count;
+    DevBuf<uint32_t> d_cand_count, d_overflow, d_hist, d_gate, d_surv_count, d_group_sync;
     DevBuf<unsigned long long> d_surv;
     PinBuf<uint32_t> h_overflow;
     da::key_t64 *d_cta = nullptr;
@@ -207,7 +207,7 @@ void free_shard(Shard &s)
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
-    s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release();
+    s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release(); s.d_group_sync.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
     s.h_up_rows.release(); s.h_up_slots.release(); s.h_up_ids.release();
@@ -322,7 +322,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_qinv.p, s.mat, s.n_rows, dim, s.inv_norm,
                                               s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.k, pl.min_sim,
                                               da::kTf32Eps, s.sm_count, s.d_cand.p, s.d_cand_count.p, s.d_hist.p,
-                                              s.d_gate.p, s.d_overflow.p, s.stream));
+                                              s.d_gate.p, s.d_overflow.p, s.d_group_sync.p, s.stream));
             CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), s.d_gate.p, s.d_surv.p,
                                          s.d_surv_count.p, s.d_overflow.p, pl.batch, s.mat, dim, s.inv_norm, s.d_queries.p,
                                          s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream));
@@ -432,6 +432,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             CU(s.d_cand_count.ensure(p->batch)); CU(s.d_gate.ensure(p->batch)); CU(s.d_surv_count.ensure(p->batch));
             CU(s.d_hist.ensure(da::tc_batch_hist_words(p->batch)));
             CU(s.d_surv.ensure((size_t)p->batch * da::kSurvivorCap));
+            CU(s.d_group_sync.ensure(1024));
             CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));
             CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
             *s.h_overflow.p = 0;

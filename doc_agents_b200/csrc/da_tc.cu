@@ -264,6 +264,7 @@ struct BatchArgs {
     uint32_t *cand_count;       // [batch]
     uint32_t *hist;             // [batch][64 coarse + 4096 fine]
     uint32_t *overflow;         // set to 1 if a query list ran out of room
+    uint32_t *group_sync;       // [n_groups] row tiles started by the members of a group (zeroed per launch)
 };
 constexpr int kHistWords = 64 + 64 * 64;
 
@@ -356,6 +357,15 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int t = t_begin; t < t_end; t++) {
+                if (a.group > 1) {
+                    // Lockstep within the group: start row tile i only when every member has started tile i-1, so at
+                    // most two row tiles per group are live in L2 (members that drift apart would each pull their own
+                    // copy from HBM and push the others' out).  All CTAs are co-resident (cooperative launch).
+                    const uint32_t need = (uint32_t)a.group * (uint32_t)(t - t_begin);
+                    volatile uint32_t *ctr = a.group_sync + grp;
+                    while (*ctr < need) __nanosleep(200);
+                    atomicAdd(a.group_sync + grp, 1u);
+                }
                 for (int mt = member; mt < m_tiles; mt += a.group) {
                     for (int kb = 0; kb < kb_count; kb++) {
                         mbar_wait(bar_empty + 8 * stage, phase ^ 1);
@@ -579,7 +589,8 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
                                        const uint32_t *doc_bitmap, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
-                                       uint32_t *gate_ordered, uint32_t *overflow, cudaStream_t stream)
+                                       uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
+                                       cudaStream_t stream)
 {
     if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
     if (batch > DA_TC_MAX_BATCH) return cudaErrorInvalidValue;
@@ -606,15 +617,25 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     const int m_tiles = tc_batch_m_tiles(batch);
     const double tile_mb = (double)TC_BN * D * 4 / 1e6, q_mb = (double)batch * D * 4 / 1e6;
     int group = 1;
-    while (group < m_tiles && group < sm_count && (sm_count / group) * tile_mb + q_mb > 60.0) group++;
+    while (group < m_tiles && group < sm_count && 2.0 * (sm_count / group) * tile_mb + q_mb > 90.0) group++;   // two live row tiles per group (lockstep window)
     if (group > m_tiles) group = m_tiles;
     int n_groups = sm_count / group;
     if ((uint32_t)n_groups > n_tiles) n_groups = (int)n_tiles;
     if (n_groups < 1) n_groups = 1;
     a.group = group;
+    a.group_sync = group_sync;
     const uint32_t grid = (uint32_t)(n_groups * group);
-    tc_batch_candidates_kernel<<<grid, TC_THREADS, TCB_SMEM_BYTES, stream>>>(map_q, map_x, a);
-    e = cudaGetLastError();
+    if (group > 1) {
+        // members of a group wait for each other: every CTA must be resident, which a cooperative launch guarantees
+        e = cudaMemsetAsync(group_sync, 0, (size_t)n_groups * 4, stream);
+        if (e != cudaSuccess) return e;
+        void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a};
+        e = cudaLaunchCooperativeKernel((const void *)tc_batch_candidates_kernel, dim3(grid), dim3(TC_THREADS), args,
+                                        TCB_SMEM_BYTES, stream);
+    } else {
+        tc_batch_candidates_kernel<<<grid, TC_THREADS, TCB_SMEM_BYTES, stream>>>(map_q, map_x, a);
+        e = cudaGetLastError();
+    }
     if (e != cudaSuccess) return e;
     batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a.floor_eps, a.two_eps, gate_ordered);
     return cudaGetLastError();
