@@ -173,7 +173,7 @@ def cpu_reference_run(steps: int, warmup: int, want_seconds: float = 12.0):
     bounded sample of the workload.  Returns (queries/s extrapolated to N_ROWS, info dict, ms_per_step)."""
     import oracle
     S = oracle.Synth()
-    threads = oracle.num_threads()
+    threads = int(os.environ.get("DA_CPU_THREADS", 0)) or oracle.num_threads()
     try:
         avail_gb = next(int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")) / 1e6
     except Exception:   # noqa: BLE001
