@@ -263,11 +263,16 @@ def main():
     import torch.distributed as dist
     from doc_agents_b200 import GpuStore, build, synth   # the GPU arm takes corpus, queries and ids from the product library
 
-    build.build()
     torch.cuda.set_device(local_rank)
     nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        if local_rank == 0:
+            build.build()          # one builder per node; the others wait for the library
+        dist.barrier()
+    else:
+        build.build()
+    if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idt = torch.tensor(list(GpuStore.nccl_unique_id()), dtype=torch.uint8, device="cuda")

@@ -8,6 +8,13 @@ import oracle
 from cases import ABS_TOL, REL_TOL, Case, check_against_oracle
 from doc_agents_b200 import GpuStore
 
+
+@pytest.fixture(autouse=True, scope="module")
+def _built(built_lib):
+    """Compile the CUDA library once if it is stale (the GPU box normally receives it pre-built)."""
+    return built_lib
+
+
 pytestmark = pytest.mark.gpu
 
 

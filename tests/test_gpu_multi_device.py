@@ -10,6 +10,13 @@ import oracle
 from doc_agents_b200 import GpuStore
 from gpu_util import device_count
 
+
+@pytest.fixture(autouse=True, scope="module")
+def _built(built_lib):
+    """Compile the CUDA library once if it is stale (the GPU box normally receives it pre-built)."""
+    return built_lib
+
+
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(device_count() < 2, reason="needs 2 GPUs in one process")]
 
 S = oracle.Synth(n_clusters=8)

@@ -15,6 +15,13 @@ from doc_agents_b200 import Chunk, Embedding, GpuStore, StoreError, Summary, cal
 from doc_agents_b200 import _lib as L
 from gpu_util import S0, device_count, doc_filter, ids_for, load_case
 
+
+@pytest.fixture(autouse=True, scope="module")
+def _built(built_lib):
+    """Compile the CUDA library once if it is stale (the GPU box normally receives it pre-built)."""
+    return built_lib
+
+
 pytestmark = pytest.mark.gpu
 
 GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "topk_cases.json")))

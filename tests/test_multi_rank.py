@@ -67,7 +67,7 @@ def test_merge_candidates_tie_rule():
 
 @pytest.mark.gpu
 @pytest.mark.skipif(device_count() < 2, reason="needs 2 GPUs")
-def test_two_ranks_under_torchrun_match_the_oracle():
+def test_two_ranks_under_torchrun_match_the_oracle(built_lib):      # the library is built once, before the ranks start
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
            "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tests", "mr_check.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)

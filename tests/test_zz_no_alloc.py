@@ -18,6 +18,13 @@ import oracle
 from doc_agents_b200 import GpuStore
 from doc_agents_b200 import _lib as L
 
+
+@pytest.fixture(autouse=True, scope="module")
+def _built(built_lib):
+    """Compile the CUDA library once if it is stale (the GPU box normally receives it pre-built)."""
+    return built_lib
+
+
 pytestmark = pytest.mark.gpu
 
 
