@@ -51,7 +51,8 @@ class da_search_params(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("flags", C.c_uint32),
                 ("doc_ids", C.c_void_p), ("n_docs", C.c_size_t),
                 ("queries", C.c_void_p), ("batch", C.c_int32), ("dim", C.c_int32),
-                ("k", C.c_int32), ("min_similarity", C.c_float), ("ivf_probes", C.c_int32)]
+                ("k", C.c_int32), ("min_similarity", C.c_float), ("ivf_probes", C.c_int32),
+                ("doc_offsets", C.c_void_p)]
 
 
 class da_ivf_params(C.Structure):

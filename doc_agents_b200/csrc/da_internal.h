@@ -54,6 +54,7 @@ struct ScanArgs {
     const uint32_t *doc_slot;      // document slot of each row
     const uint8_t *chunk_ids;      // 16 bytes per row
     const uint32_t *doc_bitmap;    // bit per document slot; nullptr = every document
+    uint32_t bitmap_stride;        // words between the bitmaps of consecutive queries; 0 = one bitmap for all
     const float *queries;          // nq x dim (device)
     const float *q_inv_norm;       // nq
     const uint32_t *row_list;      // optional: scan only these rows (IVF probe lists); nullptr = [0,n_rows)
@@ -138,7 +139,7 @@ int tc_batch_m_tiles(int batch);
 size_t tc_batch_hist_words(int batch);
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
-                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int sm_count,
+                                       const uint32_t *doc_bitmap, uint32_t bitmap_stride, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
                                        uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
                                        cudaStream_t stream);

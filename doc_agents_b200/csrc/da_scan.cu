@@ -135,17 +135,26 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         uint32_t my_row = row0 + lane;
         bool valid = (lane < R) && (my_row < n_rows);
         if (INDIRECT) my_row = valid ? a.row_list[my_row] : 0u;
-        bool wanted = valid;
+        uint32_t want_bits = 0u;                 // bit q: this lane's row is requested by query q
         float my_inv = 0.f;
         if (valid) {
             my_inv = a.inv_norm[my_row];
             if (a.doc_bitmap) {
-                uint32_t slot = a.doc_slot[my_row];
-                wanted = (a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u;
+                const uint32_t slot = a.doc_slot[my_row];
+                if (a.bitmap_stride == 0) {
+                    want_bits = ((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u) ? 0xFFFFFFFFu : 0u;
+                } else {
+#pragma unroll
+                    for (int q = 0; q < NQ; q++)
+                        if (q < a.nq)
+                            want_bits |= ((a.doc_bitmap[(size_t)q * a.bitmap_stride + (slot >> 5)] >> (slot & 31)) & 1u) << q;
+                }
+            } else {
+                want_bits = 0xFFFFFFFFu;
             }
         }
         const uint32_t valid_mask = __ballot_sync(0xFFFFFFFFu, valid);
-        const uint32_t want_mask = __ballot_sync(0xFFFFFFFFu, wanted);
+        const uint32_t want_mask = __ballot_sync(0xFFFFFFFFu, want_bits != 0u);
         const uint32_t load_mask = a.read_all ? valid_mask : want_mask;
         if (load_mask == 0) continue;
         my_rows_read += __popc(load_mask);
@@ -217,9 +226,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         for (int r = 0; r < R; r++) {
             const float inv = __shfl_sync(0xFFFFFFFFu, my_inv, r);
             const uint32_t row = INDIRECT ? __shfl_sync(0xFFFFFFFFu, my_row, r) : row0 + r;
-            if (!((want_mask >> r) & 1u) || !(inv > 0.f)) continue;     // zero-norm rows never match
+            const uint32_t wb = __shfl_sync(0xFFFFFFFFu, want_bits, r);
+            if (!wb || !(inv > 0.f)) continue;                          // zero-norm rows never match
 #pragma unroll
             for (int q = 0; q < NQ; q++) {
+                if (!((wb >> q) & 1u)) continue;                        // not in this query's document set
                 float sim = acc[r][q] * inv * q_inv_s[q];
                 sim = fminf(1.f, fmaxf(-1.f, sim));                     // pgvector clamps to [-1, 1]
                 if (!(sim >= a.min_sim)) continue;                      // also drops NaN

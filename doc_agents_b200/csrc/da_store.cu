@@ -265,6 +265,7 @@ struct SearchPlan {
     bool ivf;
     int probes;
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
+    uint32_t bitmap_stride;   // words between per-query bitmaps; 0 = one document set for the batch
 };
 
 // Enqueue one complete search on every local shard: scan passes, collective, merge.
@@ -302,7 +303,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                                          s.ivf.n_probe, s.stream));
                 da::ScanArgs a{};
                 a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
-                a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p;
+                a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p + (size_t)q * pl.bitmap_stride;
                 a.queries = c.queries; a.q_inv_norm = c.q_inv_norm;
                 a.row_list = s.ivf.probe_rows; a.n_rows_dev = s.ivf.n_probe; a.n_rows = 0; a.row_base = s.row_base;
                 a.dim = dim; a.nq = 1; a.k = pl.k; a.min_sim = pl.min_sim; a.read_all = pl.read_all ? 1 : 0;
@@ -320,7 +321,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         }
         if (pl.use_tc) {
             CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_qinv.p, s.mat, s.n_rows, dim, s.inv_norm,
-                                              s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.k, pl.min_sim,
+                                              s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.bitmap_stride, pl.k, pl.min_sim,
                                               da::kTf32Eps, s.sm_count, s.d_cand.p, s.d_cand_count.p, s.d_hist.p,
                                               s.d_gate.p, s.d_overflow.p, s.d_group_sync.p, s.stream));
             CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), s.d_gate.p, s.d_surv.p,
@@ -336,7 +337,8 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         for (int q0 = 0; q0 < pl.batch; q0 += nq_max) {
             da::ScanArgs a{};
             a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
-            a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p;
+            a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p + (size_t)q0 * pl.bitmap_stride;
+            a.bitmap_stride = pl.bitmap_stride;
             a.queries = s.d_queries.p + (size_t)q0 * dim;
             a.q_inv_norm = s.d_qinv.p + q0;
             a.row_list = nullptr;
@@ -404,13 +406,27 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         pl.probes = std::max(1, std::min(probes, std::min(st->ivf_lists, DA_IVF_MAX_PROBES)));
     }
 
-    // document filter -> bit per slot (document_id = ANY($2): postgres.go:239); unknown ids match nothing
-    std::vector<uint32_t> bitmap;
+    // document filter -> bit per slot (document_id = ANY($2): postgres.go:239); unknown ids match nothing.
+    // With doc_offsets every query has its own set: one bitmap per query, bitmap_words apart.
+    const bool per_query = !all_docs && p->doc_offsets != nullptr;
+    if (per_query) {
+        if (p->doc_offsets[0] != 0 || p->doc_offsets[p->batch] != p->n_docs)
+            return fail(DA_ERR_INVALID, "doc_offsets must start at 0 and end at n_docs");
+        for (int q = 0; q < p->batch; q++)
+            if (p->doc_offsets[q] > p->doc_offsets[q + 1]) return fail(DA_ERR_INVALID, "doc_offsets must not decrease");
+    }
+    pl.bitmap_stride = per_query ? (uint32_t)pl.bitmap_words : 0u;
+    std::vector<uint32_t> bitmap, uni;
     if (!all_docs) {
-        bitmap.assign(pl.bitmap_words, 0u);
+        bitmap.assign(pl.bitmap_words * (per_query ? (size_t)p->batch : 1), 0u);
+        uni.assign(pl.bitmap_words, 0u);
+        int q = 0;
         for (size_t i = 0; i < p->n_docs; i++) {
+            if (per_query) while (i >= p->doc_offsets[q + 1]) q++;
             auto it = st->doc_slot_of.find(load_id(p->doc_ids + 16 * i));
-            if (it != st->doc_slot_of.end()) bitmap[it->second >> 5] |= 1u << (it->second & 31);
+            if (it == st->doc_slot_of.end()) continue;
+            bitmap[(per_query ? (size_t)q * pl.bitmap_words : 0) + (it->second >> 5)] |= 1u << (it->second & 31);
+            uni[it->second >> 5] |= 1u << (it->second & 31);
         }
     }
     if (pl.k == 0) return DA_OK;
@@ -419,8 +435,8 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (!ivf && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16) {
         size_t selected = st->docs.size();
         if (!all_docs) {
-            selected = 0;
-            for (uint32_t w : bitmap) selected += (size_t)__builtin_popcount(w);
+            selected = 0;                              // documents requested by at least one query
+            for (uint32_t w : uni) selected += (size_t)__builtin_popcount(w);
         }
         pl.use_tc = selected * 4 >= st->docs.size() && selected > 0;
     }
@@ -444,9 +460,9 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         memcpy(s.h_queries.p, p->queries, nq_elems * sizeof(float));
         CU(cudaMemcpyAsync(s.d_queries.p, s.h_queries.p, nq_elems * sizeof(float), cudaMemcpyHostToDevice, s.stream));
         if (!all_docs) {
-            CU(s.d_bitmap.ensure(pl.bitmap_words)); CU(s.h_bitmap.ensure(pl.bitmap_words));
-            memcpy(s.h_bitmap.p, bitmap.data(), pl.bitmap_words * 4);
-            CU(cudaMemcpyAsync(s.d_bitmap.p, s.h_bitmap.p, pl.bitmap_words * 4, cudaMemcpyHostToDevice, s.stream));
+            CU(s.d_bitmap.ensure(bitmap.size())); CU(s.h_bitmap.ensure(bitmap.size()));
+            memcpy(s.h_bitmap.p, bitmap.data(), bitmap.size() * 4);
+            CU(cudaMemcpyAsync(s.d_bitmap.p, s.h_bitmap.p, bitmap.size() * 4, cudaMemcpyHostToDevice, s.stream));
         }
         CU(da::launch_query_inv_norm(s.d_queries.p, st->dim, p->batch, s.d_qinv.p, s.stream));
         st->launches++;
@@ -795,12 +811,13 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
 }
 
 static int topk_direct(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *queries, int32_t batch,
-                       int32_t dim, int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n)
+                       int32_t dim, int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n,
+                       const uint64_t *doc_offsets = nullptr)
 {
     da_search_params p{};
     p.struct_size = sizeof p;
     p.flags = 0;
-    p.doc_ids = doc_ids; p.n_docs = n_docs;
+    p.doc_ids = doc_ids; p.n_docs = n_docs; p.doc_offsets = doc_offsets;
     p.queries = queries; p.batch = batch; p.dim = dim;
     p.k = k;
     p.min_similarity = st->min_sim;
@@ -831,26 +848,29 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
         st->bleader = true;
         const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(st->batch_window_us);
         while (st->bqueue.size() < st->batch_max && st->bcv.wait_until(lk, deadline) != std::cv_status::timeout) {}
-        // group = queued calls with the same document list as the oldest one
-        da_store::Pending *head = st->bqueue.front();
+        // group = the oldest queued calls, each keeping its own document set (per-query masks on the device)
         std::vector<da_store::Pending *> group, rest;
         for (da_store::Pending *r : st->bqueue) {
-            const bool same = r->n_docs == head->n_docs &&
-                              (r->n_docs == 0 || r->doc_ids == head->doc_ids ||
-                               memcmp(r->doc_ids, head->doc_ids, 16 * r->n_docs) == 0);
-            if (same && group.size() < st->batch_max) group.push_back(r); else rest.push_back(r);
+            if (group.size() < st->batch_max) group.push_back(r); else rest.push_back(r);
         }
         st->bqueue.swap(rest);
         st->topk_passes++;
         lk.unlock();
         int kmax = 0;
-        for (da_store::Pending *r : group) kmax = std::max(kmax, r->k);
+        size_t total_docs = 0;
+        for (da_store::Pending *r : group) { kmax = std::max(kmax, r->k); total_docs += r->n_docs; }
         const size_t g = group.size();
         std::vector<float> qs(g * (size_t)dim), sc(g * (size_t)kmax);
-        std::vector<uint8_t> ids(g * (size_t)kmax * 16);
+        std::vector<uint8_t> ids(g * (size_t)kmax * 16), docs(total_docs * 16 + 16);
+        std::vector<uint64_t> offs(g + 1, 0);
         std::vector<int32_t> cnt(g);
-        for (size_t i = 0; i < g; i++) memcpy(&qs[i * dim], group[i]->query, (size_t)dim * 4);
-        const int rc = topk_direct(st, head->doc_ids, head->n_docs, qs.data(), (int32_t)g, dim, kmax, ids.data(), sc.data(), cnt.data());
+        for (size_t i = 0; i < g; i++) {
+            memcpy(&qs[i * dim], group[i]->query, (size_t)dim * 4);
+            if (group[i]->n_docs) memcpy(&docs[16 * offs[i]], group[i]->doc_ids, 16 * group[i]->n_docs);
+            offs[i + 1] = offs[i] + group[i]->n_docs;
+        }
+        const int rc = topk_direct(st, docs.data(), total_docs, qs.data(), (int32_t)g, dim, kmax, ids.data(), sc.data(),
+                                   cnt.data(), offs.data());
         const std::string err = rc == DA_OK ? std::string() : g_err;
         for (size_t i = 0; i < g; i++) {            // a smaller k is a prefix of the batch's top-kmax
             da_store::Pending *r = group[i];

@@ -247,7 +247,7 @@ __global__ void gather_rows_kernel(const float *mat, int D, const uint32_t *rows
 // re-scores the rest in fp32 with the scan kernel's arithmetic; a third selects the top-k.
 // ---------------------------------------------------------------------------
 constexpr int TCB_MAX_MTILES = DA_TC_MAX_BATCH / TC_BM;   // 32
-constexpr uint32_t TCB_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 + 256 + 2 * TC_BN * 4 + TCB_MAX_MTILES * TC_BM * 4;
+constexpr uint32_t TCB_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 + 256 + 4 * TC_BN * 4 + TCB_MAX_MTILES * TC_BM * 4;
 
 struct BatchArgs {
     uint32_t n_rows;            // rows resident on this shard
@@ -259,6 +259,7 @@ struct BatchArgs {
     const float *inv_norm;      // per row
     const uint32_t *doc_slot;   // per row (with doc_bitmap)
     const uint32_t *doc_bitmap; // nullptr = every document
+    uint32_t bitmap_stride;     // words between consecutive queries' bitmaps; 0 = one shared bitmap
     const float *q_inv;         // per query
     unsigned long long *cand;   // [batch][cap]   ordered(score) << 32 | local row
     uint32_t *cand_count;       // [batch]
@@ -325,7 +326,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const uint32_t tmem_slot = bar_tempty + 16;
     volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
     float *s_inv = reinterpret_cast<float *>(smem_raw + (bars + 256 - smem_u32(smem_raw)));   // [2][TC_BN]
-    float *gate_s = s_inv + 2 * TC_BN;                                                        // [m_tiles][128]
+    uint32_t *s_slot = reinterpret_cast<uint32_t *>(s_inv + 2 * TC_BN);                        // [2][TC_BN], per-query masks only
+    float *gate_s = s_inv + 4 * TC_BN;                                                        // [m_tiles][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tiles = (a.batch + TC_BM - 1) / TC_BM;
@@ -415,19 +417,23 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
             const uint32_t n0 = (uint32_t)t * TC_BN;
             // per-row factor for this row tile: 1/|row|, or 0 when the row is absent, zero or filtered out
             float *inv_t = s_inv + (t & 1) * TC_BN;
+            uint32_t *slot_t = s_slot + (t & 1) * TC_BN;
+            const bool per_query = a.doc_bitmap && a.bitmap_stride;     // each query has its own document set
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int j = etid + h * 128;
                 const uint32_t row = n0 + (uint32_t)j;
                 float f = 0.f;
+                uint32_t slot = 0;
                 if (row < a.n_rows) {
                     f = a.inv_norm[row];
                     if (a.doc_bitmap) {
-                        const uint32_t slot = a.doc_slot[row];
-                        if (!((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u)) f = 0.f;
+                        slot = a.doc_slot[row];
+                        if (!per_query && !((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u)) f = 0.f;
                     }
                 }
                 inv_t[j] = f;
+                slot_t[j] = slot;
             }
             // tighten this thread's gates from the shared histograms: often at first, then every 16 row tiles
             if (visited == next_refresh) {
@@ -448,6 +454,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 const bool q_valid = q < (uint32_t)a.batch;
                 const float qinv = q_valid ? a.q_inv[q] : 0.f;
                 const float gate = gate_s[mt * TC_BM + qlocal];
+                // per-query document sets are tested lazily, only for the few rows that pass the gate
+                const uint32_t *qmask = (per_query && q_valid) ? a.doc_bitmap + (size_t)q * a.bitmap_stride : nullptr;
                 unsigned long long *lst = a.cand + (size_t)q * a.cap;
                 uint32_t *hq = a.hist + (size_t)q * kHistWords;
                 mbar_wait(bar_tfull + 8 * as, aphase);
@@ -463,7 +471,9 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                     for (int j = 0; j < 32; j++) {
                         const float f = inv_t[c * 32 + j];
                         const float v = __uint_as_float(r[j]) * f * qinv;
-                        n_pass += (f > 0.f && v >= gate) ? 1u : 0u;
+                        bool ok = f > 0.f && v >= gate;
+                        if (ok && qmask) { const uint32_t sl = slot_t[c * 32 + j]; ok = (qmask[sl >> 5] >> (sl & 31)) & 1u; }
+                        n_pass += ok ? 1u : 0u;
                     }
                 }
                 if (!q_valid) n_pass = 0;
@@ -480,7 +490,9 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                             for (int j = 0; j < 32; j++) {
                                 const float f = inv_t[c * 32 + j];
                                 const float v = __uint_as_float(r[j]) * f * qinv;
-                                if (f > 0.f && v >= gate) {
+                                bool ok = f > 0.f && v >= gate;
+                                if (ok && qmask) { const uint32_t sl = slot_t[c * 32 + j]; ok = (qmask[sl >> 5] >> (sl & 31)) & 1u; }
+                                if (ok) {
                                     if (pos < (uint32_t)a.cap) {
                                         lst[pos] = ((unsigned long long)score_to_ordered(v) << 32) | (unsigned long long)(n0 + c * 32 + j);
                                         int hc, hf;
@@ -587,7 +599,7 @@ size_t tc_batch_hist_words(int batch) { return (size_t)batch * kHistWords; }
 
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
-                                       const uint32_t *doc_bitmap, int k, float min_sim, float eps, int sm_count,
+                                       const uint32_t *doc_bitmap, uint32_t bitmap_stride, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
                                        uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
                                        cudaStream_t stream)
@@ -604,7 +616,7 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     BatchArgs a{};
     a.n_rows = n_rows; a.K = D; a.batch = batch; a.k = k; a.cap = tc_batch_cap(k);
     a.floor_eps = min_sim - eps; a.two_eps = 2.f * eps;
-    a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.q_inv = q_inv;
+    a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
     a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
     e = cudaFuncSetAttribute(tc_batch_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
     if (e != cudaSuccess) return e;

@@ -198,7 +198,8 @@ class GpuStore:
     def search(self, queries, k: int, doc_ids: np.ndarray | None = None, *, all_docs: bool = False,
                min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
                probes: int = 0, no_tensor: bool = False):
-        """queries: dim or batch x dim.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
+        """queries: dim or batch x dim.  doc_ids: one n x 16 array for the whole batch, or a list with one
+        array per query.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
@@ -220,8 +221,18 @@ class GpuStore:
         p.struct_size = C.sizeof(L.da_search_params)
         p.flags = (L.DA_SEARCH_ALL_DOCS if all_docs else 0) | (L.DA_SEARCH_READ_ALL_ROWS if read_all_rows else 0) \
             | (L.DA_SEARCH_IVF if ivf else 0) | (L.DA_SEARCH_NO_TENSOR if no_tensor else 0)
-        d = None
-        if doc_ids is not None:
+        d = offs = None
+        if isinstance(doc_ids, (list, tuple)):                      # one document set per query
+            assert len(doc_ids) == q.shape[0]
+            parts = [np.ascontiguousarray(x, dtype=np.uint8).reshape(-1, 16) for x in doc_ids]
+            offs = np.zeros(len(parts) + 1, dtype=np.uint64)
+            offs[1:] = np.cumsum([x.shape[0] for x in parts])
+            d = np.concatenate(parts) if parts else np.zeros((0, 16), np.uint8)
+            d = np.ascontiguousarray(np.concatenate([d, np.zeros((1, 16), np.uint8)]))   # never a NULL pointer
+            p.doc_ids = d.ctypes.data
+            p.n_docs = int(offs[-1])
+            p.doc_offsets = offs.ctypes.data
+        elif doc_ids is not None:
             d = np.ascontiguousarray(doc_ids, dtype=np.uint8).reshape(-1, 16)
             p.doc_ids = _ptr(d)
             p.n_docs = d.shape[0]
@@ -232,7 +243,7 @@ class GpuStore:
         ms = self.min_similarity if min_similarity is None else min_similarity
         p.min_similarity = -math.inf if ms is None else ms
         p.ivf_probes = probes
-        return p, (q, d)
+        return p, (q, d, offs)
 
     def bench_resident(self, queries, k: int, iters: int, doc_ids=None, *, all_docs=False,
                        min_similarity=None, read_all_rows=False, ivf=False, probes=0, no_tensor=False) -> float:

@@ -68,8 +68,9 @@ typedef struct {
     uint8_t  nccl_id[DA_NCCL_ID_BYTES];   /* from da_nccl_unique_id on rank 0, same on all ranks */
     uint32_t flags;                 /* reserved, 0 */
     /* Request batching for da_store_topk (0 = off).  Concurrent calls -- one goroutine per
-     * /api/query, cmd/query/main.go:34 -- that arrive within batch_window_us of each other and ask for the same
-     * document set are answered by ONE batched pass over the corpus (at most batch_max, default 64, calls). */
+     * /api/query, cmd/query/main.go:34 -- that arrive within batch_window_us of each other
+     * are answered by ONE batched pass over the corpus (at most batch_max, default 64, calls), each call keeping
+     * its own document set. */
     uint32_t batch_window_us;
     uint32_t batch_max;
 } da_config;
@@ -110,8 +111,8 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
 #define DA_SEARCH_NO_TENSOR     0x10u /* keep a batch of >= 16 queries on the fp32 SIMT scan (default: tcgen05 TF32
                                          candidate generation + exact fp32 re-score; results are identical) */
 
-/* Same query as da_store_topk with every knob exposed, batched: `batch` queries share one
- * doc filter (one /api/query has one document set: cmd/query/main.go:20-24). */
+/* Same query as da_store_topk with every knob exposed, batched: `batch` queries share one doc filter
+ * (one /api/query has one document set: cmd/query/main.go:20-24) or carry one each (doc_offsets). */
 typedef struct {
     uint32_t struct_size;
     uint32_t flags;
@@ -120,6 +121,10 @@ typedef struct {
     int32_t k;
     float   min_similarity;  /* use -INFINITY for "no floor" */
     int32_t ivf_probes;      /* DA_SEARCH_IVF only; 0 = store default */
+    /* Optional per-query document sets (what merged /api/query requests need: each request names its own
+     * documents): query i asks for doc_ids[doc_offsets[i] .. doc_offsets[i+1]), doc_offsets has batch+1
+     * entries and n_docs == doc_offsets[batch].  NULL: one set shared by the whole batch. */
+    const uint64_t *doc_offsets;
 } da_search_params;
 
 /* Outputs are batch x k (row-major); out_n is batch counts; out_rows (optional, may be NULL)

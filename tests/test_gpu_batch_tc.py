@@ -76,3 +76,38 @@ def test_tensor_batch_small_corpus_and_padding_queries():
         qs = np.stack([oracle.gen_query(S, i, i % 2, dim) for i in range(17)])
         _compare(st, qs, 5, all_docs=True)
         _compare(st, qs, 128, all_docs=True, min_similarity=-np.inf)
+
+
+@pytest.mark.parametrize("batch", [3, 9, 24, 150])
+def test_per_query_document_sets_equal_single_searches(batch):
+    """Each query of a batch names its own documents (what merged /api/query requests need): SIMT passes
+    (batch < 16) and the tensor path (lazy per-query mask in the epilogue) against one search per query."""
+    S = oracle.Synth(n_clusters=8)
+    n, dim, k = 24_000, 1536, 10
+    n_docs = n // 200
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S, 0, n)
+        docs = oracle.doc_ids(S, 0, n_docs)
+        rng = np.random.default_rng(batch)
+        qs = np.stack([oracle.gen_query(S, i, i % 8, dim) for i in range(batch)])
+        sets = []
+        for i in range(batch):
+            if i % 7 == 3:
+                pick = np.zeros(0, dtype=np.int64)                             # an empty set: nil for that query
+            elif i % 5 == 0:
+                pick = np.arange(i % 8, n_docs, 8)                            # exactly the query's cluster
+            else:
+                pick = np.sort(rng.choice(n_docs, size=int(rng.integers(n_docs // 3, n_docs)), replace=False))
+            sets.append(docs[pick])
+        got = st.search(qs, k, sets)
+        path_rows = st.stats().last_rows_read
+        for i in range(batch):
+            one = st.search(qs[i], k, sets[i])
+            assert np.array_equal(got[2][i], one[2][0]), (i, got[2][i], one[2][0])
+            assert np.array_equal(got[1][i].view(np.uint32), one[1][0].view(np.uint32)), i
+            assert np.array_equal(got[0][i], one[0][0]), i
+        if batch >= 16:
+            assert path_rows == n                                              # union is wide: tensor path
+            simt = st.search(qs, k, sets, no_tensor=True)
+            for i in range(batch):
+                assert np.array_equal(got[2][i], simt[2][i])

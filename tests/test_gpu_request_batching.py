@@ -1,6 +1,6 @@
 """GPU test of request batching: concurrent da_store_topk calls, as the query agent
 issues them from one goroutine per HTTP request (cmd/query/main.go:34), are merged into batched passes
-when they ask for the same document set -- with results identical to unbatched calls."""
+-- each call keeping its own document set -- with results identical to unbatched calls."""
 import threading
 import uuid
 
@@ -59,7 +59,7 @@ def test_concurrent_topk_calls_are_batched_and_results_unchanged():
             assert len(got[i]) <= ks[i]
         s = batched.stats()
         assert s.topk_calls == n_threads
-        assert s.topk_passes < n_threads // 2, (s.topk_calls, s.topk_passes)        # calls were merged
+        assert s.topk_passes <= n_threads // 8, (s.topk_calls, s.topk_passes)       # calls with DIFFERENT document sets merged too
         # errors still reach the caller that caused them
         with pytest.raises(Exception):
             batched.TopK(docs_a, qs[0][:100], 5)
