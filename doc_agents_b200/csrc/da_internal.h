@@ -92,6 +92,11 @@ cudaError_t launch_finalize_rows(const float *mat, int dim, const uint32_t *rows
                                  const uint8_t *ids, uint32_t n, float *inv_norm, uint32_t *doc_slot,
                                  uint8_t *chunk_ids, cudaStream_t stream);
 cudaError_t launch_query_inv_norm(const float *queries, int dim, int nq, float *out, cudaStream_t stream);
+cudaError_t launch_validate_stage(const float *stage, uint64_t n_floats, uint64_t base, unsigned long long *first_bad,
+                                  cudaStream_t stream);
+cudaError_t launch_commit_rows(const float *stage, int dim, const uint32_t *rows, const uint32_t *slots, const uint8_t *ids,
+                               uint32_t n, float *mat, float *inv_norm, uint32_t *doc_slot, uint8_t *chunk_ids,
+                               cudaStream_t stream);
 
 struct SynthArgs {
     uint64_t seed_data, seed_centroid, seed_ids;

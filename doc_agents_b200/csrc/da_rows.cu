@@ -45,6 +45,51 @@ __global__ void finalize_rows_kernel(const float *mat, int dim, const uint32_t *
     }
 }
 
+// Finite check of staged vectors on the device (pgvector rejects NaN/Inf at insert): smallest flat index of a
+// non-finite element, or ~0 if all are finite.
+__global__ void validate_stage_kernel(const float *stage, unsigned long long n_floats, unsigned long long base,
+                                      unsigned long long *first_bad)
+{
+    const unsigned long long n4 = n_floats >> 2;
+    unsigned long long bad = ~0ull;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n4;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint4 v = reinterpret_cast<const uint4 *>(stage)[i];
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if ((w[j] & 0x7F800000u) == 0x7F800000u && base + i * 4 + j < bad) bad = base + i * 4 + j;
+    }
+    if (bad != ~0ull) atomicMin(first_bad, bad);
+}
+
+// Staged rows -> their final rows, with 1/|row|, document slot and chunk id: one warp per row, one pass.
+__global__ void commit_rows_kernel(const float *stage, int dim, const uint32_t *rows, const uint32_t *slots,
+                                   const uint8_t *ids, uint32_t n, float *mat, float *inv_norm, uint32_t *doc_slot,
+                                   uint8_t *chunk_ids)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = w; i < n; i += nw) {
+        const uint32_t row = rows[i];
+        const float4 *src = reinterpret_cast<const float4 *>(stage + (size_t)i * dim);
+        float4 *dst = reinterpret_cast<float4 *>(mat + (size_t)row * dim);
+        double ss = 0.0;
+        for (int c = lane; c < (dim >> 2); c += 32) {
+            const float4 x = src[c];
+            dst[c] = x;
+            ss += (double)x.x * x.x + (double)x.y * x.y + (double)x.z * x.z + (double)x.w * x.w;
+        }
+        ss = warp_sum_d(ss);
+        if (lane == 0) {
+            inv_norm[row] = ss > 0.0 ? (float)(1.0 / sqrt(ss)) : 0.f;
+            doc_slot[row] = slots[i];
+            reinterpret_cast<uint4 *>(chunk_ids)[row] = reinterpret_cast<const uint4 *>(ids)[i];
+        }
+    }
+}
+
 __global__ void query_inv_norm_kernel(const float *queries, int dim, int nq, float *out)
 {
     const int lane = threadIdx.x & 31;
@@ -139,6 +184,25 @@ cudaError_t launch_finalize_rows(const float *mat, int dim, const uint32_t *rows
     int blocks = (int)((n + 7) / 8);
     if (blocks > 148 * 8) blocks = 148 * 8;
     finalize_rows_kernel<<<blocks, 256, 0, stream>>>(mat, dim, rows, slots, ids, n, inv_norm, doc_slot, chunk_ids);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_validate_stage(const float *stage, uint64_t n_floats, uint64_t base, unsigned long long *first_bad,
+                                  cudaStream_t stream)
+{
+    if (n_floats == 0) return cudaSuccess;
+    validate_stage_kernel<<<148 * 4, 256, 0, stream>>>(stage, n_floats, base, first_bad);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_commit_rows(const float *stage, int dim, const uint32_t *rows, const uint32_t *slots, const uint8_t *ids,
+                               uint32_t n, float *mat, float *inv_norm, uint32_t *doc_slot, uint8_t *chunk_ids,
+                               cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    int blocks = (int)((n + 7) / 8);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    commit_rows_kernel<<<blocks, 256, 0, stream>>>(stage, dim, rows, slots, ids, n, mat, inv_norm, doc_slot, chunk_ids);
     return cudaGetLastError();
 }
 

@@ -133,6 +133,9 @@ struct Shard {
     DevBuf<uint8_t> d_up_ids;
     PinBuf<uint32_t> h_up_rows, h_up_slots;
     PinBuf<uint8_t> h_up_ids;
+    DevBuf<float> d_up_stage;                 // vectors of one upsert chunk, validated before they are committed
+    DevBuf<unsigned long long> d_up_bad;
+    PinBuf<unsigned long long> h_up_bad;
     uint64_t hbm_bytes = 0;
     // IVFFlat index over this shard's rows (centroids are identical on every shard)
     struct Ivf {
@@ -211,6 +214,7 @@ void free_shard(Shard &s)
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
     s.h_up_rows.release(); s.h_up_slots.release(); s.h_up_ids.release();
+    s.d_up_stage.release(); s.d_up_bad.release(); s.h_up_bad.release();
     if (s.ev_scan0) cudaEventDestroy(s.ev_scan0);
     if (s.ev_scan1) cudaEventDestroy(s.ev_scan1);
     if (s.ev_all0) cudaEventDestroy(s.ev_all0);
@@ -655,10 +659,8 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
     if (dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, dim);
     std::lock_guard<std::mutex> lock(st->mu);
 
-    // Validate everything before touching the device: the reference's statement is atomic.
-    const size_t total = n * (size_t)dim;
-    for (size_t i = 0; i < total; i++)
-        if (!std::isfinite(vecs[i])) return fail(DA_ERR_NONFINITE, "element %zu of embedding %zu is not finite", i % dim, i / dim);
+    // Validate everything before the store changes: the reference's statement is atomic.  Ids on the host,
+    // vector elements on the device (staged, checked, and only then committed).
     std::vector<ChunkInfo *> info(n);
     {
         std::unordered_map<Id16, size_t, Id16Hash> seen;
@@ -701,35 +703,78 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
                         (unsigned long long)st->shards[s].cap_rows);
         }
 
+    // Vectors travel host -> staging buffer -> (finite check) -> final rows.  A call that fits one staging chunk is
+    // uploaded once; a larger one is streamed twice (check pass, commit pass) so that a bad element still leaves
+    // the store untouched.
+    size_t kChunkRows = std::max<size_t>(1, ((size_t)256 << 20) / ((size_t)dim * 4));
+    if (const char *e = getenv("DA_UPSERT_CHUNK_ROWS")) kChunkRows = std::max<size_t>(1, (size_t)atoll(e));   // test knob
+    std::vector<std::vector<size_t>> idx(S);
+    for (size_t i = 0; i < n; i++) idx[tgt_shard[i]].push_back(i);
+    auto upload = [&](Shard &sh, const std::vector<size_t> &ix, size_t b, size_t e) -> int {
+        for (size_t j = b; j < e;) {                    // runs of consecutive inputs -> one copy each
+            size_t r = j + 1;
+            while (r < e && ix[r] == ix[r - 1] + 1) r++;
+            CU(cudaMemcpyAsync(sh.d_up_stage.p + (j - b) * (size_t)dim, vecs + ix[j] * (size_t)dim, (r - j) * (size_t)dim * 4,
+                               cudaMemcpyHostToDevice, sh.stream));
+            j = r;
+        }
+        return DA_OK;
+    };
+    for (int s = 0; s < S; s++) {                       // ---- check pass
+        Shard &sh = st->shards[s];
+        const size_t cnt = idx[s].size();
+        if (!cnt) continue;
+        CU(cudaSetDevice(sh.device));
+        CU(sh.d_up_stage.ensure(std::min(cnt, kChunkRows) * (size_t)dim));
+        CU(sh.d_up_bad.ensure(1)); CU(sh.h_up_bad.ensure(1));
+        CU(cudaMemsetAsync(sh.d_up_bad.p, 0xFF, sizeof(unsigned long long), sh.stream));
+        for (size_t b = 0; b < cnt; b += kChunkRows) {
+            const size_t e = std::min(cnt, b + kChunkRows);
+            int rc = upload(sh, idx[s], b, e);
+            if (rc != DA_OK) return rc;
+            CU(da::launch_validate_stage(sh.d_up_stage.p, (e - b) * (uint64_t)dim, b * (uint64_t)dim, sh.d_up_bad.p, sh.stream));
+            st->launches++;
+        }
+        CU(cudaMemcpyAsync(sh.h_up_bad.p, sh.d_up_bad.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, sh.stream));
+    }
     for (int s = 0; s < S; s++) {
         Shard &sh = st->shards[s];
-        size_t cnt = 0;
-        for (size_t i = 0; i < n; i++) cnt += (tgt_shard[i] == s);
+        if (idx[s].empty()) continue;
+        CU(cudaSetDevice(sh.device));
+        CU(cudaStreamSynchronize(sh.stream));
+        if (*sh.h_up_bad.p != ~0ull) {
+            for (auto &u : doc_assign) st->docs[u.first].shard = u.second;
+            const size_t j = (size_t)(*sh.h_up_bad.p / (uint64_t)dim);
+            return fail(DA_ERR_NONFINITE, "element %llu of embedding %zu is not finite",
+                        (unsigned long long)(*sh.h_up_bad.p % (uint64_t)dim), idx[s][j]);
+        }
+    }
+    for (int s = 0; s < S; s++) {                       // ---- commit pass
+        Shard &sh = st->shards[s];
+        const size_t cnt = idx[s].size();
         if (!cnt) continue;
         CU(cudaSetDevice(sh.device));
         CU(sh.d_up_rows.ensure(cnt)); CU(sh.d_up_slots.ensure(cnt)); CU(sh.d_up_ids.ensure(cnt * 16));
         CU(sh.h_up_rows.ensure(cnt)); CU(sh.h_up_slots.ensure(cnt)); CU(sh.h_up_ids.ensure(cnt * 16));
-        size_t j = 0;
-        for (size_t i = 0; i < n;) {
-            if (tgt_shard[i] != s) { i++; continue; }
-            // run of inputs that land on consecutive rows -> one copy
-            size_t e = i + 1;
-            while (e < n && tgt_shard[e] == s && tgt_row[e] == tgt_row[e - 1] + 1) e++;
-            CU(cudaMemcpyAsync(sh.mat + (size_t)tgt_row[i] * dim, vecs + i * (size_t)dim, (e - i) * (size_t)dim * 4,
-                               cudaMemcpyHostToDevice, sh.stream));
-            for (size_t t = i; t < e; t++, j++) {
-                sh.h_up_rows.p[j] = tgt_row[t];
-                sh.h_up_slots.p[j] = info[t]->slot;
-                memcpy(sh.h_up_ids.p + 16 * j, chunk_ids + 16 * t, 16);
-            }
-            i = e;
+        for (size_t j = 0; j < cnt; j++) {
+            const size_t t = idx[s][j];
+            sh.h_up_rows.p[j] = tgt_row[t];
+            sh.h_up_slots.p[j] = info[t]->slot;
+            memcpy(sh.h_up_ids.p + 16 * j, chunk_ids + 16 * t, 16);
         }
         CU(cudaMemcpyAsync(sh.d_up_rows.p, sh.h_up_rows.p, cnt * 4, cudaMemcpyHostToDevice, sh.stream));
         CU(cudaMemcpyAsync(sh.d_up_slots.p, sh.h_up_slots.p, cnt * 4, cudaMemcpyHostToDevice, sh.stream));
         CU(cudaMemcpyAsync(sh.d_up_ids.p, sh.h_up_ids.p, cnt * 16, cudaMemcpyHostToDevice, sh.stream));
-        CU(da::launch_finalize_rows(sh.mat, dim, sh.d_up_rows.p, sh.d_up_slots.p, sh.d_up_ids.p, (uint32_t)cnt,
-                                    sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
-        st->launches++;
+        for (size_t b = 0; b < cnt; b += kChunkRows) {
+            const size_t e = std::min(cnt, b + kChunkRows);
+            if (cnt > kChunkRows) {                     // the staging buffer was reused by the check pass: stream again
+                int rc = upload(sh, idx[s], b, e);
+                if (rc != DA_OK) return rc;
+            }
+            CU(da::launch_commit_rows(sh.d_up_stage.p, dim, sh.d_up_rows.p + b, sh.d_up_slots.p + b, sh.d_up_ids.p + 16 * b,
+                                      (uint32_t)(e - b), sh.mat, sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
+            st->launches++;
+        }
         if (st->ivf_lists) {   // keep the index current, as pgvector does on insert: nearest list for the touched rows
             CU(da::ivf_launch_assign(sh.mat, dim, sh.d_up_rows.p, (uint32_t)cnt, sh.ivf.cent, st->ivf_lists, sh.ivf.assign, 1, sh.stream));
             CU(da::ivf_launch_build_lists(sh.ivf.assign, sh.n_rows + pending[s], st->ivf_lists, sh.ivf.counts, sh.ivf.offsets,

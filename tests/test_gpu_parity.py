@@ -140,6 +140,40 @@ def test_save_embeddings_upsert_semantics():
         assert st.stats().rows == 0
 
 
+def test_large_upsert_streams_in_chunks_and_stays_atomic(monkeypatch):
+    """A call larger than the staging buffer is streamed twice (check pass, commit pass); a bad element anywhere
+    still leaves the store untouched.  The chunk size is shrunk through the library's test knob."""
+    monkeypatch.setenv("DA_UPSERT_CHUNK_ROWS", "37")
+    S = oracle.Synth(n_clusters=2)
+    dim, n = 256, 500
+    mat = oracle.gen_rows(S, 0, n, dim)
+    chunk, docs = ids_for(n, 3)
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        for d in range(3):
+            st.save_chunks_raw(docs[d], chunk[d::3])
+        order = np.random.default_rng(1).permutation(n)             # scattered input order: many short runs
+        bad = mat[order].copy()
+        bad[411, 7] = np.inf
+        with pytest.raises(StoreError) as e:
+            st.save_embeddings_raw(chunk[order], bad)
+        assert e.value.code == L.DA_ERR_NONFINITE and "embedding 411" in e.value.message and "element 7" in e.value.message
+        assert st.stats().rows == 0
+        st.save_embeddings_raw(chunk[order], mat[order])
+        assert st.stats().rows == n
+        got_v, got_inv, got_slot, got_ids = st.debug_rows(0, 0, n)
+        assert np.array_equal(got_v.view(np.uint32), mat[order].view(np.uint32))
+        assert np.array_equal(got_ids, chunk[order])
+        assert np.array_equal(got_slot, (order % 3).astype(np.uint32))
+        assert np.allclose(got_inv, 1.0 / np.linalg.norm(mat[order].astype(np.float64), axis=1), rtol=1e-6)
+        st.save_embeddings_raw(chunk[:200], mat[:200] * np.float32(2.0))     # chunked overwrite in place
+        q = oracle.gen_query(S, 0, 0, dim)
+        rows = st.search(q, 10, all_docs=True)[2][0]
+        ref = mat[order].copy()
+        pos = {int(o): i for i, o in enumerate(order)}
+        o_rows, _, _ = oracle.topk(ref, None, None, q, 10)
+        assert np.array_equal(rows, o_rows)
+
+
 @pytest.mark.parametrize("dim,row_lo,n", [(3072, 0, 400), (1536, 123400, 257), (100, 5, 9)])
 def test_device_generator_is_bit_identical_to_the_oracle(dim, row_lo, n):
     with GpuStore(dim=dim, capacity_rows=n) as st:
