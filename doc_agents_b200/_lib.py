@@ -87,6 +87,7 @@ SIGNATURES = {
     "da_store_destroy": (None, [C.c_void_p]),
     "da_store_save_chunks": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "da_store_save_embeddings": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int32]),
+    "da_store_bulk_load": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int32]),
     "da_store_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int32, C.c_int32,
                                 C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]),
     "da_store_search": (C.c_int, [C.c_void_p, C.POINTER(da_search_params), C.c_void_p, C.c_void_p,

@@ -792,6 +792,23 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
     return DA_OK;
 }
 
+int da_store_bulk_load(da_store *st, const uint8_t *chunk_ids, const uint8_t *doc_ids, const float *vecs, size_t n, int32_t dim)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    if (n == 0) return DA_OK;
+    if (!chunk_ids || !doc_ids || !vecs) return fail(DA_ERR_INVALID, "chunk_ids/doc_ids/vecs is NULL");
+    if (dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, dim);
+    // announce the chunks document by document (runs of equal document ids), then one upsert for all rows
+    for (size_t i = 0; i < n;) {
+        size_t e = i + 1;
+        while (e < n && memcmp(doc_ids + 16 * e, doc_ids + 16 * i, 16) == 0) e++;
+        int rc = da_store_save_chunks(st, doc_ids + 16 * i, chunk_ids + 16 * i, e - i);
+        if (rc != DA_OK) return rc;
+        i = e;
+    }
+    return da_store_save_embeddings(st, chunk_ids, vecs, n, dim);
+}
+
 int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids, float *out_scores,
                     uint32_t *out_rows, int32_t *out_n)
 {

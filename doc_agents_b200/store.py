@@ -167,6 +167,15 @@ class GpuStore:
         dim = vecs.shape[1] if vecs.ndim == 2 else self.dim
         _check(self._lib.da_store_save_embeddings(self._h, _ptr(chunk_ids), _ptr(vecs), n, dim))
 
+    def bulk_load(self, chunk_ids: np.ndarray, doc_ids: np.ndarray, vecs: np.ndarray) -> None:
+        """Cold start: rows of `embeddings JOIN chunks` (chunk id, document id, vector) in one call."""
+        chunk_ids = np.ascontiguousarray(chunk_ids, dtype=np.uint8).reshape(-1, 16)
+        doc_ids = np.ascontiguousarray(doc_ids, dtype=np.uint8).reshape(-1, 16)
+        vecs = np.ascontiguousarray(vecs, dtype=np.float32)
+        assert chunk_ids.shape[0] == doc_ids.shape[0] == vecs.shape[0]
+        _check(self._lib.da_store_bulk_load(self._h, _ptr(chunk_ids), _ptr(doc_ids), _ptr(vecs), chunk_ids.shape[0],
+                                            vecs.shape[1] if vecs.ndim == 2 else self.dim))
+
     def save_chunks_raw(self, doc_id: np.ndarray, chunk_ids: np.ndarray) -> None:
         doc_id = np.ascontiguousarray(doc_id, dtype=np.uint8).reshape(16)
         chunk_ids = np.ascontiguousarray(chunk_ids, dtype=np.uint8).reshape(-1, 16)

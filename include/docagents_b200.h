@@ -95,6 +95,12 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
 int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float *vecs,
                              size_t n, int32_t dim);
 
+/* Cold start: the rows of `embeddings JOIN chunks` streamed in binary (what a COPY of
+ * chunk_id, document_id, vector delivers), in any order.  Equivalent to SaveChunks + SaveEmbeddings per
+ * document, in one call: doc_ids and chunk_ids are n x 16 bytes, vecs n x dim. */
+int da_store_bulk_load(da_store *st, const uint8_t *chunk_ids, const uint8_t *doc_ids, const float *vecs,
+                       size_t n, int32_t dim);
+
 /* Store.TopK (store.go:66; postgres.go:218-285).  Rows whose chunk belongs to one of
  * doc_ids (n_docs x 16 bytes; n_docs == 0 matches nothing, :239), cosine similarity
  * 1 - (vector <=> query) >= the store's min_similarity (:223,:240), best first (:241),

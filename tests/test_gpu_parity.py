@@ -174,6 +174,23 @@ def test_large_upsert_streams_in_chunks_and_stays_atomic(monkeypatch):
         assert np.array_equal(rows, o_rows)
 
 
+def test_bulk_load_equals_per_document_saves():
+    """Cold start: one call with (chunk id, document id, vector) rows in arbitrary order."""
+    case = CASES[1]                                                   # 10 documents x 200 rows, 3072-d
+    n, dim = case.mat.shape
+    chunk, docs = ids_for(n, case.n_docs)
+    order = np.random.default_rng(5).permutation(n)
+    with GpuStore(dim=dim, capacity_rows=n) as a, GpuStore(dim=dim, capacity_rows=n) as b:
+        load_case(a, case)
+        b.bulk_load(chunk[order], docs[np.asarray(case.row_doc)[order]], case.mat[order])
+        assert b.stats().rows == n and b.stats().n_docs == case.n_docs
+        for filt in (docs[[0, 8]], docs[:case.n_docs], docs[[3]]):
+            ra = a.search(case.q, 10, filt)
+            rb = b.search(case.q, 10, filt)
+            assert np.array_equal(ra[0][0], rb[0][0])                 # same chunks (rows differ: other insertion order)
+            assert np.allclose(ra[1][0], rb[1][0], rtol=1e-6)
+
+
 @pytest.mark.parametrize("dim,row_lo,n", [(3072, 0, 400), (1536, 123400, 257), (100, 5, 9)])
 def test_device_generator_is_bit_identical_to_the_oracle(dim, row_lo, n):
     with GpuStore(dim=dim, capacity_rows=n) as st:

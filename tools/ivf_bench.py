@@ -26,9 +26,10 @@ def main():
     ap.add_argument("--queries", type=int, default=200)
     ap.add_argument("--clusters", type=int, default=1024)
     ap.add_argument("--simt", action="store_true")
+    ap.add_argument("--devices", type=int, default=1)
     a = ap.parse_args()
     S = oracle.Synth(n_clusters=a.clusters)
-    st = GpuStore(dim=a.dim, capacity_rows=a.rows)
+    st = GpuStore(dim=a.dim, capacity_rows=-(-a.rows // a.devices) + 200, devices=tuple(range(a.devices)))
     st.generate_synthetic(S, 0, a.rows)
     t0 = time.perf_counter()
     st.build_ivf(lists=a.lists, iters=a.iters, seed=1, default_probes=a.probes, simt_assign=a.simt)
@@ -49,7 +50,7 @@ def main():
         hits += len(np.intersect1d(ex, ap_))
         total += len(ex)
     out = {
-        "workload": f"IVFFlat lists={a.lists} on {a.rows}x{a.dim}, k-means {a.iters} iters, probes={a.probes}, {a.queries} queries",
+        "workload": f"IVFFlat lists={a.lists} on {a.rows}x{a.dim}, k-means {a.iters} iters, probes={a.probes}, {a.queries} queries, {a.devices} GPU(s) in one process",
         "assign": "simt fp32" if a.simt else "tcgen05 tf32",
         "build_ms": s.ivf_build_ms, "kmeans_ms": s.ivf_kmeans_ms, "assign_all_rows_ms": s.ivf_assign_ms,
         "assign_tflops": s.ivf_assign_tflops, "build_wall_s": wall,
