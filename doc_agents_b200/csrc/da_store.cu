@@ -291,6 +291,12 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             CU(cudaStreamWaitEvent(s.stream, st->shards[0].ev_done, 0));
         uint8_t *out_ids = rec_base;
         da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(rec_base + (size_t)pl.batch * pl.k * 16);
+        if (s.n_rows == 0) {               // an empty shard contributes an empty record block
+            CU(cudaMemsetAsync(rec_base, 0, rec_bytes, s.stream));
+            CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
+            continue;
+        }
         if (pl.ivf) {
             // per query: rank the centroids (the fused scan over the L x dim centroid matrix, top `probes`),
             // expand the chosen lists into one row list, run the fused scan over that row list.
@@ -386,6 +392,8 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
 int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
 {
     if (!p) return fail(DA_ERR_INVALID, "search params are NULL");
+    if (p->struct_size != sizeof(da_search_params))
+        return fail(DA_ERR_INVALID, "da_search_params.struct_size=%u, expected %zu", p->struct_size, sizeof(da_search_params));
     if (p->dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, p->dim);
     if (p->k < 0) return fail(DA_ERR_INVALID, "LIMIT must not be negative (k=%d)", p->k);
     if (p->k > DA_MAX_K) return fail(DA_ERR_INVALID, "k=%d exceeds DA_MAX_K=%d", p->k, DA_MAX_K);

@@ -298,3 +298,17 @@ def test_two_shards_in_one_process_equal_one_shard():
             for i in range(5):
                 assert np.array_equal(a[2][i], b[2][i]) and np.array_equal(a[0][i], b[0][i])
                 assert np.array_equal(a[1][i], b[1][i])
+
+
+def test_empty_store_answers_every_kind_of_search_with_nothing():
+    S = oracle.Synth()
+    dim = 1536
+    with GpuStore(dim=dim, capacity_rows=64) as st:
+        q1 = oracle.gen_query(S, 0, 0, dim)
+        q40 = np.stack([oracle.gen_query(S, i, 0, dim) for i in range(40)])
+        docs = oracle.doc_ids(S, 0, 3)
+        for qs, kw in ((q1, dict(all_docs=True)), (q1, dict(doc_ids=docs)), (q40, dict(all_docs=True)),
+                       (q40, dict(all_docs=True, min_similarity=-np.inf)), (q40[:5], dict(doc_ids=[docs] * 5))):
+            ids, sc, rows = st.search(qs, 10, **kw)
+            assert all(len(r) == 0 for r in rows)
+        assert st.TopK([], q1, 5) is None
