@@ -39,12 +39,14 @@ BATCH = 1
 FILTER_DOCS = 0          # 0 = every document requested
 READ_ALL = False
 NO_TENSOR = False
+SPLIT16 = False         # split-plane resident format (lossless; the scan reads the upper 16-bit plane only)
 METRIC = "cosine top-k queries/sec at 10M x 3072"
 UNIT = "queries/s"
 
 # Other BASELINE configs, selectable with --workload (the driver's default run is configs[2] at batch=1).
 WORKLOADS = {
     "cfg3_b1": {},
+    "cfg3_b1_split16": {"SPLIT16": True},
     "cfg3_b64": {"BATCH": 64},
     "cfg3_b64_simt": {"BATCH": 64, "NO_TENSOR": True},
     "cfg1": {"N_ROWS": 200, "TOP_K": 5, "FILTER_DOCS": 1},
@@ -58,6 +60,8 @@ def workload_name(n_gpus: int) -> str:
     flt = "all documents requested" if not FILTER_DOCS else \
         f"filtered to {FILTER_DOCS} doc IDs ({'mask as predicate, every row read' if READ_ALL else 'rows of other documents skipped'})"
     path = "fused SIMT scan" if (BATCH < 16 or NO_TENSOR or FILTER_DOCS) else "tcgen05 TF32 candidates + exact fp32 re-score"
+    if SPLIT16:
+        path = "split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"
     return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch={BATCH}, top_k={TOP_K}, "
             f"{flt}, min_similarity={MIN_SIM}, {path}, local top-k + NCCL all-gather merge")
 
@@ -294,7 +298,7 @@ def main():
     S = synth.Synth()
     lo, hi = shard_range(rank, world, N_ROWS, S.chunks_per_doc)
     st = GpuStore(dim=DIM, capacity_rows=max(1, hi - lo), devices=(local_rank,), min_similarity=MIN_SIM,
-                  world_size=world, rank=rank, nccl_id=nccl_id)
+                  world_size=world, rank=rank, nccl_id=nccl_id, split16=SPLIT16)
     st.generate_synthetic(S, lo, hi - lo)
     n_q = (warmup + steps) * BATCH if BATCH <= 64 else 2 * BATCH
     queries = np.stack([synth.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(n_q)])
@@ -359,7 +363,9 @@ def main():
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(bytes_per_launch) if args.workload == "cfg3_b1" else None,
-                     "kernel": "scan_topk_kernel" if "SIMT" in workload_name(world) else "tc_batch_candidates_kernel + rescore + select", "peak_source": peak_src,
+                     "kernel": ("scan_topk_kernel (upper plane) + split collect/rescore/select" if SPLIT16 else
+                                "scan_topk_kernel" if "SIMT" in workload_name(world) else
+                                "tc_batch_candidates_kernel + rescore + select"), "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,
                      "frac_of_nominal_8000": achieved / 8000.0},
         "result_check": {"hits": int(len(last[2][0])), "top_score": float(last[1][0][0]) if len(last[1][0]) else None},

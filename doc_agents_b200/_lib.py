@@ -33,6 +33,8 @@ DA_SEARCH_READ_ALL_ROWS = 0x2
 DA_SEARCH_IVF = 0x4
 DA_SEARCH_NO_TENSOR = 0x10
 
+DA_STORE_SPLIT16 = 0x1
+
 DA_IVF_SIMT_ASSIGN = 0x1
 
 DA_NOALLOC_MAX_K = 128

@@ -49,7 +49,9 @@ constexpr int kScanWarps = kScanThreads / 32;
 constexpr int kMaxNQ = 8;          // queries served by one pass of the SIMT scan
 
 struct ScanArgs {
-    const float *mat;              // n_rows x dim, row-major, 16-byte aligned rows
+    const float *mat;              // n_rows x dim, row-major, 16-byte aligned rows (nullptr in split-plane stores)
+    const uint16_t *hi;            // split-plane stores: upper 16 bits of every element, n_rows x dim (dim % 16 == 0)
+    float *approx;                 // split-plane stores: nq x n_rows similarities computed from the hi plane
     const float *inv_norm;         // 1/|row| (0 for a zero row)
     const uint32_t *doc_slot;      // document slot of each row
     const uint8_t *chunk_ids;      // 16 bytes per row
@@ -153,6 +155,27 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
                                   int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------
+// Split-plane layout (da_split.cu): every fp32 element lives as two 16-bit halves in two planes (lossless,
+// same bytes).  The scan reads only the upper plane (truncated-bf16 values, half the HBM traffic) and is a
+// candidate generator; candidates are re-scored from both planes with the fp32 scan's arithmetic.
+// eps bounds |cos_hi - cos_fp32|: truncation moves an element by < 2^-8 relative, so by Cauchy-Schwarz the
+// cosine moves by < 2^-8; the slack adds fp32 summation noise.
+// ---------------------------------------------------------------------------
+constexpr float kSplitEps = 4.0e-3f;
+cudaError_t launch_commit_rows_split(const float *stage, int dim, const uint32_t *rows, const uint32_t *slots,
+                                     const uint8_t *ids, uint32_t n, uint16_t *hi, uint16_t *lo, float *inv_norm,
+                                     uint32_t *doc_slot, uint8_t *chunk_ids, cudaStream_t stream);
+cudaError_t launch_split_rows(const float *src, uint32_t n, int dim, uint16_t *hi, uint16_t *lo, cudaStream_t stream);
+cudaError_t launch_join_rows(const uint16_t *hi, const uint16_t *lo, uint32_t n, int dim, float *dst, cudaStream_t stream);
+// After the hi-plane scan (top-k by approximate score in approx_keys, all approximate scores in approx):
+// collect every row that can still be in the exact top-k, re-score it exactly from both planes, select.
+cudaError_t launch_split_finish(const float *approx, uint32_t n_rows, int nq, int k, const key_t64 *approx_keys,
+                                float min_sim, float eps, key_t64 *cand, uint32_t cap, uint32_t *cand_count,
+                                uint32_t *overflow, const uint16_t *hi, const uint16_t *lo, int dim, const float *inv_norm,
+                                const float *queries, const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base,
+                                key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream);
 
 // Host restatement of the id hash of the synthetic corpus (spec: DESIGN.md).
 void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);

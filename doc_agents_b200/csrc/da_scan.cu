@@ -18,87 +18,23 @@
 //   - the last CTA to finish (ticket counter) merges all CTAs' keys, gathers the chunk
 //     ids and writes the final records: one launch per pass, no host round trip.
 #include "da_internal.h"
+#include "da_topk.cuh"
 
 namespace da {
 
 namespace {
 
-__device__ __forceinline__ float4 ldg_stream(const float4 *p)
-{
-    float4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-}
-
-// 256-bit streaming load (sm_100: LDG.256): one warp instruction covers 1 KB of a row.
-__device__ __forceinline__ void ldg_stream8(const float4 *p, float4 &a, float4 &b)
-{
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
-}
-
-__device__ __forceinline__ key_t64 warp_min_key(key_t64 v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        key_t64 t = __shfl_xor_sync(0xFFFFFFFFu, v, o);
-        v = t < v ? t : v;
-    }
-    return v;
-}
-
-// Unsorted bounded list with cached minimum.  All lanes call with identical arguments.
-__device__ __forceinline__ void warp_list_insert(key_t64 *list, int K, int &cnt, key_t64 &wmin,
-                                                 key_t64 key, int lane)
-{
-    if (cnt < K) {
-        if (lane == 0) list[cnt] = key;
-        cnt++;
-        __syncwarp();
-        if (cnt == K) {
-            key_t64 m = ~0ull;
-            for (int i = lane; i < K; i += 32) { key_t64 t = list[i]; m = t < m ? t : m; }
-            wmin = warp_min_key(m);
-        }
-        return;
-    }
-    if (key <= wmin) return;
-    // keys are unique (they embed the row), so exactly one slot holds wmin
-    for (int i = lane; i < K; i += 32)
-        if (list[i] == wmin) list[i] = key;
-    __syncwarp();
-    key_t64 m = ~0ull;
-    for (int i = lane; i < K; i += 32) { key_t64 t = list[i]; m = t < m ? t : m; }
-    wmin = warp_min_key(m);
-}
-
-// In-place descending bitonic sort of P (power of two) keys in shared memory by the whole CTA.
-__device__ void cta_bitonic_desc(key_t64 *buf, int P)
-{
-    for (int size = 2; size <= P; size <<= 1) {
-        for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            __syncthreads();
-            for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
-                int lo = 2 * t - (t & (stride - 1));
-                int hi = lo + stride;
-                bool desc = ((lo & size) == 0);
-                key_t64 a = buf[lo], b = buf[hi];
-                if ((a < b) == desc) { buf[lo] = b; buf[hi] = a; }
-            }
-        }
-    }
-    __syncthreads();
-}
-
 // INDIRECT: visit the rows listed in a.row_list (count in *a.n_rows_dev) instead of [0, n_rows):
 // the probed IVFFlat lists.  A 12 KB row is still read contiguously, so gathering by row costs
 // no bandwidth.
-// VEC = floats per lane per load: 8 (256-bit loads, rows 32-byte aligned, dim % 8 == 0) or 4.
+// VEC = elements per lane per load: 8 (256-bit loads of fp32, rows 32-byte aligned, dim % 8 == 0), 4, or 16:
+// the split-plane layout, where a 256-bit load brings 16 upper halves (truncated bf16) of a row of a.hi and every
+// row's approximate similarity is also stored to a.approx for the candidate pass (da_split.cu).
 template <int NQ, int R, int U, int VEC, bool FULL_TILES, bool INDIRECT>
 __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a)
 {
-    constexpr int V4 = VEC / 4;                 // float4 words per lane slot
+    constexpr int V4 = VEC / 4;                 // float4 words of the query per lane slot
+    constexpr int VR = VEC == 16 ? 2 : V4;      // float4 registers holding one loaded slot (raw 16-bit pairs when VEC == 16)
     const int DV = a.dim / VEC;                 // lane slots per row
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int D4 = a.dim >> 2;
@@ -156,7 +92,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         const uint32_t valid_mask = __ballot_sync(0xFFFFFFFFu, valid);
         const uint32_t want_mask = __ballot_sync(0xFFFFFFFFu, want_bits != 0u);
         const uint32_t load_mask = a.read_all ? valid_mask : want_mask;
-        if (load_mask == 0) continue;
+        if (load_mask == 0) {
+            if constexpr (VEC == 16) {              // skipped rows still need an (impossible) approximate score
+                if (valid)
+                    for (int q = 0; q < a.nq; q++) a.approx[(size_t)q * n_rows + my_row] = -3.0e38f;
+            }
+            continue;
+        }
         my_rows_read += __popc(load_mask);
 
         float acc[R][NQ];
@@ -174,7 +116,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         }
 
         for (int c0 = 0; c0 < DV; c0 += 32 * U) {
-            float4 v[R][U][V4];
+            float4 v[R][U][VR];
 #pragma unroll
             for (int r = 0; r < R; r++) {
 #pragma unroll
@@ -183,11 +125,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                     const bool ok = ((load_mask >> r) & 1u) && (FULL_TILES || c < DV);
                     const float4 *src = (INDIRECT ? rpi[r] : rp + (size_t)r * D4) + (size_t)c * V4;
                     if (ok) {
-                        if constexpr (VEC == 8) ldg_stream8(src, v[r][u][0], v[r][u][V4 - 1]);
+                        if constexpr (VEC == 16) {
+                            // 16 upper halves, kept raw (element 2j in the low 16 bits of word j, 2j+1 in the high 16 bits)
+                            ldg_stream8(reinterpret_cast<const float4 *>(a.hi + ((size_t)(row0 + r) * a.dim + (size_t)c * 16)),
+                                        v[r][u][0], v[r][u][1]);
+                        } else if constexpr (VEC == 8) ldg_stream8(src, v[r][u][0], v[r][u][1]);
                         else v[r][u][0] = ldg_stream(src);
                     } else {
 #pragma unroll
-                        for (int i = 0; i < V4; i++) v[r][u][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int i = 0; i < VR; i++) v[r][u][i] = make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
             }
@@ -202,10 +148,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                         const float4 qv = q_s[q * D4 + c * V4 + i];
 #pragma unroll
                         for (int r = 0; r < R; r++) {
-                            acc[r][q] = fmaf(v[r][u][i].x, qv.x, acc[r][q]);
-                            acc[r][q] = fmaf(v[r][u][i].y, qv.y, acc[r][q]);
-                            acc[r][q] = fmaf(v[r][u][i].z, qv.z, acc[r][q]);
-                            acc[r][q] = fmaf(v[r][u][i].w, qv.w, acc[r][q]);
+                            float4 x;
+                            if constexpr (VEC == 16) {          // widen the two raw words that hold elements 4i .. 4i+3
+                                const float4 raw = v[r][u][i >> 1];
+                                const uint32_t w0 = __float_as_uint((i & 1) ? raw.z : raw.x), w1 = __float_as_uint((i & 1) ? raw.w : raw.y);
+                                x = make_float4(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xFFFF0000u),
+                                                __uint_as_float(w1 << 16), __uint_as_float(w1 & 0xFFFF0000u));
+                            } else {
+                                x = v[r][u][i];
+                            }
+                            acc[r][q] = fmaf(x.x, qv.x, acc[r][q]);
+                            acc[r][q] = fmaf(x.y, qv.y, acc[r][q]);
+                            acc[r][q] = fmaf(x.z, qv.z, acc[r][q]);
+                            acc[r][q] = fmaf(x.w, qv.w, acc[r][q]);
                         }
                     }
                 }
@@ -227,6 +182,18 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             const float inv = __shfl_sync(0xFFFFFFFFu, my_inv, r);
             const uint32_t row = INDIRECT ? __shfl_sync(0xFFFFFFFFu, my_row, r) : row0 + r;
             const uint32_t wb = __shfl_sync(0xFFFFFFFFu, want_bits, r);
+            if constexpr (VEC == 16) {                                  // every visited row gets its approximate score
+                if (lane < NQ && lane < a.nq && ((valid_mask >> r) & 1u)) {
+                    float sv = -3.0e38f;
+                    if (((wb >> lane) & 1u) && inv > 0.f) {
+                        float t = 0.f;
+#pragma unroll
+                        for (int q = 0; q < NQ; q++) if (q == lane) t = acc[r][q];
+                        sv = fminf(1.f, fmaxf(-1.f, t * inv * q_inv_s[lane]));
+                    }
+                    a.approx[(size_t)lane * n_rows + row] = sv;
+                }
+            }
             if (!wb || !(inv > 0.f)) continue;                          // zero-norm rows never match
 #pragma unroll
             for (int q = 0; q < NQ; q++) {
@@ -296,7 +263,6 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     if (tid == 0) *a.counter = 0u;
 }
 
-int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
 template <int NQ, int R, int U, int VEC>
 cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t stream)
@@ -304,7 +270,7 @@ cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t st
     const bool full = ((a.dim / VEC) % (32 * U)) == 0;
     auto kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, false> : scan_topk_kernel<NQ, R, U, VEC, false, false>;
     if (a.row_list) {
-        if constexpr (NQ == 1) kern = full ? scan_topk_kernel<1, R, U, VEC, true, true> : scan_topk_kernel<1, R, U, VEC, false, true>;
+        if constexpr (NQ == 1 && VEC != 16) kern = full ? scan_topk_kernel<1, R, U, VEC, true, true> : scan_topk_kernel<1, R, U, VEC, false, true>;
         else return cudaErrorInvalidValue;
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -350,6 +316,16 @@ cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream,
         if (need < grid) grid = need < 1 ? 1 : (int)need;
     }
     if (grid_out) *grid_out = grid;
+    if (a.hi) {   // split-plane store: the scan reads the upper plane only
+        if (a.row_list || (a.dim % 16) || !a.approx) return cudaErrorInvalidValue;
+        switch (nqt) {
+            // measured at 10M x 3072: (R,U) = (4,2) 8.54 ms, (4,3) 8.68, (4,1) 8.94, (2,2) 10.4, (2,6) 11.2
+            case 1: return launch_one<1, 4, 2, 16>(a, grid, smem, stream);
+            case 2: return launch_one<2, 2, 2, 16>(a, grid, smem, stream);
+            case 4: return launch_one<4, 2, 1, 16>(a, grid, smem, stream);
+            default: return launch_one<8, 2, 1, 16>(a, grid, smem, stream);
+        }
+    }
     // 256-bit loads need 32-byte aligned rows; other dimensions keep the 128-bit path
     const bool v8 = (a.dim % 8) == 0 && (reinterpret_cast<uintptr_t>(a.mat) & 31) == 0;
     switch (nqt) {

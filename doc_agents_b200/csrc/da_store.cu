@@ -106,6 +106,7 @@ struct Shard {
     uint64_t cap_rows = 0;
     uint32_t n_rows = 0, row_base = 0;
     float *mat = nullptr, *inv_norm = nullptr;
+    uint16_t *hi = nullptr, *lo = nullptr;      // split-plane layout: upper / lower 16 bits of every element
     uint32_t *doc_slot = nullptr;
     uint8_t *chunk_ids = nullptr;
     cudaStream_t stream = nullptr;
@@ -120,6 +121,8 @@ struct Shard {
     DevBuf<unsigned long long> d_cand;          // batched tensor-core path: candidate lists
     DevBuf<uint32_t> d_cand_count, d_overflow, d_hist, d_gate, d_surv_count, d_group_sync;
     DevBuf<unsigned long long> d_surv;
+    DevBuf<float> d_approx;                     // split-plane layout: approximate scores of every row
+    DevBuf<unsigned long long> d_akeys;         // ... and the scan's approximate top-k
     PinBuf<uint32_t> h_overflow;
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
@@ -193,6 +196,7 @@ struct da_store {
     std::vector<Pending *> bqueue;
     bool bleader = false;
     uint64_t topk_calls = 0, topk_passes = 0;
+    bool split16 = false;          // split-plane resident format (DA_STORE_SPLIT16)
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
@@ -205,11 +209,12 @@ void free_shard(Shard &s)
     free_ivf(s);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
-    cudaFree(s.mat); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
+    cudaFree(s.mat); cudaFree(s.hi); cudaFree(s.lo); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
     cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
+    s.d_approx.release(); s.d_akeys.release();
     s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release(); s.d_group_sync.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
@@ -225,7 +230,7 @@ void free_shard(Shard &s)
     s = Shard();
 }
 
-int init_shard(Shard &s, int device, int dim, uint64_t cap_rows)
+int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16)
 {
     s.device = device;
     s.cap_rows = cap_rows;
@@ -245,7 +250,12 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows)
     CU(cudaEventCreate(&s.ev_scan0)); CU(cudaEventCreate(&s.ev_scan1));
     CU(cudaEventCreate(&s.ev_all0)); CU(cudaEventCreate(&s.ev_all1));
     CU(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
-    CU(cudaMalloc((void **)&s.mat, cap_rows * (uint64_t)dim * 4));
+    if (split16) {
+        CU(cudaMalloc((void **)&s.hi, cap_rows * (uint64_t)dim * 2));
+        CU(cudaMalloc((void **)&s.lo, cap_rows * (uint64_t)dim * 2));
+    } else {
+        CU(cudaMalloc((void **)&s.mat, cap_rows * (uint64_t)dim * 4));
+    }
     CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
     CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
     CU(cudaMalloc((void **)&s.chunk_ids, cap_rows * 16));
@@ -359,10 +369,23 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             a.out_keys = out_keys + (size_t)q0 * pl.k;
             a.out_ids = out_ids + (size_t)q0 * pl.k * 16;
             a.rows_read = s.d_rows_read;
+            if (st->split16) {             // scan the upper plane for candidates, then the exact finish from both planes
+                a.mat = nullptr; a.hi = s.hi; a.approx = s.d_approx.p;
+                a.min_sim = pl.min_sim - da::kSplitEps;
+                a.out_keys = s.d_akeys.p; a.out_ids = nullptr;
+            }
             int grid = 0;
             CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
             st->launches++;
             if (first) { st->scan_grid = grid; st->scan_launches++; }
+            if (st->split16) {
+                const uint32_t cap = (uint32_t)std::min<uint64_t>(std::max<uint32_t>(s.n_rows, 1), 1u << 20);
+                CU(da::launch_split_finish(s.d_approx.p, s.n_rows, a.nq, pl.k, s.d_akeys.p, pl.min_sim, da::kSplitEps,
+                                           s.d_cand.p, cap, s.d_cand_count.p, s.d_overflow.p, s.hi, s.lo, dim, s.inv_norm,
+                                           a.queries, a.q_inv_norm, s.chunk_ids, s.row_base,
+                                           out_keys + (size_t)q0 * pl.k, out_ids + (size_t)q0 * pl.k * 16, s.stream));
+                st->launches += 3;
+            }
         }
         CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
         if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
@@ -400,6 +423,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (p->batch < 1 || p->batch > DA_MAX_BATCH) return fail(DA_ERR_INVALID, "batch=%d out of range [1,%d]", p->batch, DA_MAX_BATCH);
     if (!p->queries) return fail(DA_ERR_INVALID, "query vector is NULL");
     const bool ivf = (p->flags & DA_SEARCH_IVF) != 0;
+    if (ivf && st->split16) return fail(DA_ERR_STATE, "IVFFlat is not available with the split-plane layout");
     if (ivf && st->ivf_lists == 0) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store (da_store_build_ivf)");
     const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
     if (!all_docs && p->n_docs && !p->doc_ids) return fail(DA_ERR_INVALID, "doc_ids is NULL with n_docs=%zu", p->n_docs);
@@ -444,7 +468,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (pl.k == 0) return DA_OK;
     // Batches of 16+ queries become a dense contraction: tensor cores generate the candidates, fp32 re-scores
     // them.  Not for narrow document filters, where the SIMT scan skips the rows it does not need.
-    if (!ivf && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16) {
+    if (!ivf && !st->split16 && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16) {
         size_t selected = st->docs.size();
         if (!all_docs) {
             selected = 0;                              // documents requested by at least one query
@@ -461,6 +485,16 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             CU(s.d_hist.ensure(da::tc_batch_hist_words(p->batch)));
             CU(s.d_surv.ensure((size_t)p->batch * da::kSurvivorCap));
             CU(s.d_group_sync.ensure(1024));
+            CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));
+            CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
+            *s.h_overflow.p = 0;
+        }
+        if (st->split16) {
+            const size_t nq = (size_t)da::scan_pick_nq(st->dim, pl.k, p->batch);
+            CU(s.d_approx.ensure(nq * std::max<size_t>(s.n_rows, 1)));
+            CU(s.d_akeys.ensure(nq * (size_t)pl.k));
+            CU(s.d_cand.ensure(nq * (size_t)std::min<uint64_t>(std::max<uint32_t>(s.n_rows, 1), 1u << 20)));
+            CU(s.d_cand_count.ensure(nq));
             CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));
             CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
             *s.h_overflow.p = 0;
@@ -515,6 +549,8 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     if (pl.ivf)   // centroid matrix per query + the probed rows (vector, inv_norm, doc slot if filtered, row number)
         st->last_bytes = (uint64_t)pl.batch * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
                          rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
+    else if (st->split16)   // upper plane of the rows read + per row: 1/|row|, approximate score out and in (+ doc slot)
+        st->last_bytes = rows_read * (uint64_t)st->dim * 2 + rows_scanned * (uint64_t)passes * (pl.all_docs ? 12 : 16);
     else if (pl.use_tc)
         st->last_bytes = rows_scanned * ((uint64_t)st->dim * 4 + (pl.all_docs ? 4 : 8));   // every row once, whatever the batch
     else
@@ -555,6 +591,7 @@ int da_store_create(const da_config *cfg, da_store **out)
     if (cfg->struct_size != sizeof(da_config)) return fail(DA_ERR_INVALID, "da_config.struct_size=%u, expected %zu", cfg->struct_size, sizeof(da_config));
     if (cfg->dim <= 0 || (cfg->dim & 3)) return fail(DA_ERR_DIM, "dim=%d must be a positive multiple of 4", cfg->dim);
     if (cfg->dim > 16384) return fail(DA_ERR_DIM, "dim=%d exceeds 16384", cfg->dim);
+    if ((cfg->flags & DA_STORE_SPLIT16) && (cfg->dim % 16)) return fail(DA_ERR_DIM, "the split-plane layout needs dim %% 16 == 0 (dim=%d)", cfg->dim);
     if (cfg->n_devices < 1 || cfg->n_devices > DA_MAX_DEVICES) return fail(DA_ERR_INVALID, "n_devices=%d out of range", cfg->n_devices);
     if (cfg->capacity_rows == 0) return fail(DA_ERR_INVALID, "capacity_rows is 0");
     const int world = cfg->world_size > 1 ? cfg->world_size : 1;
@@ -574,10 +611,11 @@ int da_store_create(const da_config *cfg, da_store **out)
     st->min_sim = cfg->min_similarity;
     st->world = world; st->rank = rank; st->total_ranks = (int)total;
     st->batch_window_us = cfg->batch_window_us;
+    st->split16 = (cfg->flags & DA_STORE_SPLIT16) != 0;
     st->batch_max = cfg->batch_max ? std::min<uint32_t>(cfg->batch_max, DA_MAX_BATCH) : 64;
     st->shards.resize(cfg->n_devices);
     for (int i = 0; i < cfg->n_devices; i++) {
-        int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows);
+        int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows, st->split16);
         if (rc != DA_OK) { da_store_destroy(st); return rc; }
         st->shards[i].row_base = (uint32_t)(((uint64_t)rank * cfg->n_devices + i) * cfg->capacity_rows);
     }
@@ -779,8 +817,12 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
                 int rc = upload(sh, idx[s], b, e);
                 if (rc != DA_OK) return rc;
             }
-            CU(da::launch_commit_rows(sh.d_up_stage.p, dim, sh.d_up_rows.p + b, sh.d_up_slots.p + b, sh.d_up_ids.p + 16 * b,
-                                      (uint32_t)(e - b), sh.mat, sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
+            if (st->split16)
+                CU(da::launch_commit_rows_split(sh.d_up_stage.p, dim, sh.d_up_rows.p + b, sh.d_up_slots.p + b, sh.d_up_ids.p + 16 * b,
+                                                (uint32_t)(e - b), sh.hi, sh.lo, sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
+            else
+                CU(da::launch_commit_rows(sh.d_up_stage.p, dim, sh.d_up_rows.p + b, sh.d_up_slots.p + b, sh.d_up_ids.p + 16 * b,
+                                          (uint32_t)(e - b), sh.mat, sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
             st->launches++;
         }
         if (st->ivf_lists) {   // keep the index current, as pgvector does on insert: nearest list for the touched rows
@@ -844,9 +886,11 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         if (rc != DA_OK) return rc;
         for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
         bool overflow = false;
-        if (pl.use_tc)
+        if (pl.use_tc || st->split16)
             for (Shard &s : st->shards) overflow = overflow || (*s.h_overflow.p != 0);
         if (!overflow) break;
+        if (st->split16)
+            return fail(DA_ERR_STATE, "split-plane search: more than 2^20 rows lie within the truncation slack of the k-th best");
         // A candidate list stayed full after pruning (a mass of scores within the TF32 slack of the k-th
         // best).  Every rank sees its own lists only, so in a multi-rank store this stays an error.
         if (st->total_ranks > 1 && st->world > 1)
@@ -1006,6 +1050,7 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     if (!st || !p) return fail(DA_ERR_INVALID, "store/params is NULL");
     if (p->struct_size != sizeof(da_ivf_params)) return fail(DA_ERR_INVALID, "da_ivf_params.struct_size mismatch");
     if (p->lists < 1 || p->lists > 65536) return fail(DA_ERR_INVALID, "lists=%d out of range [1, 65536]", p->lists);
+    if (st->split16) return fail(DA_ERR_STATE, "IVFFlat is not available with the split-plane layout");
     std::lock_guard<std::mutex> lock(st->mu);
     const int L = p->lists, D = st->dim;
     const int iters = p->iters <= 0 ? 10 : std::min(p->iters, 20);
@@ -1156,8 +1201,22 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
         a.cmul = p->cmul; a.nmul = p->nmul;
         a.row_lo = lo; a.n_rows = (uint32_t)(hi - lo); a.doc_slot_base = (uint32_t)doc_lo; a.dim = st->dim;
         CU(cudaSetDevice(s.device));
-        CU(da::launch_synth(a, s.mat, s.inv_norm, s.doc_slot, s.chunk_ids, s.stream));
-        st->launches++;
+        if (st->split16) {                 // generate fp32 rows chunk by chunk into the staging buffer, then split them
+            const uint32_t chunk = 32768;
+            CU(s.d_up_stage.ensure((size_t)std::min<uint32_t>(a.n_rows ? a.n_rows : 1, chunk) * st->dim));
+            const uint32_t total_rows = a.n_rows;
+            const uint64_t lo0 = a.row_lo;
+            for (uint32_t off = 0; off < total_rows; off += chunk) {
+                a.row_lo = lo0 + off; a.n_rows = std::min(chunk, total_rows - off);
+                CU(da::launch_synth(a, s.d_up_stage.p, s.inv_norm + off, s.doc_slot + off, s.chunk_ids + (size_t)off * 16, s.stream));
+                CU(da::launch_split_rows(s.d_up_stage.p, a.n_rows, st->dim, s.hi + (size_t)off * st->dim, s.lo + (size_t)off * st->dim, s.stream));
+                st->launches += 2;
+            }
+            a.row_lo = lo0; a.n_rows = total_rows;
+        } else {
+            CU(da::launch_synth(a, s.mat, s.inv_norm, s.doc_slot, s.chunk_ids, s.stream));
+            st->launches++;
+        }
         s.row_base = (uint32_t)lo;
         s.n_rows = (uint32_t)(hi - lo);
         lo = hi;
@@ -1232,7 +1291,14 @@ int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo
     if (row_lo + n > s.n_rows) return fail(DA_ERR_INVALID, "rows [%llu,%llu) outside the %u resident rows",
                                            (unsigned long long)row_lo, (unsigned long long)(row_lo + n), s.n_rows);
     CU(cudaSetDevice(s.device));
-    if (out_vecs) CU(cudaMemcpy(out_vecs, s.mat + row_lo * st->dim, n * st->dim * 4, cudaMemcpyDeviceToHost));
+    if (out_vecs && st->split16 && n) {
+        CU(s.d_up_stage.ensure(n * st->dim));
+        CU(da::launch_join_rows(s.hi + row_lo * st->dim, s.lo + row_lo * st->dim, (uint32_t)n, st->dim, s.d_up_stage.p, s.stream));
+        CU(cudaStreamSynchronize(s.stream));
+        CU(cudaMemcpy(out_vecs, s.d_up_stage.p, n * st->dim * 4, cudaMemcpyDeviceToHost));
+    } else if (out_vecs) {
+        CU(cudaMemcpy(out_vecs, s.mat + row_lo * st->dim, n * st->dim * 4, cudaMemcpyDeviceToHost));
+    }
     if (out_inv_norm) CU(cudaMemcpy(out_inv_norm, s.inv_norm + row_lo, n * 4, cudaMemcpyDeviceToHost));
     if (out_doc_slot) CU(cudaMemcpy(out_doc_slot, s.doc_slot + row_lo, n * 4, cudaMemcpyDeviceToHost));
     if (out_chunk_ids) CU(cudaMemcpy(out_chunk_ids, s.chunk_ids + row_lo * 16, n * 16, cudaMemcpyDeviceToHost));

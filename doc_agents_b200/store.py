@@ -81,7 +81,8 @@ class GpuStore:
 
     def __init__(self, dim: int = 3072, capacity_rows: int = 1 << 16, devices: Sequence[int] = (0,),
                  min_similarity: float = L.DA_DEFAULT_MIN_SIMILARITY, world_size: int = 1, rank: int = 0,
-                 nccl_id: bytes | None = None, batch_window_us: int = 0, batch_max: int = 0):
+                 nccl_id: bytes | None = None, batch_window_us: int = 0, batch_max: int = 0,
+                 split16: bool = False):
         lib = L.load()
         cfg = L.da_config()
         cfg.struct_size = C.sizeof(L.da_config)
@@ -94,6 +95,7 @@ class GpuStore:
         cfg.world_size = world_size
         cfg.rank = rank
         cfg.batch_window_us = batch_window_us
+        cfg.flags = L.DA_STORE_SPLIT16 if split16 else 0
         cfg.batch_max = batch_max
         if nccl_id is not None:
             assert len(nccl_id) == L.DA_NCCL_ID_BYTES

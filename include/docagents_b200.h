@@ -66,7 +66,7 @@ typedef struct {
     int32_t  world_size;
     int32_t  rank;
     uint8_t  nccl_id[DA_NCCL_ID_BYTES];   /* from da_nccl_unique_id on rank 0, same on all ranks */
-    uint32_t flags;                 /* reserved, 0 */
+    uint32_t flags;                 /* DA_STORE_* below */
     /* Request batching for da_store_topk (0 = off).  Concurrent calls -- one goroutine per
      * /api/query, cmd/query/main.go:34 -- that arrive within batch_window_us of each other
      * are answered by ONE batched pass over the corpus (at most batch_max, default 64, calls), each call keeping
@@ -74,6 +74,14 @@ typedef struct {
     uint32_t batch_window_us;
     uint32_t batch_max;
 } da_config;
+
+/* da_config.flags */
+#define DA_STORE_SPLIT16 0x1u   /* split-plane layout: every fp32 element is kept as its upper and lower
+                                   16 bits in two planes -- lossless, same HBM footprint.  The scan streams only the upper
+                                   plane (half the bytes per pass) to generate candidates, which are re-scored from both
+                                   planes with the fp32 scan's arithmetic: results are bit-identical to the default layout.
+                                   dim must be a multiple of 16; the IVFFlat and tensor-core batch paths (they read fp32
+                                   rows through TMA) are not available in this layout. */
 
 /* Fills `out` with a fresh ncclUniqueId to hand to every rank's da_config. */
 int da_nccl_unique_id(uint8_t out[DA_NCCL_ID_BYTES]);
