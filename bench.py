@@ -47,6 +47,8 @@ UNIT = "queries/s"
 WORKLOADS = {
     "cfg3_b1": {},
     "cfg3_b1_split16": {"SPLIT16": True},
+    "cfg3_b64_split16": {"BATCH": 64, "SPLIT16": True},
+    "cfg4_split16": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf"), "SPLIT16": True},
     "cfg3_b64": {"BATCH": 64},
     "cfg3_b64_simt": {"BATCH": 64, "NO_TENSOR": True},
     "cfg1": {"N_ROWS": 200, "TOP_K": 5, "FILTER_DOCS": 1},
@@ -61,7 +63,9 @@ def workload_name(n_gpus: int) -> str:
         f"filtered to {FILTER_DOCS} doc IDs ({'mask as predicate, every row read' if READ_ALL else 'rows of other documents skipped'})"
     path = "fused SIMT scan" if (BATCH < 16 or NO_TENSOR or FILTER_DOCS) else "tcgen05 TF32 candidates + exact fp32 re-score"
     if SPLIT16:
-        path = "split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"
+        path = ("split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"
+                if BATCH < 16 else
+                "split-plane layout: tcgen05 bf16 contraction of the upper planes for candidates + exact fp32 re-score")
     return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch={BATCH}, top_k={TOP_K}, "
             f"{flt}, min_similarity={MIN_SIM}, {path}, local top-k + NCCL all-gather merge")
 

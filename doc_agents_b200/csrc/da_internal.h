@@ -140,7 +140,8 @@ cudaError_t tc_launch_gather_rows(const float *mat, int D, const uint32_t *rows,
 // then exact fp32 re-score and per-query selection (da_scan.cu).  eps bounds |cos_tf32 - cos_fp32|.
 constexpr float kTf32Eps = 2.5e-3f;
 #define DA_TC_MAX_BATCH 4096
-constexpr int kSurvivorCap = 4096;        // re-scored survivors kept per query
+constexpr int kSurvivorCap = 16384;       // re-scored survivors kept per query (a 10M-row cluster mass within the
+                                          // bf16 slack of the k-th best is ~5 000 rows)
 int tc_batch_cap(int k);
 int tc_batch_m_tiles(int batch);
 size_t tc_batch_hist_words(int batch);
@@ -149,12 +150,15 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
                                        const uint32_t *doc_bitmap, uint32_t bitmap_stride, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
                                        uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
-                                       cudaStream_t stream);
+                                       cudaStream_t stream, const uint16_t *q_hi = nullptr, const uint16_t *x_hi = nullptr);
+// upper 16 bits of n floats (truncated bf16), e.g. the queries of a batch for the bf16 contraction
+cudaError_t tc_launch_truncate_bf16(const float *src, size_t n, uint16_t *dst, cudaStream_t stream);
 cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_count, int cap, const uint32_t *gate_ordered,
                                   key_t64 *surv, uint32_t *surv_count, uint32_t *overflow, int batch,
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
-                                  int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream);
+                                  int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream,
+                                  const uint16_t *hi = nullptr, const uint16_t *lo = nullptr);
 
 // ---------------------------------------------------------------------------
 // Split-plane layout (da_split.cu): every fp32 element lives as two 16-bit halves in two planes (lossless,
@@ -164,6 +168,8 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
 // cosine moves by < 2^-8; the slack adds fp32 summation noise.
 // ---------------------------------------------------------------------------
 constexpr float kSplitEps = 4.0e-3f;
+// the bf16 contraction truncates the queries too: two truncations of < 2^-8 each
+constexpr float kSplitBf16Eps = 8.5e-3f;
 cudaError_t launch_commit_rows_split(const float *stage, int dim, const uint32_t *rows, const uint32_t *slots,
                                      const uint8_t *ids, uint32_t n, uint16_t *hi, uint16_t *lo, float *inv_norm,
                                      uint32_t *doc_slot, uint8_t *chunk_ids, cudaStream_t stream);

@@ -395,13 +395,14 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
                                                                  const uint32_t *gate_ordered, key_t64 *surv,
                                                                  uint32_t *surv_count, uint32_t *overflow, const float *mat,
                                                                  int dim, const float *inv_norm, const float *queries,
-                                                                 const float *q_inv, uint32_t row_base, float min_sim)
+                                                                 const float *q_inv, uint32_t row_base, float min_sim,
+                                                                 const uint16_t *hi, const uint16_t *lo)
 {
     const uint32_t q = blockIdx.x / kRescoreBlocksPerQuery, part = blockIdx.x % kRescoreBlocksPerQuery;
     const uint32_t cnt = min(cand_count[q], (uint32_t)cap);
     const uint32_t per = (cnt + kRescoreBlocksPerQuery - 1) / kRescoreBlocksPerQuery;
-    const uint32_t lo = part * per, hi = min(cnt, lo + per);
-    if (lo >= hi) return;
+    const uint32_t e_lo = part * per, e_hi = min(cnt, e_lo + per);      // this block's share of the list
+    if (e_lo >= e_hi) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D4 = dim >> 2;
     const bool vec8 = (dim % 8) == 0 && (reinterpret_cast<uintptr_t>(mat) & 31) == 0;
@@ -409,17 +410,33 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
     const float qi = q_inv[q];
     const uint32_t gate = gate_ordered[q];
     const key_t64 *lst = cand + (size_t)q * cap;
-    for (uint32_t i0 = lo + (uint32_t)warp * 32u; i0 < hi; i0 += 8u * 32u) {
+    for (uint32_t i0 = e_lo + (uint32_t)warp * 32u; i0 < e_hi; i0 += 8u * 32u) {
         const uint32_t i = i0 + (uint32_t)lane;
-        const key_t64 e = i < hi ? lst[i] : 0ull;
-        uint32_t m = __ballot_sync(0xFFFFFFFFu, i < hi && (uint32_t)(e >> 32) >= gate);
+        const key_t64 e = i < e_hi ? lst[i] : 0ull;
+        uint32_t m = __ballot_sync(0xFFFFFFFFu, i < e_hi && (uint32_t)(e >> 32) >= gate);
         while (m) {
             const int src = __ffs(m) - 1;
             m &= m - 1;
             const uint32_t row = (uint32_t)(__shfl_sync(0xFFFFFFFFu, e, src) & 0xFFFFFFFFull);
             const float4 *rp = reinterpret_cast<const float4 *>(mat) + (size_t)row * D4;
             float acc = 0.f;
-            if (vec8) {          // the scan's 256-bit path: a lane owns 8 consecutive floats
+            if (hi) {            // split-plane store: rebuild the fp32 bits from both planes, same order as below
+                const uint4 *h = reinterpret_cast<const uint4 *>(hi + (size_t)row * dim);
+                const uint4 *l = reinterpret_cast<const uint4 *>(lo + (size_t)row * dim);
+                for (int c = lane; c < (D4 >> 1); c += 32) {
+                    const uint4 hw = __ldg(h + c), lw = __ldg(l + c);
+                    const uint32_t hh[4] = {hw.x, hw.y, hw.z, hw.w}, ll[4] = {lw.x, lw.y, lw.z, lw.w};
+                    float x[8];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        x[2 * j] = __uint_as_float((hh[j] << 16) | (ll[j] & 0xFFFFu));
+                        x[2 * j + 1] = __uint_as_float((hh[j] & 0xFFFF0000u) | (ll[j] >> 16));
+                    }
+                    const float4 w0 = qv[2 * c], w1 = qv[2 * c + 1];
+                    acc = fmaf(x[0], w0.x, acc); acc = fmaf(x[1], w0.y, acc); acc = fmaf(x[2], w0.z, acc); acc = fmaf(x[3], w0.w, acc);
+                    acc = fmaf(x[4], w1.x, acc); acc = fmaf(x[5], w1.y, acc); acc = fmaf(x[6], w1.z, acc); acc = fmaf(x[7], w1.w, acc);
+                }
+            } else if (vec8) {   // the scan's 256-bit path: a lane owns 8 consecutive floats
                 for (int c = lane; c < (D4 >> 1); c += 32) {
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
@@ -481,12 +498,14 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
                                   key_t64 *surv, uint32_t *surv_count, uint32_t *overflow, int batch,
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
-                                  int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream)
+                                  int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream,
+                                  const uint16_t *hi, const uint16_t *lo)
 {
     cudaError_t e = cudaMemsetAsync(surv_count, 0, (size_t)batch * 4, stream);
     if (e != cudaSuccess) return e;
     rescore_candidates_kernel<<<(unsigned)batch * kRescoreBlocksPerQuery, 256, 0, stream>>>(
-        cand, cand_count, cap, gate_ordered, surv, surv_count, overflow, mat, dim, inv_norm, queries, q_inv, row_base, min_sim);
+        cand, cand_count, cap, gate_ordered, surv, surv_count, overflow, mat, dim, inv_norm, queries, q_inv, row_base, min_sim,
+        hi, lo);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     int P = next_pow2(2 * k);

@@ -122,6 +122,7 @@ struct Shard {
     DevBuf<uint32_t> d_cand_count, d_overflow, d_hist, d_gate, d_surv_count, d_group_sync;
     DevBuf<unsigned long long> d_surv;
     DevBuf<float> d_approx;                     // split-plane layout: approximate scores of every row
+    DevBuf<uint16_t> d_qhi;                     // ... and the queries' upper halves for the bf16 contraction
     DevBuf<unsigned long long> d_akeys;         // ... and the scan's approximate top-k
     PinBuf<uint32_t> h_overflow;
     da::key_t64 *d_cta = nullptr;
@@ -214,7 +215,7 @@ void free_shard(Shard &s)
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
-    s.d_approx.release(); s.d_akeys.release();
+    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release();
     s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release(); s.d_group_sync.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
@@ -342,11 +343,13 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         if (pl.use_tc) {
             CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_qinv.p, s.mat, s.n_rows, dim, s.inv_norm,
                                               s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.bitmap_stride, pl.k, pl.min_sim,
-                                              da::kTf32Eps, s.sm_count, s.d_cand.p, s.d_cand_count.p, s.d_hist.p,
-                                              s.d_gate.p, s.d_overflow.p, s.d_group_sync.p, s.stream));
+                                              st->split16 ? da::kSplitBf16Eps : da::kTf32Eps, s.sm_count, s.d_cand.p,
+                                              s.d_cand_count.p, s.d_hist.p, s.d_gate.p, s.d_overflow.p, s.d_group_sync.p, s.stream,
+                                              st->split16 ? s.d_qhi.p : nullptr, st->split16 ? s.hi : nullptr));
             CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), s.d_gate.p, s.d_surv.p,
                                          s.d_surv_count.p, s.d_overflow.p, pl.batch, s.mat, dim, s.inv_norm, s.d_queries.p,
-                                         s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream));
+                                         s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream,
+                                         s.hi, s.lo));
             st->launches += 4;
             if (first) { st->scan_grid = s.sm_count; st->scan_launches++; }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
@@ -468,7 +471,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (pl.k == 0) return DA_OK;
     // Batches of 16+ queries become a dense contraction: tensor cores generate the candidates, fp32 re-scores
     // them.  Not for narrow document filters, where the SIMT scan skips the rows it does not need.
-    if (!ivf && !st->split16 && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16) {
+    if (!ivf && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16 && (!st->split16 || st->dim % 8 == 0)) {
         size_t selected = st->docs.size();
         if (!all_docs) {
             selected = 0;                              // documents requested by at least one query
@@ -512,6 +515,11 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         CU(da::launch_query_inv_norm(s.d_queries.p, st->dim, p->batch, s.d_qinv.p, s.stream));
         st->launches++;
+        if (pl.use_tc && st->split16) {       // the bf16 contraction needs the queries' upper halves
+            CU(s.d_qhi.ensure(nq_elems));
+            CU(da::tc_launch_truncate_bf16(s.d_queries.p, nq_elems, s.d_qhi.p, s.stream));
+            st->launches++;
+        }
     }
     return DA_OK;
 }
@@ -549,6 +557,8 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     if (pl.ivf)   // centroid matrix per query + the probed rows (vector, inv_norm, doc slot if filtered, row number)
         st->last_bytes = (uint64_t)pl.batch * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
                          rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
+    else if (st->split16 && pl.use_tc)   // the upper plane once, whatever the batch
+        st->last_bytes = rows_scanned * ((uint64_t)st->dim * 2 + (pl.all_docs ? 4 : 8));
     else if (st->split16)   // upper plane of the rows read + per row: 1/|row|, approximate score out and in (+ doc slot)
         st->last_bytes = rows_read * (uint64_t)st->dim * 2 + rows_scanned * (uint64_t)passes * (pl.all_docs ? 12 : 16);
     else if (pl.use_tc)
@@ -889,14 +899,19 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         if (pl.use_tc || st->split16)
             for (Shard &s : st->shards) overflow = overflow || (*s.h_overflow.p != 0);
         if (!overflow) break;
-        if (st->split16)
+        if (st->split16 && !pl.use_tc)
             return fail(DA_ERR_STATE, "split-plane search: more than 2^20 rows lie within the truncation slack of the k-th best");
         // A candidate list stayed full after pruning (a mass of scores within the TF32 slack of the k-th
         // best).  Every rank sees its own lists only, so in a multi-rank store this stays an error.
         if (st->total_ranks > 1 && st->world > 1)
             return fail(DA_ERR_STATE, "tensor-core candidate list overflow; retry with DA_SEARCH_NO_TENSOR");
         st->tc_overflows++;
-        pl.use_tc = false;                 // answer this batch with the fp32 SIMT scan instead
+        pl.use_tc = false;                 // answer this batch with the SIMT scan instead
+        for (Shard &s : st->shards) {      // the flag is sticky on the device: clear it for the second attempt
+            CU(cudaSetDevice(s.device));
+            CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
+            *s.h_overflow.p = 0;
+        }
     }
     const uint8_t *ids = s0.h_result.p;
     const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p + nk * 16);

@@ -73,6 +73,15 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da_, uint64_
     asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}"
                  ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
 }
+// kind::f16 with bf16 operands (split-plane stores: the upper 16-bit plane IS a truncated-bf16 matrix)
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da_, uint64_t db_, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
+}
+// instruction descriptor: D=f32, A=B=bf16, both K-major, N=256, M=128 (K = 16 per instruction = 32 bytes, like tf32's 8)
+constexpr uint32_t TC_IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+
 __device__ __forceinline__ void umma_commit(uint32_t bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -254,6 +263,7 @@ struct BatchArgs {
     int K, batch, k;
     int cap;                    // entries per query list
     int group;                  // CTAs that share one range of row tiles and split the query tiles among them
+    int bf16;                   // 1: operands are bf16 (64 elements per 128-byte stage row), else tf32 (32)
     float floor_eps;            // min_similarity - eps
     float two_eps;
     const float *inv_norm;      // per row
@@ -339,7 +349,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const int per_grp = (n_tiles_total + n_groups - 1) / n_groups;
     const int t_begin = grp * per_grp;
     const int t_end = min(n_tiles_total, t_begin + per_grp);
-    const int kb_count = (a.K + TC_BK - 1) / TC_BK;
+    const int bk = a.bf16 ? 2 * TC_BK : TC_BK;               // elements per 128-byte stage row
+    const int kb_count = (a.K + bk - 1) / bk;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_STAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
@@ -373,8 +384,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                         mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                         const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
                         mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
-                        tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * TC_BK, mt * TC_BM);
-                        tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * TC_BK, t * TC_BN);
+                        tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * bk, mt * TC_BM);
+                        tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * bk, t * TC_BN);
                         if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -397,8 +408,10 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                         const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
                         const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
 #pragma unroll
-                        for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
-                            umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
+                        for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {     // 4 MMAs of 32 bytes of K each, either kind
+                            if (a.bf16) umma_bf16(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC_BF16, (uint32_t)((kb | k) != 0));
+                            else umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
+                        }
                         umma_commit(bar_empty + 8 * stage);
                         if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
                     }
@@ -550,6 +563,19 @@ EncodeTiledFn encode_fn()
 }
 
 // rows x K fp32 row-major -> boxes of [box_rows][32 floats], 128-byte swizzle, zero fill out of bounds
+bool make_map_bf16(CUtensorMap *map, const uint16_t *ptr, uint64_t rows, uint64_t K, uint32_t box_rows)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {K, rows};
+    cuuint64_t strides[1] = {K * 2};
+    cuuint32_t box[2] = {(cuuint32_t)(2 * TC_BK), box_rows};        // 64 bf16 = 128 bytes
+    cuuint32_t estr[2] = {1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<uint16_t *>(ptr), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 bool make_map(CUtensorMap *map, const float *ptr, uint64_t rows, uint64_t K, uint32_t box_rows)
 {
     EncodeTiledFn fn = encode_fn();
@@ -602,13 +628,20 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
                                        const uint32_t *doc_bitmap, uint32_t bitmap_stride, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
                                        uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
-                                       cudaStream_t stream)
+                                       cudaStream_t stream, const uint16_t *q_hi, const uint16_t *x_hi)
 {
-    if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
+    const bool bf16 = q_hi && x_hi;       // split-plane store: contract the upper planes as bf16 (kind::f16)
     if (batch > DA_TC_MAX_BATCH) return cudaErrorInvalidValue;
     CUtensorMap map_q, map_x;
-    if (!make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BN))
-        return cudaErrorInvalidValue;
+    if (bf16) {
+        if ((reinterpret_cast<uintptr_t>(x_hi) & 15) || (reinterpret_cast<uintptr_t>(q_hi) & 15) || (D & 7)) return cudaErrorInvalidValue;
+        if (!make_map_bf16(&map_q, q_hi, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map_bf16(&map_x, x_hi, (uint64_t)n_rows, (uint64_t)D, TC_BN))
+            return cudaErrorInvalidValue;
+    } else {
+        if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
+        if (!make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BN))
+            return cudaErrorInvalidValue;
+    }
     cudaError_t e = cudaMemsetAsync(cand_count, 0, (size_t)batch * 4, stream);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(hist, 0, tc_batch_hist_words(batch) * 4, stream);
@@ -618,16 +651,17 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     a.floor_eps = min_sim - eps; a.two_eps = 2.f * eps;
     a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
     a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
+    a.bf16 = bf16 ? 1 : 0;
     e = cudaFuncSetAttribute(tc_batch_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
     if (e != cudaSuccess) return e;
     const uint32_t n_tiles = (n_rows + TC_BN - 1) / TC_BN;
     // Row tiles in flight across the chip (one per group) plus the queries should sit in a fraction of the
     // 126 MB L2; otherwise every query tile pulls its row tile from HBM again.  Measured on cfg4 (4096 queries,
-    // 1.25M x 1536 rows): group 1/4/16/32 -> 274/188/152/102 GB of DRAM reads for a 7.7 GB shard, 44/33/30/29 ms.
-    // Row-tile re-reads still miss L2 half of the time once the epilogue emits candidates (open issue, see
-    // profiles/README.md); with nothing emitted the kernel runs at 93 % tensor-pipe activity.
+    // 1.25M x 1536 rows, free-running groups of 1/4/16/32): 274/188/152/102 GB of DRAM reads for a 7.7 GB shard;
+    // with the members of a group in lockstep (below): 44 GB at group 4, 22.7 GB at group 8 (profiles/README.md).
     const int m_tiles = tc_batch_m_tiles(batch);
-    const double tile_mb = (double)TC_BN * D * 4 / 1e6, q_mb = (double)batch * D * 4 / 1e6;
+    const double esz = bf16 ? 2.0 : 4.0;
+    const double tile_mb = (double)TC_BN * D * esz / 1e6, q_mb = (double)batch * D * esz / 1e6;
     int group = 1;
     while (group < m_tiles && group < sm_count && 2.0 * (sm_count / group) * tile_mb + q_mb > 90.0) group++;   // two live row tiles per group (lockstep window)
     if (group > m_tiles) group = m_tiles;
@@ -650,6 +684,21 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     }
     if (e != cudaSuccess) return e;
     batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a.floor_eps, a.two_eps, gate_ordered);
+    return cudaGetLastError();
+}
+
+namespace {
+__global__ void truncate_bf16_kernel(const float *src, size_t n, uint16_t *dst)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        dst[i] = (uint16_t)(__float_as_uint(src[i]) >> 16);
+}
+}  // namespace
+
+cudaError_t tc_launch_truncate_bf16(const float *src, size_t n, uint16_t *dst, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    truncate_bf16_kernel<<<148, 256, 0, stream>>>(src, n, dst);
     return cudaGetLastError();
 }
 

@@ -80,8 +80,8 @@ typedef struct {
                                    16 bits in two planes -- lossless, same HBM footprint.  The scan streams only the upper
                                    plane (half the bytes per pass) to generate candidates, which are re-scored from both
                                    planes with the fp32 scan's arithmetic: results are bit-identical to the default layout.
-                                   dim must be a multiple of 16; the IVFFlat and tensor-core batch paths (they read fp32
-                                   rows through TMA) are not available in this layout. */
+                                   Batches of 16+ queries contract the upper planes as bf16 on the tensor cores.
+                                   dim must be a multiple of 16; the IVFFlat path (TMA over fp32 rows) is not available. */
 
 /* Fills `out` with a fresh ncclUniqueId to hand to every rank's da_config. */
 int da_nccl_unique_id(uint8_t out[DA_NCCL_ID_BYTES]);

@@ -77,6 +77,27 @@ def test_split_store_equals_fp32_store_on_synthetic_corpus():
     assert e.value.code == L.DA_ERR_DIM
 
 
+@pytest.mark.parametrize("batch,k,floor", [(16, 10, 0.7), (64, 10, 0.7), (150, 100, -np.inf), (40, 128, 0.0)])
+def test_split_store_bf16_tensor_batches_equal_fp32_store(batch, k, floor):
+    """Batches of 16+ queries on a split-plane store: tcgen05 kind::f16 over the upper planes (bf16) generates the
+    candidates, the exact re-score from both planes makes the answer bit-identical to the fp32 layout."""
+    S = oracle.Synth(n_clusters=16)
+    n, dim = 50_000, 1536
+    with GpuStore(dim=dim, capacity_rows=n, split16=True) as sp, GpuStore(dim=dim, capacity_rows=n) as fp:
+        sp.generate_synthetic(S, 0, n)
+        fp.generate_synthetic(S, 0, n)
+        docs = oracle.doc_ids(S, 0, n // 200)
+        qs = np.stack([oracle.gen_query(S, i, i % 16, dim) for i in range(batch)])
+        for kw in (dict(all_docs=True), dict(doc_ids=docs[::2]), dict(doc_ids=[docs[i % 3::3] for i in range(batch)])):
+            a = sp.search(qs, k, min_similarity=floor, **kw)
+            assert sp.stats().last_rows_read == n                        # the contraction path ran
+            b = fp.search(qs, k, min_similarity=floor, no_tensor=True, **kw)
+            for i in range(batch):
+                assert np.array_equal(a[2][i], b[2][i]), (kw.keys(), i)
+                assert np.array_equal(a[1][i].view(np.uint32), b[1][i].view(np.uint32))
+                assert np.array_equal(a[0][i], b[0][i])
+
+
 def test_split_store_full_size_10m():
     S = oracle.Synth()
     n, dim, k = 10_000_000, 3072, 10
