@@ -35,7 +35,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB
     nvcc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "bin", "nvcc")
     tmp = f"{LIB}.{os.getpid()}.tmp"            # build aside, then rename: concurrent builders never see a torn file
-    cmd = [nvcc, *NVCC_FLAGS, "-I", INCLUDE, "-o", tmp, *sources(), "-lnccl"]
+    extra = os.environ.get("DA_NVCC_EXTRA", "").split()   # e.g. -DDA_TC_PROFILE (debug counters in the batch kernel)
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-I", INCLUDE, "-o", tmp, *sources(), "-lnccl"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd), file=sys.stderr)

@@ -19,6 +19,7 @@
 #include "da_internal.h"
 
 #include <cuda.h>
+#include <cstdio>
 
 namespace da {
 
@@ -324,6 +325,14 @@ __device__ float hist_kth_lower_bound(const uint32_t *h, int k)
     return hist_edge(cbin, fbin < 0 ? 0 : fbin);   // fine counters may lag the coarse one: its edge is still valid
 }
 
+// Warp roles of the batch kernel (the epilogue warps' TMEM lane quadrant is warp % 4 either way).
+#ifdef DA_TC_LOW_ROLES
+constexpr int kProdWarp = 0, kMmaWarp = 1, kEpiFirst = 2;
+#else
+constexpr int kProdWarp = 4, kMmaWarp = 5, kEpiFirst = 0;
+#endif
+
+template <bool BF16>     // operand type of the contraction: bf16 (kind::f16) or tf32; the issue loop has no run-time choice
 __global__ void __launch_bounds__(TC_THREADS, 1)
 tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                            const BatchArgs a)
@@ -349,7 +358,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const int per_grp = (n_tiles_total + n_groups - 1) / n_groups;
     const int t_begin = grp * per_grp;
     const int t_end = min(n_tiles_total, t_begin + per_grp);
-    const int bk = a.bf16 ? 2 * TC_BK : TC_BK;               // elements per 128-byte stage row
+    const int bk = BF16 ? 2 * TC_BK : TC_BK;               // elements per 128-byte stage row
     const int kb_count = (a.K + bk - 1) / bk;
 
     if (threadIdx.x == 0) {
@@ -357,7 +366,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
         for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {
+    if (warp == kMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -366,7 +375,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot_ptr;
 
-    if (warp == 0) {
+    if (warp == kProdWarp) {
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int t = t_begin; t < t_end; t++) {
@@ -391,25 +400,40 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == kMmaWarp) {
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             int it = 0;
+#ifdef DA_TC_PROFILE
+            long long w_tempty = 0, w_full = 0, t_start = clock64(), c0;
+#endif
             for (int t = t_begin; t < t_end; t++) {
                 for (int mt = member; mt < m_tiles; mt += a.group, it++) {
                     const int as = it & 1;
                     const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+#ifdef DA_TC_PROFILE
+                    c0 = clock64();
+#endif
                     mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+#ifdef DA_TC_PROFILE
+                    w_tempty += clock64() - c0;
+#endif
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t tmem_d = tmem_base + (uint32_t)as * TC_BN;
                     for (int kb = 0; kb < kb_count; kb++) {
+#ifdef DA_TC_PROFILE
+                        c0 = clock64();
+#endif
                         mbar_wait(bar_full + 8 * stage, phase);
+#ifdef DA_TC_PROFILE
+                        w_full += clock64() - c0;
+#endif
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                         const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
                         const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
 #pragma unroll
                         for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {     // 4 MMAs of 32 bytes of K each, either kind
-                            if (a.bf16) umma_bf16(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC_BF16, (uint32_t)((kb | k) != 0));
+                            if (BF16) umma_bf16(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC_BF16, (uint32_t)((kb | k) != 0));
                             else umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
                         }
                         umma_commit(bar_empty + 8 * stage);
@@ -418,15 +442,26 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                     umma_commit(bar_tfull + 8 * as);
                 }
             }
+#ifdef DA_TC_PROFILE
+            if ((blockIdx.x % 37) == 0)
+                printf("cta %d pairs %d total %lld wait_tempty %lld wait_full %lld\n", (int)blockIdx.x, it,
+                       clock64() - t_start, w_tempty, w_full);
+#endif
         }
     } else {
-        // ===== epilogue warps 2..5: thread = query `qlocal` of every query tile =====
+        // ===== epilogue warps 0..3: thread = query `qlocal` of every query tile =====
         const uint32_t quad = (uint32_t)warp & 3u;
-        const int etid = (int)threadIdx.x - 64;                       // 0..127 among the epilogue threads
+        const int etid = (int)threadIdx.x - kEpiFirst * 32;                      // 0..127 among the epilogue threads
         const uint32_t qlocal = quad * 32u + (uint32_t)lane;
         for (int mt = member; mt < m_tiles; mt += a.group) gate_s[mt * TC_BM + qlocal] = a.floor_eps;
         int it = 0, visited = 0, next_refresh = 1;
+#ifdef DA_TC_PROFILE
+        long long e_wait = 0, e_p1 = 0, e_p2 = 0, e_pre = 0, e0;
+#endif
         for (int t = t_begin; t < t_end; t++, visited++) {
+#ifdef DA_TC_PROFILE
+            e0 = clock64();
+#endif
             const uint32_t n0 = (uint32_t)t * TC_BN;
             // per-row factor for this row tile: 1/|row|, or 0 when the row is absent, zero or filtered out
             float *inv_t = s_inv + (t & 1) * TC_BN;
@@ -445,7 +480,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                         if (!per_query && !((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u)) f = 0.f;
                     }
                 }
-                inv_t[j] = f;
+                inv_t[j] = f > 0.f ? f : __int_as_float(0x7fc00000);   // NaN: never passes a gate
                 slot_t[j] = slot;
             }
             // tighten this thread's gates from the shared histograms: often at first, then every 16 row tiles
@@ -460,53 +495,102 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 }
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
+#ifdef DA_TC_PROFILE
+            e_pre += clock64() - e0;
+#endif
             for (int mt = member; mt < m_tiles; mt += a.group, it++) {
                 const int as = it & 1;
                 const uint32_t aphase = (uint32_t)(it >> 1) & 1;
                 const uint32_t q = (uint32_t)mt * TC_BM + qlocal;
                 const bool q_valid = q < (uint32_t)a.batch;
                 const float qinv = q_valid ? a.q_inv[q] : 0.f;
+                // gate on the un-normalised product: acc * (1/|row|) >= gate / (1/|q|), one multiply and one compare per
+                // row.  The factor of an unwanted row is NaN, which fails every comparison; a zero query scores 0
+                // everywhere; an absent query (padding of the last query tile) takes nothing.
                 const float gate = gate_s[mt * TC_BM + qlocal];
+                float thr = __int_as_float(0x7f800000);
+                if (q_valid) {
+                    if (qinv > 0.f) { thr = gate / qinv; thr -= fabsf(thr) * 9.5367431640625e-7f; }
+                    else if (gate <= 0.f) thr = -thr;
+                }
                 // per-query document sets are tested lazily, only for the few rows that pass the gate
                 const uint32_t *qmask = (per_query && q_valid) ? a.doc_bitmap + (size_t)q * a.bitmap_stride : nullptr;
                 unsigned long long *lst = a.cand + (size_t)q * a.cap;
                 uint32_t *hq = a.hist + (size_t)q * kHistWords;
+#ifdef DA_TC_PROFILE
+                e0 = clock64();
+#endif
                 mbar_wait(bar_tfull + 8 * as, aphase);
+#ifdef DA_TC_PROFILE
+                e_wait += clock64() - e0; e0 = clock64();
+#endif
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * TC_BN;
-                // pass 1: how many of the 256 rows pass this query's gate (no memory traffic at all)
-                uint32_t n_pass = 0;
+                // pass 1, branch-free: how many of the 256 rows pass this query's gate, and in which 32-row chunks
+                uint32_t n_pass = 0, hits = 0;
 #pragma unroll 1
                 for (int c = 0; c < TC_BN / 32; c++) {
                     uint32_t r[32];
                     tmem_ld32(taddr + (uint32_t)c * 32u, r);
+                    const float4 *f4 = reinterpret_cast<const float4 *>(inv_t + c * 32);
+                    uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        const float f = inv_t[c * 32 + j];
-                        const float v = __uint_as_float(r[j]) * f * qinv;
-                        bool ok = f > 0.f && v >= gate;
-                        if (ok && qmask) { const uint32_t sl = slot_t[c * 32 + j]; ok = (qmask[sl >> 5] >> (sl & 31)) & 1u; }
-                        n_pass += ok ? 1u : 0u;
+                    for (int j = 0; j < 8; j++) {
+                        const float4 f = f4[j];
+                        c0 += (__uint_as_float(r[4 * j + 0]) * f.x >= thr) ? 1u : 0u;
+                        c1 += (__uint_as_float(r[4 * j + 1]) * f.y >= thr) ? 1u : 0u;
+                        c2 += (__uint_as_float(r[4 * j + 2]) * f.z >= thr) ? 1u : 0u;
+                        c3 += (__uint_as_float(r[4 * j + 3]) * f.w >= thr) ? 1u : 0u;
                     }
+                    const uint32_t cc = (c0 + c1) + (c2 + c3);
+                    n_pass += cc;
+                    hits |= (cc ? 1u : 0u) << c;
                 }
-                if (!q_valid) n_pass = 0;
-                // pass 2 (only if some query of this warp has survivors): one slot reservation per query, then
-                // plain stores and fire-and-forget histogram increments
-                if (__any_sync(0xFFFFFFFFu, n_pass != 0)) {
-                    uint32_t pos = n_pass ? atomicAdd(a.cand_count + q, n_pass) : 0u;
-#pragma unroll 1
-                    for (int c = 0; c < TC_BN / 32; c++) {
+                // per-query document sets: recount exactly, visiting only the chunks that had gate survivors
+                if (per_query) {
+                    uint32_t wh = __reduce_or_sync(0xFFFFFFFFu, hits), kept = 0;
+                    n_pass = 0;
+                    while (wh) {
+                        const int c = __ffs(wh) - 1;
+                        wh &= wh - 1;
                         uint32_t r[32];
                         tmem_ld32(taddr + (uint32_t)c * 32u, r);
-                        if (n_pass) {
+                        if ((hits >> c) & 1u) {
 #pragma unroll
                             for (int j = 0; j < 32; j++) {
-                                const float f = inv_t[c * 32 + j];
-                                const float v = __uint_as_float(r[j]) * f * qinv;
-                                bool ok = f > 0.f && v >= gate;
-                                if (ok && qmask) { const uint32_t sl = slot_t[c * 32 + j]; ok = (qmask[sl >> 5] >> (sl & 31)) & 1u; }
-                                if (ok) {
+                                if (__uint_as_float(r[j]) * inv_t[c * 32 + j] >= thr) {
+                                    const uint32_t sl = slot_t[c * 32 + j];
+                                    if ((qmask[sl >> 5] >> (sl & 31)) & 1u) { n_pass++; kept |= 1u << c; }
+                                }
+                            }
+                        }
+                    }
+                    hits = kept;
+                }
+#ifdef DA_TC_PROFILE
+                e_p1 += clock64() - e0; e0 = clock64();
+#endif
+                // pass 2 (chunks with survivors only): one slot reservation per query, then plain stores and
+                // fire-and-forget histogram increments
+                uint32_t wh = __reduce_or_sync(0xFFFFFFFFu, hits);
+                if (wh) {
+                    uint32_t pos = n_pass ? atomicAdd(a.cand_count + q, n_pass) : 0u;
+                    while (wh) {
+                        const int c = __ffs(wh) - 1;
+                        wh &= wh - 1;
+                        uint32_t r[32];
+                        tmem_ld32(taddr + (uint32_t)c * 32u, r);
+                        if ((hits >> c) & 1u) {
+#pragma unroll
+                            for (int j = 0; j < 32; j++) {
+                                const float pv = __uint_as_float(r[j]) * inv_t[c * 32 + j];
+                                if (pv >= thr) {
+                                    if (qmask) {
+                                        const uint32_t sl = slot_t[c * 32 + j];
+                                        if (!((qmask[sl >> 5] >> (sl & 31)) & 1u)) continue;
+                                    }
                                     if (pos < (uint32_t)a.cap) {
+                                        const float v = pv * qinv;
                                         lst[pos] = ((unsigned long long)score_to_ordered(v) << 32) | (unsigned long long)(n0 + c * 32 + j);
                                         int hc, hf;
                                         hist_bins(fminf(1.f, fmaxf(-1.f, v)), hc, hf);
@@ -521,16 +605,23 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                         }
                     }
                 }
+#ifdef DA_TC_PROFILE
+                e_p2 += clock64() - e0;
+#endif
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
             }
         }
+#ifdef DA_TC_PROFILE
+        if ((blockIdx.x % 37) == 0 && lane == 0)
+            printf("cta %d warp %d pre %lld wait_tfull %lld pass1 %lld pass2 %lld\n", (int)blockIdx.x, warp, e_pre, e_wait, e_p1, e_p2);
+#endif
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 1) {
+    if (warp == kMmaWarp) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
     }
@@ -652,7 +743,8 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
     a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
     a.bf16 = bf16 ? 1 : 0;
-    e = cudaFuncSetAttribute(tc_batch_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
+    const void *kernel = bf16 ? (const void *)tc_batch_candidates_kernel<true> : (const void *)tc_batch_candidates_kernel<false>;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
     if (e != cudaSuccess) return e;
     const uint32_t n_tiles = (n_rows + TC_BN - 1) / TC_BN;
     // Row tiles in flight across the chip (one per group) plus the queries should sit in a fraction of the
@@ -671,16 +763,14 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     a.group = group;
     a.group_sync = group_sync;
     const uint32_t grid = (uint32_t)(n_groups * group);
+    void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a};
     if (group > 1) {
         // members of a group wait for each other: every CTA must be resident, which a cooperative launch guarantees
         e = cudaMemsetAsync(group_sync, 0, (size_t)n_groups * 4, stream);
         if (e != cudaSuccess) return e;
-        void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a};
-        e = cudaLaunchCooperativeKernel((const void *)tc_batch_candidates_kernel, dim3(grid), dim3(TC_THREADS), args,
-                                        TCB_SMEM_BYTES, stream);
+        e = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(TC_THREADS), args, TCB_SMEM_BYTES, stream);
     } else {
-        tc_batch_candidates_kernel<<<grid, TC_THREADS, TCB_SMEM_BYTES, stream>>>(map_q, map_x, a);
-        e = cudaGetLastError();
+        e = cudaLaunchKernel(kernel, dim3(grid), dim3(TC_THREADS), args, TCB_SMEM_BYTES, stream);
     }
     if (e != cudaSuccess) return e;
     batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a.floor_eps, a.two_eps, gate_ordered);
