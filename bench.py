@@ -77,6 +77,15 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_tensor_peak(bf16: bool):
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        v = float(json.load(open(p))["bf16_tflops"])
+        return (v, "measured (MEASURED_PEAKS.json bf16_tflops, burst)") if bf16 else \
+               (v / 2, "measured (MEASURED_PEAKS.json bf16_tflops / 2: tf32 runs at half the bf16 rate)")
+    return (2250.0, "nominal dense bf16") if bf16 else (1125.0, "nominal dense tf32")
+
+
 def recorded_traffic(bytes_per_launch: int):
     """dram bytes per scan launch from the committed ncu --set full capture (taken at 10M rows on one
     GPU), scaled by this run's algorithmic bytes per launch when the shard size differs."""
@@ -353,6 +362,7 @@ def main():
 
     peak, peak_src = measured_peak()
     achieved = bytes_per_launch / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
+    tensor_path = "tcgen05" in workload_name(world)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
         "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -374,6 +384,16 @@ def main():
                      "frac_of_nominal_8000": achieved / 8000.0},
         "result_check": {"hits": int(len(last[2][0])), "top_score": float(last[1][0][0]) if len(last[1][0]) else None},
     }
+    if tensor_path:
+        # batched searches are a contraction: the bound is the tensor pipe, not HBM.  Algorithmic flops of one pass =
+        # 2 x rows x queries x dim; peak = the measured cuBLAS bf16 rate (tf32 runs at half of it).
+        flops = 2.0 * (hi - lo) * BATCH * DIM
+        tpeak, tsrc = measured_tensor_peak(bf16=SPLIT16)
+        tach = flops / (scan_ms / 1e3) / 1e12 if scan_ms > 0 else 0.0
+        line["roofline"] = {"bound": "tensor", "achieved": tach, "peak": tpeak, "unit": "TFLOP/s", "frac": tach / tpeak,
+                            "traffic": None, "kernel": "tc_batch_candidates_kernel (+ exact re-score and select, inside kernel_ms)",
+                            "peak_source": tsrc, "flops_per_launch": flops, "kernel_ms": scan_ms,
+                            "launches_timed": scan_launches}
     st.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "cfg3_b1":
         _, info, _ = cpu_reference_run(steps=8, warmup=1)

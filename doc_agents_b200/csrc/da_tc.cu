@@ -19,7 +19,6 @@
 #include "da_internal.h"
 
 #include <cuda.h>
-#include <cstdio>
 
 namespace da {
 
@@ -87,6 +86,53 @@ __device__ __forceinline__ void umma_commit(uint32_t bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// ---- CTA pairs (cta_group::2): two CTAs of one cluster on one TPC run each MMA together.  Every CTA stages its own
+// 128 A rows and HALF of the B tile; the leader (cluster rank 0) issues the MMAs, whose completion is multicast to the
+// barriers of both CTAs; both CTAs' TMA loads complete on the leader's barrier.
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr)
+{
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, uint32_t bar_cluster, int c0, int c1)
+{
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t da_, uint64_t db_, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t da_, uint64_t db_, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar)      // arrives on `bar` of BOTH CTAs of the pair
+{
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+// pair instruction descriptors: M = 256 (128 rows of D in each CTA's TMEM), N = 256
+constexpr uint32_t TC_IDESC_PAIR = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)((2 * TC_BM) >> 4) << 24);
+constexpr uint32_t TC_IDESC_BF16_PAIR = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)((2 * TC_BM) >> 4) << 24);
+
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
 {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -332,16 +378,23 @@ constexpr int kProdWarp = 0, kMmaWarp = 1, kEpiFirst = 2;
 constexpr int kProdWarp = 4, kMmaWarp = 5, kEpiFirst = 0;
 #endif
 
-template <bool BF16>     // operand type of the contraction: bf16 (kind::f16) or tf32; the issue loop has no run-time choice
+// BF16: operand type of the contraction, bf16 (kind::f16) or tf32, fixed at compile time (the issue loop has no
+// run-time choice).  NCTA = 2: CTA pairs (cluster of two), each pair takes TWO query tiles against one row tile per
+// accumulator; a CTA stages its own query tile and half of the row tile, which halves the shared-memory traffic per
+// MMA (the limit of the single-CTA tf32 form) and the L2 traffic per query tile.
+template <bool BF16, int NCTA>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                            const BatchArgs a)
 {
+    constexpr uint32_t B_BYTES = TC_B_BYTES / NCTA;
+    constexpr uint32_t STAGE_BYTES = TC_A_BYTES + B_BYTES;
+    constexpr int STAGES = TC_STAGES * (int)TC_STAGE_BYTES / (int)STAGE_BYTES;      // 4 x 48 KB or 6 x 32 KB
     extern __shared__ unsigned char smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bars = base + TC_STAGES * TC_STAGE_BYTES;
-    const uint32_t bar_full = bars, bar_empty = bars + 8 * TC_STAGES;
-    const uint32_t bar_tfull = bars + 16 * TC_STAGES, bar_tempty = bar_tfull + 16;
+    const uint32_t bars = base + STAGES * STAGE_BYTES;
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * STAGES;
+    const uint32_t bar_tfull = bars + 16 * STAGES, bar_tempty = bar_tfull + 16;
     const uint32_t tmem_slot = bar_tempty + 16;
     volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
     float *s_inv = reinterpret_cast<float *>(smem_raw + (bars + 256 - smem_u32(smem_raw)));   // [2][TC_BN]
@@ -349,12 +402,16 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     float *gate_s = s_inv + 4 * TC_BN;                                                        // [m_tiles][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;        // 0 = leader of the pair
     const int m_tiles = (a.batch + TC_BM - 1) / TC_BM;
+    const int m_units = (m_tiles + NCTA - 1) / NCTA;                // query tiles (pairs of them) dealt to a unit
     const int n_tiles_total = (int)((a.n_rows + TC_BN - 1) / TC_BN);
-    // `group` neighbouring CTAs share one range of row tiles (the tile reaches them through L2) and deal the
-    // query tiles out among themselves, so that the row tiles in flight across the chip stay L2-resident.
-    const int n_groups = (int)gridDim.x / a.group;
-    const int grp = (int)blockIdx.x / a.group, member = (int)blockIdx.x % a.group;
+    // A unit is one CTA (or CTA pair).  `group` neighbouring units share one range of row tiles (the tile reaches
+    // them through L2) and deal the query tiles out among themselves, so that the row tiles in flight across the
+    // chip stay L2-resident.
+    const int unit = (int)blockIdx.x / NCTA;
+    const int n_groups = ((int)gridDim.x / NCTA) / a.group;
+    const int grp = unit / a.group, member = unit % a.group;
     const int per_grp = (n_tiles_total + n_groups - 1) / n_groups;
     const int t_begin = grp * per_grp;
     const int t_end = min(n_tiles_total, t_begin + per_grp);
@@ -362,106 +419,109 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const int kb_count = (a.K + bk - 1) / bk;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < TC_STAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4); }
+        for (int s = 0; s < STAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4 * NCTA); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kMmaWarp) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TC_TMEM_COLS) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (NCTA == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TC_TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TC_TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
+    if (NCTA == 2) cluster_sync_all(); else __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot_ptr;
+    // barriers that live on the leader only: "stage full" (both CTAs' loads land on it) and "accumulator drained"
+    const uint32_t lead_full = NCTA == 2 ? mapa_rank(bar_full, 0) : bar_full;
+    const uint32_t lead_tempty = NCTA == 2 ? mapa_rank(bar_tempty, 0) : bar_tempty;
 
     if (warp == kProdWarp) {
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
+            bool lockstep = true;
             for (int t = t_begin; t < t_end; t++) {
-                if (a.group > 1) {
+                if (a.group > 1 && rank == 0) {
                     // Lockstep within the group: start row tile i only when every member has started tile i-1, so at
                     // most two row tiles per group are live in L2 (members that drift apart would each pull their own
-                    // copy from HBM and push the others' out).  All CTAs are co-resident (cooperative launch).
+                    // copy from HBM and push the others' out).  It is a locality measure, not a correctness one: a
+                    // member that waits a millisecond (its neighbours are not resident yet, say, because another
+                    // kernel holds their SMs) stops waiting for good, so the kernel needs no co-residency guarantee.
+                    // The second CTA of a pair follows its leader through the stage barriers.
                     const uint32_t need = (uint32_t)a.group * (uint32_t)(t - t_begin);
                     volatile uint32_t *ctr = a.group_sync + grp;
-                    while (*ctr < need) __nanosleep(200);
+                    for (int spins = 0; lockstep && *ctr < need; spins++) {
+                        __nanosleep(200);
+                        if (spins > 5000) lockstep = false;
+                    }
                     atomicAdd(a.group_sync + grp, 1u);
                 }
-                for (int mt = member; mt < m_tiles; mt += a.group) {
+                for (int mu = member; mu < m_units; mu += a.group) {
+                    const int mt = mu * NCTA + rank;
                     for (int kb = 0; kb < kb_count; kb++) {
                         mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                        const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
-                        mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
-                        tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * bk, mt * TC_BM);
-                        tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * bk, t * TC_BN);
-                        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                        const uint32_t sa = base + stage * STAGE_BYTES, sb = sa + TC_A_BYTES;
+                        if (NCTA == 2) {
+                            if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * STAGE_BYTES);
+                            tma_load_2d_pair(sa, &map_q, lead_full + 8 * stage, kb * bk, mt * TC_BM);
+                            tma_load_2d_pair(sb, &map_x, lead_full + 8 * stage, kb * bk, t * TC_BN + rank * (TC_BN / 2));
+                        } else {
+                            mbar_expect_tx(bar_full + 8 * stage, STAGE_BYTES);
+                            tma_load_2d(sa, &map_q, bar_full + 8 * stage, kb * bk, mt * TC_BM);
+                            tma_load_2d(sb, &map_x, bar_full + 8 * stage, kb * bk, t * TC_BN);
+                        }
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
             }
         }
     } else if (warp == kMmaWarp) {
-        if (lane == 0) {
+        if (lane == 0 && rank == 0) {
             int stage = 0; uint32_t phase = 0;
             int it = 0;
-#ifdef DA_TC_PROFILE
-            long long w_tempty = 0, w_full = 0, t_start = clock64(), c0;
-#endif
             for (int t = t_begin; t < t_end; t++) {
-                for (int mt = member; mt < m_tiles; mt += a.group, it++) {
+                for (int mu = member; mu < m_units; mu += a.group, it++) {
                     const int as = it & 1;
                     const uint32_t aphase = (uint32_t)(it >> 1) & 1;
-#ifdef DA_TC_PROFILE
-                    c0 = clock64();
-#endif
                     mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
-#ifdef DA_TC_PROFILE
-                    w_tempty += clock64() - c0;
-#endif
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t tmem_d = tmem_base + (uint32_t)as * TC_BN;
                     for (int kb = 0; kb < kb_count; kb++) {
-#ifdef DA_TC_PROFILE
-                        c0 = clock64();
-#endif
                         mbar_wait(bar_full + 8 * stage, phase);
-#ifdef DA_TC_PROFILE
-                        w_full += clock64() - c0;
-#endif
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                        const uint32_t sa = base + stage * STAGE_BYTES, sb = sa + TC_A_BYTES;
                         const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
 #pragma unroll
                         for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {     // 4 MMAs of 32 bytes of K each, either kind
-                            if (BF16) umma_bf16(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC_BF16, (uint32_t)((kb | k) != 0));
-                            else umma_tf32(tmem_d, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb | k) != 0));
+                            const uint64_t da_ = da0 + (uint64_t)(k * 2), db_ = db0 + (uint64_t)(k * 2);
+                            const uint32_t acc = (uint32_t)((kb | k) != 0);
+                            if (NCTA == 2) {
+                                if (BF16) umma_bf16_pair(tmem_d, da_, db_, TC_IDESC_BF16_PAIR, acc);
+                                else umma_tf32_pair(tmem_d, da_, db_, TC_IDESC_PAIR, acc);
+                            } else {
+                                if (BF16) umma_bf16(tmem_d, da_, db_, TC_IDESC_BF16, acc);
+                                else umma_tf32(tmem_d, da_, db_, TC_IDESC, acc);
+                            }
                         }
-                        umma_commit(bar_empty + 8 * stage);
-                        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                        if (NCTA == 2) umma_commit_pair(bar_empty + 8 * stage); else umma_commit(bar_empty + 8 * stage);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
-                    umma_commit(bar_tfull + 8 * as);
+                    if (NCTA == 2) umma_commit_pair(bar_tfull + 8 * as); else umma_commit(bar_tfull + 8 * as);
                 }
             }
-#ifdef DA_TC_PROFILE
-            if ((blockIdx.x % 37) == 0)
-                printf("cta %d pairs %d total %lld wait_tempty %lld wait_full %lld\n", (int)blockIdx.x, it,
-                       clock64() - t_start, w_tempty, w_full);
-#endif
         }
     } else {
         // ===== epilogue warps 0..3: thread = query `qlocal` of every query tile =====
         const uint32_t quad = (uint32_t)warp & 3u;
         const int etid = (int)threadIdx.x - kEpiFirst * 32;                      // 0..127 among the epilogue threads
         const uint32_t qlocal = quad * 32u + (uint32_t)lane;
-        for (int mt = member; mt < m_tiles; mt += a.group) gate_s[mt * TC_BM + qlocal] = a.floor_eps;
+        for (int mu = member; mu < m_units; mu += a.group) gate_s[(mu * NCTA + rank) * TC_BM + qlocal] = a.floor_eps;
         int it = 0, visited = 0, next_refresh = 1;
-#ifdef DA_TC_PROFILE
-        long long e_wait = 0, e_p1 = 0, e_p2 = 0, e_pre = 0, e0;
-#endif
         for (int t = t_begin; t < t_end; t++, visited++) {
-#ifdef DA_TC_PROFILE
-            e0 = clock64();
-#endif
             const uint32_t n0 = (uint32_t)t * TC_BN;
             // per-row factor for this row tile: 1/|row|, or 0 when the row is absent, zero or filtered out
             float *inv_t = s_inv + (t & 1) * TC_BN;
@@ -486,7 +546,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
             // tighten this thread's gates from the shared histograms: often at first, then every 16 row tiles
             if (visited == next_refresh) {
                 next_refresh = visited < 4 ? visited + 1 : (visited < 16 ? visited + 2 : visited + 16);
-                for (int mt = member; mt < m_tiles; mt += a.group) {
+                for (int mu = member; mu < m_units; mu += a.group) {
+                    const int mt = mu * NCTA + rank;
                     const uint32_t q = (uint32_t)mt * TC_BM + qlocal;
                     if (q < (uint32_t)a.batch) {
                         const float lb = hist_kth_lower_bound(a.hist + (size_t)q * kHistWords, a.k);
@@ -495,10 +556,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 }
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
-#ifdef DA_TC_PROFILE
-            e_pre += clock64() - e0;
-#endif
-            for (int mt = member; mt < m_tiles; mt += a.group, it++) {
+            for (int mu = member; mu < m_units; mu += a.group, it++) {
+                const int mt = mu * NCTA + rank;
                 const int as = it & 1;
                 const uint32_t aphase = (uint32_t)(it >> 1) & 1;
                 const uint32_t q = (uint32_t)mt * TC_BM + qlocal;
@@ -517,13 +576,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 const uint32_t *qmask = (per_query && q_valid) ? a.doc_bitmap + (size_t)q * a.bitmap_stride : nullptr;
                 unsigned long long *lst = a.cand + (size_t)q * a.cap;
                 uint32_t *hq = a.hist + (size_t)q * kHistWords;
-#ifdef DA_TC_PROFILE
-                e0 = clock64();
-#endif
                 mbar_wait(bar_tfull + 8 * as, aphase);
-#ifdef DA_TC_PROFILE
-                e_wait += clock64() - e0; e0 = clock64();
-#endif
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * TC_BN;
                 // pass 1, branch-free: how many of the 256 rows pass this query's gate, and in which 32-row chunks
@@ -564,12 +617,10 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                                 }
                             }
                         }
+                        __syncwarp();
                     }
                     hits = kept;
                 }
-#ifdef DA_TC_PROFILE
-                e_p1 += clock64() - e0; e0 = clock64();
-#endif
                 // pass 2 (chunks with survivors only): one slot reservation per query, then plain stores and
                 // fire-and-forget histogram increments
                 uint32_t wh = __reduce_or_sync(0xFFFFFFFFu, hits);
@@ -603,27 +654,26 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                                 }
                             }
                         }
+                        __syncwarp();       // the next TMEM load is warp-wide
                     }
                 }
-#ifdef DA_TC_PROFILE
-                e_p2 += clock64() - e0;
-#endif
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+                if (lane == 0) {
+                    if (NCTA == 2) mbar_arrive_cluster(lead_tempty + 8 * as); else mbar_arrive(bar_tempty + 8 * as);
+                }
             }
         }
-#ifdef DA_TC_PROFILE
-        if ((blockIdx.x % 37) == 0 && lane == 0)
-            printf("cta %d warp %d pre %lld wait_tfull %lld pass1 %lld pass2 %lld\n", (int)blockIdx.x, warp, e_pre, e_wait, e_p1, e_p2);
-#endif
     }
 
+    // a pair leaves together: the leader's MMAs read the other CTA's shared memory and write its TMEM
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
+    __syncwarp();
+    if (NCTA == 2) cluster_sync_all(); else __syncthreads();
     if (warp == kMmaWarp) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
+        if (NCTA == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS) : "memory");
     }
 }
 
@@ -723,14 +773,20 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
 {
     const bool bf16 = q_hi && x_hi;       // split-plane store: contract the upper planes as bf16 (kind::f16)
     if (batch > DA_TC_MAX_BATCH) return cudaErrorInvalidValue;
+    const int m_tiles = tc_batch_m_tiles(batch);
+    // CTA pairs need two query tiles to work on; DA_TC_SINGLE_CTA=1 keeps the single-CTA form (for comparisons)
+    static const bool single_only = [] { const char *v = getenv("DA_TC_SINGLE_CTA"); return v && v[0] == '1'; }();
+    const int ncta = (m_tiles >= 2 && !single_only) ? 2 : 1;
     CUtensorMap map_q, map_x;
     if (bf16) {
         if ((reinterpret_cast<uintptr_t>(x_hi) & 15) || (reinterpret_cast<uintptr_t>(q_hi) & 15) || (D & 7)) return cudaErrorInvalidValue;
-        if (!make_map_bf16(&map_q, q_hi, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map_bf16(&map_x, x_hi, (uint64_t)n_rows, (uint64_t)D, TC_BN))
+        if (!make_map_bf16(&map_q, q_hi, (uint64_t)batch, (uint64_t)D, TC_BM) ||
+            !make_map_bf16(&map_x, x_hi, (uint64_t)n_rows, (uint64_t)D, TC_BN / ncta))
             return cudaErrorInvalidValue;
     } else {
         if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
-        if (!make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, TC_BM) || !make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BN))
+        if (!make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, TC_BM) ||
+            !make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BN / ncta))
             return cudaErrorInvalidValue;
     }
     cudaError_t e = cudaMemsetAsync(cand_count, 0, (size_t)batch * 4, stream);
@@ -743,35 +799,51 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
     a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
     a.bf16 = bf16 ? 1 : 0;
-    const void *kernel = bf16 ? (const void *)tc_batch_candidates_kernel<true> : (const void *)tc_batch_candidates_kernel<false>;
+    const void *kernel = ncta == 2
+        ? (bf16 ? (const void *)tc_batch_candidates_kernel<true, 2> : (const void *)tc_batch_candidates_kernel<false, 2>)
+        : (bf16 ? (const void *)tc_batch_candidates_kernel<true, 1> : (const void *)tc_batch_candidates_kernel<false, 1>);
     e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
     if (e != cudaSuccess) return e;
+
+    cudaLaunchAttribute attrs[1];
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = TCB_SMEM_BYTES; cfg.stream = stream;
+    cfg.attrs = attrs; cfg.numAttrs = 0;
+    int n_units = sm_count / ncta;           // CTAs, or CTA pairs, that can be resident at once
+    if (ncta == 2) {
+        attrs[cfg.numAttrs].id = cudaLaunchAttributeClusterDimension;
+        attrs[cfg.numAttrs].val.clusterDim.x = 2; attrs[cfg.numAttrs].val.clusterDim.y = 1; attrs[cfg.numAttrs].val.clusterDim.z = 1;
+        cfg.numAttrs++;
+        cfg.gridDim = dim3((unsigned)(2 * n_units));
+        int max_pairs = 0;
+        e = cudaOccupancyMaxActiveClusters(&max_pairs, kernel, &cfg);
+        if (e != cudaSuccess) return e;
+        if (max_pairs < 1) return cudaErrorLaunchOutOfResources;
+        if (n_units > max_pairs) n_units = max_pairs;
+    }
     const uint32_t n_tiles = (n_rows + TC_BN - 1) / TC_BN;
     // Row tiles in flight across the chip (one per group) plus the queries should sit in a fraction of the
     // 126 MB L2; otherwise every query tile pulls its row tile from HBM again.  Measured on cfg4 (4096 queries,
-    // 1.25M x 1536 rows, free-running groups of 1/4/16/32): 274/188/152/102 GB of DRAM reads for a 7.7 GB shard;
+    // 1.25M x 1536 rows, free-running groups of 1/4/16/32 CTAs): 274/188/152/102 GB of DRAM reads for a 7.7 GB shard;
     // with the members of a group in lockstep (below): 44 GB at group 4, 22.7 GB at group 8 (profiles/README.md).
-    const int m_tiles = tc_batch_m_tiles(batch);
+    const int m_units = (m_tiles + ncta - 1) / ncta;
     const double esz = bf16 ? 2.0 : 4.0;
     const double tile_mb = (double)TC_BN * D * esz / 1e6, q_mb = (double)batch * D * esz / 1e6;
     int group = 1;
-    while (group < m_tiles && group < sm_count && 2.0 * (sm_count / group) * tile_mb + q_mb > 90.0) group++;   // two live row tiles per group (lockstep window)
-    if (group > m_tiles) group = m_tiles;
-    int n_groups = sm_count / group;
+    while (group < m_units && group < n_units && 2.0 * (n_units / group) * tile_mb + q_mb > 90.0) group++;   // two live row tiles per group (lockstep window)
+    if (group > m_units) group = m_units;
+    int n_groups = n_units / group;
     if ((uint32_t)n_groups > n_tiles) n_groups = (int)n_tiles;
     if (n_groups < 1) n_groups = 1;
     a.group = group;
     a.group_sync = group_sync;
-    const uint32_t grid = (uint32_t)(n_groups * group);
-    void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a};
+    cfg.gridDim = dim3((unsigned)(n_groups * group * ncta));
     if (group > 1) {
-        // members of a group wait for each other: every CTA must be resident, which a cooperative launch guarantees
         e = cudaMemsetAsync(group_sync, 0, (size_t)n_groups * 4, stream);
         if (e != cudaSuccess) return e;
-        e = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(TC_THREADS), args, TCB_SMEM_BYTES, stream);
-    } else {
-        e = cudaLaunchKernel(kernel, dim3(grid), dim3(TC_THREADS), args, TCB_SMEM_BYTES, stream);
     }
+    void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a};
+    e = cudaLaunchKernelExC(&cfg, kernel, args);
     if (e != cudaSuccess) return e;
     batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a.floor_eps, a.two_eps, gate_ordered);
     return cudaGetLastError();
