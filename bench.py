@@ -390,6 +390,7 @@ def main():
         flops = 2.0 * (hi - lo) * BATCH * DIM
         tpeak, tsrc = measured_tensor_peak(bf16=SPLIT16)
         tach = flops / (scan_ms / 1e3) / 1e12 if scan_ms > 0 else 0.0
+    if tensor_path and flops / (tpeak * 1e12) > bytes_per_launch / (peak * 1e9):     # else reading the rows once costs more: HBM-bound
         line["roofline"] = {"bound": "tensor", "achieved": tach, "peak": tpeak, "unit": "TFLOP/s", "frac": tach / tpeak,
                             "traffic": None, "kernel": "tc_batch_candidates_kernel (+ exact re-score and select, inside kernel_ms)",
                             "peak_source": tsrc, "flops_per_launch": flops, "kernel_ms": scan_ms,
