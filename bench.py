@@ -354,7 +354,7 @@ def main():
     t0 = time.perf_counter()
     last = None
     for i in range(steps):
-        last = st.search(qbatch(warmup + i), TOP_K, **skw)
+        last = st.search_arrays(qbatch(warmup + i), TOP_K, **skw)
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
@@ -382,7 +382,7 @@ def main():
                                 "tc_batch_candidates_kernel + rescore + select"), "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,
                      "frac_of_nominal_8000": achieved / 8000.0},
-        "result_check": {"hits": int(len(last[2][0])), "top_score": float(last[1][0][0]) if len(last[1][0]) else None},
+        "result_check": {"hits": int(last[3][0]), "top_score": float(last[1][0][0]) if last[3][0] else None},
     }
     if tensor_path:
         # batched searches are a contraction: the bound is the tensor pipe, not HBM.  Algorithmic flops of one pass =

@@ -211,6 +211,20 @@ class GpuStore:
                probes: int = 0, no_tensor: bool = False):
         """queries: dim or batch x dim.  doc_ids: one n x 16 array for the whole batch, or a list with one
         array per query.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
+        out_ids, out_scores, out_rows, out_n = self.search_arrays(
+            queries, k, doc_ids, all_docs=all_docs, min_similarity=min_similarity, read_all_rows=read_all_rows,
+            ivf=ivf, probes=probes, no_tensor=no_tensor)
+        b = out_n.shape[0]
+        return ([out_ids[i, :out_n[i]] for i in range(b)],
+                [out_scores[i, :out_n[i]] for i in range(b)],
+                [out_rows[i, :out_n[i]] for i in range(b)])
+
+    def search_arrays(self, queries, k: int, doc_ids=None, *, all_docs: bool = False,
+                      min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
+                      probes: int = 0, no_tensor: bool = False):
+        """The C-ABI call as it is: (chunk_ids[b,k,16], scores[b,k], rows[b,k], n[b]); query i has n[i] hits,
+        the rest of its k slots are zero.  No per-query Python objects (a batch of 4096 would spend longer
+        building lists than searching)."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
@@ -223,9 +237,7 @@ class GpuStore:
         _check(self._lib.da_store_search(self._h, C.byref(p), out_ids.ctypes.data, out_scores.ctypes.data,
                                          out_rows.ctypes.data, out_n.ctypes.data))
         del keep
-        return ([out_ids[i, :out_n[i]].copy() for i in range(b)],
-                [out_scores[i, :out_n[i]].copy() for i in range(b)],
-                [out_rows[i, :out_n[i]].copy() for i in range(b)])
+        return out_ids, out_scores, out_rows, out_n
 
     def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False):
         p = L.da_search_params()
