@@ -40,6 +40,7 @@ FILTER_DOCS = 0          # 0 = every document requested
 READ_ALL = False
 NO_TENSOR = False
 SPLIT16 = False         # split-plane resident format (lossless; the scan reads the upper 16-bit plane only)
+Q8 = False              # int8 sidecar next to the fp32 rows (the scan reads one byte per element, answers stay exact)
 METRIC = "cosine top-k queries/sec at 10M x 3072"
 UNIT = "queries/s"
 
@@ -47,6 +48,9 @@ UNIT = "queries/s"
 WORKLOADS = {
     "cfg3_b1": {},
     "cfg3_b1_split16": {"SPLIT16": True},
+    "cfg3_b1_q8": {"Q8": True},
+    "cfg3_b8_q8": {"Q8": True, "BATCH": 8},
+    "cfg2_predicate_q8": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16, "READ_ALL": True, "Q8": True},
     "cfg3_b64_split16": {"BATCH": 64, "SPLIT16": True},
     "cfg4_split16": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf"), "SPLIT16": True},
     "cfg3_b64": {"BATCH": 64},
@@ -66,6 +70,8 @@ def workload_name(n_gpus: int) -> str:
         path = ("split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"
                 if BATCH < 16 else
                 "split-plane layout: tcgen05 bf16 contraction of the upper planes for candidates + exact fp32 re-score")
+    if Q8 and (BATCH < 16 or NO_TENSOR or FILTER_DOCS):
+        path = "int8 sidecar: dp4a scan of one byte per element for candidates + exact fp32 re-score from the fp32 rows"
     return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch={BATCH}, top_k={TOP_K}, "
             f"{flt}, min_similarity={MIN_SIM}, {path}, local top-k + NCCL all-gather merge")
 
@@ -311,7 +317,7 @@ def main():
     S = synth.Synth()
     lo, hi = shard_range(rank, world, N_ROWS, S.chunks_per_doc)
     st = GpuStore(dim=DIM, capacity_rows=max(1, hi - lo), devices=(local_rank,), min_similarity=MIN_SIM,
-                  world_size=world, rank=rank, nccl_id=nccl_id, split16=SPLIT16)
+                  world_size=world, rank=rank, nccl_id=nccl_id, split16=SPLIT16, q8_sidecar=Q8)
     st.generate_synthetic(S, lo, hi - lo)
     n_q = (warmup + steps) * BATCH if BATCH <= 64 else 2 * BATCH
     queries = np.stack([synth.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(n_q)])
@@ -378,6 +384,7 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(bytes_per_launch) if args.workload == "cfg3_b1" else None,
                      "kernel": ("scan_topk_kernel (upper plane) + split collect/rescore/select" if SPLIT16 else
+                                "q8_scan_kernel + collect/rescore/select" if "int8 sidecar" in workload_name(world) else
                                 "scan_topk_kernel" if "SIMT" in workload_name(world) else
                                 "tc_batch_candidates_kernel + rescore + select"), "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,

@@ -158,7 +158,8 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
                                   int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream,
-                                  const uint16_t *hi = nullptr, const uint16_t *lo = nullptr);
+                                  const uint16_t *hi = nullptr, const uint16_t *lo = nullptr,
+                                  bool gate_bounds_exact = false);   // true: the gate also bounds the k-th best EXACT score
 
 // ---------------------------------------------------------------------------
 // Split-plane layout (da_split.cu): every fp32 element lives as two 16-bit halves in two planes (lossless,
@@ -188,5 +189,18 @@ void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);
 void synth_vector_host(uint64_t seed_noise, uint64_t noise_index, uint64_t seed_centroid, uint64_t cluster,
                        int cmul, int nmul, int dim, float *out);
 void synth_id_host(uint64_t seed_ids, int kind, uint64_t index, uint8_t out[16]);
+
+// ---------------------------------------------------------------------------
+// int8 sidecar (da_q8.cu): candidates from one byte per element, exact answers after the fp32 re-score
+// ---------------------------------------------------------------------------
+// rows [first, first + n), or the n rows listed in `rows` (device), of `mat` -> q8 / factor / err
+cudaError_t launch_q8_quantize_rows(const float *mat, int dim, const uint32_t *rows, uint32_t first, uint32_t n,
+                                    const float *inv_norm, int8_t *q8, float *factor, float *err, cudaStream_t stream);
+// quantise a.nq queries, scan the int8 rows, collect every row whose interval reaches the k-th best lower end;
+// candidates are left for launch_rescore_select (cand / cand_count / gate_ordered)
+cudaError_t launch_q8_candidates(const ScanArgs &a, const int8_t *q8, const float *factor, const float *err,
+                                 int8_t *q8_queries, float *qfactor, float *qerr, key_t64 *cand, uint32_t cap,
+                                 uint32_t *cand_count, uint32_t *gate_ordered, uint32_t *overflow, int sm_count,
+                                 cudaStream_t stream, int *grid_out);
 
 }  // namespace da

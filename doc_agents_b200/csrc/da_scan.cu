@@ -212,55 +212,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         if (lane == 0 && tot) atomicAdd(a.rows_read, (unsigned long long)tot);
     }
 
-    // ---- CTA epilogue: k best of this CTA per query -> global scratch
-    for (int q = 0; q < a.nq; q++) {
-        cta_bitonic_desc(lists + (size_t)q * P, P);
-        for (int i = tid; i < K; i += kScanThreads)
-            a.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
-    }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        unsigned int t = atomicAdd(a.counter, 1u);
-        is_last_s = (t == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!is_last_s) return;
-    __threadfence();
-
-    // ---- last CTA: merge gridDim.x * K keys per query, then write the records
-    for (int q = 0; q < a.nq; q++) {
-        key_t64 *buf = lists + (size_t)q * P;
-        const uint32_t total = gridDim.x * (uint32_t)K;
-        for (int i = tid; i < K; i += kScanThreads) buf[i] = 0ull;
-        uint32_t done = 0;
-        while (done < total) {
-            __syncthreads();
-            const uint32_t room = (uint32_t)(P - K);
-            for (uint32_t i = tid; i < room; i += kScanThreads) {
-                uint32_t j = done + i;
-                key_t64 v = 0ull;
-                if (j < total) {
-                    uint32_t cta = j / K, idx = j % K;
-                    v = __ldcg(&a.cta_out[((size_t)cta * a.nq + q) * K + idx]);
-                }
-                buf[K + i] = v;
-            }
-            cta_bitonic_desc(buf, P);
-            done += room;
-        }
-        for (int i = tid; i < K; i += kScanThreads) {
-            key_t64 key = buf[i];
-            a.out_keys[(size_t)q * K + i] = key;
-            if (a.out_ids) {
-                uint4 id = make_uint4(0, 0, 0, 0);
-                if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
-                reinterpret_cast<uint4 *>(a.out_ids)[(size_t)q * K + i] = id;
-            }
-        }
-        __syncthreads();
-    }
-    if (tid == 0) *a.counter = 0u;
+    scan_cta_epilogue(a, lists, &is_last_s);
 }
 
 
@@ -386,7 +338,6 @@ __global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gat
 // ---------------------------------------------------------------------------
 namespace {
 
-constexpr int kRescoreBlocksPerQuery = 4;
 
 // Candidates below the query's final gate are dropped without touching their rows; the others get their
 // exact fp32 score with the scan kernel's own arithmetic (same lane ownership, x-y-z-w FMA order, xor-shuffle
@@ -396,11 +347,12 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
                                                                  uint32_t *surv_count, uint32_t *overflow, const float *mat,
                                                                  int dim, const float *inv_norm, const float *queries,
                                                                  const float *q_inv, uint32_t row_base, float min_sim,
-                                                                 const uint16_t *hi, const uint16_t *lo)
+                                                                 const uint16_t *hi, const uint16_t *lo, uint32_t blocks_per_query,
+                                                                 int gate_bounds_exact)
 {
-    const uint32_t q = blockIdx.x / kRescoreBlocksPerQuery, part = blockIdx.x % kRescoreBlocksPerQuery;
+    const uint32_t q = blockIdx.x / blocks_per_query, part = blockIdx.x % blocks_per_query;
     const uint32_t cnt = min(cand_count[q], (uint32_t)cap);
-    const uint32_t per = (cnt + kRescoreBlocksPerQuery - 1) / kRescoreBlocksPerQuery;
+    const uint32_t per = (cnt + blocks_per_query - 1) / blocks_per_query;
     const uint32_t e_lo = part * per, e_hi = min(cnt, e_lo + per);      // this block's share of the list
     if (e_lo >= e_hi) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -409,6 +361,8 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
     const float4 *qv = reinterpret_cast<const float4 *>(queries + (size_t)q * dim);
     const float qi = q_inv[q];
     const uint32_t gate = gate_ordered[q];
+    // int8 sidecar: the gate is also a lower bound of the k-th best EXACT score, so exact scores below it are out
+    const float exact_floor = gate_bounds_exact ? fmaxf(min_sim, ordered_to_score(gate)) : min_sim;
     const key_t64 *lst = cand + (size_t)q * cap;
     for (uint32_t i0 = e_lo + (uint32_t)warp * 32u; i0 < e_hi; i0 += 8u * 32u) {
         const uint32_t i = i0 + (uint32_t)lane;
@@ -437,11 +391,25 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
                     acc = fmaf(x[4], w1.x, acc); acc = fmaf(x[5], w1.y, acc); acc = fmaf(x[6], w1.z, acc); acc = fmaf(x[7], w1.w, acc);
                 }
             } else if (vec8) {   // the scan's 256-bit path: a lane owns 8 consecutive floats
-                for (int c = lane; c < (D4 >> 1); c += 32) {
+                // four slots of loads in flight per lane (a warp works on one row at a time, so the row's latency is
+                // paid per candidate); the FMAs keep the scan's order
+                for (int c0 = lane; c0 < (D4 >> 1); c0 += 32 * 4) {
+                    float4 v[4][2];
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        const float4 v = ldg_stream(rp + 2 * c + h), w = qv[2 * c + h];
-                        acc = fmaf(v.x, w.x, acc); acc = fmaf(v.y, w.y, acc); acc = fmaf(v.z, w.z, acc); acc = fmaf(v.w, w.w, acc);
+                    for (int u = 0; u < 4; u++) {
+                        const int c = c0 + 32 * u;
+                        if (c < (D4 >> 1)) { v[u][0] = ldg_stream(rp + 2 * c); v[u][1] = ldg_stream(rp + 2 * c + 1); }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const int c = c0 + 32 * u;
+                        if (c < (D4 >> 1)) {
+#pragma unroll
+                            for (int h = 0; h < 2; h++) {
+                                const float4 x = v[u][h], w = qv[2 * c + h];
+                                acc = fmaf(x.x, w.x, acc); acc = fmaf(x.y, w.y, acc); acc = fmaf(x.z, w.z, acc); acc = fmaf(x.w, w.w, acc);
+                            }
+                        }
                     }
                 }
             } else {
@@ -454,7 +422,7 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
             for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
             float sim = acc * inv_norm[row] * qi;
             sim = fminf(1.f, fmaxf(-1.f, sim));
-            if (lane == 0 && sim >= min_sim) {
+            if (lane == 0 && sim >= exact_floor) {
                 const uint32_t pos = atomicAdd(surv_count + q, 1u);
                 if (pos < (uint32_t)kSurvivorCap) surv[(size_t)q * kSurvivorCap + pos] = make_key(sim, row_base + row);
                 else *overflow = 1u;
@@ -464,7 +432,7 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
 }
 
 // One CTA per query: top-k of its re-scored survivors, then the chunk-id gather.
-__global__ void __launch_bounds__(256) select_candidates_kernel(const key_t64 *surv, const uint32_t *surv_count, int k, int P,
+__global__ void __launch_bounds__(1024) select_candidates_kernel(const key_t64 *surv, const uint32_t *surv_count, int k, int P,
                                                                 const uint8_t *chunk_ids, uint32_t row_base,
                                                                 key_t64 *out_keys, uint8_t *out_ids)
 {
@@ -499,19 +467,24 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
                                   const float *mat, int dim, const float *inv_norm, const float *queries,
                                   const float *q_inv, const uint8_t *chunk_ids, uint32_t row_base, float min_sim,
                                   int k, key_t64 *out_keys, uint8_t *out_ids, cudaStream_t stream,
-                                  const uint16_t *hi, const uint16_t *lo)
+                                  const uint16_t *hi, const uint16_t *lo, bool gate_bounds_exact)
 {
     cudaError_t e = cudaMemsetAsync(surv_count, 0, (size_t)batch * 4, stream);
     if (e != cudaSuccess) return e;
-    rescore_candidates_kernel<<<(unsigned)batch * kRescoreBlocksPerQuery, 256, 0, stream>>>(
+    // a few queries with long lists (the int8 sidecar) or thousands with short ones (the tensor path): about two
+    // blocks per SM either way, never fewer than four per query
+    uint32_t bpq = (uint32_t)((2 * 148 + batch - 1) / batch);
+    if (bpq < 4) bpq = 4;
+    rescore_candidates_kernel<<<(unsigned)batch * bpq, 256, 0, stream>>>(
         cand, cand_count, cap, gate_ordered, surv, surv_count, overflow, mat, dim, inv_norm, queries, q_inv, row_base, min_sim,
-        hi, lo);
+        hi, lo, bpq, gate_bounds_exact ? 1 : 0);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    const bool few = batch <= kMaxNQ;           // one CTA per query: give it more threads and wider rounds when CTAs are few
     int P = next_pow2(2 * k);
-    if (P < 1024) P = 1024;
-    select_candidates_kernel<<<batch, 256, (size_t)P * sizeof(key_t64), stream>>>(surv, surv_count, k, P, chunk_ids, row_base,
-                                                                                  out_keys, out_ids);
+    if (P < (few ? 2048 : 1024)) P = few ? 2048 : 1024;
+    select_candidates_kernel<<<batch, few ? 1024 : 256, (size_t)P * sizeof(key_t64), stream>>>(surv, surv_count, k, P, chunk_ids,
+                                                                                            row_base, out_keys, out_ids);
     return cudaGetLastError();
 }
 

@@ -107,6 +107,8 @@ struct Shard {
     uint32_t n_rows = 0, row_base = 0;
     float *mat = nullptr, *inv_norm = nullptr;
     uint16_t *hi = nullptr, *lo = nullptr;      // split-plane layout: upper / lower 16 bits of every element
+    int8_t *q8 = nullptr;                       // int8 sidecar (DA_STORE_Q8_SIDECAR): rint(x / scale) of every element
+    float *q8_factor = nullptr, *q8_err = nullptr;   // ... per row: scale / |row|, and its quantisation error bound
     uint32_t *doc_slot = nullptr;
     uint8_t *chunk_ids = nullptr;
     cudaStream_t stream = nullptr;
@@ -124,6 +126,8 @@ struct Shard {
     DevBuf<float> d_approx;                     // split-plane layout: approximate scores of every row
     DevBuf<uint16_t> d_qhi;                     // ... and the queries' upper halves for the bf16 contraction
     DevBuf<unsigned long long> d_akeys;         // ... and the scan's approximate top-k
+    DevBuf<int8_t> d_q8q;                       // int8 sidecar: quantised queries, their factors and error bounds
+    DevBuf<float> d_q8qf, d_q8qe;
     PinBuf<uint32_t> h_overflow;
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
@@ -198,6 +202,7 @@ struct da_store {
     bool bleader = false;
     uint64_t topk_calls = 0, topk_passes = 0;
     bool split16 = false;          // split-plane resident format (DA_STORE_SPLIT16)
+    bool q8 = false;               // int8 sidecar next to the fp32 rows (DA_STORE_Q8_SIDECAR)
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
@@ -210,12 +215,12 @@ void free_shard(Shard &s)
     free_ivf(s);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
-    cudaFree(s.mat); cudaFree(s.hi); cudaFree(s.lo); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
+    cudaFree(s.mat); cudaFree(s.hi); cudaFree(s.lo); cudaFree(s.q8); cudaFree(s.q8_factor); cudaFree(s.q8_err); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
     cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
-    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release();
+    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release(); s.d_q8q.release(); s.d_q8qf.release(); s.d_q8qe.release();
     s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release(); s.d_group_sync.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
@@ -231,7 +236,7 @@ void free_shard(Shard &s)
     s = Shard();
 }
 
-int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16)
+int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, bool q8)
 {
     s.device = device;
     s.cap_rows = cap_rows;
@@ -243,7 +248,7 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16)
     s.sm_count = prop.multiProcessorCount;
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
-    const uint64_t need = cap_rows * ((uint64_t)dim * 4 + 4 + 4 + 16);
+    const uint64_t need = cap_rows * ((uint64_t)dim * 4 + 4 + 4 + 16 + (q8 ? (uint64_t)dim + 8 : 0));
     if (need + (512ull << 20) > free_b)
         return fail(DA_ERR_CAPACITY, "capacity_rows=%llu x dim=%d needs %.2f GB on device %d, %.2f GB free (no CPU fallback)",
                     (unsigned long long)cap_rows, dim, need / 1e9, device, free_b / 1e9);
@@ -256,6 +261,11 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16)
         CU(cudaMalloc((void **)&s.lo, cap_rows * (uint64_t)dim * 2));
     } else {
         CU(cudaMalloc((void **)&s.mat, cap_rows * (uint64_t)dim * 4));
+    }
+    if (q8) {
+        CU(cudaMalloc((void **)&s.q8, cap_rows * (uint64_t)dim));
+        CU(cudaMalloc((void **)&s.q8_factor, cap_rows * 4));
+        CU(cudaMalloc((void **)&s.q8_err, cap_rows * 4));
     }
     CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
     CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
@@ -280,6 +290,7 @@ struct SearchPlan {
     bool ivf;
     int probes;
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
+    bool use_q8;       // int8 sidecar scan for the candidates + exact re-score from the fp32 rows
     uint32_t bitmap_stride;   // words between per-query bitmaps; 0 = one document set for the batch
 };
 
@@ -378,6 +389,19 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 a.out_keys = s.d_akeys.p; a.out_ids = nullptr;
             }
             int grid = 0;
+            if (pl.use_q8) {   // int8 sidecar: intervals for every row, candidates, exact re-score from the fp32 rows
+                const uint32_t cap = (uint32_t)std::min<uint64_t>(std::max<uint32_t>(s.n_rows, 1), 1u << 20);
+                a.approx = s.d_approx.p; a.out_keys = s.d_akeys.p; a.out_ids = nullptr;
+                CU(da::launch_q8_candidates(a, s.q8, s.q8_factor, s.q8_err, s.d_q8q.p, s.d_q8qf.p, s.d_q8qe.p, s.d_cand.p, cap,
+                                            s.d_cand_count.p, s.d_gate.p, s.d_overflow.p, s.sm_count, s.stream, &grid));
+                CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, (int)cap, s.d_gate.p, s.d_surv.p, s.d_surv_count.p,
+                                             s.d_overflow.p, a.nq, s.mat, dim, s.inv_norm, a.queries, a.q_inv_norm, s.chunk_ids,
+                                             s.row_base, pl.min_sim, pl.k, out_keys + (size_t)q0 * pl.k,
+                                             out_ids + (size_t)q0 * pl.k * 16, s.stream, nullptr, nullptr, true));
+                st->launches += 5;
+                if (first) { st->scan_grid = grid; st->scan_launches++; }
+                continue;
+            }
             CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
             st->launches++;
             if (first) { st->scan_grid = grid; st->scan_launches++; }
@@ -479,9 +503,22 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         pl.use_tc = selected * 4 >= st->docs.size() && selected > 0;
     }
+    pl.use_q8 = st->q8 && !ivf && !pl.use_tc && !(p->flags & DA_SEARCH_NO_Q8);
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
+        if (pl.use_q8) {
+            const size_t nq = (size_t)da::scan_pick_nq(st->dim, pl.k, p->batch);
+            CU(s.d_approx.ensure(nq * std::max<size_t>(s.n_rows, 1)));
+            CU(s.d_akeys.ensure(nq * (size_t)pl.k));
+            CU(s.d_cand.ensure(nq * (size_t)std::min<uint64_t>(std::max<uint32_t>(s.n_rows, 1), 1u << 20)));
+            CU(s.d_cand_count.ensure(nq)); CU(s.d_gate.ensure(nq)); CU(s.d_surv_count.ensure(nq));
+            CU(s.d_surv.ensure(nq * (size_t)da::kSurvivorCap));
+            CU(s.d_q8q.ensure(nq * (size_t)st->dim)); CU(s.d_q8qf.ensure(nq)); CU(s.d_q8qe.ensure(nq));
+            CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1));
+            CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
+            *s.h_overflow.p = 0;
+        }
         if (pl.use_tc) {
             CU(s.d_cand.ensure((size_t)p->batch * da::tc_batch_cap(pl.k)));
             CU(s.d_cand_count.ensure(p->batch)); CU(s.d_gate.ensure(p->batch)); CU(s.d_surv_count.ensure(p->batch));
@@ -561,6 +598,8 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
         st->last_bytes = rows_scanned * ((uint64_t)st->dim * 2 + (pl.all_docs ? 4 : 8));
     else if (st->split16)   // upper plane of the rows read + per row: 1/|row|, approximate score out and in (+ doc slot)
         st->last_bytes = rows_read * (uint64_t)st->dim * 2 + rows_scanned * (uint64_t)passes * (pl.all_docs ? 12 : 16);
+    else if (pl.use_q8)     // int8 rows read + per row: factor, error bound, upper end out and in (+ doc slot)
+        st->last_bytes = rows_read * (uint64_t)st->dim + rows_scanned * (uint64_t)passes * (pl.all_docs ? 16 : 20);
     else if (pl.use_tc)
         st->last_bytes = rows_scanned * ((uint64_t)st->dim * 4 + (pl.all_docs ? 4 : 8));   // every row once, whatever the batch
     else
@@ -601,6 +640,8 @@ int da_store_create(const da_config *cfg, da_store **out)
     if (cfg->struct_size != sizeof(da_config)) return fail(DA_ERR_INVALID, "da_config.struct_size=%u, expected %zu", cfg->struct_size, sizeof(da_config));
     if (cfg->dim <= 0 || (cfg->dim & 3)) return fail(DA_ERR_DIM, "dim=%d must be a positive multiple of 4", cfg->dim);
     if (cfg->dim > 16384) return fail(DA_ERR_DIM, "dim=%d exceeds 16384", cfg->dim);
+    if ((cfg->flags & DA_STORE_Q8_SIDECAR) && (cfg->dim % 32)) return fail(DA_ERR_DIM, "the int8 sidecar needs dim %% 32 == 0 (dim=%d)", cfg->dim);
+    if ((cfg->flags & DA_STORE_Q8_SIDECAR) && (cfg->flags & DA_STORE_SPLIT16)) return fail(DA_ERR_INVALID, "DA_STORE_Q8_SIDECAR and DA_STORE_SPLIT16 exclude each other");
     if ((cfg->flags & DA_STORE_SPLIT16) && (cfg->dim % 16)) return fail(DA_ERR_DIM, "the split-plane layout needs dim %% 16 == 0 (dim=%d)", cfg->dim);
     if (cfg->n_devices < 1 || cfg->n_devices > DA_MAX_DEVICES) return fail(DA_ERR_INVALID, "n_devices=%d out of range", cfg->n_devices);
     if (cfg->capacity_rows == 0) return fail(DA_ERR_INVALID, "capacity_rows is 0");
@@ -622,10 +663,11 @@ int da_store_create(const da_config *cfg, da_store **out)
     st->world = world; st->rank = rank; st->total_ranks = (int)total;
     st->batch_window_us = cfg->batch_window_us;
     st->split16 = (cfg->flags & DA_STORE_SPLIT16) != 0;
+    st->q8 = (cfg->flags & DA_STORE_Q8_SIDECAR) != 0;
     st->batch_max = cfg->batch_max ? std::min<uint32_t>(cfg->batch_max, DA_MAX_BATCH) : 64;
     st->shards.resize(cfg->n_devices);
     for (int i = 0; i < cfg->n_devices; i++) {
-        int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows, st->split16);
+        int rc = init_shard(st->shards[i], cfg->device_ids[i], cfg->dim, cfg->capacity_rows, st->split16, st->q8);
         if (rc != DA_OK) { da_store_destroy(st); return rc; }
         st->shards[i].row_base = (uint32_t)(((uint64_t)rank * cfg->n_devices + i) * cfg->capacity_rows);
     }
@@ -834,6 +876,11 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
                 CU(da::launch_commit_rows(sh.d_up_stage.p, dim, sh.d_up_rows.p + b, sh.d_up_slots.p + b, sh.d_up_ids.p + 16 * b,
                                           (uint32_t)(e - b), sh.mat, sh.inv_norm, sh.doc_slot, sh.chunk_ids, sh.stream));
             st->launches++;
+            if (st->q8) {
+                CU(da::launch_q8_quantize_rows(sh.mat, dim, sh.d_up_rows.p + b, 0, (uint32_t)(e - b), sh.inv_norm, sh.q8,
+                                               sh.q8_factor, sh.q8_err, sh.stream));
+                st->launches++;
+            }
         }
         if (st->ivf_lists) {   // keep the index current, as pgvector does on insert: nearest list for the touched rows
             CU(da::ivf_launch_assign(sh.mat, dim, sh.d_up_rows.p, (uint32_t)cnt, sh.ivf.cent, st->ivf_lists, sh.ivf.assign, 1, sh.stream));
@@ -896,7 +943,7 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         if (rc != DA_OK) return rc;
         for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
         bool overflow = false;
-        if (pl.use_tc || st->split16)
+        if (pl.use_tc || pl.use_q8 || st->split16)
             for (Shard &s : st->shards) overflow = overflow || (*s.h_overflow.p != 0);
         if (!overflow) break;
         if (st->split16 && !pl.use_tc)
@@ -904,9 +951,10 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         // A candidate list stayed full after pruning (a mass of scores within the TF32 slack of the k-th
         // best).  Every rank sees its own lists only, so in a multi-rank store this stays an error.
         if (st->total_ranks > 1 && st->world > 1)
-            return fail(DA_ERR_STATE, "tensor-core candidate list overflow; retry with DA_SEARCH_NO_TENSOR");
+            return fail(DA_ERR_STATE, "candidate list overflow; retry with DA_SEARCH_NO_TENSOR | DA_SEARCH_NO_Q8");
         st->tc_overflows++;
         pl.use_tc = false;                 // answer this batch with the SIMT scan instead
+        pl.use_q8 = false;                 // ... of the fp32 rows
         for (Shard &s : st->shards) {      // the flag is sticky on the device: clear it for the second attempt
             CU(cudaSetDevice(s.device));
             CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
@@ -1231,6 +1279,10 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
         } else {
             CU(da::launch_synth(a, s.mat, s.inv_norm, s.doc_slot, s.chunk_ids, s.stream));
             st->launches++;
+            if (st->q8) {
+                CU(da::launch_q8_quantize_rows(s.mat, st->dim, nullptr, 0, a.n_rows, s.inv_norm, s.q8, s.q8_factor, s.q8_err, s.stream));
+                st->launches++;
+            }
         }
         s.row_base = (uint32_t)lo;
         s.n_rows = (uint32_t)(hi - lo);

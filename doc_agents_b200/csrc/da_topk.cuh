@@ -75,6 +75,63 @@ __device__ void cta_bitonic_desc(key_t64 *buf, int P)
     __syncthreads();
 }
 
+// Tail of the scan kernels: the k best keys of this CTA per query go to global scratch; the last CTA to arrive
+// merges gridDim.x * k keys per query, writes a.out_keys and (if a.out_ids) gathers the chunk ids.
+// `lists` = a.nq x a.P keys in shared memory, filled by the warps (unused slots 0); blockDim.x = kScanThreads.
+__device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned int *is_last_s)
+{
+    const int tid = threadIdx.x, K = a.k, P = a.P;
+    // ---- CTA epilogue: k best of this CTA per query -> global scratch
+    for (int q = 0; q < a.nq; q++) {
+        cta_bitonic_desc(lists + (size_t)q * P, P);
+        for (int i = tid; i < K; i += kScanThreads)
+            a.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        unsigned int t = atomicAdd(a.counter, 1u);
+        *is_last_s = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!*is_last_s) return;
+    __threadfence();
+
+    // ---- last CTA: merge gridDim.x * K keys per query, then write the records
+    for (int q = 0; q < a.nq; q++) {
+        key_t64 *buf = lists + (size_t)q * P;
+        const uint32_t total = gridDim.x * (uint32_t)K;
+        for (int i = tid; i < K; i += kScanThreads) buf[i] = 0ull;
+        uint32_t done = 0;
+        while (done < total) {
+            __syncthreads();
+            const uint32_t room = (uint32_t)(P - K);
+            for (uint32_t i = tid; i < room; i += kScanThreads) {
+                uint32_t j = done + i;
+                key_t64 v = 0ull;
+                if (j < total) {
+                    uint32_t cta = j / K, idx = j % K;
+                    v = __ldcg(&a.cta_out[((size_t)cta * a.nq + q) * K + idx]);
+                }
+                buf[K + i] = v;
+            }
+            cta_bitonic_desc(buf, P);
+            done += room;
+        }
+        for (int i = tid; i < K; i += kScanThreads) {
+            key_t64 key = buf[i];
+            a.out_keys[(size_t)q * K + i] = key;
+            if (a.out_ids) {
+                uint4 id = make_uint4(0, 0, 0, 0);
+                if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
+                reinterpret_cast<uint4 *>(a.out_ids)[(size_t)q * K + i] = id;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *a.counter = 0u;
+}
+
 inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
 }  // namespace

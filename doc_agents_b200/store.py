@@ -82,7 +82,7 @@ class GpuStore:
     def __init__(self, dim: int = 3072, capacity_rows: int = 1 << 16, devices: Sequence[int] = (0,),
                  min_similarity: float = L.DA_DEFAULT_MIN_SIMILARITY, world_size: int = 1, rank: int = 0,
                  nccl_id: bytes | None = None, batch_window_us: int = 0, batch_max: int = 0,
-                 split16: bool = False):
+                 split16: bool = False, q8_sidecar: bool = False):
         lib = L.load()
         cfg = L.da_config()
         cfg.struct_size = C.sizeof(L.da_config)
@@ -95,7 +95,7 @@ class GpuStore:
         cfg.world_size = world_size
         cfg.rank = rank
         cfg.batch_window_us = batch_window_us
-        cfg.flags = L.DA_STORE_SPLIT16 if split16 else 0
+        cfg.flags = (L.DA_STORE_SPLIT16 if split16 else 0) | (L.DA_STORE_Q8_SIDECAR if q8_sidecar else 0)
         cfg.batch_max = batch_max
         if nccl_id is not None:
             assert len(nccl_id) == L.DA_NCCL_ID_BYTES
@@ -208,12 +208,12 @@ class GpuStore:
     # -- everything-exposed search on raw arrays -----------------------------------------
     def search(self, queries, k: int, doc_ids: np.ndarray | None = None, *, all_docs: bool = False,
                min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
-               probes: int = 0, no_tensor: bool = False):
+               probes: int = 0, no_tensor: bool = False, no_q8: bool = False):
         """queries: dim or batch x dim.  doc_ids: one n x 16 array for the whole batch, or a list with one
         array per query.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
         out_ids, out_scores, out_rows, out_n = self.search_arrays(
             queries, k, doc_ids, all_docs=all_docs, min_similarity=min_similarity, read_all_rows=read_all_rows,
-            ivf=ivf, probes=probes, no_tensor=no_tensor)
+            ivf=ivf, probes=probes, no_tensor=no_tensor, no_q8=no_q8)
         b = out_n.shape[0]
         return ([out_ids[i, :out_n[i]] for i in range(b)],
                 [out_scores[i, :out_n[i]] for i in range(b)],
@@ -221,14 +221,14 @@ class GpuStore:
 
     def search_arrays(self, queries, k: int, doc_ids=None, *, all_docs: bool = False,
                       min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
-                      probes: int = 0, no_tensor: bool = False):
+                      probes: int = 0, no_tensor: bool = False, no_q8: bool = False):
         """The C-ABI call as it is: (chunk_ids[b,k,16], scores[b,k], rows[b,k], n[b]); query i has n[i] hits,
         the rest of its k slots are zero.  No per-query Python objects (a batch of 4096 would spend longer
         building lists than searching)."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8)
         b, kk = q.shape[0], max(int(k), 1)
         out_ids = np.zeros((b, kk, 16), dtype=np.uint8)
         out_scores = np.zeros((b, kk), dtype=np.float32)
@@ -239,11 +239,12 @@ class GpuStore:
         del keep
         return out_ids, out_scores, out_rows, out_n
 
-    def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False):
+    def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False, no_q8=False):
         p = L.da_search_params()
         p.struct_size = C.sizeof(L.da_search_params)
         p.flags = (L.DA_SEARCH_ALL_DOCS if all_docs else 0) | (L.DA_SEARCH_READ_ALL_ROWS if read_all_rows else 0) \
-            | (L.DA_SEARCH_IVF if ivf else 0) | (L.DA_SEARCH_NO_TENSOR if no_tensor else 0)
+            | (L.DA_SEARCH_IVF if ivf else 0) | (L.DA_SEARCH_NO_TENSOR if no_tensor else 0) \
+            | (L.DA_SEARCH_NO_Q8 if no_q8 else 0)
         d = offs = None
         if isinstance(doc_ids, (list, tuple)):                      # one document set per query
             assert len(doc_ids) == q.shape[0]
@@ -269,12 +270,13 @@ class GpuStore:
         return p, (q, d, offs)
 
     def bench_resident(self, queries, k: int, iters: int, doc_ids=None, *, all_docs=False,
-                       min_similarity=None, read_all_rows=False, ivf=False, probes=0, no_tensor=False) -> float:
+                       min_similarity=None, read_all_rows=False, ivf=False, probes=0, no_tensor=False,
+                       no_q8=False) -> float:
         """Total CUDA-event milliseconds of `iters` searches with inputs resident in HBM."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8)
         ms = C.c_float(0)
         _check(self._lib.da_store_bench_resident(self._h, C.byref(p), iters, C.byref(ms)))
         del keep

@@ -82,6 +82,12 @@ typedef struct {
                                    planes with the fp32 scan's arithmetic: results are bit-identical to the default layout.
                                    Batches of 16+ queries contract the upper planes as bf16 on the tensor cores.
                                    dim must be a multiple of 16; the IVFFlat path (TMA over fp32 rows) is not available. */
+#define DA_STORE_Q8_SIDECAR 0x2u /* int8 sidecar: next to the fp32 rows the store keeps every row as dim int8
+                                   values with a per-row scale and the row's own quantisation-error bound (dim + 8 more bytes
+                                   per row).  Searches of fewer than 16 queries scan the int8 rows (a quarter of the bytes),
+                                   keep every row whose score interval can still reach the k-th best, and re-score those
+                                   from the fp32 rows with the fp32 scan's arithmetic: results are bit-identical to the
+                                   default layout.  dim must be a multiple of 32; excludes DA_STORE_SPLIT16. */
 
 /* Fills `out` with a fresh ncclUniqueId to hand to every rank's da_config. */
 int da_nccl_unique_id(uint8_t out[DA_NCCL_ID_BYTES]);
@@ -124,6 +130,7 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
 #define DA_SEARCH_IVF           0x4u  /* probe the IVFFlat lists instead of the exact scan */
 #define DA_SEARCH_NO_TENSOR     0x10u /* keep a batch of >= 16 queries on the fp32 SIMT scan (default: tcgen05 TF32
                                          candidate generation + exact fp32 re-score; results are identical) */
+#define DA_SEARCH_NO_Q8         0x20u /* DA_STORE_Q8_SIDECAR stores: scan the fp32 rows for this search (comparisons) */
 
 /* Same query as da_store_topk with every knob exposed, batched: `batch` queries share one doc filter
  * (one /api/query has one document set: cmd/query/main.go:20-24) or carry one each (doc_offsets). */
