@@ -310,7 +310,7 @@ cudaError_t launch_q8_candidates(const ScanArgs &a_in, const int8_t *q8, const f
         case 1: e = q8_launch_one<1, 2, 3>(qa, grid, smem, stream); break;
         case 2: e = q8_launch_one<2, 2, 3>(qa, grid, smem, stream); break;
         case 4: e = q8_launch_one<4, 2, 3>(qa, grid, smem, stream); break;
-        default: e = q8_launch_one<8, 2, 1>(qa, grid, smem, stream); break;
+        default: e = q8_launch_one<8, 4, 1>(qa, grid, smem, stream); break;
     }
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(cand_count, 0, (size_t)a.nq * 4, stream);

@@ -88,3 +88,18 @@ def test_split_plane_store_on_two_shards_equals_fp32_single_shard():
                 for i in range(batch):
                     assert np.array_equal(a[2][i], b[2][i]) and np.array_equal(a[0][i], b[0][i])
                     assert np.array_equal(a[1][i].view(np.uint32), b[1][i].view(np.uint32))
+
+
+def test_int8_sidecar_store_on_two_shards_equals_fp32_single_shard():
+    docs = oracle.doc_ids(S, 0, N // 200)
+    with GpuStore(dim=DIM, capacity_rows=N) as one, GpuStore(dim=DIM, capacity_rows=N, devices=(0, 1), q8_sidecar=True) as two:
+        one.generate_synthetic(S, 0, N)
+        two.generate_synthetic(S, 0, N)
+        qs = np.stack([oracle.gen_query(S, i, i % 8, DIM) for i in range(24)])
+        for batch in (1, 7, 24):                          # int8 scan, two passes of it, tensor path over the fp32 rows
+            for kw in (dict(all_docs=True), dict(doc_ids=docs[::3])):
+                a = one.search(qs[:batch], K, no_tensor=True, **kw)
+                b = two.search(qs[:batch], K, **kw)
+                for i in range(batch):
+                    assert np.array_equal(a[2][i], b[2][i]) and np.array_equal(a[0][i], b[0][i])
+                    assert np.array_equal(a[1][i].view(np.uint32), b[1][i].view(np.uint32))
