@@ -33,8 +33,12 @@ __device__ __forceinline__ key_t64 warp_min_key(key_t64 v)
 }
 
 // Unsorted bounded list with cached minimum.  All lanes call with identical arguments.
-__device__ __forceinline__ void warp_list_insert(key_t64 *list, int K, int &cnt, key_t64 &wmin,
-                                                 key_t64 key, int lane)
+// The rare part (append, or replace the minimum and find the new one) is one out-of-line function: the scan
+// kernels expand the call once per (row, query) of their unrolled tails, and inlining the slow path there made
+// the multi-query variants instruction-cache bound (ncu: `no_instruction` the top stall at 8 queries per pass).
+struct ListState { int cnt; key_t64 wmin; };
+
+__device__ __noinline__ ListState warp_list_insert_slow(key_t64 *list, int K, int cnt, key_t64 wmin, key_t64 key, int lane)
 {
     if (cnt < K) {
         if (lane == 0) list[cnt] = key;
@@ -45,16 +49,24 @@ __device__ __forceinline__ void warp_list_insert(key_t64 *list, int K, int &cnt,
             for (int i = lane; i < K; i += 32) { key_t64 t = list[i]; m = t < m ? t : m; }
             wmin = warp_min_key(m);
         }
-        return;
+        return ListState{cnt, wmin};
     }
-    if (key <= wmin) return;
     // keys are unique (they embed the row), so exactly one slot holds wmin
     for (int i = lane; i < K; i += 32)
         if (list[i] == wmin) list[i] = key;
     __syncwarp();
     key_t64 m = ~0ull;
     for (int i = lane; i < K; i += 32) { key_t64 t = list[i]; m = t < m ? t : m; }
-    wmin = warp_min_key(m);
+    return ListState{cnt, warp_min_key(m)};
+}
+
+__device__ __forceinline__ void warp_list_insert(key_t64 *list, int K, int &cnt, key_t64 &wmin,
+                                                 key_t64 key, int lane)
+{
+    if (cnt >= K && key <= wmin) return;
+    const ListState st = warp_list_insert_slow(list, K, cnt, wmin, key, lane);
+    cnt = st.cnt;
+    wmin = st.wmin;
 }
 
 // In-place descending bitonic sort of P (power of two) keys in shared memory by the whole CTA.
