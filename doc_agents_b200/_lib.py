@@ -33,6 +33,7 @@ DA_SEARCH_READ_ALL_ROWS = 0x2
 DA_SEARCH_IVF = 0x4
 DA_SEARCH_NO_TENSOR = 0x10
 DA_SEARCH_NO_Q8 = 0x20
+DA_SEARCH_NO_COMPACT = 0x40
 
 DA_STORE_SPLIT16 = 0x1
 DA_STORE_Q8_SIDECAR = 0x2

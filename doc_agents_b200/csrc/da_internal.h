@@ -82,6 +82,10 @@ int scan_pick_nq(int dim, int k, int batch);   // how many queries one pass may 
 cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t stream, int *grid_out);
 int scan_grid_for(int sm_count);
 
+// Rows whose document bit is set in `bitmap`, compacted (in no particular order) into rows[0 .. *n_out).
+cudaError_t launch_filter_compact(const uint32_t *doc_slot, const uint32_t *bitmap, uint32_t n_rows, uint32_t *rows,
+                                  uint32_t *n_out, cudaStream_t stream);
+
 // Merge of G gathered candidate blocks (one block per rank, layout: batch*k ids of 16 B, then batch*k keys).
 cudaError_t launch_merge(const uint8_t *gathered, int G, int batch, int k, key_t64 *out_keys,
                          uint8_t *out_ids, cudaStream_t stream);

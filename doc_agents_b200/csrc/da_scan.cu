@@ -65,14 +65,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     const uint32_t gstride = gridDim.x * kScanWarps;
     unsigned int my_rows_read = 0;
 
-    for (uint32_t g = blockIdx.x * kScanWarps + warp; g < n_groups; g += gstride) {
-        const uint32_t row0 = g * R;
-        // lane r (< R) looks at row0 + r: document mask and 1/|row|
-        uint32_t my_row = row0 + lane;
-        bool valid = (lane < R) && (my_row < n_rows);
-        if (INDIRECT) my_row = valid ? a.row_list[my_row] : 0u;
-        uint32_t want_bits = 0u;                 // bit q: this lane's row is requested by query q
-        float my_inv = 0.f;
+    // What a lane learns about "its" row: 1/|row| and, per query, whether the row's document is requested.
+    auto row_facts = [&](uint32_t my_row, bool valid, uint32_t &want_bits, float &my_inv) {
+        want_bits = 0u;                          // bit q: this lane's row is requested by query q
+        my_inv = 0.f;
         if (valid) {
             my_inv = a.inv_norm[my_row];
             if (a.doc_bitmap) {
@@ -89,6 +85,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 want_bits = 0xFFFFFFFFu;
             }
         }
+    };
+
+    // One group of R rows starting at row0; lanes 0..R-1 carry the facts of rows row0 .. row0+R-1.
+    auto process_group = [&](const uint32_t row0, const uint32_t my_row, const bool valid, const uint32_t want_bits,
+                             const float my_inv) {
         const uint32_t valid_mask = __ballot_sync(0xFFFFFFFFu, valid);
         const uint32_t want_mask = __ballot_sync(0xFFFFFFFFu, want_bits != 0u);
         const uint32_t load_mask = a.read_all ? valid_mask : want_mask;
@@ -97,7 +98,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 if (valid)
                     for (int q = 0; q < a.nq; q++) a.approx[(size_t)q * n_rows + my_row] = -3.0e38f;
             }
-            continue;
+            return;
         }
         my_rows_read += __popc(load_mask);
 
@@ -205,6 +206,48 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 warp_list_insert(lists + (size_t)q * P + warp * K, K, cnt[q], wmin[q], key, lane);
             }
         }
+    };
+
+    if (!INDIRECT && a.doc_bitmap && !a.read_all) {
+        // Document filter with rows skipped: the filter itself is the work when few rows qualify (the reference's
+        // own case: one to sixteen documents), so a warp looks at 32 rows per step -- one per lane -- and hands
+        // only the groups that contain a requested row to the row loop.
+        const uint32_t n_super = (n_rows + 31) / 32;
+        constexpr uint32_t kGroupBits = R >= 32 ? 0xFFFFFFFFu : ((1u << R) - 1u);
+        for (uint32_t sg = blockIdx.x * kScanWarps + warp; sg < n_super; sg += gstride) {
+            const uint32_t row = sg * 32 + lane;
+            const bool valid = row < n_rows;
+            uint32_t want_bits;
+            float inv;
+            row_facts(row, valid, want_bits, inv);
+            uint32_t wm = __ballot_sync(0xFFFFFFFFu, want_bits != 0u);
+            if constexpr (VEC == 16) {              // rows of groups that are skipped still need an (impossible) score
+                const uint32_t base = (uint32_t)(lane / R) * R;
+                if (valid && !((wm >> base) & kGroupBits))
+                    for (int q = 0; q < a.nq; q++) a.approx[(size_t)q * n_rows + row] = -3.0e38f;
+            }
+            while (wm) {
+                const uint32_t base = (uint32_t)((__ffs(wm) - 1) / R) * R;
+                wm &= ~(kGroupBits << base);
+                const int src = (int)((base + lane) & 31u);
+                const bool g_valid = __shfl_sync(0xFFFFFFFFu, valid ? 1 : 0, src) && lane < R;
+                const uint32_t g_want = __shfl_sync(0xFFFFFFFFu, want_bits, src);
+                const float g_inv = __shfl_sync(0xFFFFFFFFu, inv, src);
+                process_group(sg * 32 + base, sg * 32 + base + lane, g_valid, lane < R ? g_want : 0u, lane < R ? g_inv : 0.f);
+            }
+        }
+    } else {
+        for (uint32_t g = blockIdx.x * kScanWarps + warp; g < n_groups; g += gstride) {
+            const uint32_t row0 = g * R;
+            // lane r (< R) looks at row0 + r: document mask and 1/|row|
+            uint32_t my_row = row0 + lane;
+            const bool valid = (lane < R) && (my_row < n_rows);
+            if (INDIRECT) my_row = valid ? a.row_list[my_row] : 0u;
+            uint32_t want_bits;
+            float my_inv;
+            row_facts(my_row, valid, want_bits, my_inv);
+            process_group(row0, my_row, valid, want_bits, my_inv);
+        }
     }
 
     if (a.rows_read) {
@@ -222,7 +265,7 @@ cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t st
     const bool full = ((a.dim / VEC) % (32 * U)) == 0;
     auto kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, false> : scan_topk_kernel<NQ, R, U, VEC, false, false>;
     if (a.row_list) {
-        if constexpr (NQ == 1 && VEC != 16) kern = full ? scan_topk_kernel<1, R, U, VEC, true, true> : scan_topk_kernel<1, R, U, VEC, false, true>;
+        if constexpr (VEC != 16) kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, true> : scan_topk_kernel<NQ, R, U, VEC, false, true>;
         else return cudaErrorInvalidValue;
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -485,6 +528,47 @@ cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_coun
     if (P < (few ? 2048 : 1024)) P = few ? 2048 : 1024;
     select_candidates_kernel<<<batch, few ? 1024 : 256, (size_t)P * sizeof(key_t64), stream>>>(surv, surv_count, k, P, chunk_ids,
                                                                                             row_base, out_keys, out_ids);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Narrow document filters (the reference's own case: document_id = ANY of one to sixteen ids, postgres.go:237-239).
+// The requested rows sit in a few runs of ~200, which the grid-strided row loop would leave to a handful of warps;
+// so the filter runs first, alone -- 4 bytes per row -- and compacts the requested rows into a list that the
+// INDIRECT scan then spreads over every warp of the chip.
+// ---------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) filter_compact_kernel(const uint32_t *doc_slot, const uint32_t *bitmap, uint32_t n_rows,
+                                                             uint32_t *rows, uint32_t *n_out)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t rounds = (n_rows + stride - 1) / stride;
+    for (uint32_t it = 0, r = blockIdx.x * blockDim.x + threadIdx.x; it < rounds; it++, r += stride) {
+        bool want = false;
+        if (r < n_rows) {
+            const uint32_t slot = doc_slot[r];
+            want = (bitmap[slot >> 5] >> (slot & 31)) & 1u;
+        }
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, want);
+        if (m) {
+            uint32_t pos = 0;
+            if (lane == 0) pos = atomicAdd(n_out, (uint32_t)__popc(m));
+            pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+            if (want) rows[pos + __popc(m & ((1u << lane) - 1u))] = r;
+        }
+    }
+}
+}  // namespace
+
+cudaError_t launch_filter_compact(const uint32_t *doc_slot, const uint32_t *bitmap, uint32_t n_rows, uint32_t *rows,
+                                  uint32_t *n_out, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(n_out, 0, 4, stream);
+    if (e != cudaSuccess || n_rows == 0) return e;
+    uint32_t blocks = (n_rows + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    filter_compact_kernel<<<blocks, 256, 0, stream>>>(doc_slot, bitmap, n_rows, rows, n_out);
     return cudaGetLastError();
 }
 

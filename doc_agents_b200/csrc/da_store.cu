@@ -126,6 +126,7 @@ struct Shard {
     DevBuf<float> d_approx;                     // split-plane layout: approximate scores of every row
     DevBuf<uint16_t> d_qhi;                     // ... and the queries' upper halves for the bf16 contraction
     DevBuf<unsigned long long> d_akeys;         // ... and the scan's approximate top-k
+    DevBuf<uint32_t> d_flt_rows, d_flt_n;       // narrow document filter: the requested rows, compacted, and their count
     DevBuf<int8_t> d_q8q;                       // int8 sidecar: quantised queries, their factors and error bounds
     DevBuf<float> d_q8qf, d_q8qe;
     PinBuf<uint32_t> h_overflow;
@@ -220,7 +221,7 @@ void free_shard(Shard &s)
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
-    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release(); s.d_q8q.release(); s.d_q8qf.release(); s.d_q8qe.release();
+    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release(); s.d_q8q.release(); s.d_q8qf.release(); s.d_q8qe.release(); s.d_flt_rows.release(); s.d_flt_n.release();
     s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release(); s.d_group_sync.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
@@ -291,6 +292,7 @@ struct SearchPlan {
     int probes;
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
     bool use_q8;       // int8 sidecar scan for the candidates + exact re-score from the fp32 rows
+    bool compact;      // narrow document filter: compact the requested rows first, then scan that list
     uint32_t bitmap_stride;   // words between per-query bitmaps; 0 = one document set for the batch
 };
 
@@ -363,6 +365,33 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                                          s.hi, s.lo));
             st->launches += 4;
             if (first) { st->scan_grid = s.sm_count; st->scan_launches++; }
+            CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
+            continue;
+        }
+        if (pl.compact) {
+            // one list per document set: shared by the batch (up to kMaxNQ queries per pass over it), or one per query
+            const int step = pl.bitmap_stride ? 1 : da::scan_pick_nq(dim, pl.k, pl.batch);
+            for (int q0 = 0; q0 < pl.batch; q0 += step) {
+                if (q0 == 0 || pl.bitmap_stride) {
+                    CU(da::launch_filter_compact(s.doc_slot, s.d_bitmap.p + (size_t)q0 * pl.bitmap_stride, s.n_rows,
+                                                 s.d_flt_rows.p, s.d_flt_n.p, s.stream));
+                    st->launches++;
+                }
+                da::ScanArgs a{};
+                a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
+                a.doc_bitmap = nullptr;                         // every listed row is requested
+                a.queries = s.d_queries.p + (size_t)q0 * dim; a.q_inv_norm = s.d_qinv.p + q0;
+                a.row_list = s.d_flt_rows.p; a.n_rows_dev = s.d_flt_n.p; a.n_rows = 0; a.row_base = s.row_base;
+                a.dim = dim; a.nq = std::min(step, pl.batch - q0); a.k = pl.k; a.min_sim = pl.min_sim; a.read_all = 0;
+                a.cta_out = s.d_cta; a.counter = s.d_counter;
+                a.out_keys = out_keys + (size_t)q0 * pl.k; a.out_ids = out_ids + (size_t)q0 * pl.k * 16;
+                a.rows_read = s.d_rows_read;
+                int grid = 0;
+                CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
+                st->launches++;
+                if (first) { st->scan_grid = grid; st->scan_launches++; }
+            }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
@@ -503,10 +532,26 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         pl.use_tc = selected * 4 >= st->docs.size() && selected > 0;
     }
-    pl.use_q8 = st->q8 && !ivf && !pl.use_tc && !(p->flags & DA_SEARCH_NO_Q8);
+    // A filter that names few documents (the reference's case): the requested rows are compacted into a list first.
+    if (!ivf && !all_docs && !pl.read_all && !pl.use_tc && !st->split16 && !(p->flags & DA_SEARCH_NO_COMPACT)) {
+        size_t selected = 0;
+        for (uint32_t w : uni) selected += (size_t)__builtin_popcount(w);
+        pl.compact = selected * 16 <= st->docs.size();
+    }
+    // The int8 sidecar pays when most rows are read; a narrow document filter reads so few rows that the fp32 scan
+    // (one kernel, no candidate passes) is the shorter way.
+    if (st->q8 && !ivf && !pl.use_tc && !(p->flags & DA_SEARCH_NO_Q8)) {
+        size_t selected = st->docs.size();
+        if (!all_docs && !pl.read_all) {
+            selected = 0;
+            for (uint32_t w : uni) selected += (size_t)__builtin_popcount(w);
+        }
+        pl.use_q8 = selected * 4 >= st->docs.size() && selected > 0;
+    }
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
+        if (pl.compact) { CU(s.d_flt_rows.ensure(std::max<size_t>(s.n_rows, 1))); CU(s.d_flt_n.ensure(1)); }
         if (pl.use_q8) {
             const size_t nq = (size_t)da::scan_pick_nq(st->dim, pl.k, p->batch);
             CU(s.d_approx.ensure(nq * std::max<size_t>(s.n_rows, 1)));

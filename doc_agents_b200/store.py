@@ -208,12 +208,13 @@ class GpuStore:
     # -- everything-exposed search on raw arrays -----------------------------------------
     def search(self, queries, k: int, doc_ids: np.ndarray | None = None, *, all_docs: bool = False,
                min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
-               probes: int = 0, no_tensor: bool = False, no_q8: bool = False):
+               probes: int = 0, no_tensor: bool = False, no_q8: bool = False,
+               no_compact: bool = False):
         """queries: dim or batch x dim.  doc_ids: one n x 16 array for the whole batch, or a list with one
         array per query.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
         out_ids, out_scores, out_rows, out_n = self.search_arrays(
             queries, k, doc_ids, all_docs=all_docs, min_similarity=min_similarity, read_all_rows=read_all_rows,
-            ivf=ivf, probes=probes, no_tensor=no_tensor, no_q8=no_q8)
+            ivf=ivf, probes=probes, no_tensor=no_tensor, no_q8=no_q8, no_compact=no_compact)
         b = out_n.shape[0]
         return ([out_ids[i, :out_n[i]] for i in range(b)],
                 [out_scores[i, :out_n[i]] for i in range(b)],
@@ -221,14 +222,15 @@ class GpuStore:
 
     def search_arrays(self, queries, k: int, doc_ids=None, *, all_docs: bool = False,
                       min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
-                      probes: int = 0, no_tensor: bool = False, no_q8: bool = False):
+                      probes: int = 0, no_tensor: bool = False, no_q8: bool = False,
+                      no_compact: bool = False):
         """The C-ABI call as it is: (chunk_ids[b,k,16], scores[b,k], rows[b,k], n[b]); query i has n[i] hits,
         the rest of its k slots are zero.  No per-query Python objects (a batch of 4096 would spend longer
         building lists than searching)."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8, no_compact)
         b, kk = q.shape[0], max(int(k), 1)
         out_ids = np.zeros((b, kk, 16), dtype=np.uint8)
         out_scores = np.zeros((b, kk), dtype=np.float32)
@@ -239,12 +241,13 @@ class GpuStore:
         del keep
         return out_ids, out_scores, out_rows, out_n
 
-    def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False, no_q8=False):
+    def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False, no_q8=False,
+                no_compact=False):
         p = L.da_search_params()
         p.struct_size = C.sizeof(L.da_search_params)
         p.flags = (L.DA_SEARCH_ALL_DOCS if all_docs else 0) | (L.DA_SEARCH_READ_ALL_ROWS if read_all_rows else 0) \
             | (L.DA_SEARCH_IVF if ivf else 0) | (L.DA_SEARCH_NO_TENSOR if no_tensor else 0) \
-            | (L.DA_SEARCH_NO_Q8 if no_q8 else 0)
+            | (L.DA_SEARCH_NO_Q8 if no_q8 else 0) | (L.DA_SEARCH_NO_COMPACT if no_compact else 0)
         d = offs = None
         if isinstance(doc_ids, (list, tuple)):                      # one document set per query
             assert len(doc_ids) == q.shape[0]
@@ -271,12 +274,12 @@ class GpuStore:
 
     def bench_resident(self, queries, k: int, iters: int, doc_ids=None, *, all_docs=False,
                        min_similarity=None, read_all_rows=False, ivf=False, probes=0, no_tensor=False,
-                       no_q8=False) -> float:
+                       no_q8=False, no_compact=False) -> float:
         """Total CUDA-event milliseconds of `iters` searches with inputs resident in HBM."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8, no_compact)
         ms = C.c_float(0)
         _check(self._lib.da_store_bench_resident(self._h, C.byref(p), iters, C.byref(ms)))
         del keep

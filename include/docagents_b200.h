@@ -130,6 +130,8 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
 #define DA_SEARCH_IVF           0x4u  /* probe the IVFFlat lists instead of the exact scan */
 #define DA_SEARCH_NO_TENSOR     0x10u /* keep a batch of >= 16 queries on the fp32 SIMT scan (default: tcgen05 TF32
                                          candidate generation + exact fp32 re-score; results are identical) */
+#define DA_SEARCH_NO_COMPACT    0x40u /* a filter naming at most 1/16 of the documents is served by compacting the requested rows
+                                         into a list and scanning that; this flag keeps the row loop with the bitmap (comparisons) */
 #define DA_SEARCH_NO_Q8         0x20u /* DA_STORE_Q8_SIDECAR stores: scan the fp32 rows for this search (comparisons) */
 
 /* Same query as da_store_topk with every knob exposed, batched: `batch` queries share one doc filter
@@ -210,7 +212,7 @@ typedef struct {
     float    ivf_assign_ms;         /* final assignment GEMM over every resident row of shard 0 */
     float    ivf_assign_tflops;     /* 2 * rows * lists * dim / ivf_assign_ms */
     int32_t  peer_gather;           /* 1: shards deliver their records into shard 0 over NVLink (no collective) */
-    uint64_t tensor_overflows;      /* batches answered by the SIMT scan because a candidate list overflowed */
+    uint64_t tensor_overflows;      /* searches answered by the fp32 SIMT scan because a candidate list (tensor path, int8 sidecar) overflowed */
     uint64_t topk_calls;            /* da_store_topk calls answered */
     uint64_t topk_passes;           /* searches run for them (== topk_calls unless request batching merged some) */
 } da_stats;

@@ -48,8 +48,12 @@ def test_tensor_batch_equals_simt_scan_and_oracle(batch, dim):
         wide = docs[[d for d in range(n // 200) if d % 3 != 1]]
         _compare(st, qs, k, doc_ids=wide)
         narrow = st.search(qs, k, doc_ids=docs[:5])
-        assert st.stats().last_rows_read == 5 * 200 * ((batch + 7) // 8)   # SIMT scan, rows of other documents skipped
+        assert st.stats().last_rows_read == 5 * 200 * ((batch + 7) // 8)   # compacted list of 1000 rows, 8 queries per pass
         assert all(len(r) <= k for r in narrow[2])
+        loop = st.search(qs, k, doc_ids=docs[:5], no_compact=True)
+        assert st.stats().last_rows_read == 5 * 200 * ((batch + 7) // 8)   # SIMT row loop, rows of other documents skipped
+        for i in range(batch):
+            assert np.array_equal(narrow[2][i], loop[2][i]) and np.array_equal(narrow[1][i], loop[1][i])
 
 
 def test_tensor_batch_no_floor_top100_exercises_pruning():

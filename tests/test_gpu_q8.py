@@ -127,3 +127,25 @@ def test_sidecar_full_size_10m():
             o_rows, o_sc, _ = oracle.topk(sub, None, None, q, k)
             assert np.array_equal(a[2][0], sub_rows[o_rows])
             assert np.allclose(a[1][0], o_sc, rtol=REL_TOL)
+
+
+def test_sidecar_overflow_falls_back_to_the_fp32_scan():
+    """More rows inside the interval slack than the survivor list holds (here: 20 000 copies of one row): the
+    overflow flag sends the search to the fp32 scan, and the answer is still the fp32 scan's."""
+    rng = np.random.default_rng(11)
+    n, dim, k = 20_000, 64, 10
+    base = rng.standard_normal(dim).astype(np.float32)
+    mat = np.tile(base, (n, 1))
+    mat[::7] *= np.float32(1.5)                               # same direction, other norms
+    chunk = rng.integers(0, 256, (n, 16), dtype=np.uint8)
+    chunk[:, :4] = np.arange(n, dtype=np.uint32).view(np.uint8).reshape(n, 4)      # unique ids
+    doc = rng.integers(0, 256, 16, dtype=np.uint8)
+    with GpuStore(dim=dim, capacity_rows=n, q8_sidecar=True) as st:
+        st.save_chunks_raw(doc, chunk)
+        st.save_embeddings_raw(chunk, mat)
+        before = st.stats().tensor_overflows
+        a = st.search(base, k, all_docs=True, min_similarity=-np.inf)
+        assert st.stats().tensor_overflows == before + 1
+        b = st.search(base, k, all_docs=True, min_similarity=-np.inf, no_q8=True)
+        same(a, b, 0)
+        assert len(a[2][0]) == k
