@@ -343,8 +343,8 @@ def main():
     n_docs = N_ROWS // S.chunks_per_doc
     skw = dict(all_docs=True) if not FILTER_DOCS else dict(
         doc_ids=np.stack([synth.doc_ids(S, d, 1)[0] for d in
-                          ([(0 * 37) % S.n_clusters + j * S.n_clusters for j in range(FILTER_DOCS // 2)] +
-                           [7 + j * (n_docs // FILTER_DOCS) for j in range(FILTER_DOCS - FILTER_DOCS // 2)])]),
+                          ([((0 * 37) % S.n_clusters + j * S.n_clusters) % n_docs for j in range(FILTER_DOCS // 2)] +
+                           [(7 + j * (n_docs // FILTER_DOCS)) % n_docs for j in range(FILTER_DOCS - FILTER_DOCS // 2)])]),
         read_all_rows=READ_ALL)
     skw.update(min_similarity=MIN_SIM, no_tensor=NO_TENSOR, no_q8=side_variant)
 

@@ -208,10 +208,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         }
     };
 
-    if (!INDIRECT && a.doc_bitmap && !a.read_all) {
+    if (!INDIRECT && a.doc_bitmap && !a.read_all && n_rows >= 32768u) {
         // Document filter with rows skipped: the filter itself is the work when few rows qualify (the reference's
         // own case: one to sixteen documents), so a warp looks at 32 rows per step -- one per lane -- and hands
-        // only the groups that contain a requested row to the row loop.
+        // only the groups that contain a requested row to the row loop.  (Small stores keep the plain loop: there the
+        // requested rows are most of the rows, and 32 of them in one warp's hands would serialise the search.)
         const uint32_t n_super = (n_rows + 31) / 32;
         constexpr uint32_t kGroupBits = R >= 32 ? 0xFFFFFFFFu : ((1u << R) - 1u);
         for (uint32_t sg = blockIdx.x * kScanWarps + warp; sg < n_super; sg += gstride) {
@@ -255,7 +256,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         if (lane == 0 && tot) atomicAdd(a.rows_read, (unsigned long long)tot);
     }
 
-    scan_cta_epilogue(a, lists, &is_last_s);
+    scan_cta_epilogue(a, lists, &is_last_s, reinterpret_cast<key_t64 *>(smem_raw),
+                      (int)(((size_t)NQ * D4 * sizeof(float4) + (size_t)NQ * P * sizeof(key_t64)) / sizeof(key_t64)));
 }
 
 

@@ -293,6 +293,7 @@ struct SearchPlan {
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
     bool use_q8;       // int8 sidecar scan for the candidates + exact re-score from the fp32 rows
     bool compact;      // narrow document filter: compact the requested rows first, then scan that list
+    bool none_requested;   // the filter names no document this store knows: zero rows, as `= ANY('{}')` (postgres.go:237-239)
     uint32_t bitmap_stride;   // words between per-query bitmaps; 0 = one document set for the batch
 };
 
@@ -315,7 +316,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             CU(cudaStreamWaitEvent(s.stream, st->shards[0].ev_done, 0));
         uint8_t *out_ids = rec_base;
         da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(rec_base + (size_t)pl.batch * pl.k * 16);
-        if (s.n_rows == 0) {               // an empty shard contributes an empty record block
+        if (s.n_rows == 0 || pl.none_requested) {   // an empty shard, or no known document requested: an empty record block
             CU(cudaMemsetAsync(rec_base, 0, rec_bytes, s.stream));
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
@@ -531,6 +532,11 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             for (uint32_t w : uni) selected += (size_t)__builtin_popcount(w);
         }
         pl.use_tc = selected * 4 >= st->docs.size() && selected > 0;
+    }
+    if (!all_docs) {
+        size_t selected = 0;
+        for (uint32_t w : uni) selected += (size_t)__builtin_popcount(w);
+        pl.none_requested = selected == 0 && !pl.read_all;     // (the mask-as-predicate mode reads every row by definition)
     }
     // A filter that names few documents (the reference's case): the requested rows are compacted into a list first.
     if (!ivf && !all_docs && !pl.read_all && !pl.use_tc && !st->split16 && !(p->flags & DA_SEARCH_NO_COMPACT)) {
