@@ -53,6 +53,8 @@ WORKLOADS = {
     "cfg2_predicate_q8": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16, "READ_ALL": True, "Q8": True},
     "cfg3_b64_split16": {"BATCH": 64, "SPLIT16": True},
     "cfg4_split16": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf"), "SPLIT16": True},
+    "cfg3_b2": {"BATCH": 2},
+    "cfg3_b4": {"BATCH": 4},
     "cfg3_b8": {"BATCH": 8},
     "cfg3_b64": {"BATCH": 64},
     "cfg3_b64_simt": {"BATCH": 64, "NO_TENSOR": True},

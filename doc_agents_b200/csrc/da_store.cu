@@ -468,6 +468,19 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
     return DA_OK;
 }
 
+// Smallest batch that goes to the tensor path.  DA_TC_MIN_BATCH overrides (measurements).
+int tc_min_batch(const da_store *st)
+{
+    static const int env = [] { const char *v = getenv("DA_TC_MIN_BATCH"); return v ? atoi(v) : 0; }();
+    if (env > 0) return env;
+    // Measured at 10M x 3072 (ms per batch, fp32 SIMT scan vs tensor path): b=2 16.7 / 20.2, b=4 21.3 / 20.0,
+    // b=8 34.3 / 19.7 -- the SIMT scan pays 2*dim FMAs and dim shared-memory words per row and query, the tensor
+    // path reads the rows once whatever the batch.  The int8 sidecar scan serves 8 queries in 12.6 ms.
+    if (st->split16) return 16;
+    if (st->q8) return 12;
+    return 4;
+}
+
 // Validate + stage the inputs of a search on every local shard.
 int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
 {
@@ -523,9 +536,9 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
     }
     if (pl.k == 0) return DA_OK;
-    // Batches of 16+ queries become a dense contraction: tensor cores generate the candidates, fp32 re-scores
+    // Batches of tc_min_batch() or more queries become a dense contraction: tensor cores generate the candidates, fp32 re-scores
     // them.  Not for narrow document filters, where the SIMT scan skips the rows it does not need.
-    if (!ivf && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= 16 && (!st->split16 || st->dim % 8 == 0)) {
+    if (!ivf && !pl.read_all && !(p->flags & DA_SEARCH_NO_TENSOR) && p->batch >= tc_min_batch(st) && (!st->split16 || st->dim % 8 == 0)) {
         size_t selected = st->docs.size();
         if (!all_docs) {
             selected = 0;                              // documents requested by at least one query
