@@ -49,6 +49,8 @@ WORKLOADS = {
     "cfg3_b1": {},
     "cfg3_b1_split16": {"SPLIT16": True},
     "cfg3_b1_q8": {"Q8": True},
+    "cfg3_b2_q8": {"Q8": True, "BATCH": 2},
+    "cfg3_b4_q8": {"Q8": True, "BATCH": 4},
     "cfg3_b8_q8": {"Q8": True, "BATCH": 8},
     "cfg2_predicate_q8": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16, "READ_ALL": True, "Q8": True},
     "cfg3_b64_split16": {"BATCH": 64, "SPLIT16": True},
@@ -68,12 +70,13 @@ WORKLOADS = {
 def workload_name(n_gpus: int) -> str:
     flt = "all documents requested" if not FILTER_DOCS else \
         f"filtered to {FILTER_DOCS} doc IDs ({'mask as predicate, every row read' if READ_ALL else 'rows of other documents skipped'})"
-    path = "fused SIMT scan" if (BATCH < 16 or NO_TENSOR or FILTER_DOCS) else "tcgen05 TF32 candidates + exact fp32 re-score"
+    tc_min = 16 if SPLIT16 else 12 if Q8 else 4          # tc_min_batch() in da_store.cu
+    path = "fused SIMT scan" if (BATCH < tc_min or NO_TENSOR or FILTER_DOCS) else "tcgen05 TF32 candidates + exact fp32 re-score"
     if SPLIT16:
         path = ("split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"
                 if BATCH < 16 else
                 "split-plane layout: tcgen05 bf16 contraction of the upper planes for candidates + exact fp32 re-score")
-    if Q8 and (BATCH < 16 or NO_TENSOR or FILTER_DOCS):
+    if Q8 and (BATCH < tc_min or NO_TENSOR) and not (FILTER_DOCS and not READ_ALL):
         path = "int8 sidecar: dp4a scan of one byte per element for candidates + exact fp32 re-score from the fp32 rows"
     return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch={BATCH}, top_k={TOP_K}, "
             f"{flt}, min_similarity={MIN_SIM}, {path}, local top-k + NCCL all-gather merge")

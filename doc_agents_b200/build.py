@@ -35,7 +35,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB
     nvcc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "bin", "nvcc")
     tmp = f"{LIB}.{os.getpid()}.tmp"            # build aside, then rename: concurrent builders never see a torn file
-    extra = os.environ.get("DA_NVCC_EXTRA", "").split()   # e.g. -DDA_TC_PROFILE (debug counters in the batch kernel)
+    extra = os.environ.get("DA_NVCC_EXTRA", "").split()   # extra nvcc flags for experiments (-D..., -Xptxas=...)
     cmd = [nvcc, *NVCC_FLAGS, *extra, "-I", INCLUDE, "-o", tmp, *sources(), "-lnccl"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")

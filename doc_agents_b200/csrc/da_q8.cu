@@ -310,8 +310,9 @@ cudaError_t launch_q8_candidates(const ScanArgs &a_in, const int8_t *q8, const f
     switch (nqt) {
         // measured at 10M x 3072 (ms per search): (R,U) = (1,3) 6.28, (2,3) 4.96, (3,3) 4.55, (4,2) 4.55, (4,3) 4.52 with spills
         case 1: e = q8_launch_one<1, 4, 2>(qa, grid, smem, stream); break;
-        case 2: e = q8_launch_one<2, 2, 3>(qa, grid, smem, stream); break;
-        case 4: e = q8_launch_one<4, 2, 3>(qa, grid, smem, stream); break;
+        // two queries: (2,3) 6.04 ms, (4,2) 4.89, (4,1) 5.05, (3,3) 4.91; four: (2,3) 8.58, (4,2) 6.93 (spills), (4,1) 6.49, (2,2) 8.15
+        case 2: e = q8_launch_one<2, 4, 2>(qa, grid, smem, stream); break;
+        case 4: e = q8_launch_one<4, 4, 1>(qa, grid, smem, stream); break;
         default: e = q8_launch_one<8, 4, 1>(qa, grid, smem, stream); break;
     }
     if (e != cudaSuccess) return e;

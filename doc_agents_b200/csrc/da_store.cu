@@ -664,6 +664,8 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
         st->last_bytes = rows_read * (uint64_t)st->dim * 2 + rows_scanned * (uint64_t)passes * (pl.all_docs ? 12 : 16);
     else if (pl.use_q8)     // int8 rows read + per row: factor, error bound, upper end out and in (+ doc slot)
         st->last_bytes = rows_read * (uint64_t)st->dim + rows_scanned * (uint64_t)passes * (pl.all_docs ? 16 : 20);
+    else if (pl.compact)    // filter pass: every row's slot once per document set; then the listed rows (vector, row number, 1/|row|)
+        st->last_bytes = rows_scanned * 4ull * (uint64_t)(pl.bitmap_stride ? pl.batch : 1) + rows_read * ((uint64_t)st->dim * 4 + 8);
     else if (pl.use_tc)
         st->last_bytes = rows_scanned * ((uint64_t)st->dim * 4 + (pl.all_docs ? 4 : 8));   // every row once, whatever the batch
     else

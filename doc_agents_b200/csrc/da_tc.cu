@@ -310,7 +310,6 @@ struct BatchArgs {
     int K, batch, k;
     int cap;                    // entries per query list
     int group;                  // CTAs that share one range of row tiles and split the query tiles among them
-    int bf16;                   // 1: operands are bf16 (64 elements per 128-byte stage row), else tf32 (32)
     float floor_eps;            // min_similarity - eps
     float two_eps;
     const float *inv_norm;      // per row
@@ -371,12 +370,9 @@ __device__ float hist_kth_lower_bound(const uint32_t *h, int k)
     return hist_edge(cbin, fbin < 0 ? 0 : fbin);   // fine counters may lag the coarse one: its edge is still valid
 }
 
-// Warp roles of the batch kernel (the epilogue warps' TMEM lane quadrant is warp % 4 either way).
-#ifdef DA_TC_LOW_ROLES
-constexpr int kProdWarp = 0, kMmaWarp = 1, kEpiFirst = 2;
-#else
+// Warp roles of the batch kernel: warps 0..3 epilogue (TMEM lane quadrant = warp % 4), warp 4 TMA producer, warp 5
+// TMEM owner + MMA issuer.
 constexpr int kProdWarp = 4, kMmaWarp = 5, kEpiFirst = 0;
-#endif
 
 // BF16: operand type of the contraction, bf16 (kind::f16) or tf32, fixed at compile time (the issue loop has no
 // run-time choice).  NCTA = 2: CTA pairs (cluster of two), each pair takes TWO query tiles against one row tile per
@@ -798,7 +794,6 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     a.floor_eps = min_sim - eps; a.two_eps = 2.f * eps;
     a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
     a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
-    a.bf16 = bf16 ? 1 : 0;
     const void *kernel = ncta == 2
         ? (bf16 ? (const void *)tc_batch_candidates_kernel<true, 2> : (const void *)tc_batch_candidates_kernel<false, 2>)
         : (bf16 ? (const void *)tc_batch_candidates_kernel<true, 1> : (const void *)tc_batch_candidates_kernel<false, 1>);
