@@ -118,3 +118,20 @@ def test_library_synthetic_queries_and_ids_equal_the_oracle(built_lib):
                 assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
         assert np.array_equal(oracle.chunk_ids(so, 12345, 50), synth.chunk_ids(sp, 12345, 50))
         assert np.array_equal(oracle.doc_ids(so, 0, 50), synth.doc_ids(sp, 0, 50))
+
+
+def test_python_flag_constants_match_the_header():
+    """The ctypes twin restates the header's flag and error constants by hand: keep them equal."""
+    import re
+    from doc_agents_b200 import _lib as L
+    text = open(HEADER).read()
+    seen = 0
+    for name, value in re.findall(r"#define\s+(DA_(?:SEARCH|STORE|IVF|ERR)_[A-Z0-9_]+)\s+\(?(-?0x[0-9a-fA-F]+|-?\d+)u?\)?", text):
+        if hasattr(L, name):
+            assert getattr(L, name) == int(value, 0), name
+            seen += 1
+    assert seen >= 9
+    for name, value in re.findall(r"\b(DA_(?:OK|ERR_[A-Z_]+))\s*=\s*(-?\d+)", text):      # the status enum
+        assert getattr(L, name) == int(value), name
+    for name in ("DA_STORE_SPLIT16", "DA_STORE_Q8_SIDECAR", "DA_SEARCH_NO_TENSOR", "DA_SEARCH_NO_Q8", "DA_SEARCH_NO_COMPACT"):
+        assert hasattr(L, name) and re.search(r"#define\s+%s\b" % name, text), name
