@@ -52,6 +52,9 @@ WORKLOADS = {
     "cfg3_b2_q8": {"Q8": True, "BATCH": 2},
     "cfg3_b4_q8": {"Q8": True, "BATCH": 4},
     "cfg3_b8_q8": {"Q8": True, "BATCH": 8},
+    "cfg3_b16_q8": {"Q8": True, "BATCH": 16},
+    "cfg3_b64_q8": {"Q8": True, "BATCH": 64},
+    "cfg4_q8": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf"), "Q8": True},
     "cfg2_predicate_q8": {"N_ROWS": 1_000_000, "FILTER_DOCS": 16, "READ_ALL": True, "Q8": True},
     "cfg3_b64_split16": {"BATCH": 64, "SPLIT16": True},
     "cfg4_split16": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf"), "SPLIT16": True},
@@ -76,6 +79,8 @@ def workload_name(n_gpus: int) -> str:
         path = ("split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"
                 if BATCH < 16 else
                 "split-plane layout: tcgen05 bf16 contraction of the upper planes for candidates + exact fp32 re-score")
+    if Q8 and not (BATCH < tc_min or NO_TENSOR or FILTER_DOCS):
+        path = "int8 sidecar: tcgen05 kind::i8 contraction of the int8 rows for candidates + exact fp32 re-score from the fp32 rows"
     if Q8 and (BATCH < tc_min or NO_TENSOR) and not (FILTER_DOCS and not READ_ALL):
         path = "int8 sidecar: dp4a scan of one byte per element for candidates + exact fp32 re-score from the fp32 rows"
     return (f"exact scan, {N_ROWS}x{DIM} fp32 corpus row-sharded across {n_gpus} B200, batch={BATCH}, top_k={TOP_K}, "
@@ -441,6 +446,8 @@ def main():
         # 2 x rows x queries x dim; peak = the measured cuBLAS bf16 rate (tf32 runs at half of it).
         flops = 2.0 * (hi - lo) * BATCH * DIM
         tpeak, tsrc = measured_tensor_peak(bf16=SPLIT16)
+        if Q8:
+            tpeak, tsrc = 2 * measured_tensor_peak(bf16=True)[0], "2 x measured bf16 (MEASURED_PEAKS.json): int8 runs at twice the bf16 rate"
         tach = flops / (scan_ms / 1e3) / 1e12 if scan_ms > 0 else 0.0
     if tensor_path and flops / (tpeak * 1e12) > bytes_per_launch / (peak * 1e9):     # else reading the rows once costs more: HBM-bound
         line["roofline"] = {"bound": "tensor", "achieved": tach, "peak": tpeak, "unit": "TFLOP/s", "frac": tach / tpeak,

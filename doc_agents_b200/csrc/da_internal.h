@@ -140,6 +140,10 @@ cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *c
                              unsigned long long *packed_scratch, uint32_t *out_assign, cudaStream_t stream);
 cudaError_t tc_launch_gather_rows(const float *mat, int D, const uint32_t *rows, uint32_t n, float *out, cudaStream_t stream);
 
+// int8 sidecar operands of the batched path (kind::i8): then `inv_norm` = scale/|row| per row, `q_inv` = scale/|q| per
+// query, `eps` = the largest quantisation-error bound of a resident row, q_err = the queries' own bounds.
+struct TcInt8Operands { const int8_t *queries; const int8_t *rows; const float *q_err; };
+
 // Batched queries on the tensor cores (da_tc.cu): TF32 candidate generation behind a global per-query gate,
 // then exact fp32 re-score and per-query selection (da_scan.cu).  eps bounds |cos_tf32 - cos_fp32|.
 constexpr float kTf32Eps = 2.5e-3f;
@@ -154,7 +158,8 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
                                        const uint32_t *doc_bitmap, uint32_t bitmap_stride, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
                                        uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
-                                       cudaStream_t stream, const uint16_t *q_hi = nullptr, const uint16_t *x_hi = nullptr);
+                                       cudaStream_t stream, const uint16_t *q_hi = nullptr, const uint16_t *x_hi = nullptr,
+                                       const struct TcInt8Operands *i8 = nullptr);
 // upper 16 bits of n floats (truncated bf16), e.g. the queries of a batch for the bf16 contraction
 cudaError_t tc_launch_truncate_bf16(const float *src, size_t n, uint16_t *dst, cudaStream_t stream);
 cudaError_t launch_rescore_select(const key_t64 *cand, const uint32_t *cand_count, int cap, const uint32_t *gate_ordered,
@@ -199,9 +204,13 @@ void synth_id_host(uint64_t seed_ids, int kind, uint64_t index, uint8_t out[16])
 // ---------------------------------------------------------------------------
 // rows [first, first + n), or the n rows listed in `rows` (device), of `mat` -> q8 / factor / err
 cudaError_t launch_q8_quantize_rows(const float *mat, int dim, const uint32_t *rows, uint32_t first, uint32_t n,
-                                    const float *inv_norm, int8_t *q8, float *factor, float *err, cudaStream_t stream);
+                                    const float *inv_norm, int8_t *q8, float *factor, float *err, float *err_max,
+                                    cudaStream_t stream);    // err_max: running maximum of err over every row written
 // quantise a.nq queries, scan the int8 rows, collect every row whose interval reaches the k-th best lower end;
 // candidates are left for launch_rescore_select (cand / cand_count / gate_ordered)
+// queries -> int8 + scale/|q| + error bound (one warp per query)
+cudaError_t launch_q8_quantize_queries(const float *queries, int nq, int dim, const float *q_inv, int8_t *q8, float *factor,
+                                       float *err, cudaStream_t stream);
 cudaError_t launch_q8_candidates(const ScanArgs &a, const int8_t *q8, const float *factor, const float *err,
                                  int8_t *q8_queries, float *qfactor, float *qerr, key_t64 *cand, uint32_t cap,
                                  uint32_t *cand_count, uint32_t *gate_ordered, uint32_t *overflow, int sm_count,

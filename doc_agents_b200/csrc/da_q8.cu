@@ -24,7 +24,8 @@ namespace {
 constexpr float kQ8Margin = 2.0e-5f;      // fp32 rounding of the approximate score, of E and of the exact re-score
 
 // One warp quantises one vector of `dim` floats (dim % 4 == 0).  inv = 1/|x| (0: zero vector -> everything 0).
-__device__ void q8_quantize_vector(const float *x, int dim, float inv, int8_t *out, float *factor, float *err, int lane)
+__device__ void q8_quantize_vector(const float *x, int dim, float inv, int8_t *out, float *factor, float *err, int lane,
+                                   float *err_max = nullptr)
 {
     const float4 *x4 = reinterpret_cast<const float4 *>(x);
     const int D4 = dim >> 2;
@@ -58,19 +59,21 @@ __device__ void q8_quantize_vector(const float *x, int dim, float inv, int8_t *o
     if (lane == 0) {
         *factor = scale * inv;
         // rounded up: the sum of squares and the square root carry a few ulps each
-        *err = live ? sqrtf(e2) * inv * 1.0001f + 1.0e-7f : 0.f;
+        const float e = live ? sqrtf(e2) * inv * 1.0001f + 1.0e-7f : 0.f;
+        *err = e;
+        if (err_max && e > 0.f) atomicMax(reinterpret_cast<unsigned int *>(err_max), __float_as_uint(e));   // e >= 0: bits order as u32
     }
 }
 
 // rows [first, first + n) of the resident matrix, or the rows listed in `rows` (upserts)
 __global__ void q8_quantize_rows_kernel(const float *mat, int dim, const uint32_t *rows, uint32_t first, uint32_t n,
-                                        const float *inv_norm, int8_t *q8, float *factor, float *err)
+                                        const float *inv_norm, int8_t *q8, float *factor, float *err, float *err_max)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = w; i < n; i += nw) {
         const uint32_t r = rows ? rows[i] : first + i;
-        q8_quantize_vector(mat + (size_t)r * dim, dim, inv_norm[r], q8 + (size_t)r * dim, factor + r, err + r, lane);
+        q8_quantize_vector(mat + (size_t)r * dim, dim, inv_norm[r], q8 + (size_t)r * dim, factor + r, err + r, lane, err_max);
     }
 }
 
@@ -270,12 +273,21 @@ cudaError_t q8_launch_one(const Q8Args &qa, int grid, size_t smem, cudaStream_t 
 }  // namespace
 
 cudaError_t launch_q8_quantize_rows(const float *mat, int dim, const uint32_t *rows, uint32_t first, uint32_t n,
-                                    const float *inv_norm, int8_t *q8, float *factor, float *err, cudaStream_t stream)
+                                    const float *inv_norm, int8_t *q8, float *factor, float *err, float *err_max,
+                                    cudaStream_t stream)
 {
     if (n == 0) return cudaSuccess;
     int blocks = (int)((n + 7) / 8);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    q8_quantize_rows_kernel<<<blocks, 256, 0, stream>>>(mat, dim, rows, first, n, inv_norm, q8, factor, err);
+    q8_quantize_rows_kernel<<<blocks, 256, 0, stream>>>(mat, dim, rows, first, n, inv_norm, q8, factor, err, err_max);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_q8_quantize_queries(const float *queries, int nq, int dim, const float *q_inv, int8_t *q8, float *factor,
+                                       float *err, cudaStream_t stream)
+{
+    if (nq <= 0) return cudaSuccess;
+    q8_quantize_queries_kernel<<<(nq * 32 + 255) / 256, 256, 0, stream>>>(queries, nq, dim, q_inv, q8, factor, err);
     return cudaGetLastError();
 }
 

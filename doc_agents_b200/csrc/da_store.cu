@@ -109,6 +109,9 @@ struct Shard {
     uint16_t *hi = nullptr, *lo = nullptr;      // split-plane layout: upper / lower 16 bits of every element
     int8_t *q8 = nullptr;                       // int8 sidecar (DA_STORE_Q8_SIDECAR): rint(x / scale) of every element
     float *q8_factor = nullptr, *q8_err = nullptr;   // ... per row: scale / |row|, and its quantisation error bound
+    float *q8_errmax = nullptr;                 // ... device: the largest bound of any row written so far (bits ordered as u32)
+    float q8_err_max = 0.f;                     // ... its host copy, refreshed before a search when rows were written
+    bool q8_dirty = false;
     uint32_t *doc_slot = nullptr;
     uint8_t *chunk_ids = nullptr;
     cudaStream_t stream = nullptr;
@@ -216,7 +219,7 @@ void free_shard(Shard &s)
     free_ivf(s);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
-    cudaFree(s.mat); cudaFree(s.hi); cudaFree(s.lo); cudaFree(s.q8); cudaFree(s.q8_factor); cudaFree(s.q8_err); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
+    cudaFree(s.mat); cudaFree(s.hi); cudaFree(s.lo); cudaFree(s.q8); cudaFree(s.q8_factor); cudaFree(s.q8_err); cudaFree(s.q8_errmax); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
     cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
@@ -267,6 +270,8 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, b
         CU(cudaMalloc((void **)&s.q8, cap_rows * (uint64_t)dim));
         CU(cudaMalloc((void **)&s.q8_factor, cap_rows * 4));
         CU(cudaMalloc((void **)&s.q8_err, cap_rows * 4));
+        CU(cudaMalloc((void **)&s.q8_errmax, 4));
+        CU(cudaMemset(s.q8_errmax, 0, 4));
     }
     CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
     CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
@@ -292,6 +297,7 @@ struct SearchPlan {
     int probes;
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
     bool use_q8;       // int8 sidecar scan for the candidates + exact re-score from the fp32 rows
+    bool tc_i8;        // tensor path over the int8 sidecar (kind::i8) instead of the fp32 rows (TF32)
     bool compact;      // narrow document filter: compact the requested rows first, then scan that list
     bool none_requested;   // the filter names no document this store knows: zero rows, as `= ANY('{}')` (postgres.go:237-239)
     uint32_t bitmap_stride;   // words between per-query bitmaps; 0 = one document set for the batch
@@ -350,6 +356,21 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 st->launches += 3;
                 if (first) { st->scan_grid = grid; st->scan_launches++; }
             }
+            CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
+            if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
+            continue;
+        }
+        if (pl.use_tc && pl.tc_i8) {
+            const da::TcInt8Operands ops{s.d_q8q.p, s.q8, s.d_q8qe.p};
+            CU(da::tc_launch_batch_candidates(s.d_queries.p, pl.batch, s.d_q8qf.p, s.mat, s.n_rows, dim, s.q8_factor,
+                                              s.doc_slot, pl.all_docs ? nullptr : s.d_bitmap.p, pl.bitmap_stride, pl.k, pl.min_sim,
+                                              s.q8_err_max, s.sm_count, s.d_cand.p, s.d_cand_count.p, s.d_hist.p, s.d_gate.p,
+                                              s.d_overflow.p, s.d_group_sync.p, s.stream, nullptr, nullptr, &ops));
+            CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, da::tc_batch_cap(pl.k), s.d_gate.p, s.d_surv.p,
+                                         s.d_surv_count.p, s.d_overflow.p, pl.batch, s.mat, dim, s.inv_norm, s.d_queries.p,
+                                         s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream));
+            st->launches += 4;
+            if (first) { st->scan_grid = s.sm_count; st->scan_launches++; }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
@@ -477,7 +498,7 @@ int tc_min_batch(const da_store *st)
     // b=8 34.3 / 19.7 -- the SIMT scan pays 2*dim FMAs and dim shared-memory words per row and query, the tensor
     // path reads the rows once whatever the batch.  The int8 sidecar scan serves 8 queries in 12.6 ms.
     if (st->split16) return 16;
-    if (st->q8) return 12;
+    if (st->q8) return 3;          // int8 SIMT scan: 2 queries 4.9 ms, 4 queries 6.4; int8 tensor path: 5.2-5.8 ms for 4..16
     return 4;
 }
 
@@ -545,6 +566,10 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             for (uint32_t w : uni) selected += (size_t)__builtin_popcount(w);
         }
         pl.use_tc = selected * 4 >= st->docs.size() && selected > 0;
+        // The int8 contraction's slack (2 x ~0.02) is wide: it needs a similarity floor to bound the candidate set from
+        // the first row tile on.  Without one the running k-th best sits at noise level for a long while and half the
+        // rows would pass (measured: configs[3], no floor, k = 100, overflows every list); those searches keep TF32.
+        pl.tc_i8 = pl.use_tc && st->q8 && !(p->flags & DA_SEARCH_NO_Q8) && st->dim % 16 == 0 && pl.min_sim >= 0.5f;
     }
     if (!all_docs) {
         size_t selected = 0;
@@ -583,6 +608,14 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
             *s.h_overflow.p = 0;
         }
+        if (pl.tc_i8) {
+            CU(s.d_q8q.ensure(nq_elems)); CU(s.d_q8qf.ensure(p->batch)); CU(s.d_q8qe.ensure(p->batch));
+            if (s.q8_dirty) {            // rows were written since the last look: fetch the rows' error bound (4 bytes)
+                CU(cudaMemcpyAsync(&s.q8_err_max, s.q8_errmax, 4, cudaMemcpyDeviceToHost, s.stream));
+                CU(cudaStreamSynchronize(s.stream));
+                s.q8_dirty = false;
+            }
+        }
         if (pl.use_tc) {
             CU(s.d_cand.ensure((size_t)p->batch * da::tc_batch_cap(pl.k)));
             CU(s.d_cand_count.ensure(p->batch)); CU(s.d_gate.ensure(p->batch)); CU(s.d_surv_count.ensure(p->batch));
@@ -616,6 +649,10 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         CU(da::launch_query_inv_norm(s.d_queries.p, st->dim, p->batch, s.d_qinv.p, s.stream));
         st->launches++;
+        if (pl.tc_i8) {                       // the int8 contraction needs the queries as int8 with their scales and bounds
+            CU(da::launch_q8_quantize_queries(s.d_queries.p, p->batch, st->dim, s.d_qinv.p, s.d_q8q.p, s.d_q8qf.p, s.d_q8qe.p, s.stream));
+            st->launches++;
+        }
         if (pl.use_tc && st->split16) {       // the bf16 contraction needs the queries' upper halves
             CU(s.d_qhi.ensure(nq_elems));
             CU(da::tc_launch_truncate_bf16(s.d_queries.p, nq_elems, s.d_qhi.p, s.stream));
@@ -662,6 +699,8 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
         st->last_bytes = rows_scanned * ((uint64_t)st->dim * 2 + (pl.all_docs ? 4 : 8));
     else if (st->split16)   // upper plane of the rows read + per row: 1/|row|, approximate score out and in (+ doc slot)
         st->last_bytes = rows_read * (uint64_t)st->dim * 2 + rows_scanned * (uint64_t)passes * (pl.all_docs ? 12 : 16);
+    else if (pl.use_tc && pl.tc_i8)     // the int8 plane once, whatever the batch (+ factor, doc slot)
+        st->last_bytes = rows_scanned * ((uint64_t)st->dim + (pl.all_docs ? 4 : 8));
     else if (pl.use_q8)     // int8 rows read + per row: factor, error bound, upper end out and in (+ doc slot)
         st->last_bytes = rows_read * (uint64_t)st->dim + rows_scanned * (uint64_t)passes * (pl.all_docs ? 16 : 20);
     else if (pl.compact)    // filter pass: every row's slot once per document set; then the listed rows (vector, row number, 1/|row|)
@@ -944,7 +983,8 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
             st->launches++;
             if (st->q8) {
                 CU(da::launch_q8_quantize_rows(sh.mat, dim, sh.d_up_rows.p + b, 0, (uint32_t)(e - b), sh.inv_norm, sh.q8,
-                                               sh.q8_factor, sh.q8_err, sh.stream));
+                                               sh.q8_factor, sh.q8_err, sh.q8_errmax, sh.stream));
+                sh.q8_dirty = true;
                 st->launches++;
             }
         }
@@ -998,7 +1038,7 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     if (pl.k == 0) return DA_OK;
     if (!out_chunk_ids || !out_scores) return fail(DA_ERR_INVALID, "output buffers are NULL");
     const size_t nk = (size_t)pl.batch * pl.k, rec_bytes = nk * 24;
-    for (int attempt = 0; attempt < 2; attempt++) {
+    for (int attempt = 0; attempt < 3; attempt++) {
         rc = enqueue_search(st, pl);
         if (rc != DA_OK) return rc;
         CU(cudaSetDevice(s0.device));
@@ -1019,7 +1059,12 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         if (st->total_ranks > 1 && st->world > 1)
             return fail(DA_ERR_STATE, "candidate list overflow; retry with DA_SEARCH_NO_TENSOR | DA_SEARCH_NO_Q8");
         st->tc_overflows++;
-        pl.use_tc = false;                 // answer this batch with the SIMT scan instead
+        if (pl.use_tc && pl.tc_i8) {
+            pl.tc_i8 = false;              // int8 slack too wide for this batch: the TF32 contraction of the fp32 rows next
+        } else {
+            pl.use_tc = false;             // answer this batch with the SIMT scan instead
+            pl.tc_i8 = false;
+        }
         pl.use_q8 = false;                 // ... of the fp32 rows
         for (Shard &s : st->shards) {      // the flag is sticky on the device: clear it for the second attempt
             CU(cudaSetDevice(s.device));
@@ -1346,7 +1391,9 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
             CU(da::launch_synth(a, s.mat, s.inv_norm, s.doc_slot, s.chunk_ids, s.stream));
             st->launches++;
             if (st->q8) {
-                CU(da::launch_q8_quantize_rows(s.mat, st->dim, nullptr, 0, a.n_rows, s.inv_norm, s.q8, s.q8_factor, s.q8_err, s.stream));
+                CU(da::launch_q8_quantize_rows(s.mat, st->dim, nullptr, 0, a.n_rows, s.inv_norm, s.q8, s.q8_factor, s.q8_err,
+                                               s.q8_errmax, s.stream));
+                s.q8_dirty = true;
                 st->launches++;
             }
         }

@@ -129,6 +129,20 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar)      // arrives o
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                  ::"r"(bar), "h"((uint16_t)3) : "memory");
 }
+// kind::i8, signed 8-bit operands, s32 accumulators (int8 sidecar stores): 32 elements of K per instruction
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da_, uint64_t db_, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_i8_pair(uint32_t tmem_d, uint64_t da_, uint64_t db_, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(da_), "l"(db_), "r"(idesc), "r"(accumulate) : "memory");
+}
+// D = s32 (2 << 4), A = B = signed 8 bit (1 << 7, 1 << 10)
+constexpr uint32_t TC_IDESC_I8 = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+constexpr uint32_t TC_IDESC_I8_PAIR = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)((2 * TC_BM) >> 4) << 24);
 // pair instruction descriptors: M = 256 (128 rows of D in each CTA's TMEM), N = 256
 constexpr uint32_t TC_IDESC_PAIR = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)((2 * TC_BM) >> 4) << 24);
 constexpr uint32_t TC_IDESC_BF16_PAIR = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)((2 * TC_BM) >> 4) << 24);
@@ -310,8 +324,9 @@ struct BatchArgs {
     int K, batch, k;
     int cap;                    // entries per query list
     int group;                  // CTAs that share one range of row tiles and split the query tiles among them
-    float floor_eps;            // min_similarity - eps
-    float two_eps;
+    float min_sim;              // similarity floor (exact scores)
+    float eps;                  // bound of |approximate - exact| over rows (and queries, unless q_err adds the query's own part)
+    const float *q_err;         // int8 operands: per query, its quantisation error bound (the gate slack becomes per query)
     const float *inv_norm;      // per row
     const uint32_t *doc_slot;   // per row (with doc_bitmap)
     const uint32_t *doc_bitmap; // nullptr = every document
@@ -370,15 +385,32 @@ __device__ float hist_kth_lower_bound(const uint32_t *h, int k)
     return hist_edge(cbin, fbin < 0 ? 0 : fbin);   // fine counters may lag the coarse one: its edge is still valid
 }
 
+constexpr int OP_TF32 = 0, OP_BF16 = 1, OP_I8 = 2;
+
+// Slack of query q: |approximate - exact| <= eps for every row.  int8 operands: the rows' bound a.eps (the largest
+// quantisation error of a resident row) combined with the query's own (da_q8.cu: e_x + e_q + e_x e_q, + rounding).
+__device__ __forceinline__ float batch_eps(const BatchArgs &a, uint32_t q)
+{
+    if (!a.q_err || q >= (uint32_t)a.batch) return a.eps;
+    const float qe = a.q_err[q];
+    return a.eps + qe + a.eps * qe + 2.0e-5f;
+}
+// accumulator word -> float (s32 accumulators with int8 operands)
+template <bool I8> __device__ __forceinline__ float acc_value(uint32_t w)
+{
+    return I8 ? (float)(int)w : __uint_as_float(w);
+}
+
 // Warp roles of the batch kernel: warps 0..3 epilogue (TMEM lane quadrant = warp % 4), warp 4 TMA producer, warp 5
 // TMEM owner + MMA issuer.
 constexpr int kProdWarp = 4, kMmaWarp = 5, kEpiFirst = 0;
 
-// BF16: operand type of the contraction, bf16 (kind::f16) or tf32, fixed at compile time (the issue loop has no
+// OP: operand type of the contraction -- OP_TF32, OP_BF16 (kind::f16) or OP_I8 (kind::i8, s32 accumulators: the int8
+// sidecar; the per-row factor is then scale/|row|, the per-query one scale/|q|) --, fixed at compile time (the issue loop has no
 // run-time choice).  NCTA = 2: CTA pairs (cluster of two), each pair takes TWO query tiles against one row tile per
 // accumulator; a CTA stages its own query tile and half of the row tile, which halves the shared-memory traffic per
 // MMA (the limit of the single-CTA tf32 form) and the L2 traffic per query tile.
-template <bool BF16, int NCTA>
+template <int OP, int NCTA>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                            const BatchArgs a)
@@ -411,7 +443,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const int per_grp = (n_tiles_total + n_groups - 1) / n_groups;
     const int t_begin = grp * per_grp;
     const int t_end = min(n_tiles_total, t_begin + per_grp);
-    const int bk = BF16 ? 2 * TC_BK : TC_BK;               // elements per 128-byte stage row
+    constexpr bool BF16 = OP == OP_BF16, I8 = OP == OP_I8;
+    const int bk = I8 ? 4 * TC_BK : BF16 ? 2 * TC_BK : TC_BK;     // elements per 128-byte stage row
     const int kb_count = (a.K + bk - 1) / bk;
 
     if (threadIdx.x == 0) {
@@ -496,10 +529,12 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                             const uint64_t da_ = da0 + (uint64_t)(k * 2), db_ = db0 + (uint64_t)(k * 2);
                             const uint32_t acc = (uint32_t)((kb | k) != 0);
                             if (NCTA == 2) {
-                                if (BF16) umma_bf16_pair(tmem_d, da_, db_, TC_IDESC_BF16_PAIR, acc);
+                                if (I8) umma_i8_pair(tmem_d, da_, db_, TC_IDESC_I8_PAIR, acc);
+                                else if (BF16) umma_bf16_pair(tmem_d, da_, db_, TC_IDESC_BF16_PAIR, acc);
                                 else umma_tf32_pair(tmem_d, da_, db_, TC_IDESC_PAIR, acc);
                             } else {
-                                if (BF16) umma_bf16(tmem_d, da_, db_, TC_IDESC_BF16, acc);
+                                if (I8) umma_i8(tmem_d, da_, db_, TC_IDESC_I8, acc);
+                                else if (BF16) umma_bf16(tmem_d, da_, db_, TC_IDESC_BF16, acc);
                                 else umma_tf32(tmem_d, da_, db_, TC_IDESC, acc);
                             }
                         }
@@ -515,7 +550,10 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
         const uint32_t quad = (uint32_t)warp & 3u;
         const int etid = (int)threadIdx.x - kEpiFirst * 32;                      // 0..127 among the epilogue threads
         const uint32_t qlocal = quad * 32u + (uint32_t)lane;
-        for (int mu = member; mu < m_units; mu += a.group) gate_s[(mu * NCTA + rank) * TC_BM + qlocal] = a.floor_eps;
+        for (int mu = member; mu < m_units; mu += a.group) {
+            const uint32_t q = (uint32_t)(mu * NCTA + rank) * TC_BM + qlocal;
+            gate_s[(mu * NCTA + rank) * TC_BM + qlocal] = a.min_sim - batch_eps(a, q);
+        }
         int it = 0, visited = 0, next_refresh = 1;
         for (int t = t_begin; t < t_end; t++, visited++) {
             const uint32_t n0 = (uint32_t)t * TC_BN;
@@ -547,7 +585,8 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                     const uint32_t q = (uint32_t)mt * TC_BM + qlocal;
                     if (q < (uint32_t)a.batch) {
                         const float lb = hist_kth_lower_bound(a.hist + (size_t)q * kHistWords, a.k);
-                        gate_s[mt * TC_BM + qlocal] = fmaxf(a.floor_eps, lb - a.two_eps);
+                        const float eps = batch_eps(a, q);
+                        gate_s[mt * TC_BM + qlocal] = fmaxf(a.min_sim - eps, lb - 2.f * eps);
                     }
                 }
             }
@@ -586,10 +625,10 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
 #pragma unroll
                     for (int j = 0; j < 8; j++) {
                         const float4 f = f4[j];
-                        c0 += (__uint_as_float(r[4 * j + 0]) * f.x >= thr) ? 1u : 0u;
-                        c1 += (__uint_as_float(r[4 * j + 1]) * f.y >= thr) ? 1u : 0u;
-                        c2 += (__uint_as_float(r[4 * j + 2]) * f.z >= thr) ? 1u : 0u;
-                        c3 += (__uint_as_float(r[4 * j + 3]) * f.w >= thr) ? 1u : 0u;
+                        c0 += (acc_value<I8>(r[4 * j + 0]) * f.x >= thr) ? 1u : 0u;
+                        c1 += (acc_value<I8>(r[4 * j + 1]) * f.y >= thr) ? 1u : 0u;
+                        c2 += (acc_value<I8>(r[4 * j + 2]) * f.z >= thr) ? 1u : 0u;
+                        c3 += (acc_value<I8>(r[4 * j + 3]) * f.w >= thr) ? 1u : 0u;
                     }
                     const uint32_t cc = (c0 + c1) + (c2 + c3);
                     n_pass += cc;
@@ -607,7 +646,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                         if ((hits >> c) & 1u) {
 #pragma unroll
                             for (int j = 0; j < 32; j++) {
-                                if (__uint_as_float(r[j]) * inv_t[c * 32 + j] >= thr) {
+                                if (acc_value<I8>(r[j]) * inv_t[c * 32 + j] >= thr) {
                                     const uint32_t sl = slot_t[c * 32 + j];
                                     if ((qmask[sl >> 5] >> (sl & 31)) & 1u) { n_pass++; kept |= 1u << c; }
                                 }
@@ -630,7 +669,7 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                         if ((hits >> c) & 1u) {
 #pragma unroll
                             for (int j = 0; j < 32; j++) {
-                                const float pv = __uint_as_float(r[j]) * inv_t[c * 32 + j];
+                                const float pv = acc_value<I8>(r[j]) * inv_t[c * 32 + j];
                                 if (pv >= thr) {
                                     if (qmask) {
                                         const uint32_t sl = slot_t[c * 32 + j];
@@ -674,12 +713,13 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
 }
 
 // Final gate per query, read by the re-score kernel.
-__global__ void batch_final_gate_kernel(const uint32_t *hist, int batch, int k, float floor_eps, float two_eps, uint32_t *gate_ordered)
+__global__ void batch_final_gate_kernel(const uint32_t *hist, int batch, int k, const BatchArgs a, uint32_t *gate_ordered)
 {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= batch) return;
     const float lb = hist_kth_lower_bound(hist + (size_t)q * kHistWords, k);
-    gate_ordered[q] = score_to_ordered(fmaxf(floor_eps, lb - two_eps));
+    const float eps = batch_eps(a, (uint32_t)q);
+    gate_ordered[q] = score_to_ordered(fmaxf(a.min_sim - eps, lb - 2.f * eps));
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -760,21 +800,41 @@ int tc_batch_cap(int k) { (void)k; return 65536; }
 int tc_batch_m_tiles(int batch) { return (batch + TC_BM - 1) / TC_BM; }
 size_t tc_batch_hist_words(int batch) { return (size_t)batch * kHistWords; }
 
+bool make_map_i8(CUtensorMap *map, const int8_t *ptr, uint64_t rows, uint64_t K, uint32_t box_rows)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {K, rows};
+    cuuint64_t strides[1] = {K};
+    cuuint32_t box[2] = {(cuuint32_t)(4 * TC_BK), box_rows};        // 128 int8 = 128 bytes
+    cuuint32_t estr[2] = {1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t *>(ptr), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const float *q_inv, const float *mat,
                                        uint32_t n_rows, int D, const float *inv_norm, const uint32_t *doc_slot,
                                        const uint32_t *doc_bitmap, uint32_t bitmap_stride, int k, float min_sim, float eps, int sm_count,
                                        unsigned long long *cand, uint32_t *cand_count, uint32_t *hist,
                                        uint32_t *gate_ordered, uint32_t *overflow, uint32_t *group_sync,
-                                       cudaStream_t stream, const uint16_t *q_hi, const uint16_t *x_hi)
+                                       cudaStream_t stream, const uint16_t *q_hi, const uint16_t *x_hi, const TcInt8Operands *i8)
 {
     const bool bf16 = q_hi && x_hi;       // split-plane store: contract the upper planes as bf16 (kind::f16)
+    // int8 sidecar: contract the quantised queries and rows (kind::i8); `inv_norm` / `q_inv` then carry scale/|row| and
+    // scale/|q|, `eps` the rows' quantisation-error bound, i8->q_err the queries' own
+    if (i8 && (bf16 || !i8->queries || !i8->rows || !i8->q_err)) return cudaErrorInvalidValue;
     if (batch > DA_TC_MAX_BATCH) return cudaErrorInvalidValue;
     const int m_tiles = tc_batch_m_tiles(batch);
     // CTA pairs need two query tiles to work on; DA_TC_SINGLE_CTA=1 keeps the single-CTA form (for comparisons)
     static const bool single_only = [] { const char *v = getenv("DA_TC_SINGLE_CTA"); return v && v[0] == '1'; }();
     const int ncta = (m_tiles >= 2 && !single_only) ? 2 : 1;
     CUtensorMap map_q, map_x;
-    if (bf16) {
+    if (i8) {
+        if ((reinterpret_cast<uintptr_t>(i8->rows) & 15) || (reinterpret_cast<uintptr_t>(i8->queries) & 15) || (D & 15)) return cudaErrorInvalidValue;
+        if (!make_map_i8(&map_q, i8->queries, (uint64_t)batch, (uint64_t)D, TC_BM) ||
+            !make_map_i8(&map_x, i8->rows, (uint64_t)n_rows, (uint64_t)D, TC_BN / ncta))
+            return cudaErrorInvalidValue;
+    } else if (bf16) {
         if ((reinterpret_cast<uintptr_t>(x_hi) & 15) || (reinterpret_cast<uintptr_t>(q_hi) & 15) || (D & 7)) return cudaErrorInvalidValue;
         if (!make_map_bf16(&map_q, q_hi, (uint64_t)batch, (uint64_t)D, TC_BM) ||
             !make_map_bf16(&map_x, x_hi, (uint64_t)n_rows, (uint64_t)D, TC_BN / ncta))
@@ -791,12 +851,14 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     if (e != cudaSuccess) return e;
     BatchArgs a{};
     a.n_rows = n_rows; a.K = D; a.batch = batch; a.k = k; a.cap = tc_batch_cap(k);
-    a.floor_eps = min_sim - eps; a.two_eps = 2.f * eps;
+    a.min_sim = min_sim; a.eps = eps; a.q_err = i8 ? i8->q_err : nullptr;
     a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
     a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow;
     const void *kernel = ncta == 2
-        ? (bf16 ? (const void *)tc_batch_candidates_kernel<true, 2> : (const void *)tc_batch_candidates_kernel<false, 2>)
-        : (bf16 ? (const void *)tc_batch_candidates_kernel<true, 1> : (const void *)tc_batch_candidates_kernel<false, 1>);
+        ? (i8 ? (const void *)tc_batch_candidates_kernel<OP_I8, 2> : bf16 ? (const void *)tc_batch_candidates_kernel<OP_BF16, 2>
+                                                                          : (const void *)tc_batch_candidates_kernel<OP_TF32, 2>)
+        : (i8 ? (const void *)tc_batch_candidates_kernel<OP_I8, 1> : bf16 ? (const void *)tc_batch_candidates_kernel<OP_BF16, 1>
+                                                                          : (const void *)tc_batch_candidates_kernel<OP_TF32, 1>);
     e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TCB_SMEM_BYTES);
     if (e != cudaSuccess) return e;
 
@@ -822,7 +884,7 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     // 1.25M x 1536 rows, free-running groups of 1/4/16/32 CTAs): 274/188/152/102 GB of DRAM reads for a 7.7 GB shard;
     // with the members of a group in lockstep (below): 44 GB at group 4, 22.7 GB at group 8 (profiles/README.md).
     const int m_units = (m_tiles + ncta - 1) / ncta;
-    const double esz = bf16 ? 2.0 : 4.0;
+    const double esz = i8 ? 1.0 : bf16 ? 2.0 : 4.0;
     const double tile_mb = (double)TC_BN * D * esz / 1e6, q_mb = (double)batch * D * esz / 1e6;
     int group = 1;
     while (group < m_units && group < n_units && 2.0 * (n_units / group) * tile_mb + q_mb > 90.0) group++;   // two live row tiles per group (lockstep window)
@@ -840,7 +902,7 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a};
     e = cudaLaunchKernelExC(&cfg, kernel, args);
     if (e != cudaSuccess) return e;
-    batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a.floor_eps, a.two_eps, gate_ordered);
+    batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a, gate_ordered);
     return cudaGetLastError();
 }
 

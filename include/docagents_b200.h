@@ -84,10 +84,11 @@ typedef struct {
                                    dim must be a multiple of 16; the IVFFlat path (TMA over fp32 rows) is not available. */
 #define DA_STORE_Q8_SIDECAR 0x2u /* int8 sidecar: next to the fp32 rows the store keeps every row as dim int8
                                    values with a per-row scale and the row's own quantisation-error bound (dim + 8 more bytes
-                                   per row).  Searches of fewer than 12 queries scan the int8 rows (a quarter of the bytes),
+                                   per row).  Searches of one or two queries scan the int8 rows (a quarter of the bytes),
                                    keep every row whose score interval can still reach the k-th best, and re-score those
-                                   from the fp32 rows with the fp32 scan's arithmetic: results are bit-identical to the
-                                   default layout.  dim must be a multiple of 32; excludes DA_STORE_SPLIT16. */
+                                   from the fp32 rows with the fp32 scan's arithmetic; batches with a similarity floor of
+                                   at least 0.5 contract the int8 rows on the tensor cores (kind::i8) for their candidates.
+                                   Results are bit-identical to the default layout.  dim must be a multiple of 32; excludes DA_STORE_SPLIT16. */
 
 /* Fills `out` with a fresh ncclUniqueId to hand to every rank's da_config. */
 int da_nccl_unique_id(uint8_t out[DA_NCCL_ID_BYTES]);
@@ -128,7 +129,7 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
 #define DA_SEARCH_READ_ALL_ROWS 0x2u  /* doc mask as a predicate: read every row even if its document is
                                          not requested (configs[1] "HBM-bound" measurement); default skips them */
 #define DA_SEARCH_IVF           0x4u  /* probe the IVFFlat lists instead of the exact scan */
-#define DA_SEARCH_NO_TENSOR     0x10u /* keep a batch on the fp32 SIMT scan (default from 4 queries up -- 12 with the int8 sidecar, 16 in the
+#define DA_SEARCH_NO_TENSOR     0x10u /* keep a batch on the fp32 SIMT scan (default from 4 queries up -- 3 with the int8 sidecar, 16 in the
                                          split-plane layout --: tcgen05 TF32
                                          candidate generation + exact fp32 re-score; results are identical) */
 #define DA_SEARCH_NO_COMPACT    0x40u /* a filter naming at most 1/16 of the documents is served by compacting the requested rows

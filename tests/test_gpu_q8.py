@@ -149,3 +149,33 @@ def test_sidecar_overflow_falls_back_to_the_fp32_scan():
         b = st.search(base, k, all_docs=True, min_similarity=-np.inf, no_q8=True)
         same(a, b, 0)
         assert len(a[2][0]) == k
+
+
+@pytest.mark.parametrize("batch,k,floor", [(3, 5, 0.7), (16, 10, 0.7), (64, 10, 0.7), (300, 128, 0.55), (150, 100, -np.inf),
+                                           (300, 128, 0.0)])
+def test_sidecar_int8_tensor_batches_equal_fp32_scan(batch, k, floor):
+    """Batches on a sidecar store: tcgen05 kind::i8 over the int8 rows and queries generates the candidates (slack =
+    the rows' largest error bound combined with each query's own), the exact re-score from the fp32 rows makes the
+    answer bit-identical to the fp32 scan.  Searches without a floor of at least 0.5 keep the TF32 contraction."""
+    S = oracle.Synth(n_clusters=16)
+    n, dim = 50_000, 1536
+    with GpuStore(dim=dim, capacity_rows=n, q8_sidecar=True) as st, GpuStore(dim=dim, capacity_rows=n) as fp:
+        st.generate_synthetic(S, 0, n)
+        fp.generate_synthetic(S, 0, n)
+        docs = oracle.doc_ids(S, 0, n // 200)
+        qs = np.stack([oracle.gen_query(S, i, i % 16, dim) for i in range(batch)])
+        for kw in (dict(all_docs=True), dict(doc_ids=docs[::2]), dict(doc_ids=[docs[i % 3::3] for i in range(batch)])):
+            a = st.search(qs, k, min_similarity=floor, **kw)
+            assert st.stats().last_rows_read == n                        # the contraction path ran
+            if floor >= 0.5:
+                assert st.stats().last_bytes_algorithmic < n * (dim + 9)  # ... over the int8 plane
+            else:                                                         # no floor to bound the int8 slack: TF32 over fp32 rows
+                assert st.stats().last_bytes_algorithmic >= n * dim * 4
+            b = fp.search(qs, k, min_similarity=floor, no_tensor=True, **kw)
+            for i in range(batch):
+                same(a, b, i, (list(kw.keys()), i))
+        # the same store through the TF32 path over its fp32 rows
+        c = st.search(qs, k, min_similarity=floor, all_docs=True, no_q8=True)
+        d = st.search(qs, k, min_similarity=floor, all_docs=True)
+        for i in range(batch):
+            same(c, d, i)
