@@ -207,7 +207,9 @@ def cpu_reference_run(steps: int, warmup: int, want_seconds: float = 12.0):
     bounded sample of the workload.  Returns (queries/s extrapolated to N_ROWS, info dict, ms_per_step)."""
     import oracle
     S = oracle.Synth()
-    threads = int(os.environ.get("DA_CPU_THREADS", 0)) or oracle.num_threads()
+    # every host thread this process may run on (torchrun presets OMP_NUM_THREADS=1 for its workers: not a reason to
+    # time the CPU path on one core)
+    threads = int(os.environ.get("DA_CPU_THREADS", 0)) or len(os.sched_getaffinity(0)) or oracle.num_threads()
     try:
         avail_gb = next(int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")) / 1e6
     except Exception:   # noqa: BLE001
