@@ -570,6 +570,19 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         // the first row tile on.  Without one the running k-th best sits at noise level for a long while and half the
         // rows would pass (measured: configs[3], no floor, k = 100, overflows every list); those searches keep TF32.
         pl.tc_i8 = pl.use_tc && st->q8 && !(p->flags & DA_SEARCH_NO_Q8) && st->dim % 16 == 0 && pl.min_sim >= 0.5f;
+        if (pl.tc_i8) {
+            // The contraction's slack is ONE bound for all rows, the largest of any resident row: a single row that
+            // quantises badly (one huge element) would widen it for everybody, so such stores keep TF32 for batches.
+            for (Shard &s : st->shards) {
+                if (s.q8_dirty) {        // rows were written since the last look: fetch the rows' error bound (4 bytes)
+                    CU(cudaSetDevice(s.device));
+                    CU(cudaMemcpyAsync(&s.q8_err_max, s.q8_errmax, 4, cudaMemcpyDeviceToHost, s.stream));
+                    CU(cudaStreamSynchronize(s.stream));
+                    s.q8_dirty = false;
+                }
+                if (s.q8_err_max > 0.05f) pl.tc_i8 = false;
+            }
+        }
     }
     if (!all_docs) {
         size_t selected = 0;
@@ -610,11 +623,6 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         if (pl.tc_i8) {
             CU(s.d_q8q.ensure(nq_elems)); CU(s.d_q8qf.ensure(p->batch)); CU(s.d_q8qe.ensure(p->batch));
-            if (s.q8_dirty) {            // rows were written since the last look: fetch the rows' error bound (4 bytes)
-                CU(cudaMemcpyAsync(&s.q8_err_max, s.q8_errmax, 4, cudaMemcpyDeviceToHost, s.stream));
-                CU(cudaStreamSynchronize(s.stream));
-                s.q8_dirty = false;
-            }
         }
         if (pl.use_tc) {
             CU(s.d_cand.ensure((size_t)p->batch * da::tc_batch_cap(pl.k)));

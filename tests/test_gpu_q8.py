@@ -179,3 +179,27 @@ def test_sidecar_int8_tensor_batches_equal_fp32_scan(batch, k, floor):
         d = st.search(qs, k, min_similarity=floor, all_docs=True)
         for i in range(batch):
             same(c, d, i)
+
+
+def test_one_badly_quantised_row_keeps_batches_on_tf32():
+    """The int8 contraction has one slack for all rows; a row whose own bound is large (one huge element) must not
+    widen it for every batch: such a store answers batches through TF32, single searches still through the int8 scan."""
+    S = oracle.Synth(n_clusters=16)
+    n, dim, batch, k = 20_000, 1024, 32, 10
+    mat = np.array(oracle.gen_rows(S, 0, n, dim))
+    mat[123, 7] = np.float32(2.0)        # ~64x a typical element: the others keep only ~2 levels, e_x ~ 0.065
+    chunk = oracle.chunk_ids(S, 0, n)
+    docs = oracle.doc_ids(S, 0, n // 200)
+    qs = np.stack([oracle.gen_query(S, i, i % 16, dim) for i in range(batch)])
+    with GpuStore(dim=dim, capacity_rows=n, q8_sidecar=True) as st:
+        for d in range(n // 200):
+            st.save_chunks_raw(docs[d], chunk[d * 200:(d + 1) * 200])
+        st.save_embeddings_raw(chunk, mat)
+        a = st.search(qs, k, all_docs=True)
+        assert st.stats().last_bytes_algorithmic >= n * dim * 4          # fp32 rows, not the int8 plane
+        assert st.stats().tensor_overflows == 0
+        b = st.search(qs, k, all_docs=True, no_tensor=True, no_q8=True)
+        for i in range(batch):
+            same(a, b, i)
+        st.search(qs[0], k, all_docs=True)
+        assert st.stats().last_bytes_algorithmic < n * (dim + 20)
