@@ -20,7 +20,10 @@ def _built(built_lib):
 pytestmark = pytest.mark.gpu
 
 
-def test_concurrent_topk_calls_are_batched_and_results_unchanged():
+@pytest.mark.parametrize("sidecar", [False, True], ids=["fp32", "int8_sidecar"])
+def test_concurrent_topk_calls_are_batched_and_results_unchanged(sidecar):
+    """`sidecar`: the batched store also keeps the int8 copy, so merged calls (floor 0.7) ride the kind::i8 contraction
+    while the plain store answers each call with the fp32 scan: the results must still be identical."""
     S = oracle.Synth(n_clusters=8)
     n, dim = 60_000, 1536
     docs_a = [uuid.UUID(bytes=bytes(b)) for b in oracle.doc_ids(S, 0, n // 200)[::2]]
@@ -29,7 +32,7 @@ def test_concurrent_topk_calls_are_batched_and_results_unchanged():
     qs = [oracle.gen_query(S, i, i % 8, dim) for i in range(n_threads)]
     ks = [5 if i % 3 else 10 for i in range(n_threads)]
     with GpuStore(dim=dim, capacity_rows=n) as plain, \
-            GpuStore(dim=dim, capacity_rows=n, batch_window_us=20_000, batch_max=32) as batched:
+            GpuStore(dim=dim, capacity_rows=n, batch_window_us=20_000, batch_max=32, q8_sidecar=sidecar) as batched:
         plain.generate_synthetic(S, 0, n)
         batched.generate_synthetic(S, 0, n)
         want = [plain.TopK(docs_a if i % 2 == 0 else docs_b, qs[i], ks[i]) for i in range(n_threads)]
