@@ -81,3 +81,37 @@ def test_random_configurations_match_the_oracle(seed):
                     assert np.allclose(b[1][i], scores[0], rtol=REL_TOL, atol=ABS_TOL), info
             except AssertionError as e:
                 raise AssertionError(f"{info}: {e}") from e
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_random_configurations_every_path_gives_the_same_answer(seed):
+    """The same random cases on a store with the int8 sidecar: the default routing (int8 scan, int8/TF32 contraction,
+    compacted lists) against the plain fp32 row loop, bit for bit, for one query and for batches of 3 and 20."""
+    rng = np.random.default_rng(5000 + seed)
+    S0 = oracle.Synth()
+    done = 0
+    while done < 10:
+        c = _random_case(rng, seed * 100 + done)
+        n, dim = c.mat.shape
+        if dim % 32:
+            continue
+        done += 1
+        chunk = oracle.chunk_ids(S0, 0, n)
+        docs = oracle.doc_ids(S0, 0, c.n_docs + 8)
+        info = dict(name=c.name, n=n, dim=dim, k=c.k, docs=c.docs, min_sim=c.min_sim, n_docs=c.n_docs)
+        with GpuStore(dim=dim, capacity_rows=n + 4, q8_sidecar=True) as st:
+            for d in range(c.n_docs):
+                st.save_chunks_raw(docs[d], chunk[c.row_doc == d])
+            st.save_embeddings_raw(chunk, c.mat)
+            filt = docs[: c.n_docs] if c.docs is None else (docs[np.asarray(c.docs, dtype=np.int64)] if len(c.docs) else docs[:0])
+            for batch in (1, 3, 20):
+                qs = np.stack([c.q * np.float32(1 + 0.01 * i) + np.float32(0.02 * i / np.sqrt(dim)) * rng.standard_normal(dim).astype(np.float32)
+                               for i in range(batch)]).astype(np.float32)
+                a = st.search(qs, c.k, filt, min_similarity=c.min_sim)
+                b = st.search(qs, c.k, filt, min_similarity=c.min_sim, no_q8=True, no_tensor=True, no_compact=True)
+                for i in range(batch):
+                    assert np.array_equal(a[2][i], b[2][i]), (info, batch, i)
+                    assert np.array_equal(a[1][i].view(np.uint32), b[1][i].view(np.uint32)), (info, batch, i)
+                    assert np.array_equal(a[0][i], b[0][i]), (info, batch, i)
+            check_against_oracle(c, st.search(c.q, c.k, filt, min_similarity=c.min_sim)[2][0],
+                                 st.search(c.q, c.k, filt, min_similarity=c.min_sim)[1][0])
