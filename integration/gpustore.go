@@ -42,6 +42,8 @@ type GPUOptions struct {
 	Devices       []int   // GPU_DEVICES
 	CapacityRows  uint64  // GPU_CAPACITY_ROWS, per device
 	MinSimilarity float32 // GPU_MIN_SIMILARITY, default 0.7 (postgres.go:223)
+	Int8Sidecar   bool    // GPU_INT8_SIDECAR: keep an int8 copy of every row (25 % more HBM, ~3.6x queries/s, same answers)
+	BatchWindowUs uint32  // GPU_BATCH_WINDOW_US: merge TopK calls that arrive within this window into one pass (0 = off)
 }
 
 func gpuErr(rc C.int) error {
@@ -62,6 +64,10 @@ func NewGPU(pg *PostgresStore, o GPUOptions) (*GPUStore, error) {
 	}
 	cfg.capacity_rows = C.uint64_t(o.CapacityRows)
 	cfg.min_similarity = C.float(o.MinSimilarity)
+	if o.Int8Sidecar {
+		cfg.flags |= C.DA_STORE_Q8_SIDECAR
+	}
+	cfg.batch_window_us = C.uint32_t(o.BatchWindowUs)
 	s := &GPUStore{PostgresStore: pg}
 	if err := gpuErr(C.da_store_create(&cfg, &s.h)); err != nil {
 		return nil, err
