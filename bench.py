@@ -202,56 +202,151 @@ def merge_candidates(per_rank, k: int):
     return scores[order], rows[order]
 
 
-def cpu_reference_run(steps: int, warmup: int, want_seconds: float = 12.0):
-    """The reference path's CPU implementation (oracle, pgvector-flag build, all host threads) on a
-    bounded sample of the workload.  Returns (queries/s extrapolated to N_ROWS, info dict, ms_per_step)."""
+def host_mem_available_gb() -> float:
+    try:
+        return next(int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")) / 1e6
+    except Exception:   # noqa: BLE001
+        return 0.0
+
+
+def cpu_rows_that_fit(full: bool) -> int:
+    """Rows of the corpus the CPU arm scans.  full=True (the --impl reference arm): all N_ROWS when the host has
+    1.15 x the corpus in available memory, else the largest multiple of 1M rows that fits.  full=False (the
+    cpu_baseline leg of the GPU arm): a bounded sample, at most 1M rows."""
+    if os.environ.get("DA_CPU_SAMPLE_ROWS"):
+        return min(N_ROWS, int(os.environ["DA_CPU_SAMPLE_ROWS"]))
+    avail = host_mem_available_gb() * 1e9
+    row_bytes = DIM * 4
+    if not full:
+        return min(N_ROWS, 1_000_000 if avail > 64e9 else 400_000)
+    fit = int(avail / 1.15 / row_bytes)
+    if fit >= N_ROWS:
+        return N_ROWS
+    return max(min(N_ROWS, 400_000), fit // 1_000_000 * 1_000_000)
+
+
+def cpu_reference_run(steps: int, warmup: int, full: bool = False):
+    """The reference path's CPU implementation (oracle, pgvector-flag build, all host threads).
+    Returns (queries/s at N_ROWS, info dict, measured ms per step, rows scanned per step)."""
     import oracle
     S = oracle.Synth()
     # every host thread this process may run on (torchrun presets OMP_NUM_THREADS=1 for its workers: not a reason to
     # time the CPU path on one core)
     threads = int(os.environ.get("DA_CPU_THREADS", 0)) or len(os.sched_getaffinity(0)) or oracle.num_threads()
-    try:
-        avail_gb = next(int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")) / 1e6
-    except Exception:   # noqa: BLE001
-        avail_gb = 0.0
-    default_sample = 1_000_000 if avail_gb > 64 else 400_000      # 12.3 GB (= configs[1]) when the box has the RAM
-    sample = int(os.environ.get("DA_CPU_SAMPLE_ROWS", min(N_ROWS, default_sample)))
+    oracle.set_num_threads(threads)
+    sample = cpu_rows_that_fit(full)
+    t_gen = time.perf_counter()
     mat = oracle.gen_rows(S, 0, sample, DIM)
+    t_gen = time.perf_counter() - t_gen
     qs = [oracle.gen_query(S, i, (i * 37) % S.n_clusters, DIM) for i in range(max(1, steps + warmup))]
-    one = None
-    for i in range(warmup):
-        t0 = time.perf_counter()
-        oracle.topk(mat, None, None, qs[i], TOP_K, MIN_SIM, fast=True, threads=threads)
-        one = time.perf_counter() - t0
-    if one is None:
-        t0 = time.perf_counter()
-        oracle.topk(mat, None, None, qs[0], TOP_K, MIN_SIM, fast=True, threads=threads)
-        one = time.perf_counter() - t0
+    for i in range(max(1, warmup)):
+        oracle.topk(mat, None, None, qs[i % len(qs)], TOP_K, MIN_SIM, fast=True, threads=threads)
     t0 = time.perf_counter()
     for i in range(steps):
-        oracle.topk(mat, None, None, qs[warmup + i], TOP_K, MIN_SIM, fast=True, threads=threads)
+        oracle.topk(mat, None, None, qs[(warmup + i) % len(qs)], TOP_K, MIN_SIM, fast=True, threads=threads)
     dt = (time.perf_counter() - t0) / steps
     qps_sample = 1.0 / dt
     qps_full = qps_sample * sample / N_ROWS
+    whole = sample == N_ROWS
     info = {"value": qps_full, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": (f"{sample} of {N_ROWS} rows x {DIM} ({sample * DIM * 4 / 1e9:.2f} GB) scanned once per step by "
-                       f"oracle/oracle_fast.c (pgvector build flags, OpenMP, {threads} threads), {steps} steps; "
-                       f"{qps_sample:.2f} queries/s on the sample, linearly extrapolated to {N_ROWS} rows; "
-                       f"{sample * (DIM * 4 + 8) / dt / 1e9:.1f} GB/s effective"),
+                       f"oracle/oracle_fast.c (pgvector build flags, OpenMP, {threads} threads), {steps} steps; " +
+                       ("the whole corpus: measured, not extrapolated; " if whole else
+                        f"{qps_sample:.2f} queries/s on the sample, linearly extrapolated to {N_ROWS} rows; ") +
+                       f"{sample * (DIM * 4 + 8) / dt / 1e9:.1f} GB/s effective; corpus generated in {t_gen:.1f} s (untimed)"),
+            "rows_scanned": sample, "extrapolated": not whole,
             "gbs": sample * (DIM * 4 + 8) / dt / 1e9}
-    return qps_full, info, dt * 1e3 * N_ROWS / sample
+    del mat
+    return qps_full, info, dt * 1e3, sample
+
+
+SEEDS = {"data": hex(0xD0C5EED), "centroids": hex(0xC0FFEE), "queries": hex(0xBEEF)}    # asserted against Synth() in both arms
+
+
+def bench_config(n_gpus: int, workload_key: str) -> dict:
+    """The `config` object of the JSON line: the same dict, key for key, in the GPU arm and the reference arm."""
+    per_gpu = -(-N_ROWS // max(1, n_gpus))
+    return {"workload": workload_name(n_gpus), "workload_key": workload_key, "rows": N_ROWS, "dim": DIM, "top_k": TOP_K,
+            "batch": BATCH, "min_similarity": MIN_SIM if MIN_SIM == MIN_SIM and abs(MIN_SIM) != float("inf") else None,
+            "filter_docs": FILTER_DOCS, "n_gpus": n_gpus,
+            "l2": "inputs larger than any cache: %.2f GB of rows read per step (%.2f GB per GPU vs 126 MB of L2)"
+                  % (N_ROWS * DIM * 4 / 1e9, per_gpu * DIM * 4 / 1e9),
+            "seeds": SEEDS}
+
+
+def check_against_oracle(last, queries, cluster_of, filter_doc_indexes, max_queries: int = 8):
+    """Checks the answer of the last timed end-to-end step against the CPU oracle (checker only, never timed).
+
+    With a similarity floor of 0.7 -- or, with no floor, k rows that all come from the query's own cluster (same-
+    cluster cosine ~0.8 against ~0 +- 0.02 across clusters) -- a row can only qualify if its document belongs to the
+    query's cluster, so the oracle scores exactly those documents (49 x 200 rows at 10M rows): milliseconds per
+    query.  Acceptance rule of BASELINE.json: scores within 1e-5 relative, same rows in the same order except
+    where the oracle's scores tie within that tolerance."""
+    import oracle
+    S = oracle.Synth()
+    assert SEEDS == {"data": hex(S.seed_data), "centroids": hex(S.seed_centroid), "queries": hex(S.seed_query)}
+    out_ids, out_scores, out_rows, out_n = last
+    n_docs = -(-N_ROWS // S.chunks_per_doc)
+    b = queries.shape[0]
+    picks = sorted(set(int(round(i * (b - 1) / max(1, min(b, max_queries) - 1))) for i in range(min(b, max_queries))))
+    rows_checked, max_rel, problems = 0, 0.0, []
+    for qi in picks:
+        cl = cluster_of(qi)
+        docs = [d for d in range(cl, n_docs, S.n_clusters)]
+        if filter_doc_indexes is not None:
+            docs = sorted(set(filter_doc_indexes))           # every requested document, whatever its cluster
+        spans = [(d * S.chunks_per_doc, min(N_ROWS, (d + 1) * S.chunks_per_doc)) for d in docs]
+        spans = [(lo, hi) for lo, hi in spans if hi > lo]
+        if not spans:
+            if int(out_n[qi]) != 0:
+                problems.append(f"query {qi}: {int(out_n[qi])} hits but no candidate document")
+            continue
+        sub_rows = np.concatenate([np.arange(lo, hi, dtype=np.int64) for lo, hi in spans])
+        sub = np.concatenate([oracle.gen_rows(S, lo, hi - lo, DIM) for lo, hi in spans])
+        o_rows, o_scores, _ = oracle.topk(sub, None, None, queries[qi], TOP_K, MIN_SIM)
+        o_rows = sub_rows[o_rows]
+        if MIN_SIM == float("-inf") and len(o_scores) and float(o_scores[-1]) < 0.3:
+            problems.append(f"query {qi}: oracle's k-th score {float(o_scores[-1]):.3f} is not a same-cluster score; "
+                            "the cluster-restricted check does not apply")
+            continue
+        n = int(out_n[qi])
+        g_rows, g_scores = out_rows[qi, :n].astype(np.int64), out_scores[qi, :n]
+        rows_checked += n
+        if n != len(o_rows):
+            problems.append(f"query {qi}: {n} hits, oracle {len(o_rows)}")
+            continue
+        if n == 0:
+            continue
+        rel = np.abs(g_scores.astype(np.float64) - o_scores.astype(np.float64)) / np.maximum(1e-30, np.abs(o_scores.astype(np.float64)))
+        max_rel = max(max_rel, float(rel.max()))
+        if rel.max() > 1e-5:
+            problems.append(f"query {qi}: score off by {rel.max():.2e} relative")
+        i = 0
+        while i < n:                                         # runs of oracle scores that tie within the tolerance
+            j = i + 1
+            while j < n and abs(float(o_scores[j]) - float(o_scores[j - 1])) <= 1e-5 * abs(float(o_scores[j - 1])):
+                j += 1
+            if set(g_rows[i:j].tolist()) != set(o_rows[i:j].tolist()):
+                problems.append(f"query {qi}: rows {g_rows[i:j].tolist()} at ranks {i}..{j - 1}, oracle {o_rows[i:j].tolist()}")
+                break
+            i = j
+    return {"matches_oracle": not problems, "queries_checked": len(picks), "rows_checked": rows_checked,
+            "max_rel_err": max_rel, "tolerance_rel": 1e-5, "problems": problems[:4],
+            "how": "oracle/oracle.c over the documents of each checked query's cluster (or the requested documents)"}
 
 
 def run_reference_arm(args, rank: int, emit):
     if rank != 0:
         return
     steps = max(1, args.steps)
-    qps, info, ms = cpu_reference_run(steps, max(0, args.warmup))
+    qps, info, ms, rows = cpu_reference_run(steps, max(0, args.warmup), full=True)
     line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.gpus), "note": "CPU path: pgvector semantics restated in C "
-                       "(the reference's Go + Postgres/pgvector cannot run on this box)"},
+            "config": bench_config(args.gpus, args.workload),
+            "note": "CPU path: pgvector semantics restated in C (the reference's Go + Postgres/pgvector cannot run on "
+                    "this box); ms_per_step is the measured time of one scan of rows_scanned rows",
+            "rows_scanned": rows, "extrapolated": info["extrapolated"],
             "cpu_baseline": info,
             "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
@@ -353,11 +448,12 @@ def main():
         return queries[lo_:lo_ + BATCH]
 
     n_docs = N_ROWS // S.chunks_per_doc
+    filter_doc_list = None
+    if FILTER_DOCS:      # half of the requested documents from query 0's cluster, the rest spread over the corpus
+        filter_doc_list = ([((0 * 37) % S.n_clusters + j * S.n_clusters) % n_docs for j in range(FILTER_DOCS // 2)] +
+                           [(7 + j * (n_docs // FILTER_DOCS)) % n_docs for j in range(FILTER_DOCS - FILTER_DOCS // 2)])
     skw = dict(all_docs=True) if not FILTER_DOCS else dict(
-        doc_ids=np.stack([synth.doc_ids(S, d, 1)[0] for d in
-                          ([((0 * 37) % S.n_clusters + j * S.n_clusters) % n_docs for j in range(FILTER_DOCS // 2)] +
-                           [(7 + j * (n_docs // FILTER_DOCS)) % n_docs for j in range(FILTER_DOCS - FILTER_DOCS // 2)])]),
-        read_all_rows=READ_ALL)
+        doc_ids=np.stack([synth.doc_ids(S, d, 1)[0] for d in filter_doc_list]), read_all_rows=READ_ALL)
     skw.update(min_similarity=MIN_SIM, no_tensor=NO_TENSOR, no_q8=side_variant)
 
     # warm-up (untimed): W full searches through the public call
@@ -399,9 +495,8 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
         "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(world), "rows_per_gpu": hi - lo, "dim": DIM, "top_k": TOP_K,
-                   "batch": BATCH, "workload_key": args.workload, "l2": "inputs larger than L2 (%.1f GB per GPU per step vs 126 MB)" % ((hi - lo) * DIM * 4 / 1e9),
-                   "seeds": {"data": hex(S.seed_data), "centroids": hex(S.seed_centroid), "queries": hex(S.seed_query)}},
+        "config": bench_config(world, args.workload),
+        "rows_this_rank": hi - lo,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * DIM * 4 + (0 if not FILTER_DOCS else (n_docs + 31) // 32 * 4),
                 "d2h_bytes_per_step": BATCH * TOP_K * 24,
                 "ms_per_step": e2e_s * 1e3 / steps},
@@ -409,14 +504,24 @@ def main():
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(bytes_per_launch) if args.workload == "cfg3_b1" else None,
+                     "traffic_source": ("ncu --set full capture of this kernel at 10M rows on one GPU (profiles/scan_traffic.json), "
+                                        "scaled by this run's algorithmic bytes per launch; not re-measured in this run")
+                                       if args.workload == "cfg3_b1" else None,
                      "kernel": ("scan_topk_kernel (upper plane) + split collect/rescore/select" if SPLIT16 else
                                 "q8_scan_kernel + collect/rescore/select" if "int8 sidecar" in workload_name(world) else
                                 "scan_topk_kernel" if "SIMT" in workload_name(world) else
                                 "tc_batch_candidates_kernel + rescore + select"), "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "kernel_ms": scan_ms, "launches_timed": scan_launches,
                      "frac_of_nominal_8000": achieved / 8000.0},
-        "result_check": {"hits": int(last[3][0]), "top_score": float(last[1][0][0]) if last[3][0] else None},
     }
+    assert SEEDS == {"data": hex(S.seed_data), "centroids": hex(S.seed_centroid), "queries": hex(S.seed_query)}
+    if rank == 0:
+        # the answer of the last timed end-to-end step (merged over all ranks) against the CPU oracle
+        q_lo = ((warmup + steps - 1) * BATCH) % (n_q - BATCH + 1) if n_q > BATCH else 0
+        chk = check_against_oracle(last, qbatch(warmup + steps - 1), lambda i: ((q_lo + i) * 37) % S.n_clusters,
+                                   filter_doc_list)
+        chk.update(hits=int(last[3][0]), top_score=float(last[1][0][0]) if last[3][0] else None)
+        line["result_check"] = chk
     if side_variant:
         vkw = dict(skw, no_q8=False)
         for i in range(warmup):
@@ -458,12 +563,15 @@ def main():
                             "launches_timed": scan_launches}
     st.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "cfg3_b1":
-        _, info, _ = cpu_reference_run(steps=8, warmup=1)
+        _, info, _, _ = cpu_reference_run(steps=8, warmup=1, full=False)
         line["cpu_baseline"] = info
     if world > 1:
         dist.destroy_process_group()
     if rank == 0:
         emit(line)
+        if not line["result_check"]["matches_oracle"]:
+            print("bench: the answer of the last step does not match the oracle: %s" % line["result_check"]["problems"], file=sys.stderr)
+            sys.exit(1)
 
 
 if __name__ == "__main__":

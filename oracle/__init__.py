@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
         L.orc_table_upsert.argtypes = [C.c_void_p, C.c_void_p, fp, C.c_uint64, C.c_int]
         L.orc_table_upsert.restype = C.c_int
         L.orc_num_threads.restype = C.c_int
+        L.orc_set_num_threads.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -223,3 +224,7 @@ class Table:
 
 def num_threads() -> int:
     return lib().orc_num_threads()
+
+
+def set_num_threads(n: int) -> None:
+    lib().orc_set_num_threads(int(n))

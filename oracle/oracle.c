@@ -348,4 +348,15 @@ int orc_num_threads(void)
     return 1;
 #endif
 }
+
+/* Threads used by the parallel loops that take no explicit count (the corpus generator).  Harness plumbing:
+ * torchrun presets OMP_NUM_THREADS=1 for its workers. */
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
 #endif /* !ORC_FAST */
