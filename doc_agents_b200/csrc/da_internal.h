@@ -81,14 +81,18 @@ int scan_pick_nq(int dim, int k, int batch);   // how many queries one pass may 
 // Launches the fused scan on `stream`; grid is chosen inside (persistent, multiple of SM count).
 cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t stream, int *grid_out);
 int scan_grid_for(int sm_count);
+// Forces the (lazy) loading, on the current device, of every kernel a one-query, non-indirect launch_scan can pick.
+cudaError_t scan_preload_single_query_variants();
 
 // Rows whose document bit is set in `bitmap`, compacted (in no particular order) into rows[0 .. *n_out).
 cudaError_t launch_filter_compact(const uint32_t *doc_slot, const uint32_t *bitmap, uint32_t n_rows, uint32_t *rows,
                                   uint32_t *n_out, cudaStream_t stream);
 
-// Merge of G gathered candidate blocks (one block per rank, layout: batch*k ids of 16 B, then batch*k keys).
+// Merge of G gathered candidate blocks (one block per rank, `block_bytes` apart -- 0 = packed --, layout: batch*k ids
+// of 16 B, then batch*k keys, then an optional trailer whose first word is the rank's overflow flag; the OR of the
+// trailers goes to *out_flags when it is not null).
 cudaError_t launch_merge(const uint8_t *gathered, int G, int batch, int k, key_t64 *out_keys,
-                         uint8_t *out_ids, cudaStream_t stream);
+                         uint8_t *out_ids, cudaStream_t stream, size_t block_bytes = 0, uint32_t *out_flags = nullptr);
 
 // ---------------------------------------------------------------------------
 // Row maintenance

@@ -21,8 +21,12 @@
 //     16384, the device must have at most DA_NOALLOC_MAX_CTAS (256) SMs.  Anything beyond is
 //     rejected with DA_ERR_CAPACITY / DA_ERR_INVALID and a message; nothing is launched.
 //   - the first call on each device looks up the device address of the scratch array
-//     (cudaGetSymbolAddress) and the SM count, and loads the kernels.  Make that first call
-//     during start-up, before any stream capture begins on that device.
+//     (cudaGetSymbolAddress) and the SM count, and loads every kernel variant this entry point can
+//     ever launch (the scan picks a variant by dim % 8, pointer alignment and tile shape; CUDA
+//     loads a function lazily on first use, which allocates and synchronises -- so they are all
+//     loaded here, not by some later call with another dim).  Make that first call during
+//     start-up, before any stream capture begins on that device.
+//   - the calling thread's current CUDA device is left as it was found.
 //   - all calls on one device share the one scratch array, and it keeps whatever the last call
 //     left in it.  Each call therefore clears what has to start from zero (the ticket counter
 //     and the result slots) on the caller's stream before the scan.  Two calls whose kernels
@@ -109,13 +113,24 @@ extern "C" int da_scan_topk_noalloc(int32_t device, const float *d_mat, const fl
     if (k > kMaxK)
         return fail(DA_ERR_CAPACITY, "k=" + std::to_string(k) + " exceeds the no-allocation limit DA_NOALLOC_MAX_K=" +
                                          std::to_string(kMaxK) + " (the scratch array is fixed at build time)");
-    if (n_rows > 0xFFFFFFF0ull) return fail(DA_ERR_CAPACITY, "n_rows exceeds 2^32");
+    if (n_rows > 0xFFFFFFF0ull || (uint64_t)row_base + n_rows > 0xFFFFFFF0ull)
+        return fail(DA_ERR_CAPACITY, "row_base + n_rows exceeds 2^32 - 16 (rows are numbered in 32 bits)");
     if ((reinterpret_cast<uintptr_t>(d_mat) & 15) || (reinterpret_cast<uintptr_t>(d_query) & 15) ||
         (reinterpret_cast<uintptr_t>(d_chunk_ids) & 15) || (reinterpret_cast<uintptr_t>(d_out_chunk_ids) & 15))
         return fail(DA_ERR_INVALID, "d_mat, d_query, d_chunk_ids and d_out_chunk_ids must be 16-byte aligned");
 
-    cudaError_t e = cudaSetDevice(device);
-    if (e != cudaSuccess) return fail(DA_ERR_CUDA, std::string("cudaSetDevice failed: ") + cudaGetErrorString(e));
+    // the caller's current device is restored on every way out
+    struct DeviceGuard {
+        int prev = -1;
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
+    cudaError_t e = cudaGetDevice(&guard.prev);
+    if (e != cudaSuccess) { guard.prev = -1; cudaGetLastError(); }
+    if (guard.prev == device) guard.prev = -1;           // nothing to restore
+    else {
+        e = cudaSetDevice(device);
+        if (e != cudaSuccess) return fail(DA_ERR_CUDA, std::string("cudaSetDevice failed: ") + cudaGetErrorString(e));
+    }
 
     DeviceSetup su;
     {
@@ -130,6 +145,12 @@ extern "C" int da_scan_topk_noalloc(int32_t device, const float *d_mat, const fl
             int sms = 0;
             e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
             if (e != cudaSuccess) return fail(DA_ERR_CUDA, std::string("cudaDeviceGetAttribute failed: ") + cudaGetErrorString(e));
+            // load every function a later call may launch, now (lazy loading allocates and synchronises)
+            cudaFuncAttributes fa;
+            e = cudaFuncGetAttributes(&fa, noalloc_reset_kernel);
+            if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, noalloc_decode_kernel);
+            if (e == cudaSuccess) e = da::scan_preload_single_query_variants();
+            if (e != cudaSuccess) return fail(DA_ERR_CUDA, std::string("loading the scan kernels failed: ") + cudaGetErrorString(e));
             slot.scratch = ptr;
             slot.sm_count = sms;
             slot.ready = true;

@@ -208,6 +208,10 @@ cudaError_t launch_commit_rows(const float *stage, int dim, const uint32_t *rows
 
 cudaError_t launch_query_inv_norm(const float *queries, int dim, int nq, float *out, cudaStream_t stream)
 {
+    if (nq <= 0) {              // nothing to compute: only make sure the (lazily loaded) kernel is resident
+        cudaFuncAttributes fa;
+        return cudaFuncGetAttributes(&fa, query_inv_norm_kernel);
+    }
     int blocks = (nq + 7) / 8;
     query_inv_norm_kernel<<<blocks, 256, 0, stream>>>(queries, dim, nq, out);
     return cudaGetLastError();

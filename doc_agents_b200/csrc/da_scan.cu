@@ -299,6 +299,19 @@ int scan_pick_nq(int dim, int k, int batch)
 
 int scan_grid_for(int sm_count) { return sm_count; }
 
+cudaError_t scan_preload_single_query_variants()
+{
+    // the NQ = 1 row of launch_scan's table: 256-bit and 128-bit loads, whole and ragged tiles
+    const void *fns[] = {(const void *)scan_topk_kernel<1, 2, 3, 8, true, false>, (const void *)scan_topk_kernel<1, 2, 3, 8, false, false>,
+                         (const void *)scan_topk_kernel<1, 4, 4, 4, true, false>, (const void *)scan_topk_kernel<1, 4, 4, 4, false, false>};
+    for (const void *f : fns) {
+        cudaFuncAttributes fa;
+        cudaError_t e = cudaFuncGetAttributes(&fa, f);
+        if (e != cudaSuccess) return e;
+    }
+    return launch_query_inv_norm(nullptr, 0, 0, nullptr, nullptr);     // nq = 0: loads the kernel, launches nothing
+}
+
 cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream, int *grid_out)
 {
     ScanArgs a = a_in;
@@ -343,13 +356,21 @@ namespace {
 constexpr int kMergeThreads = 256;
 
 __global__ void __launch_bounds__(kMergeThreads) merge_kernel(const uint8_t *gathered, int G, int batch, int k,
-                                                              int P, key_t64 *out_keys, uint8_t *out_ids)
+                                                              int P, key_t64 *out_keys, uint8_t *out_ids,
+                                                              size_t block_bytes, uint32_t *out_flags)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     key_t64 *keys = reinterpret_cast<key_t64 *>(smem_raw);        // P
     const int q = blockIdx.x;
-    const size_t block_bytes = (size_t)batch * k * 24;
     const int total = G * k;
+    // trailer word of every rank's block (candidate-list overflow on that rank): every rank sees the OR, so the
+    // decision to answer the batch another way is the same everywhere
+    if (out_flags && q == 0 && threadIdx.x == 0) {
+        uint32_t f = 0;
+        for (int g = 0; g < G; g++)
+            f |= *reinterpret_cast<const uint32_t *>(gathered + (size_t)g * block_bytes + (size_t)batch * k * 24);
+        *out_flags = f;
+    }
     for (int i = threadIdx.x; i < P; i += kMergeThreads) {
         key_t64 v = 0ull;
         if (i < total) {
@@ -575,11 +596,13 @@ cudaError_t launch_filter_compact(const uint32_t *doc_slot, const uint32_t *bitm
 }
 
 cudaError_t launch_merge(const uint8_t *gathered, int G, int batch, int k, key_t64 *out_keys,
-                         uint8_t *out_ids, cudaStream_t stream)
+                         uint8_t *out_ids, cudaStream_t stream, size_t block_bytes, uint32_t *out_flags)
 {
     int P = next_pow2(G * k);
     if (P < 2) P = 2;
-    merge_kernel<<<batch, kMergeThreads, (size_t)P * sizeof(key_t64), stream>>>(gathered, G, batch, k, P, out_keys, out_ids);
+    if (block_bytes == 0) block_bytes = (size_t)batch * k * 24;
+    merge_kernel<<<batch, kMergeThreads, (size_t)P * sizeof(key_t64), stream>>>(gathered, G, batch, k, P, out_keys, out_ids,
+                                                                                block_bytes, out_flags);
     return cudaGetLastError();
 }
 

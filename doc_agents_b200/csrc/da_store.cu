@@ -68,6 +68,7 @@ struct Id16Hash {
 inline Id16 load_id(const uint8_t *p) { Id16 k; memcpy(&k, p, 16); return k; }
 
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+constexpr size_t kRecTrailer = 16;      // bytes after a rank's record block in a multi-process store: its overflow flag
 
 struct ChunkInfo { uint32_t slot; int32_t shard; uint32_t row; };
 struct DocInfo { Id16 id; int32_t shard; };
@@ -309,6 +310,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
 {
     const int dim = st->dim;
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
+    const size_t trailer = st->world > 1 ? kRecTrailer : 0;     // per-rank flags travel with the records (below)
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
         const bool first = (&s == &st->shards[0]);
@@ -354,7 +356,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 int grid = 0;
                 CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
                 st->launches += 3;
-                if (first) { st->scan_grid = grid; st->scan_launches++; }
+                if (first) st->scan_grid = grid;
             }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
@@ -370,7 +372,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                                          s.d_surv_count.p, s.d_overflow.p, pl.batch, s.mat, dim, s.inv_norm, s.d_queries.p,
                                          s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream));
             st->launches += 4;
-            if (first) { st->scan_grid = s.sm_count; st->scan_launches++; }
+            if (first) st->scan_grid = s.sm_count;
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
@@ -386,7 +388,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                                          s.d_qinv.p, s.chunk_ids, s.row_base, pl.min_sim, pl.k, out_keys, out_ids, s.stream,
                                          s.hi, s.lo));
             st->launches += 4;
-            if (first) { st->scan_grid = s.sm_count; st->scan_launches++; }
+            if (first) st->scan_grid = s.sm_count;
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
@@ -412,7 +414,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 int grid = 0;
                 CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
                 st->launches++;
-                if (first) { st->scan_grid = grid; st->scan_launches++; }
+                if (first) st->scan_grid = grid;
             }
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
@@ -450,12 +452,12 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                                              s.row_base, pl.min_sim, pl.k, out_keys + (size_t)q0 * pl.k,
                                              out_ids + (size_t)q0 * pl.k * 16, s.stream, nullptr, nullptr, true));
                 st->launches += 5;
-                if (first) { st->scan_grid = grid; st->scan_launches++; }
+                if (first) st->scan_grid = grid;
                 continue;
             }
             CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
             st->launches++;
-            if (first) { st->scan_grid = grid; st->scan_launches++; }
+            if (first) st->scan_grid = grid;
             if (st->split16) {
                 const uint32_t cap = (uint32_t)std::min<uint64_t>(std::max<uint32_t>(s.n_rows, 1), 1u << 20);
                 CU(da::launch_split_finish(s.d_approx.p, s.n_rows, a.nq, pl.k, s.d_akeys.p, pl.min_sim, da::kSplitEps,
@@ -468,21 +470,31 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
         if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
     }
+    st->scan_launches++;        // one timed unit per search: scan_ms_sum and last_bytes both cover ALL passes of a search
     if (st->total_ranks > 1) {
         Shard &s0 = st->shards[0];
         if (st->p2p_gather) {
             CU(cudaSetDevice(s0.device));
             for (size_t g = 1; g < st->shards.size(); g++) CU(cudaStreamWaitEvent(s0.stream, st->shards[g].ev_done, 0));
         } else {
+            // Several processes: a rank sees only its own candidate lists, so each block carries a trailer with the
+            // rank's overflow flag; after the gather every rank holds every flag and takes the same decision.
+            const bool lists = pl.use_tc || pl.use_q8 || st->split16;
+            if (trailer && lists)
+                for (Shard &s : st->shards) {
+                    CU(cudaSetDevice(s.device));
+                    CU(cudaMemcpyAsync(s.d_out.p + rec_bytes, s.d_overflow.p, 4, cudaMemcpyDeviceToDevice, s.stream));
+                }
             NC(ncclGroupStart());
             for (Shard &s : st->shards)
-                NC(ncclAllGather(s.d_out.p, s.d_gather.p, rec_bytes, ncclChar, s.comm, s.stream));
+                NC(ncclAllGather(s.d_out.p, s.d_gather.p, rec_bytes + trailer, ncclChar, s.comm, s.stream));
             NC(ncclGroupEnd());
         }
         CU(cudaSetDevice(s0.device));
         CU(da::launch_merge(s0.d_gather.p, st->total_ranks, pl.batch, pl.k,
                             reinterpret_cast<da::key_t64 *>(s0.d_final.p + (size_t)pl.batch * pl.k * 16),
-                            s0.d_final.p, s0.stream));
+                            s0.d_final.p, s0.stream, rec_bytes + trailer,
+                            trailer ? reinterpret_cast<uint32_t *>(s0.d_final.p + rec_bytes) : nullptr));
         st->launches++;
         if (st->p2p_gather) CU(cudaEventRecord(s0.ev_done, s0.stream));   // gather blocks may be overwritten after this
     }
@@ -646,8 +658,13 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         CU(s.d_queries.ensure(nq_elems)); CU(s.d_qinv.ensure(p->batch));
         CU(s.h_queries.ensure(nq_elems));
-        CU(s.d_out.ensure(rec_bytes)); CU(s.h_result.ensure(rec_bytes));
-        if (st->total_ranks > 1) { CU(s.d_gather.ensure(rec_bytes * st->total_ranks)); CU(s.d_final.ensure(rec_bytes)); }
+        const size_t trailer = st->world > 1 ? kRecTrailer : 0;
+        CU(s.d_out.ensure(rec_bytes + trailer)); CU(s.h_result.ensure(rec_bytes + trailer));
+        if (st->total_ranks > 1) { CU(s.d_gather.ensure((rec_bytes + trailer) * st->total_ranks)); CU(s.d_final.ensure(rec_bytes + trailer)); }
+        if (trailer) {
+            CU(cudaMemsetAsync(s.d_out.p + rec_bytes, 0, trailer, s.stream));
+            if (!s.d_overflow.p) { CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1)); CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream)); *s.h_overflow.p = 0; }
+        }
         memcpy(s.h_queries.p, p->queries, nq_elems * sizeof(float));
         CU(cudaMemcpyAsync(s.d_queries.p, s.h_queries.p, nq_elems * sizeof(float), cudaMemcpyHostToDevice, s.stream));
         if (!all_docs) {
@@ -1051,21 +1068,23 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         if (rc != DA_OK) return rc;
         CU(cudaSetDevice(s0.device));
         const uint8_t *src = st->total_ranks > 1 ? s0.d_final.p : s0.d_out.p;
-        CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes, cudaMemcpyDeviceToHost, s0.stream));
+        const size_t trailer = st->world > 1 ? kRecTrailer : 0;
+        CU(cudaMemcpyAsync(s0.h_result.p, src, rec_bytes + trailer, cudaMemcpyDeviceToHost, s0.stream));
         CU(cudaEventRecord(s0.ev_all1, s0.stream));
         rc = enqueue_stats_readback(st);
         if (rc != DA_OK) return rc;
         for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
         bool overflow = false;
-        if (pl.use_tc || pl.use_q8 || st->split16)
+        if (trailer)         // several processes: the OR of every rank's flag, the same word on every rank
+            overflow = *reinterpret_cast<const uint32_t *>(s0.h_result.p + rec_bytes) != 0;
+        else if (pl.use_tc || pl.use_q8 || st->split16)
             for (Shard &s : st->shards) overflow = overflow || (*s.h_overflow.p != 0);
         if (!overflow) break;
         if (st->split16 && !pl.use_tc)
             return fail(DA_ERR_STATE, "split-plane search: more than 2^20 rows lie within the truncation slack of the k-th best");
-        // A candidate list stayed full after pruning (a mass of scores within the TF32 slack of the k-th
-        // best).  Every rank sees its own lists only, so in a multi-rank store this stays an error.
-        if (st->total_ranks > 1 && st->world > 1)
-            return fail(DA_ERR_STATE, "candidate list overflow; retry with DA_SEARCH_NO_TENSOR | DA_SEARCH_NO_Q8");
+        // A candidate list stayed full after pruning (a mass of scores within the TF32 slack of the k-th best) on
+        // this rank or, in a multi-process store, on any rank: every rank answers the batch again another way
+        // (the collective call sequence stays the same on all of them: one gather per attempt).
         st->tc_overflows++;
         if (pl.use_tc && pl.tc_i8) {
             pl.tc_i8 = false;              // int8 slack too wide for this batch: the TF32 contraction of the fp32 rows next
@@ -1077,6 +1096,7 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         for (Shard &s : st->shards) {      // the flag is sticky on the device: clear it for the second attempt
             CU(cudaSetDevice(s.device));
             CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream));
+            if (trailer) CU(cudaMemsetAsync(s.d_out.p + rec_bytes, 0, trailer, s.stream));
             *s.h_overflow.p = 0;
         }
     }
@@ -1132,6 +1152,13 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
         }
         return topk_direct(st, doc_ids, n_docs, query, 1, dim, k, out_chunk_ids, out_scores, out_n);
     }
+    // A call is checked on its own before it may join a batch, so that a bad request fails alone (pgvector rejects
+    // NaN/Inf for the statement that carries them, not for its neighbours).
+    for (int32_t i = 0; i < dim; i++)
+        if (!std::isfinite(query[i])) {
+            { std::lock_guard<std::mutex> lk(st->bmu); st->topk_calls++; }
+            return fail(DA_ERR_NONFINITE, "query element %d is not finite", (int)i);
+        }
     // Request batching: the first caller to find no leader becomes one, waits for the window (or a full
     // batch), then answers every queued call that asks for the same document set with one batched pass.
     da_store::Pending me{doc_ids, n_docs, query, k, out_chunk_ids, out_scores, out_n};
@@ -1168,9 +1195,18 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
         const int rc = topk_direct(st, docs.data(), total_docs, qs.data(), (int32_t)g, dim, kmax, ids.data(), sc.data(),
                                    cnt.data(), offs.data());
         const std::string err = rc == DA_OK ? std::string() : g_err;
+        uint64_t extra_passes = 0;
         for (size_t i = 0; i < g; i++) {            // a smaller k is a prefix of the batch's top-kmax
             da_store::Pending *r = group[i];
             r->rc = rc; r->err = err;
+            if (rc != DA_OK && g > 1) {
+                // the merged pass failed: every member is answered on its own, so each gets its own verdict and a
+                // fault that belongs to one request (or to the batched path) does not fail the others
+                r->rc = topk_direct(st, r->doc_ids, r->n_docs, r->query, 1, dim, r->k, r->out_ids, r->out_scores, r->out_n);
+                r->err = r->rc == DA_OK ? std::string() : g_err;
+                extra_passes++;
+                continue;
+            }
             if (rc == DA_OK) {
                 const int n = std::min(cnt[i], r->k);
                 memcpy(r->out_ids, &ids[i * (size_t)kmax * 16], (size_t)n * 16);
@@ -1179,6 +1215,7 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
             }
         }
         lk.lock();
+        st->topk_passes += extra_passes;
         for (da_store::Pending *r : group) r->done = true;
         st->bleader = false;
         st->bcv.notify_all();

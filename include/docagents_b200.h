@@ -206,8 +206,8 @@ typedef struct {
     uint64_t kernel_launches;       /* cumulative count of this library's kernel launches */
     int32_t  ivf_lists;             /* 0 = no index */
     int32_t  scan_grid;             /* CTAs of the last scan launch */
-    double   scan_ms_sum;           /* cumulative CUDA-event time of scan launches on shard 0 */
-    uint64_t scan_launches;         /* how many launches scan_ms_sum covers */
+    double   scan_ms_sum;           /* cumulative CUDA-event time of the searches' scan stages on shard 0 (all passes of a search) */
+    uint64_t scan_launches;         /* how many searches scan_ms_sum covers (last_bytes_algorithmic is per search too) */
     /* last da_store_build_ivf, CUDA events on shard 0's stream: */
     float    ivf_build_ms;          /* whole build */
     float    ivf_kmeans_ms;         /* all k-means iterations (assignment GEMM + accumulate + finalize + all-reduce) */

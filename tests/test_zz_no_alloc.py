@@ -6,8 +6,10 @@ the library instead of cudaMalloc'ed buffers.
 The test plays such a host: it brings its own device buffers (made here with torch, which is only
 the harness's way to obtain device memory), calls the entry point through the C ABI twice in a row
 -- the second call finds the scratch array as the first one left it -- and checks both answers
-against the allocating entry point (da_store_search) on the same rows.  The file name makes pytest
-collect it last, so a failure here cannot hide the other tests under `-x`.
+against the allocating entry point (da_store_search) on the same rows and, so that the entry point
+stands on its own, against the CPU oracle.  A later call with a dimension that selects another
+kernel variant (128-bit loads, ragged tiles) and a non-zero row base follows.  The file name makes
+pytest collect it last, so a failure here cannot hide the other tests under `-x`.
 """
 import ctypes as C
 
@@ -83,6 +85,37 @@ def test_no_alloc_scan_matches_store_search_twice_in_a_row():
             assert np.array_equal(got_rows, ref_rows[0])
             assert np.allclose(got_scores, ref_scores[0], rtol=1e-5, atol=0)   # the tolerance of the parity suite
             assert np.array_equal(got_ids, ref_ids[0])
+            # ... and against the oracle on the same 5 000 rows
+            allowed = np.zeros(25, np.uint8)
+            allowed[wanted if use_filter else slice(None)] = 1
+            o_rows, o_scores, _ = oracle.topk(vecs, oracle.row_docs(S, 0, n), allowed, q, k)
+            assert np.array_equal(got_rows, o_rows)
+            assert np.allclose(got_scores, o_scores, rtol=1e-5, atol=0)
+            assert np.array_equal(got_ids, oracle.chunk_ids(S, 0, n)[o_rows])
+
+        # another kernel variant (dim % 8 != 0: 128-bit loads, ragged tiles) and a row base, after the first calls
+        dim2, n2, base = 772, 1000, 7000
+        rng = np.random.default_rng(5)
+        q2 = oracle.normalize(rng.standard_normal(dim2).astype(np.float32))
+        m2 = (0.6 * q2[None, :] + rng.standard_normal((n2, dim2)).astype(np.float32) / np.sqrt(dim2)).astype(np.float32)
+        inv2 = (1.0 / np.linalg.norm(m2.astype(np.float64), axis=1)).astype(np.float32)
+        ids2 = oracle.chunk_ids(S, 0, n2)
+        t_m2, t_inv2, t_ids2, t_q2 = (torch.from_numpy(a).to(dev) for a in (m2, inv2, ids2, q2))
+        prev = torch.cuda.current_device()
+        rc = lib.da_scan_topk_noalloc(0, _dev(t_m2), _dev(t_inv2), None, _dev(t_ids2), None, _dev(t_q2), n2, base, dim2,
+                                      k, 0.3, None, _dev(d_scores), _dev(d_rows), _dev(d_out_ids), _dev(d_n))
+        assert rc == L.DA_OK, L.last_error()
+        torch.cuda.synchronize()
+        assert torch.cuda.current_device() == prev
+        o_rows, o_scores, _ = oracle.topk(m2, None, None, q2, k, 0.3)
+        cnt = int(d_n.cpu()[0])
+        assert cnt == len(o_rows)
+        assert np.array_equal(d_rows.cpu().numpy().astype(np.uint32)[:cnt], o_rows + base)
+        assert np.allclose(d_scores.cpu().numpy()[:cnt], o_scores, rtol=1e-5, atol=0)
+        assert np.array_equal(d_out_ids.cpu().numpy().reshape(k, 16)[:cnt], ids2[o_rows])
+        rc = lib.da_scan_topk_noalloc(0, _dev(t_m2), _dev(t_inv2), None, _dev(t_ids2), None, _dev(t_q2), n2, 0xFFFFFF00, dim2,
+                                      k, 0.3, None, _dev(d_scores), _dev(d_rows), _dev(d_out_ids), _dev(d_n))
+        assert rc == L.DA_ERR_CAPACITY and "row_base" in L.last_error()
 
         # requests beyond the fixed scratch are refused with a clear error and launch nothing
         rc = lib.da_scan_topk_noalloc(0, _dev(d_mat), _dev(d_inv), None, _dev(d_ids), None, _dev(d_q), n, 0, dim,
