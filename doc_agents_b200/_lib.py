@@ -39,6 +39,7 @@ DA_STORE_SPLIT16 = 0x1
 DA_STORE_Q8_SIDECAR = 0x2
 
 DA_IVF_SIMT_ASSIGN = 0x1
+DA_IVF_NO_SPLIT = 0x2
 
 DA_NOALLOC_MAX_K = 128
 DA_NOALLOC_MAX_CTAS = 256
@@ -69,7 +70,8 @@ class da_ivf_params(C.Structure):
 class da_synth_params(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("seed_data", C.c_uint64), ("seed_centroid", C.c_uint64),
                 ("seed_ids", C.c_uint64), ("chunks_per_doc", C.c_uint32), ("n_clusters", C.c_uint32),
-                ("cmul", C.c_int32), ("nmul", C.c_int32), ("row_lo", C.c_uint64), ("n_rows", C.c_uint64)]
+                ("cmul", C.c_int32), ("nmul", C.c_int32), ("row_lo", C.c_uint64), ("n_rows", C.c_uint64),
+                ("smul", C.c_int32), ("super_group", C.c_uint32)]
 
 
 class da_stats(C.Structure):
@@ -107,6 +109,7 @@ SIGNATURES = {
     "da_store_debug_read_rows": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p]),
     "da_store_debug_read_ivf": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "da_store_debug_read_probes": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "da_scan_topk_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_float,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -59,8 +59,17 @@ struct ScanArgs {
     uint32_t bitmap_stride;        // words between the bitmaps of consecutive queries; 0 = one bitmap for all
     const float *queries;          // nq x dim (device)
     const float *q_inv_norm;       // nq
-    const uint32_t *row_list;      // optional: scan only these rows (IVF probe lists); nullptr = [0,n_rows)
+    const uint32_t *row_list;      // optional: scan only these rows (compacted document filter); nullptr = [0,n_rows)
     const uint32_t *n_rows_dev;    // with row_list: device-resident count of entries
+    // IVFFlat probe mode (one launch for a whole batch, blockIdx.y = query; every query scans its own lists):
+    // probe_keys[q][probes] name the lists (key row = list id, 0 = none), list_offsets/list_rows are the index.
+    // Per-query pieces (queries, q_inv_norm, doc_bitmap with bitmap_stride, counter, cta_out, out_keys, out_ids)
+    // are indexed by blockIdx.y inside the kernel; nq must be 1.
+    const key_t64 *probe_keys;
+    int probes;
+    int probe_batch;               // queries of the launch (grid.y)
+    const uint32_t *list_offsets;  // lists + 1
+    const uint32_t *list_rows;     // rows grouped by list
     uint32_t n_rows;               // rows to visit when row_list is null
     uint32_t row_base;             // global row of local row 0
     int dim;
@@ -112,6 +121,7 @@ struct SynthArgs {
     uint64_t seed_data, seed_centroid, seed_ids;
     uint32_t chunks_per_doc, n_clusters;
     int32_t cmul, nmul;
+    int32_t smul; uint32_t super_group;   // optional second level: + smul * direction of the cluster's group (0 = off)
     uint64_t row_lo;               // global row of local row 0
     uint32_t n_rows;
     uint32_t doc_slot_base;        // global doc index mapped to slot 0
@@ -128,15 +138,31 @@ cudaError_t ivf_launch_assign(const float *mat, int D, const uint32_t *row_idx, 
                               uint32_t *out_assign, int out_by_row, cudaStream_t stream);
 cudaError_t ivf_launch_sample(uint32_t n_rows, uint32_t n_sample, uint64_t seed, uint32_t *out, cudaStream_t stream);
 cudaError_t ivf_launch_init_centroids(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
-                                      uint32_t n_sample, int L, float *cent, float *cent_inv, cudaStream_t stream);
+                                      uint32_t n_sample, int L, uint64_t seed, float *cent, float *cent_inv, cudaStream_t stream);
+// counts[assign[i]] += 1 over the sample (counts zeroed by the caller)
+cudaError_t ivf_launch_count(const uint32_t *assign, uint32_t n, float *counts, cudaStream_t stream);
+// One balancing round after k-means: the heaviest lists (by `counts`, the same on every rank) each split into
+// themselves and one empty list, along a direction taken from one of their members in this shard's sample.
+size_t ivf_split_scratch_bytes(int L);
+cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, const float *mat, int D, const float *inv_norm,
+                                   const uint32_t *sample, uint32_t n_sample, const uint32_t *assign, uint64_t seed,
+                                   float *cent, cudaStream_t stream);
+// Batched query -> centroid ranking: partial[ks][batch][L] scores (da_tc.cu) -> out_keys[batch][probes]
+constexpr int kIvfSelectMaxLists = 49152;          // the select kernel keeps a query's L scores in shared memory
+cudaError_t ivf_launch_select_probes(const float *partial, int ks, int batch, int L, int probes, key_t64 *out_keys,
+                                     cudaStream_t stream);
+// scores[split][m][n] = <A[m], B[n]> over the split's slice of the dimension, TF32 on the tensor cores (da_tc.cu).
+// *ks_out = number of slices written (the caller sizes `out` with tc_scores_max_splits()).
+int tc_scores_splits(int M, int N, int D, int sm_count);
+cudaError_t tc_launch_scores(const float *A, int M, const float *B, int N, int D, int ks, float *out, cudaStream_t stream);
 cudaError_t ivf_launch_accumulate(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
                                   uint32_t n_sample, const uint32_t *assign, float *sums, float *counts,
                                   cudaStream_t stream);
 cudaError_t ivf_launch_finalize(const float *sums, const float *counts, int L, int D, float *cent, cudaStream_t stream);
 cudaError_t ivf_launch_build_lists(const uint32_t *assign, uint32_t n, int L, uint32_t *counts, uint32_t *offsets,
                                    uint32_t *cursor, uint32_t *list_rows, cudaStream_t stream);
-cudaError_t ivf_launch_expand(const key_t64 *probe_keys, int probes, const uint32_t *offsets, const uint32_t *list_rows,
-                              uint32_t *out_rows, uint32_t *out_n, cudaStream_t stream);
+// CTAs per query of a probe-mode scan over `batch` queries (the scratch of the launch is batch x this x k keys).
+int scan_probe_ctas_per_query(int sm_count, int batch);
 
 // Tensor-core assignment (da_tc.cu): out_assign[m] = argmax_l <mat[m], cent[l]>, tcgen05 kind::tf32.
 size_t tc_assign_scratch_bytes(uint32_t M);
@@ -200,7 +226,7 @@ cudaError_t launch_split_finish(const float *approx, uint32_t n_rows, int nq, in
 // Host restatement of the id hash of the synthetic corpus (spec: DESIGN.md).
 void synth_doc_id(uint64_t seed_ids, uint64_t doc, uint8_t out[16]);
 void synth_vector_host(uint64_t seed_noise, uint64_t noise_index, uint64_t seed_centroid, uint64_t cluster,
-                       int cmul, int nmul, int dim, float *out);
+                       int cmul, int nmul, int dim, float *out, int smul = 0, uint32_t super_group = 0);
 void synth_id_host(uint64_t seed_ids, int kind, uint64_t index, uint8_t out[16]);
 
 // ---------------------------------------------------------------------------

@@ -142,12 +142,16 @@ __global__ void sample_rows_kernel(uint32_t n_rows, uint32_t n_sample, unsigned 
     out[i] = (uint32_t)(i * step + off);
 }
 
-// centroid l starts as the unit-length copy of the (l * n_sample / L)-th sample row
+// centroid l starts as the unit-length copy of a sample row: stratum l of the sample (n_sample / L consecutive
+// entries), hashed position inside it -- distinct rows, and no fixed stride that could beat against a period of the
+// corpus (the evenly spaced picks of round 1 did, against 200-row documents dealt round-robin to clusters)
 __global__ void init_centroids_kernel(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
-                                      uint32_t n_sample, int L, float *cent)
+                                      uint32_t n_sample, int L, unsigned long long seed, float *cent)
 {
     const int l = blockIdx.x;
-    const uint32_t row = sample[(unsigned long long)l * n_sample / L];
+    const unsigned long long lo = (unsigned long long)l * n_sample / L, hi = (unsigned long long)(l + 1) * n_sample / L;
+    const unsigned long long span = hi > lo ? hi - lo : 1;
+    const uint32_t row = sample[lo + ivf_mix64(seed ^ (0xC3A5C85C97CB3127ull * (unsigned long long)(l + 1))) % span];
     const float inv = inv_norm[row];
     for (int c = threadIdx.x; c < D; c += blockDim.x) cent[(size_t)l * D + c] = mat[(size_t)row * D + c] * inv;
 }
@@ -228,28 +232,185 @@ __global__ void list_scatter_kernel(const uint32_t *assign, uint32_t n, uint32_t
         list_rows[atomicAdd(cursor + assign[i], 1u)] = i;
 }
 
-// Concatenate the rows of the probed lists.  probe_keys: the centroid scan's result (row = list id).
-__global__ void expand_probes_kernel(const key_t64 *probe_keys, int probes, const uint32_t *offsets,
-                                     const uint32_t *list_rows, uint32_t *out_rows, uint32_t *out_n)
+// ---------------------------------------------------------------------------
+// Splitting heavy lists into empty ones (after the k-means iterations).
+//
+// Spherical k-means cannot keep two centroids inside one isotropic cluster in high dimension: the mean of more
+// members is a better representative of EVERY member (its noise part is smaller), so the larger sibling wins
+// rows from the smaller one until that one is empty -- measured in round 1: 2 716 of 4 096 lists empty on the
+// BASELINE corpus, whole 9 800-row clusters in single lists.  An index wants balanced lists, so after the
+// iterations the heaviest lists donate to the empty ones: donor centroid c and a direction d orthogonal to it
+// (the off-centroid part of one of its members) become  normalize(c + e d)  and  normalize(c - e d).  The pair
+// is symmetric -- neither has the larger-sibling advantage -- and e is large enough for the split to survive
+// TF32 rounding of the assignment GEMM.  The pair is NOT re-averaged (that would collapse it again).
+// ---------------------------------------------------------------------------
+constexpr float kSplitStep = 0.25f;
+
+__global__ void count_assign_kernel(const uint32_t *assign, uint32_t n, float *counts)
 {
-    __shared__ uint32_t start[DA_IVF_MAX_PROBES + 1];
-    __shared__ uint32_t src[DA_IVF_MAX_PROBES];
-    if (threadIdx.x == 0) {
-        uint32_t run = 0;
-        for (int p = 0; p < probes; p++) {
-            const key_t64 key = probe_keys[p];
-            uint32_t len = 0, off = 0;
-            if (key) { const uint32_t l = key_row(key); off = offsets[l]; len = offsets[l + 1] - off; }
-            start[p] = run; src[p] = off; run += len;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) atomicAdd(counts + assign[i], 1.0f);
+}
+
+// One CTA.  keys (P = pow2 >= L entries of scratch): (count << 32 | ~list), sorted descending; then the j-th
+// heaviest list is paired with the j-th list from the empty end while the donor holds more than 1.5 x the mean
+// and the receiver nothing.  pairs[2j] = donor, pairs[2j+1] = receiver; *n_pairs = number of pairs.
+__global__ void __launch_bounds__(1024) plan_splits_kernel(const float *counts, int L, int P, unsigned long long *keys,
+                                                          uint32_t *pairs, uint32_t *n_pairs)
+{
+    __shared__ float total_s;
+    __shared__ uint32_t n_s;
+    const int tid = threadIdx.x;
+    if (tid == 0) { total_s = 0.f; n_s = 0u; }
+    __syncthreads();
+    float part = 0.f;
+    for (int i = tid; i < P; i += blockDim.x) {
+        unsigned long long k = 0ull;
+        if (i < L) { const float c = counts[i]; part += c; k = ((unsigned long long)(uint32_t)c << 32) | (unsigned long long)(~(uint32_t)i); }
+        keys[i] = k;
+    }
+    atomicAdd(&total_s, part);
+    for (int size = 2; size <= P; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = tid; t < (P >> 1); t += blockDim.x) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const bool desc = ((lo & size) == 0);
+                const unsigned long long a = keys[lo], b = keys[hi];
+                if ((a < b) == desc) { keys[lo] = b; keys[hi] = a; }
+            }
         }
-        start[probes] = run;
-        *out_n = run;
+    __syncthreads();
+    const float heavy = 1.5f * total_s / (float)L;
+    for (int j = tid; j < L / 2; j += blockDim.x) {
+        const unsigned long long d = keys[j], r = keys[L - 1 - j];
+        if ((float)(uint32_t)(d >> 32) > heavy && (uint32_t)(r >> 32) == 0u) {
+            // pairs are a prefix of j (counts descend from the head, ascend from the tail), so slot j is dense
+            pairs[2 * j] = ~(uint32_t)(d & 0xFFFFFFFFull);
+            pairs[2 * j + 1] = ~(uint32_t)(r & 0xFFFFFFFFull);
+            atomicAdd(&n_s, 1u);
+        }
     }
     __syncthreads();
-    for (int p = 0; p < probes; p++) {
-        const uint32_t len = start[p + 1] - start[p];
-        for (uint32_t i = threadIdx.x; i < len; i += blockDim.x) out_rows[start[p] + i] = list_rows[src[p] + i];
+    if (tid == 0) *n_pairs = n_s;
+}
+
+// Block j splits pair j.  The direction comes from the first member of the donor list found in the sample from a
+// hashed start (a heavy list holds many sample rows, so the walk is short).
+__global__ void __launch_bounds__(256) split_lists_kernel(const uint32_t *pairs, const uint32_t *n_pairs, const float *mat, int D,
+                                                          const float *inv_norm, const uint32_t *sample, uint32_t n_sample,
+                                                          const uint32_t *assign, unsigned long long seed, float *cent)
+{
+    if (blockIdx.x >= *n_pairs) return;
+    const uint32_t donor = pairs[2 * blockIdx.x], recv = pairs[2 * blockIdx.x + 1];
+    __shared__ uint32_t found_s;
+    __shared__ float red[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) found_s = 0xFFFFFFFFu;
+    __syncthreads();
+    const uint32_t start = (uint32_t)(ivf_mix64(seed ^ (0x9E3779B97F4A7C15ull * (donor + 1ull))) % n_sample);
+    for (uint32_t base = 0; base < n_sample; base += blockDim.x) {
+        const uint32_t off = base + (uint32_t)tid;
+        if (off < n_sample && assign[(start + off) % n_sample] == donor) atomicMin(&found_s, off);
+        __syncthreads();
+        const uint32_t f = found_s;
+        __syncthreads();                                     // everybody has read it before the next round may write
+        if (f != 0xFFFFFFFFu) break;
     }
+    if (found_s == 0xFFFFFFFFu) return;                      // no member in this sample: leave the pair as it is
+    const uint32_t row = sample[(start + found_s) % n_sample];
+    const float inv = inv_norm[row];
+    const float *x = mat + (size_t)row * D;
+    float *c = cent + (size_t)donor * D, *e = cent + (size_t)recv * D;
+    auto block_sum = [&](float v) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        __syncthreads();
+        if (lane == 0) red[warp] = v;
+        __syncthreads();
+        float t = 0.f;
+        for (int i = 0; i < 8; i++) t += red[i];
+        return t;
+    };
+    float dot = 0.f;
+    for (int i = tid; i < D; i += blockDim.x) dot += x[i] * inv * c[i];
+    dot = block_sum(dot);
+    float dd = 0.f;                                          // |x/|x| - dot c|^2
+    for (int i = tid; i < D; i += blockDim.x) { const float d = x[i] * inv - dot * c[i]; dd += d * d; }
+    dd = block_sum(dd);
+    if (!(dd > 1e-12f)) return;                              // the member IS the centroid: nothing to split along
+    const float step = kSplitStep * rsqrtf(dd), scale = rsqrtf(1.f + kSplitStep * kSplitStep);
+    for (int i = tid; i < D; i += blockDim.x) {
+        const float ci = c[i], d = (x[i] * inv - dot * ci) * step;
+        e[i] = (ci + d) * scale;
+        c[i] = (ci - d) * scale;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Batched query -> centroid ranking: the scores come from the tensor-core GEMM (da_tc.cu: queries x centroids^T,
+// ks partial sums over slices of the dimension), this kernel adds the partials in a fixed order and keeps each
+// query's `probes` best lists.  One CTA per query; the L scores sit in shared memory as order-preserving integers;
+// a 4 x 8-bit radix select finds the probes-th largest value exactly; lists above it, then the lowest-numbered
+// lists equal to it, are emitted in list order (deterministic).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) select_probes_kernel(const float *partial, int ks, int batch, int L, int probes,
+                                                            key_t64 *out_keys)
+{
+    extern __shared__ uint32_t sc[];                         // L ordered scores
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t sel_prefix, sel_mask, sel_remaining;
+    __shared__ uint32_t scan_gt[257], scan_eq[257];
+    const int q = blockIdx.x, tid = threadIdx.x;
+    for (int i = tid; i < L; i += blockDim.x) {
+        float s = 0.f;
+        for (int j = 0; j < ks; j++) s += partial[((size_t)j * batch + q) * L + i];
+        sc[i] = score_to_ordered(s);
+    }
+    const int want = probes < L ? probes : L;
+    if (tid == 0) { sel_prefix = 0u; sel_mask = 0u; sel_remaining = (uint32_t)want; }
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        hist[tid] = 0u;
+        __syncthreads();
+        const uint32_t prefix = sel_prefix, mask = sel_mask;
+        for (int i = tid; i < L; i += blockDim.x) {
+            const uint32_t v = sc[i];
+            if ((v & mask) == prefix) atomicAdd(&hist[(v >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t rem = sel_remaining, b = 255u;
+            for (;; b--) {
+                if (hist[b] >= rem || b == 0u) break;
+                rem -= hist[b];
+            }
+            sel_remaining = rem;
+            sel_prefix = prefix | (b << shift);
+            sel_mask = mask | (255u << shift);
+        }
+        __syncthreads();
+    }
+    const uint32_t T = sel_prefix, take_eq = sel_remaining;     // the want-th largest value; how many of its equals to keep
+    const int per = (L + (int)blockDim.x - 1) / (int)blockDim.x;
+    const int i0 = tid * per, i1 = min(L, i0 + per);
+    uint32_t gt = 0, eq = 0;
+    for (int i = i0; i < i1; i++) { const uint32_t v = sc[i]; gt += v > T; eq += v == T; }
+    scan_gt[tid + 1] = gt; scan_eq[tid + 1] = eq;
+    __syncthreads();
+    if (tid == 0) {
+        scan_gt[0] = 0u; scan_eq[0] = 0u;
+        for (int t = 1; t <= (int)blockDim.x; t++) { scan_gt[t] += scan_gt[t - 1]; scan_eq[t] += scan_eq[t - 1]; }
+    }
+    __syncthreads();
+    const uint32_t n_gt = scan_gt[blockDim.x];
+    uint32_t pg = scan_gt[tid], pe = scan_eq[tid];
+    key_t64 *out = out_keys + (size_t)q * probes;
+    for (int i = i0; i < i1; i++) {
+        const uint32_t v = sc[i];
+        const key_t64 key = ((key_t64)v << 32) | (key_t64)(~(uint32_t)i);
+        if (v > T) out[pg++] = key;
+        else if (v == T) { if (pe < take_eq) out[n_gt + pe] = key; pe++; }
+    }
+    for (int i = want + tid; i < probes; i += blockDim.x) out[i] = 0ull;
 }
 
 }  // namespace
@@ -270,9 +431,9 @@ cudaError_t ivf_launch_sample(uint32_t n_rows, uint32_t n_sample, uint64_t seed,
 }
 
 cudaError_t ivf_launch_init_centroids(const float *mat, int D, const float *inv_norm, const uint32_t *sample,
-                                      uint32_t n_sample, int L, float *cent, float *cent_inv, cudaStream_t stream)
+                                      uint32_t n_sample, int L, uint64_t seed, float *cent, float *cent_inv, cudaStream_t stream)
 {
-    init_centroids_kernel<<<L, 256, 0, stream>>>(mat, D, inv_norm, sample, n_sample, L, cent);
+    init_centroids_kernel<<<L, 256, 0, stream>>>(mat, D, inv_norm, sample, n_sample, L, seed, cent);
     fill_ones_kernel<<<(L + 255) / 256, 256, 0, stream>>>(cent_inv, L);
     return cudaGetLastError();
 }
@@ -305,10 +466,47 @@ cudaError_t ivf_launch_build_lists(const uint32_t *assign, uint32_t n, int L, ui
     return cudaGetLastError();
 }
 
-cudaError_t ivf_launch_expand(const key_t64 *probe_keys, int probes, const uint32_t *offsets, const uint32_t *list_rows,
-                              uint32_t *out_rows, uint32_t *out_n, cudaStream_t stream)
+cudaError_t ivf_launch_count(const uint32_t *assign, uint32_t n, float *counts, cudaStream_t stream)
 {
-    expand_probes_kernel<<<1, 1024, 0, stream>>>(probe_keys, probes, offsets, list_rows, out_rows, out_n);
+    if (n == 0) return cudaSuccess;
+    count_assign_kernel<<<148 * 2, 256, 0, stream>>>(assign, n, counts);
+    return cudaGetLastError();
+}
+
+size_t ivf_split_scratch_bytes(int L)
+{
+    int P = 1;
+    while (P < L) P <<= 1;
+    return (size_t)P * 8 + (size_t)L * 4 + 16;             // sort keys, (donor, receiver) pairs, pair count
+}
+
+cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, const float *mat, int D, const float *inv_norm,
+                                   const uint32_t *sample, uint32_t n_sample, const uint32_t *assign, uint64_t seed,
+                                   float *cent, cudaStream_t stream)
+{
+    if (L < 2) return cudaSuccess;
+    int P = 1;
+    while (P < L) P <<= 1;
+    unsigned long long *keys = static_cast<unsigned long long *>(scratch);
+    uint32_t *pairs = reinterpret_cast<uint32_t *>(keys + P);
+    uint32_t *n_pairs = pairs + (size_t)(L / 2) * 2;
+    plan_splits_kernel<<<1, 1024, 0, stream>>>(counts, L, P, keys, pairs, n_pairs);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    split_lists_kernel<<<L / 2, 256, 0, stream>>>(pairs, n_pairs, mat, D, inv_norm, sample, n_sample, assign, seed, cent);
+    return cudaGetLastError();
+}
+
+size_t ivf_select_smem_bytes(int L) { return (size_t)L * 4; }
+
+cudaError_t ivf_launch_select_probes(const float *partial, int ks, int batch, int L, int probes, key_t64 *out_keys,
+                                     cudaStream_t stream)
+{
+    const size_t smem = ivf_select_smem_bytes(L);
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(select_probes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    select_probes_kernel<<<batch, 256, smem, stream>>>(partial, ks, batch, L, probes, out_keys);
     return cudaGetLastError();
 }
 

@@ -105,6 +105,7 @@ __global__ void query_inv_norm_kernel(const float *queries, int dim, int nq, flo
 // ---------------------------------------------------------------------------
 constexpr unsigned long long kGold = 0x9E3779B97F4A7C15ull;
 constexpr unsigned long long kPair = 0xD1B54A32D192ED03ull;
+constexpr unsigned long long kSuperTag = 0x5C0DE5C0DE5C0DE5ull;     // seed_centroid ^ this = the stream of group directions
 
 __host__ __device__ inline unsigned long long mix64(unsigned long long z)
 {
@@ -141,6 +142,8 @@ __global__ void synth_kernel(const SynthArgs a, float *mat, float *inv_norm, uin
         const uint32_t doc = (uint32_t)(grow / a.chunks_per_doc);
         const unsigned long long kn = stream_key(a.seed_data, grow);
         const unsigned long long kc = stream_key(a.seed_centroid, doc % a.n_clusters);
+        const bool two_level = a.smul != 0 && a.super_group != 0;
+        const unsigned long long ks = two_level ? stream_key(a.seed_centroid ^ kSuperTag, (doc % a.n_clusters) / a.super_group) : 0ull;
         float2 *out = reinterpret_cast<float2 *>(mat + (size_t)r * a.dim);
         long long ss = 0;
         for (int p = lane; p < pairs; p += 32) {
@@ -148,6 +151,11 @@ __global__ void synth_kernel(const SynthArgs a, float *mat, float *inv_norm, uin
             unsigned long long hc = mix64(kc + (unsigned long long)(p + 1) * kPair);
             int u0 = a.cmul * ih4((uint32_t)hc) + a.nmul * ih4((uint32_t)hn);
             int u1 = a.cmul * ih4((uint32_t)(hc >> 32)) + a.nmul * ih4((uint32_t)(hn >> 32));
+            if (two_level) {
+                const unsigned long long hs = mix64(ks + (unsigned long long)(p + 1) * kPair);
+                u0 += a.smul * ih4((uint32_t)hs);
+                u1 += a.smul * ih4((uint32_t)(hs >> 32));
+            }
             ss += (long long)u0 * u0 + (long long)u1 * u1;
             out[p] = make_float2((float)u0, (float)u1);
         }
@@ -229,16 +237,22 @@ cudaError_t launch_synth(const SynthArgs &a, float *mat, float *inv_norm, uint32
 
 // Host statement of one synthetic vector (queries for benches/tests): same integer-exact spec as synth_kernel.
 void synth_vector_host(uint64_t seed_noise, uint64_t noise_index, uint64_t seed_centroid, uint64_t cluster,
-                       int cmul, int nmul, int dim, float *out)
+                       int cmul, int nmul, int dim, float *out, int smul, uint32_t super_group)
 {
     const unsigned long long kn = stream_key(seed_noise, noise_index), kc = stream_key(seed_centroid, cluster);
+    const bool two_level = smul != 0 && super_group != 0;
+    const unsigned long long ks = two_level ? stream_key(seed_centroid ^ kSuperTag, cluster / super_group) : 0ull;
     long long ss = 0;
     for (int c = 0; c < dim; c++) {
         const unsigned long long hn = mix64(kn + (unsigned long long)((c >> 1) + 1) * kPair);
         const unsigned long long hc = mix64(kc + (unsigned long long)((c >> 1) + 1) * kPair);
         const uint32_t wn = (c & 1) ? (uint32_t)(hn >> 32) : (uint32_t)hn;
         const uint32_t wc = (c & 1) ? (uint32_t)(hc >> 32) : (uint32_t)hc;
-        const int u = cmul * ih4(wc) + nmul * ih4(wn);
+        int u = cmul * ih4(wc) + nmul * ih4(wn);
+        if (two_level) {
+            const unsigned long long hs = mix64(ks + (unsigned long long)((c >> 1) + 1) * kPair);
+            u += smul * ih4((c & 1) ? (uint32_t)(hs >> 32) : (uint32_t)hs);
+        }
         ss += (long long)u * u;
         out[c] = (float)u;
     }

@@ -31,8 +31,39 @@ namespace {
 // the split-plane layout, where a 256-bit load brings 16 upper halves (truncated bf16) of a row of a.hi and every
 // row's approximate similarity is also stored to a.approx for the candidate pass (da_split.cu).
 template <int NQ, int R, int U, int VEC, bool FULL_TILES, bool INDIRECT>
-__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a)
+__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a_in)
 {
+    ScanArgs a = a_in;
+    // IVFFlat probe mode: this CTA serves query blockIdx.y; its rows are the concatenation of that query's lists
+    __shared__ uint32_t p_start[DA_IVF_MAX_PROBES + 1];       // first flat index of each probed list (+ total)
+    __shared__ uint32_t p_src[DA_IVF_MAX_PROBES];             // where the list starts in list_rows
+    const bool probe_mode = INDIRECT && a.probe_keys != nullptr;
+    if (probe_mode) {
+        const size_t qy = blockIdx.y;
+        a.queries += qy * a.dim;
+        a.q_inv_norm += qy;
+        if (a.doc_bitmap) a.doc_bitmap += qy * a.bitmap_stride;
+        a.bitmap_stride = 0;
+        a.cta_out += qy * gridDim.x * a.k;
+        a.counter += qy;
+        a.out_keys += qy * a.k;
+        if (a.out_ids) a.out_ids += qy * a.k * 16;
+        a.probe_keys += qy * a.probes;
+        if (threadIdx.x < (unsigned)a.probes) {
+            const key_t64 key = a.probe_keys[threadIdx.x];
+            uint32_t off = 0, len = 0;
+            if (key) { const uint32_t l = key_row(key); off = a.list_offsets[l]; len = a.list_offsets[l + 1] - off; }
+            p_src[threadIdx.x] = off;
+            p_start[threadIdx.x + 1] = len;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t run = 0;
+            p_start[0] = 0;
+            for (int p = 0; p < a.probes; p++) { run += p_start[p + 1]; p_start[p + 1] = run; }
+        }
+        // (the barrier after the query staging below publishes the table)
+    }
     constexpr int V4 = VEC / 4;                 // float4 words of the query per lane slot
     constexpr int VR = VEC == 16 ? 2 : V4;      // float4 registers holding one loaded slot (raw 16-bit pairs when VEC == 16)
     const int DV = a.dim / VEC;                 // lane slots per row
@@ -60,7 +91,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 #pragma unroll
     for (int q = 0; q < NQ; q++) { cnt[q] = 0; wmin[q] = 0ull; }
 
-    const uint32_t n_rows = INDIRECT ? *a.n_rows_dev : a.n_rows;
+    const uint32_t n_rows = probe_mode ? p_start[a.probes] : INDIRECT ? *a.n_rows_dev : a.n_rows;
     const uint32_t n_groups = (n_rows + R - 1) / R;
     const uint32_t gstride = gridDim.x * kScanWarps;
     unsigned int my_rows_read = 0;
@@ -243,7 +274,22 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             // lane r (< R) looks at row0 + r: document mask and 1/|row|
             uint32_t my_row = row0 + lane;
             const bool valid = (lane < R) && (my_row < n_rows);
-            if (INDIRECT) my_row = valid ? a.row_list[my_row] : 0u;
+            if (INDIRECT) {
+                if (probe_mode) {
+                    uint32_t r = 0u;
+                    if (valid) {                     // which list holds flat index my_row: last p with p_start[p] <= my_row
+                        int lo = 0, hi = a.probes - 1;
+                        while (lo < hi) {
+                            const int mid = (lo + hi + 1) >> 1;
+                            if (p_start[mid] <= my_row) lo = mid; else hi = mid - 1;
+                        }
+                        r = a.list_rows[p_src[lo] + (my_row - p_start[lo])];
+                    }
+                    my_row = r;
+                } else {
+                    my_row = valid ? a.row_list[my_row] : 0u;
+                }
+            }
             uint32_t want_bits;
             float my_inv;
             row_facts(my_row, valid, want_bits, my_inv);
@@ -266,13 +312,13 @@ cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t st
 {
     const bool full = ((a.dim / VEC) % (32 * U)) == 0;
     auto kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, false> : scan_topk_kernel<NQ, R, U, VEC, false, false>;
-    if (a.row_list) {
+    if (a.row_list || a.probe_keys) {
         if constexpr (VEC != 16) kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, true> : scan_topk_kernel<NQ, R, U, VEC, false, true>;
         else return cudaErrorInvalidValue;
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<grid, kScanThreads, smem, stream>>>(a);
+    kern<<<dim3((unsigned)grid, a.probe_keys ? (unsigned)a.probe_batch : 1u), kScanThreads, smem, stream>>>(a);
     return cudaGetLastError();
 }
 
@@ -299,6 +345,15 @@ int scan_pick_nq(int dim, int k, int batch)
 
 int scan_grid_for(int sm_count) { return sm_count; }
 
+// A probe-mode launch runs batch x this many CTAs (one CTA per SM at a time): a single query gets the whole chip,
+// a large batch about four CTAs' worth of work per SM so that the tail of the last wave stays short.
+int scan_probe_ctas_per_query(int sm_count, int batch)
+{
+    if (batch <= 1) return sm_count;
+    const int c = (4 * sm_count + batch - 1) / batch;
+    return c < 1 ? 1 : (c > sm_count ? sm_count : c);
+}
+
 cudaError_t scan_preload_single_query_variants()
 {
     // the NQ = 1 row of launch_scan's table: 256-bit and 128-bit loads, whole and ragged tiles
@@ -319,7 +374,11 @@ cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream,
     size_t smem = scan_smem_bytes(a.dim, nqt, a.k, &a.P);
     if (smem > kSmemBudget || (a.dim & 3) || a.nq < 1 || a.nq > kMaxNQ) return cudaErrorInvalidValue;
     int grid = scan_grid_for(sm_count);
-    if (!a.row_list) {   // small stores (the reference's own scale) and centroid scans: no more CTAs than row groups need
+    if (a.probe_keys) {
+        if (a.nq != 1 || a.hi || a.probes < 1 || a.probes > DA_IVF_MAX_PROBES || a.probe_batch < 1 || !a.list_offsets || !a.list_rows)
+            return cudaErrorInvalidValue;
+        grid = scan_probe_ctas_per_query(sm_count, a.probe_batch);
+    } else if (!a.row_list) {   // small stores (the reference's own scale) and centroid scans: no more CTAs than row groups need
         const int r = 2;                                            // smallest R of any variant below
         const long long groups = ((long long)a.n_rows + r - 1) / r;
         const long long need = (groups + kScanWarps - 1) / kScanWarps;

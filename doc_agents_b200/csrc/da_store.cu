@@ -131,6 +131,10 @@ struct Shard {
     DevBuf<uint16_t> d_qhi;                     // ... and the queries' upper halves for the bf16 contraction
     DevBuf<unsigned long long> d_akeys;         // ... and the scan's approximate top-k
     DevBuf<uint32_t> d_flt_rows, d_flt_n;       // narrow document filter: the requested rows, compacted, and their count
+    DevBuf<unsigned long long> d_probe_keys;    // IVFFlat: the lists each query of the batch probes (key row = list id)
+    DevBuf<unsigned long long> d_ivf_cta;       // ... per-query CTA candidates of the probe-mode scan
+    DevBuf<unsigned int> d_ivf_counter;         // ... per-query tickets (left at zero by the kernel)
+    DevBuf<float> d_ivf_scores;                 // ... partial query x centroid scores of the tensor-core ranking
     DevBuf<int8_t> d_q8q;                       // int8 sidecar: quantised queries, their factors and error bounds
     DevBuf<float> d_q8qf, d_q8qe;
     PinBuf<uint32_t> h_overflow;
@@ -154,9 +158,9 @@ struct Shard {
     struct Ivf {
         float *cent = nullptr, *cent_inv = nullptr, *sums = nullptr, *counts_f = nullptr;
         uint32_t *assign = nullptr, *offsets = nullptr, *cursor = nullptr, *counts = nullptr;
-        uint32_t *list_rows = nullptr, *probe_rows = nullptr, *n_probe = nullptr;
+        uint32_t *list_rows = nullptr;
         uint32_t *sample = nullptr, *sample_assign = nullptr;
-        da::key_t64 *probe_keys = nullptr;
+        void *split_scratch = nullptr;            // sort keys and (donor, receiver) pairs of the balancing rounds
         float *sample_mat = nullptr;              // the k-means sample, gathered once (tensor-core path)
         unsigned long long *packed = nullptr;     // per-row packed (score, list) for the tensor-core argmax
         uint32_t n_sample = 0;
@@ -169,8 +173,8 @@ void free_ivf(Shard &s)
     Shard::Ivf &v = s.ivf;
     cudaFree(v.cent); cudaFree(v.cent_inv); cudaFree(v.sums); cudaFree(v.counts_f);
     cudaFree(v.assign); cudaFree(v.offsets); cudaFree(v.cursor); cudaFree(v.counts);
-    cudaFree(v.list_rows); cudaFree(v.probe_rows); cudaFree(v.n_probe);
-    cudaFree(v.sample); cudaFree(v.sample_assign); cudaFree(v.probe_keys);
+    cudaFree(v.list_rows); cudaFree(v.split_scratch);
+    cudaFree(v.sample); cudaFree(v.sample_assign);
     cudaFree(v.sample_mat); cudaFree(v.packed);
     s.hbm_bytes -= v.bytes;
     v = Shard::Ivf();
@@ -225,7 +229,7 @@ void free_shard(Shard &s)
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
     s.d_out.release(); s.d_gather.release(); s.d_final.release();
     s.d_cand.release(); s.d_cand_count.release(); s.d_overflow.release(); s.h_overflow.release();
-    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release(); s.d_q8q.release(); s.d_q8qf.release(); s.d_q8qe.release(); s.d_flt_rows.release(); s.d_flt_n.release();
+    s.d_approx.release(); s.d_akeys.release(); s.d_qhi.release(); s.d_probe_keys.release(); s.d_ivf_cta.release(); s.d_ivf_counter.release(); s.d_ivf_scores.release(); s.d_q8q.release(); s.d_q8qf.release(); s.d_q8qe.release(); s.d_flt_rows.release(); s.d_flt_n.release();
     s.d_hist.release(); s.d_gate.release(); s.d_surv_count.release(); s.d_surv.release(); s.d_group_sync.release();
     s.h_queries.release(); s.h_bitmap.release(); s.h_result.release(); s.h_rows_read.release();
     s.d_up_rows.release(); s.d_up_slots.release(); s.d_up_ids.release();
@@ -296,6 +300,8 @@ struct SearchPlan {
     size_t bitmap_words;
     bool ivf;
     int probes;
+    bool ivf_tc;       // IVFFlat: rank the centroids for the whole batch with one tensor-core GEMM (batches of 8+)
+    int ivf_ks;        // ... slices of the dimension of that GEMM
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
     bool use_q8;       // int8 sidecar scan for the candidates + exact re-score from the fp32 rows
     bool tc_i8;        // tensor path over the int8 sidecar (kind::i8) instead of the fp32 rows (TF32)
@@ -331,33 +337,45 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             continue;
         }
         if (pl.ivf) {
-            // per query: rank the centroids (the fused scan over the L x dim centroid matrix, top `probes`),
-            // expand the chosen lists into one row list, run the fused scan over that row list.
+            // (1) rank the centroids for every query of the batch: one tcgen05 GEMM (queries x centroids^T) + a
+            //     per-query selection of the `probes` best lists, or -- small batches -- the fused SIMT scan over the
+            //     lists x dim centroid matrix (up to 8 queries per pass, top `probes`);
+            // (2) ONE probe-mode scan for the whole batch: blockIdx.y = query, each query walks its own lists.
             const float ninf = -std::numeric_limits<float>::infinity();
-            for (int q = 0; q < pl.batch; q++) {
-                da::ScanArgs c{};
-                c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
-                c.queries = s.d_queries.p + (size_t)q * dim; c.q_inv_norm = s.d_qinv.p + q;
-                c.n_rows = (uint32_t)st->ivf_lists; c.row_base = 0;
-                c.dim = dim; c.nq = 1; c.k = pl.probes; c.min_sim = ninf;
-                c.cta_out = s.d_cta; c.counter = s.d_counter; c.out_keys = s.ivf.probe_keys;
-                CU(da::launch_scan(c, s.sm_count, s.stream, nullptr));
-                CU(da::ivf_launch_expand(s.ivf.probe_keys, pl.probes, s.ivf.offsets, s.ivf.list_rows, s.ivf.probe_rows,
-                                         s.ivf.n_probe, s.stream));
-                da::ScanArgs a{};
-                a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
-                a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p + (size_t)q * pl.bitmap_stride;
-                a.queries = c.queries; a.q_inv_norm = c.q_inv_norm;
-                a.row_list = s.ivf.probe_rows; a.n_rows_dev = s.ivf.n_probe; a.n_rows = 0; a.row_base = s.row_base;
-                a.dim = dim; a.nq = 1; a.k = pl.k; a.min_sim = pl.min_sim; a.read_all = pl.read_all ? 1 : 0;
-                a.cta_out = s.d_cta; a.counter = s.d_counter;
-                a.out_keys = out_keys + (size_t)q * pl.k; a.out_ids = out_ids + (size_t)q * pl.k * 16;
-                a.rows_read = s.d_rows_read;
-                int grid = 0;
-                CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
-                st->launches += 3;
-                if (first) st->scan_grid = grid;
+            const int L = st->ivf_lists;
+            da::key_t64 *probe_keys = reinterpret_cast<da::key_t64 *>(s.d_probe_keys.p);
+            if (pl.ivf_tc) {
+                CU(da::tc_launch_scores(s.d_queries.p, pl.batch, s.ivf.cent, L, dim, pl.ivf_ks, s.d_ivf_scores.p, s.stream));
+                CU(da::ivf_launch_select_probes(s.d_ivf_scores.p, pl.ivf_ks, pl.batch, L, pl.probes, probe_keys, s.stream));
+                st->launches += 2;
+            } else {
+                const int step = da::scan_pick_nq(dim, pl.probes, pl.batch);
+                for (int q0 = 0; q0 < pl.batch; q0 += step) {
+                    da::ScanArgs c{};
+                    c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
+                    c.queries = s.d_queries.p + (size_t)q0 * dim; c.q_inv_norm = s.d_qinv.p + q0;
+                    c.n_rows = (uint32_t)L; c.row_base = 0;
+                    c.dim = dim; c.nq = std::min(step, pl.batch - q0); c.k = pl.probes; c.min_sim = ninf;
+                    c.cta_out = s.d_cta; c.counter = s.d_counter; c.out_keys = probe_keys + (size_t)q0 * pl.probes;
+                    CU(da::launch_scan(c, s.sm_count, s.stream, nullptr));
+                    st->launches++;
+                }
             }
+            da::ScanArgs a{};
+            a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
+            a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p; a.bitmap_stride = pl.bitmap_stride;
+            a.queries = s.d_queries.p; a.q_inv_norm = s.d_qinv.p;
+            a.probe_keys = probe_keys; a.probes = pl.probes; a.probe_batch = pl.batch;
+            a.list_offsets = s.ivf.offsets; a.list_rows = s.ivf.list_rows;
+            a.n_rows = 0; a.row_base = s.row_base;
+            a.dim = dim; a.nq = 1; a.k = pl.k; a.min_sim = pl.min_sim; a.read_all = pl.read_all ? 1 : 0;
+            a.cta_out = reinterpret_cast<da::key_t64 *>(s.d_ivf_cta.p); a.counter = s.d_ivf_counter.p;
+            a.out_keys = out_keys; a.out_ids = out_ids;
+            a.rows_read = s.d_rows_read;
+            int grid = 0;
+            CU(da::launch_scan(a, s.sm_count, s.stream, &grid));
+            st->launches++;
+            if (first) st->scan_grid = grid;
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
             continue;
@@ -514,6 +532,12 @@ int tc_min_batch(const da_store *st)
     return 4;
 }
 
+int ivf_tc_min_batch()
+{
+    static const int env = [] { const char *v = getenv("DA_IVF_TC_MIN_BATCH"); return v ? atoi(v) : 0; }();
+    return env > 0 ? env : 8;
+}
+
 // Validate + stage the inputs of a search on every local shard.
 int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
 {
@@ -543,6 +567,10 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (ivf) {
         int probes = p->ivf_probes > 0 ? p->ivf_probes : st->ivf_default_probes;
         pl.probes = std::max(1, std::min(probes, std::min(st->ivf_lists, DA_IVF_MAX_PROBES)));
+        // batches of 8 or more rank the centroids as one dense contraction on the tensor cores (TF32 only steers
+        // which lists are probed; every returned score comes from the fp32 scan of the probed rows)
+        pl.ivf_tc = p->batch >= ivf_tc_min_batch() && !(p->flags & DA_SEARCH_NO_TENSOR) && st->ivf_lists <= da::kIvfSelectMaxLists;
+        pl.ivf_ks = pl.ivf_tc ? da::tc_scores_splits(p->batch, st->ivf_lists, st->dim, st->shards[0].sm_count) : 0;
     }
 
     // document filter -> bit per slot (document_id = ANY($2): postgres.go:239); unknown ids match nothing.
@@ -621,6 +649,15 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
         if (pl.compact) { CU(s.d_flt_rows.ensure(std::max<size_t>(s.n_rows, 1))); CU(s.d_flt_n.ensure(1)); }
+        if (pl.ivf && pl.k > 0) {
+            CU(s.d_probe_keys.ensure((size_t)p->batch * pl.probes));
+            CU(s.d_ivf_cta.ensure((size_t)p->batch * da::scan_probe_ctas_per_query(s.sm_count, p->batch) * pl.k));
+            if (s.d_ivf_counter.cap < (size_t)p->batch) {        // tickets start at zero and every launch leaves them there
+                CU(s.d_ivf_counter.ensure((size_t)p->batch));
+                CU(cudaMemsetAsync(s.d_ivf_counter.p, 0, s.d_ivf_counter.cap * sizeof(unsigned int), s.stream));
+            }
+            if (pl.ivf_tc) CU(s.d_ivf_scores.ensure((size_t)pl.ivf_ks * p->batch * st->ivf_lists));
+        }
         if (pl.use_q8) {
             const size_t nq = (size_t)da::scan_pick_nq(st->dim, pl.k, p->batch);
             CU(s.d_approx.ensure(nq * std::max<size_t>(s.n_rows, 1)));
@@ -717,9 +754,12 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     st->last_rows_read = rows_read;
     // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
     // + doc_slot (4 B) of every row visited when a document filter is present.
-    if (pl.ivf)   // centroid matrix per query + the probed rows (vector, inv_norm, doc slot if filtered, row number)
-        st->last_bytes = (uint64_t)pl.batch * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
+    if (pl.ivf) {  // centroid matrix once per pass of the ranking step + the probed rows (vector, inv_norm, doc slot if filtered, row number)
+        const int cstep = da::scan_pick_nq(st->dim, pl.probes, pl.batch);
+        const uint64_t cpasses = pl.ivf_tc ? 1 : (uint64_t)((pl.batch + cstep - 1) / cstep);
+        st->last_bytes = cpasses * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
                          rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
+    }
     else if (st->split16 && pl.use_tc)   // the upper plane once, whatever the batch
         st->last_bytes = rows_scanned * ((uint64_t)st->dim * 2 + (pl.all_docs ? 4 : 8));
     else if (st->split16)   // upper plane of the rows read + per row: 1/|row|, approximate score out and in (+ doc slot)
@@ -1297,12 +1337,11 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
         CU(cudaMalloc((void **)&v.cent, cd)); CU(cudaMalloc((void **)&v.sums, cd));
         CU(cudaMalloc((void **)&v.cent_inv, (size_t)L * 4)); CU(cudaMalloc((void **)&v.counts_f, (size_t)L * 4));
         CU(cudaMalloc((void **)&v.assign, s.cap_rows * 4)); CU(cudaMalloc((void **)&v.list_rows, s.cap_rows * 4));
-        CU(cudaMalloc((void **)&v.probe_rows, s.cap_rows * 4)); CU(cudaMalloc((void **)&v.n_probe, 4));
+        CU(cudaMalloc(&v.split_scratch, da::ivf_split_scratch_bytes(L)));
         CU(cudaMalloc((void **)&v.offsets, (size_t)(L + 1) * 4)); CU(cudaMalloc((void **)&v.cursor, (size_t)L * 4));
         CU(cudaMalloc((void **)&v.counts, (size_t)L * 4));
         CU(cudaMalloc((void **)&v.sample, (size_t)v.n_sample * 4)); CU(cudaMalloc((void **)&v.sample_assign, (size_t)v.n_sample * 4));
-        CU(cudaMalloc((void **)&v.probe_keys, DA_IVF_MAX_PROBES * sizeof(da::key_t64)));
-        v.bytes = 2 * cd + (size_t)L * 20 + s.cap_rows * 12 + (size_t)v.n_sample * 8 + 4096;
+        v.bytes = 2 * cd + (size_t)L * 20 + s.cap_rows * 8 + (size_t)v.n_sample * 8 + da::ivf_split_scratch_bytes(L);
         if (use_tc) {
             CU(cudaMalloc((void **)&v.sample_mat, (size_t)v.n_sample * D * 4));
             CU(cudaMalloc((void **)&v.packed, da::tc_assign_scratch_bytes((uint32_t)s.cap_rows)));
@@ -1322,7 +1361,7 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
         Shard &s0 = st->shards[0];
         CU(cudaSetDevice(s0.device));
         if (st->rank == 0) {
-            CU(da::ivf_launch_init_centroids(s0.mat, D, s0.inv_norm, s0.ivf.sample, s0.ivf.n_sample, L, s0.ivf.cent,
+            CU(da::ivf_launch_init_centroids(s0.mat, D, s0.inv_norm, s0.ivf.sample, s0.ivf.n_sample, L, p->seed, s0.ivf.cent,
                                              s0.ivf.cent_inv, s0.stream));
             st->launches += 2;
         }
@@ -1359,6 +1398,39 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
             CU(cudaSetDevice(s.device));
             CU(da::ivf_launch_finalize(s.ivf.sums, s.ivf.counts_f, L, D, s.ivf.cent, s.stream));
             st->launches++;
+        }
+    }
+    // Balancing rounds (da_ivf.cu, "Splitting heavy lists"): count the sample per list under the current centroids
+    // (globally: all-reduce), let the heaviest lists split into the empty ones on global rank 0, hand the centroids
+    // to everybody.  A list of c x the mean needs log2(c) rounds; four cover 16 x.
+    const int split_rounds = (p->flags & DA_IVF_NO_SPLIT) ? 0 : 4;
+    for (int round = 0; round < split_rounds; round++) {
+        for (Shard &s : st->shards) {
+            Shard::Ivf &v = s.ivf;
+            CU(cudaSetDevice(s.device));
+            if (use_tc) CU(da::tc_launch_assign(v.sample_mat, v.n_sample, D, v.cent, L, v.packed, v.sample_assign, s.stream));
+            else CU(da::ivf_launch_assign(s.mat, D, v.sample, v.n_sample, v.cent, L, v.sample_assign, 0, s.stream));
+            CU(cudaMemsetAsync(v.counts_f, 0, (size_t)L * 4, s.stream));
+            CU(da::ivf_launch_count(v.sample_assign, v.n_sample, v.counts_f, s.stream));
+            st->launches += 2;
+        }
+        if (st->total_ranks > 1) {
+            NC(ncclGroupStart());
+            for (Shard &s : st->shards) NC(ncclAllReduce(s.ivf.counts_f, s.ivf.counts_f, (size_t)L, ncclFloat, ncclSum, s.comm, s.stream));
+            NC(ncclGroupEnd());
+        }
+        if (st->rank == 0) {
+            Shard &s0 = st->shards[0];
+            CU(cudaSetDevice(s0.device));
+            CU(da::ivf_launch_split_round(s0.ivf.counts_f, L, s0.ivf.split_scratch, s0.mat, D, s0.inv_norm, s0.ivf.sample,
+                                          s0.ivf.n_sample, s0.ivf.sample_assign, p->seed + 0xB5 * (uint64_t)(round + 1),
+                                          s0.ivf.cent, s0.stream));
+            st->launches += 2;
+        }
+        if (st->total_ranks > 1) {
+            NC(ncclGroupStart());
+            for (Shard &s : st->shards) NC(ncclBroadcast(s.ivf.cent, s.ivf.cent, (size_t)L * D, ncclFloat, 0, s.comm, s.stream));
+            NC(ncclGroupEnd());
         }
     }
     // every resident row joins the list of its nearest centroid
@@ -1417,7 +1489,7 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
         da::SynthArgs a{};
         a.seed_data = p->seed_data; a.seed_centroid = p->seed_centroid; a.seed_ids = p->seed_ids;
         a.chunks_per_doc = p->chunks_per_doc; a.n_clusters = p->n_clusters;
-        a.cmul = p->cmul; a.nmul = p->nmul;
+        a.cmul = p->cmul; a.nmul = p->nmul; a.smul = p->smul; a.super_group = p->super_group;
         a.row_lo = lo; a.n_rows = (uint32_t)(hi - lo); a.doc_slot_base = (uint32_t)doc_lo; a.dim = st->dim;
         CU(cudaSetDevice(s.device));
         if (st->split16) {                 // generate fp32 rows chunk by chunk into the staging buffer, then split them
@@ -1466,7 +1538,7 @@ int da_synth_query(const da_synth_params *p, uint64_t seed_query, uint64_t qi, u
     if (!p || !out) return fail(DA_ERR_INVALID, "params/out is NULL");
     if (p->struct_size != sizeof(da_synth_params)) return fail(DA_ERR_INVALID, "da_synth_params.struct_size mismatch");
     if (dim <= 0) return fail(DA_ERR_DIM, "dim=%d", dim);
-    da::synth_vector_host(seed_query, qi, p->seed_centroid, cluster, p->cmul, p->nmul, dim, out);
+    da::synth_vector_host(seed_query, qi, p->seed_centroid, cluster, p->cmul, p->nmul, dim, out, p->smul, p->super_group);
     return DA_OK;
 }
 
@@ -1543,6 +1615,21 @@ int da_store_debug_read_ivf(da_store *st, int32_t device_index, uint32_t *out_of
     if (out_offsets) CU(cudaMemcpy(out_offsets, s.ivf.offsets, (size_t)(L + 1) * 4, cudaMemcpyDeviceToHost));
     if (out_list_rows) CU(cudaMemcpy(out_list_rows, s.ivf.list_rows, (size_t)s.n_rows * 4, cudaMemcpyDeviceToHost));
     if (out_centroids) CU(cudaMemcpy(out_centroids, s.ivf.cent, (size_t)L * st->dim * 4, cudaMemcpyDeviceToHost));
+    return DA_OK;
+}
+
+int da_store_debug_read_probes(da_store *st, int32_t device_index, int32_t batch, int32_t probes, uint32_t *out_lists)
+{
+    if (!st || !out_lists) return fail(DA_ERR_INVALID, "store/out is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
+    Shard &s = st->shards[device_index];
+    if (batch < 1 || probes < 1 || (size_t)batch * probes > s.d_probe_keys.cap)
+        return fail(DA_ERR_INVALID, "no IVFFlat search of that shape has run on this shard");
+    std::vector<unsigned long long> keys((size_t)batch * probes);
+    CU(cudaSetDevice(s.device));
+    CU(cudaMemcpy(keys.data(), s.d_probe_keys.p, keys.size() * 8, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < keys.size(); i++) out_lists[i] = keys[i] ? da::key_row(keys[i]) : 0xFFFFFFFFu;
     return DA_OK;
 }
 

@@ -281,6 +281,115 @@ tc_rowargmax_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     }
 }
 
+// ---------------------------------------------------------------------------
+// Plain score tiles for the batched IVFFlat query -> centroid step: out[split][m][n] = sum over the split's slice
+// of the dimension of A[m][k] * B[n][k], A = the queries of a batch, B = the centroids.  The problem is small
+// (64 x 4096 x 3072 = 1.6 GFLOP, 50 MB of centroids) and short of tiles (16 for that shape), so the dimension is
+// cut into `ks` slices, one CTA per (tile, slice): every SM streams a share of the centroid matrix, and the partial
+// sums are added in a fixed order by the selection kernel (da_ivf.cu) -- deterministic, no atomics.
+// Same pipeline as above (TMA -> 4-stage ring -> tcgen05.mma kind::tf32 -> TMEM), one accumulator per CTA.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_scores_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 uint32_t M, uint32_t N, int kb_total, int kb_per_split, int n_tiles, float *__restrict__ out)
+{
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = base + TC_STAGES * TC_STAGE_BYTES;
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * TC_STAGES, bar_tfull = bars + 16 * TC_STAGES;
+    const uint32_t tmem_slot = bar_tfull + 8;
+    volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t tile = blockIdx.x, split = blockIdx.y;
+    const uint32_t m0 = (tile / (uint32_t)n_tiles) * TC_BM, n0 = (tile % (uint32_t)n_tiles) * TC_BN;
+    const int kb_begin = (int)split * kb_per_split;
+    const int kb_end = min(kb_total, kb_begin + kb_per_split);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        mbar_init(bar_tfull, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)TC_BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int kb = kb_begin; kb < kb_end; kb++) {
+                mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                mbar_expect_tx(bar_full + 8 * stage, TC_STAGE_BYTES);
+                tma_load_2d(sa, &map_a, bar_full + 8 * stage, kb * TC_BK, (int)m0);
+                tma_load_2d(sb, &map_b, bar_full + 8 * stage, kb * TC_BK, (int)n0);
+                if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int kb = kb_begin; kb < kb_end; kb++) {
+                mbar_wait(bar_full + 8 * stage, phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = base + stage * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
+                const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
+#pragma unroll
+                for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
+                    umma_tf32(tmem_base, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), TC_IDESC, (uint32_t)((kb > kb_begin) | (k != 0)));
+                umma_commit(bar_empty + 8 * stage);
+                if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(bar_tfull);
+        }
+    } else {
+        // epilogue warps 2..5: thread = one row of A (one query), 256 scores in eight chunks of 32
+        const uint32_t quad = (uint32_t)warp & 3u;
+        const uint32_t m = m0 + quad * 32 + (uint32_t)lane;
+        const bool any = kb_begin < kb_end;
+        if (any) {
+            mbar_wait(bar_tfull, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        float *dst = out + ((size_t)split * M + m) * N;
+        const bool vec = (N & 3u) == 0u;
+#pragma unroll 1
+        for (int c = 0; c < TC_BN / 32; c++) {
+            uint32_t r[32];
+            if (any) tmem_ld32(tmem_base + ((quad * 32u) << 16) + (uint32_t)c * 32u, r);
+            else {
+#pragma unroll
+                for (int j = 0; j < 32; j++) r[j] = 0u;
+            }
+            const uint32_t nb = n0 + (uint32_t)c * 32u;
+            if (m < M) {
+                if (vec && nb + 32u <= N) {
+#pragma unroll
+                    for (int j = 0; j < 8; j++)
+                        reinterpret_cast<float4 *>(dst + nb)[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                                                             __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; j++)
+                        if (nb + (uint32_t)j < N) dst[nb + j] = __uint_as_float(r[j]);
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC_BN) : "memory");
+    }
+}
+
 __global__ void unpack_assign_kernel(const unsigned long long *packed, uint32_t n, uint32_t *assign)
 {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
@@ -791,6 +900,37 @@ cudaError_t tc_launch_assign(const float *mat, uint32_t M, int D, const float *c
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     unpack_assign_kernel<<<148 * 4, 256, 0, stream>>>(packed_scratch, M, out_assign);
+    return cudaGetLastError();
+}
+
+// How many slices of the dimension the score GEMM is cut into: enough (tile, slice) CTAs to occupy the chip, at most 16.
+int tc_scores_splits(int M, int N, int D, int sm_count)
+{
+    const int tiles = ((M + TC_BM - 1) / TC_BM) * ((N + TC_BN - 1) / TC_BN);
+    const int kb_total = (D + TC_BK - 1) / TC_BK;
+    int ks = sm_count / (tiles > 0 ? tiles : 1);
+    if (ks > 16) ks = 16;
+    if (ks > kb_total) ks = kb_total;
+    if (ks < 1) ks = 1;
+    const int per = (kb_total + ks - 1) / ks;
+    return (kb_total + per - 1) / per;                       // slices that actually receive work
+}
+
+cudaError_t tc_launch_scores(const float *A, int M, const float *B, int N, int D, int ks, float *out, cudaStream_t stream)
+{
+    if (M <= 0 || N <= 0) return cudaSuccess;
+    if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) || (reinterpret_cast<uintptr_t>(out) & 15) || (D & 3))
+        return cudaErrorInvalidValue;
+    CUtensorMap map_a, map_b;
+    if (!make_map(&map_a, A, (uint64_t)M, (uint64_t)D, TC_BM) || !make_map(&map_b, B, (uint64_t)N, (uint64_t)D, TC_BN))
+        return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(tc_scores_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    const int n_tiles = (N + TC_BN - 1) / TC_BN, m_tiles = (M + TC_BM - 1) / TC_BM;
+    const int kb_total = (D + TC_BK - 1) / TC_BK;
+    const int per = (kb_total + ks - 1) / ks;
+    tc_scores_kernel<<<dim3((unsigned)(m_tiles * n_tiles), (unsigned)ks), TC_THREADS, TC_SMEM_BYTES, stream>>>(
+        map_a, map_b, (uint32_t)M, (uint32_t)N, kb_total, per, n_tiles, out);
     return cudaGetLastError();
 }
 

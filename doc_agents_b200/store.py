@@ -292,15 +292,16 @@ class GpuStore:
         p.seed_data, p.seed_centroid, p.seed_ids = synth.seed_data, synth.seed_centroid, synth.seed_ids
         p.chunks_per_doc, p.n_clusters = synth.chunks_per_doc, synth.n_clusters
         p.cmul, p.nmul = synth.cmul, synth.nmul
+        p.smul, p.super_group = getattr(synth, "smul", 0), getattr(synth, "super_group", 0)
         p.row_lo, p.n_rows = row_lo, n_rows
         _check(self._lib.da_store_generate_synthetic(self._h, C.byref(p)))
 
     def build_ivf(self, lists: int = 100, iters: int = 10, sample_rows: int = 0, seed: int = 1,
-                  default_probes: int = 1, simt_assign: bool = False) -> None:
+                  default_probes: int = 1, simt_assign: bool = False, split: bool = True) -> None:
         p = L.da_ivf_params()
         p.struct_size = C.sizeof(L.da_ivf_params)
         p.lists, p.iters, p.sample_rows, p.seed, p.default_probes = lists, iters, sample_rows, seed, default_probes
-        p.flags = L.DA_IVF_SIMT_ASSIGN if simt_assign else 0
+        p.flags = (L.DA_IVF_SIMT_ASSIGN if simt_assign else 0) | (0 if split else L.DA_IVF_NO_SPLIT)
         _check(self._lib.da_store_build_ivf(self._h, C.byref(p)))
 
     def stats(self) -> L.da_stats:
@@ -328,6 +329,13 @@ class GpuStore:
         _check(self._lib.da_store_debug_read_ivf(self._h, device_index, off.ctypes.data, rows.ctypes.data,
                                                  cent.ctypes.data))
         return off, rows, cent
+
+
+    def debug_probes(self, batch: int, probes: int, device_index: int = 0) -> np.ndarray:
+        """The lists each query of the last IVFFlat search probed on one shard (batch x probes, -1 = none)."""
+        out = np.empty((batch, probes), dtype=np.uint32)
+        _check(self._lib.da_store_debug_read_probes(self._h, device_index, batch, probes, out.ctypes.data))
+        return out.astype(np.int64) - (out == 0xFFFFFFFF) * (1 << 32)
 
 
 def calculate_avg_similarity(results) -> np.float32:

@@ -22,12 +22,15 @@ class Synth:
     n_clusters: int = 1024
     cmul: int = 2
     nmul: int = 1
+    smul: int = 0
+    super_group: int = 0
 
     def c(self) -> L.da_synth_params:
         p = L.da_synth_params()
         p.struct_size = C.sizeof(L.da_synth_params)
         p.seed_data, p.seed_centroid, p.seed_ids = self.seed_data, self.seed_centroid, self.seed_ids
         p.chunks_per_doc, p.n_clusters, p.cmul, p.nmul = self.chunks_per_doc, self.n_clusters, self.cmul, self.nmul
+        p.smul, p.super_group = self.smul, self.super_group
         return p
 
 

@@ -159,7 +159,10 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
 
 /* The IVFFlat index of the reference DDL (postgres.go:95-99: lists = 100, vector_cosine_ops):
  * spherical k-means on a sample, every row assigned to its nearest centroid, rows regrouped
- * by list.  Searches with DA_SEARCH_IVF rank the centroids and scan `probes` lists. */
+ * by list.  Searches with DA_SEARCH_IVF rank the centroids and scan `probes` lists: a batch of 8 or more queries
+ * ranks them with one tensor-core GEMM (queries x centroids^T, TF32 -- it only steers which lists are probed),
+ * smaller batches with the fp32 scan of the centroid matrix; then ONE scan launch serves the whole batch, every
+ * query walking its own lists.  Returned scores always come from the fp32 rows. */
 typedef struct {
     uint32_t struct_size;
     int32_t  lists;          /* 100 in the reference DDL; 4096 in BASELINE configs[4] */
@@ -167,9 +170,10 @@ typedef struct {
     uint64_t sample_rows;    /* 0 = max(lists*50, 10000), pgvector's rule */
     uint64_t seed;
     int32_t  default_probes; /* pgvector default is 1 (ivfflat.probes) */
-    uint32_t flags;          /* DA_IVF_SIMT_ASSIGN: assign with the fp32 SIMT GEMM instead of tcgen05 TF32 */
+    uint32_t flags;          /* DA_IVF_* below */
 } da_ivf_params;
-#define DA_IVF_SIMT_ASSIGN 0x1u
+#define DA_IVF_SIMT_ASSIGN 0x1u  /* assign with the fp32 SIMT GEMM instead of tcgen05 TF32 */
+#define DA_IVF_NO_SPLIT    0x2u  /* skip the balancing rounds after k-means (heavy lists split into empty ones); comparisons */
 int da_store_build_ivf(da_store *st, const da_ivf_params *p);
 
 /* Device-side synthetic corpus (bench/tests only; SURVEY.md section 8d, DESIGN.md
@@ -182,6 +186,11 @@ typedef struct {
     uint32_t chunks_per_doc, n_clusters;
     int32_t  cmul, nmul;
     uint64_t row_lo, n_rows;
+    /* Optional second level (0 = off, the BASELINE corpus): clusters are grouped `super_group` at a time and every
+     * vector also carries smul x the direction of its cluster's group, so clusters of one group overlap (cosine
+     * smul^2 / (smul^2 + cmul^2 + nmul^2) between them) -- a corpus on which an approximate index can lose recall. */
+    int32_t  smul;
+    uint32_t super_group;
 } da_synth_params;
 int da_store_generate_synthetic(da_store *st, const da_synth_params *p);
 
@@ -234,6 +243,10 @@ int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo
  * one entry per resident row (rows grouped by list), out_centroids lists x dim.  Any may be NULL. */
 int da_store_debug_read_ivf(da_store *st, int32_t device_index, uint32_t *out_offsets,
                             uint32_t *out_list_rows, float *out_centroids);
+
+/* Test-harness view of the last DA_SEARCH_IVF search on one shard: the lists each of its `batch` queries probed
+ * (batch x probes list numbers, 0xFFFFFFFF = none), in no particular order. */
+int da_store_debug_read_probes(da_store *st, int32_t device_index, int32_t batch, int32_t probes, uint32_t *out_lists);
 
 /* No counterpart in the reference.  The exact scan of da_store_search for hosts that must not
  * allocate: a serving loop that cannot afford cudaMalloc's device-wide synchronisation, a process

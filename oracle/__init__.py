@@ -36,7 +36,7 @@ class _Synth(C.Structure):
     _fields_ = [("seed_data", C.c_uint64), ("seed_centroid", C.c_uint64),
                 ("seed_query", C.c_uint64), ("seed_ids", C.c_uint64),
                 ("chunks_per_doc", C.c_uint32), ("n_clusters", C.c_uint32),
-                ("cmul", C.c_int32), ("nmul", C.c_int32)]
+                ("cmul", C.c_int32), ("nmul", C.c_int32), ("smul", C.c_int32), ("super_group", C.c_uint32)]
 
 
 @dataclass(frozen=True)
@@ -50,10 +50,12 @@ class Synth:
     n_clusters: int = 1024
     cmul: int = 2   # centroid multiplier  } sigma = nmul / cmul = 0.5
     nmul: int = 1   # noise multiplier     } same-cluster cosine ~ 0.8
+    smul: int = 0          # optional second level: + smul x the direction of the cluster's group of
+    super_group: int = 0   # `super_group` clusters (0 = off): clusters of one group overlap
 
     def c(self) -> _Synth:
         return _Synth(self.seed_data, self.seed_centroid, self.seed_query, self.seed_ids,
-                      self.chunks_per_doc, self.n_clusters, self.cmul, self.nmul)
+                      self.chunks_per_doc, self.n_clusters, self.cmul, self.nmul, self.smul, self.super_group)
 
 
 _lib = None
@@ -66,6 +68,7 @@ def lib() -> C.CDLL:
         L = C.CDLL(_LIB_PATH)
         fp = C.POINTER(C.c_float)
         L.orc_gen_rows.argtypes = [C.POINTER(_Synth), C.c_uint64, C.c_uint64, C.c_int, fp]
+        L.orc_gen_rows_at.argtypes = [C.POINTER(_Synth), C.c_void_p, C.c_uint64, C.c_int, fp]
         L.orc_gen_query.argtypes = [C.POINTER(_Synth), C.c_uint64, C.c_uint32, C.c_int, fp]
         L.orc_chunk_id.argtypes = [C.POINTER(_Synth), C.c_uint64, C.c_void_p]
         L.orc_doc_id.argtypes = [C.POINTER(_Synth), C.c_uint64, C.c_void_p]
@@ -107,6 +110,16 @@ def gen_rows(p: Synth, row_lo: int, n: int, dim: int) -> np.ndarray:
     if n:
         s = p.c()
         lib().orc_gen_rows(C.byref(s), row_lo, n, dim, _fp(out))
+    return out
+
+
+def gen_rows_at(p: Synth, rows, dim: int) -> np.ndarray:
+    """Rows of the synthetic corpus by global row number, in the order given."""
+    rows = np.ascontiguousarray(rows, dtype=np.uint64)
+    out = np.empty((rows.shape[0], dim), dtype=np.float32)
+    if rows.shape[0]:
+        s = p.c()
+        lib().orc_gen_rows_at(C.byref(s), rows.ctypes.data, rows.shape[0], dim, _fp(out))
     return out
 
 

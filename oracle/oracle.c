@@ -86,14 +86,22 @@ static inline int32_t orc_elem(uint64_t key, uint32_t col)
 /* u[col] = cmul * centroid[cluster][col] + nmul * noise[stream][col], all int32.
  * x = float(u) / float(sqrt(double(sum u^2)))  -- the normalisation of
  * openai.go:146-158 with the float64 sum of squares computed exactly. */
+#define ORC_SUPER_TAG 0x5C0DE5C0DE5C0DE5ULL   /* seed_centroid ^ this = the stream of group directions */
+
+/* Optional second level (smul != 0 and super_group != 0): clusters are grouped super_group at a time and a vector
+ * also carries smul x the direction of its cluster's group, so the clusters of one group overlap. */
 static void orc_gen_vec(uint64_t seed_noise, uint64_t noise_index, uint64_t seed_centroid,
-                        uint64_t cluster, int32_t cmul, int32_t nmul, int dim, float *out)
+                        uint64_t cluster, int32_t cmul, int32_t nmul, int32_t smul, uint32_t super_group,
+                        int dim, float *out)
 {
     uint64_t kn = orc_stream_key(seed_noise, noise_index);
     uint64_t kc = orc_stream_key(seed_centroid, cluster);
+    int two_level = smul != 0 && super_group != 0;
+    uint64_t ks = two_level ? orc_stream_key(seed_centroid ^ ORC_SUPER_TAG, cluster / super_group) : 0;
     int64_t ss = 0;
     for (int c = 0; c < dim; c++) {
         int32_t u = cmul * orc_elem(kc, (uint32_t)c) + nmul * orc_elem(kn, (uint32_t)c);
+        if (two_level) u += smul * orc_elem(ks, (uint32_t)c);
         ss += (int64_t)u * (int64_t)u;
         out[c] = (float)u;
     }
@@ -106,6 +114,7 @@ typedef struct {
     uint64_t seed_data, seed_centroid, seed_query, seed_ids;
     uint32_t chunks_per_doc, n_clusters;
     int32_t cmul, nmul;
+    int32_t smul; uint32_t super_group;
 } orc_synth;
 
 uint32_t orc_row_doc(const orc_synth *p, uint64_t row) { return (uint32_t)(row / p->chunks_per_doc); }
@@ -117,14 +126,25 @@ void orc_gen_rows(const orc_synth *p, uint64_t row_lo, uint64_t n, int dim, floa
     for (int64_t i = 0; i < (int64_t)n; i++) {
         uint64_t row = row_lo + (uint64_t)i;
         uint32_t cl = orc_doc_cluster(p, orc_row_doc(p, row));
-        orc_gen_vec(p->seed_data, row, p->seed_centroid, cl, p->cmul, p->nmul, dim,
+        orc_gen_vec(p->seed_data, row, p->seed_centroid, cl, p->cmul, p->nmul, p->smul, p->super_group, dim,
+                    out + (size_t)i * dim);
+    }
+}
+
+/* The same generator for an arbitrary list of global rows (the members of probed IVFFlat lists, say). */
+void orc_gen_rows_at(const orc_synth *p, const uint64_t *rows, uint64_t n, int dim, float *out)
+{
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        uint32_t cl = orc_doc_cluster(p, orc_row_doc(p, rows[i]));
+        orc_gen_vec(p->seed_data, rows[i], p->seed_centroid, cl, p->cmul, p->nmul, p->smul, p->super_group, dim,
                     out + (size_t)i * dim);
     }
 }
 
 void orc_gen_query(const orc_synth *p, uint64_t qi, uint32_t cluster, int dim, float *out)
 {
-    orc_gen_vec(p->seed_query, qi, p->seed_centroid, cluster, p->cmul, p->nmul, dim, out);
+    orc_gen_vec(p->seed_query, qi, p->seed_centroid, cluster, p->cmul, p->nmul, p->smul, p->super_group, dim, out);
 }
 
 /* 16-byte ids: two hashes, RFC 4122 version-4 / variant bits forced so they

@@ -225,7 +225,18 @@ def test_batched_queries_equal_single_queries(batch):
             assert np.allclose(sc_b[i], o_sc, rtol=REL_TOL)
 
 
-def _full_size_check(n_rows, dim, k, n_filter_docs):
+def _cluster_oracle(S, n_rows, dim, q, cluster, k, min_sim=0.7):
+    """Oracle top-k over the documents of one cluster (the only rows that can rank: same-cluster cosine ~0.8 against
+    ~0 across clusters).  Returns global rows and scores."""
+    n_docs = n_rows // S.chunks_per_doc
+    cl_docs = list(range(cluster, n_docs, S.n_clusters))
+    sub_rows = np.concatenate([np.arange(d * 200, d * 200 + 200) for d in cl_docs])
+    sub = np.concatenate([oracle.gen_rows(S, d * 200, 200, dim) for d in cl_docs])
+    o_rows, o_sc, _ = oracle.topk(sub, None, None, q, k, min_sim)
+    return sub_rows[o_rows], o_sc
+
+
+def _full_size_check(n_rows, dim, k, n_filter_docs, big_batch=0):
     """Parity at a BASELINE size: the document filter (or the 0.7 floor plus the cluster
     structure) leaves only a few thousand rows that can qualify; the oracle scores exactly those."""
     S = S0
@@ -267,14 +278,49 @@ def _full_size_check(n_rows, dim, k, n_filter_docs):
         for i in range(4):
             one = st.search(qs[i], k, all_docs=True)
             assert np.array_equal(b[2][i], one[2][0]) and np.allclose(b[1][i], one[1][0], rtol=1e-6)
+        if big_batch:
+            # configs[2] at batch = 64: the tcgen05 candidate path + exact re-score, against the oracle on sampled queries
+            qs = np.stack([oracle.gen_query(S, 500 + i, (37 * i) % S.n_clusters, dim) for i in range(big_batch)])
+            l0 = st.stats().kernel_launches
+            b = st.search(qs, k, all_docs=True)
+            assert st.stats().kernel_launches - l0 <= 6                      # one contraction, not 8 SIMT passes
+            assert st.stats().tensor_overflows == 0
+            for i in range(0, big_batch, max(1, big_batch // 8)):
+                o_rows, o_sc = _cluster_oracle(S, n_rows, dim, qs[i], (37 * i) % S.n_clusters, k)
+                assert same_rows_up_to_ties(b[2][i], o_rows, o_sc), (i, b[2][i], o_rows)
+                assert np.allclose(b[1][i], o_sc, rtol=REL_TOL)
+                assert np.array_equal(b[0][i], np.stack([oracle.chunk_ids(S, int(r), 1)[0] for r in b[2][i]]))
 
 
 def test_config2_exact_scan_1m_x_3072_filtered_to_16_docs():
     _full_size_check(1_000_000, 3072, 10, 16)
 
 
-def test_config3_exact_scan_10m_x_3072_single_gpu():
-    _full_size_check(10_000_000, 3072, 10, 16)
+def test_config3_exact_scan_10m_x_3072_single_gpu_batch_1_and_64():
+    _full_size_check(10_000_000, 3072, 10, 16, big_batch=64)
+
+
+def test_config4_one_shard_4096_queries_x_1p25m_x_1536_top100_no_floor():
+    """One GPU's share of BASELINE configs[3] (4 096 questions x 10M x 1536 over 8 GPUs, k = 100, no floor): the
+    tensor-core score GEMM fused with the per-query candidate select, then the exact re-score; sampled queries
+    against the oracle, every query for size-independent properties."""
+    S = S0
+    n_rows, dim, k, batch = 1_250_000, 1536, 100, 4096
+    with GpuStore(dim=dim, capacity_rows=n_rows) as st:
+        st.generate_synthetic(S, 0, n_rows)
+        qs = np.stack([oracle.gen_query(S, 9000 + i, (37 * i) % S.n_clusters, dim) for i in range(batch)])
+        ids, sc, rows, cnt = st.search_arrays(qs, k, all_docs=True, min_similarity=-np.inf)
+        assert st.stats().tensor_overflows == 0
+        assert np.all(cnt == k)
+        assert np.all(np.diff(sc, axis=1) <= 0)                                  # best first, every query
+        assert all(len(np.unique(rows[i])) == k for i in range(0, batch, 97))    # no row twice
+        for i in (0, 1, 511, 1024, 2047, 3000, 4000, 4095):
+            o_rows, o_sc = _cluster_oracle(S, n_rows, dim, qs[i], (37 * i) % S.n_clusters, k, -np.inf)
+            assert o_sc[-1] > 0.5                                                # all k come from the query's own cluster
+            assert same_rows_up_to_ties(rows[i], o_rows, o_sc), i
+            assert np.allclose(sc[i], o_sc, rtol=REL_TOL)
+        one = st.search(qs[1024], k, all_docs=True, min_similarity=-np.inf)      # the SIMT scan answers the same
+        assert np.array_equal(one[2][0], rows[1024]) and np.array_equal(one[1][0], sc[1024])
 
 
 def test_dim_1536_store():
