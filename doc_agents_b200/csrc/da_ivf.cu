@@ -239,7 +239,7 @@ __global__ void list_scatter_kernel(const uint32_t *assign, uint32_t n, uint32_t
 // members is a better representative of EVERY member (its noise part is smaller), so the larger sibling wins
 // rows from the smaller one until that one is empty -- measured in round 1: 2 716 of 4 096 lists empty on the
 // BASELINE corpus, whole 9 800-row clusters in single lists.  An index wants balanced lists, so after the
-// iterations the heaviest lists donate to the empty ones: donor centroid c and a direction d orthogonal to it
+// iterations the heaviest lists donate to the empty (or nearly empty) ones: donor centroid c and a direction d orthogonal to it
 // (the off-centroid part of one of its members) become  normalize(c + e d)  and  normalize(c - e d).  The pair
 // is symmetric -- neither has the larger-sibling advantage -- and e is large enough for the split to survive
 // TF32 rounding of the assignment GEMM.  The pair is NOT re-averaged (that would collapse it again).
@@ -252,8 +252,10 @@ __global__ void count_assign_kernel(const uint32_t *assign, uint32_t n, float *c
 }
 
 // One CTA.  keys (P = pow2 >= L entries of scratch): (count << 32 | ~list), sorted descending; then the j-th
-// heaviest list is paired with the j-th list from the empty end while the donor holds more than 1.5 x the mean
-// and the receiver nothing.  pairs[2j] = donor, pairs[2j+1] = receiver; *n_pairs = number of pairs.
+// heaviest list is paired with the j-th list from the light end while the donor holds more than 1.5 x the mean
+// and the receiver less than a quarter of it (an empty list, or the stub a starved sibling has shrunk to: a few
+// rows around its seed, which simply join their next-nearest list).  pairs[2j] = donor, pairs[2j+1] = receiver;
+// *n_pairs = number of pairs.
 __global__ void __launch_bounds__(1024) plan_splits_kernel(const float *counts, int L, int P, unsigned long long *keys,
                                                           uint32_t *pairs, uint32_t *n_pairs)
 {
@@ -280,10 +282,10 @@ __global__ void __launch_bounds__(1024) plan_splits_kernel(const float *counts, 
             }
         }
     __syncthreads();
-    const float heavy = 1.5f * total_s / (float)L;
+    const float heavy = 1.5f * total_s / (float)L, light = 0.25f * total_s / (float)L;
     for (int j = tid; j < L / 2; j += blockDim.x) {
         const unsigned long long d = keys[j], r = keys[L - 1 - j];
-        if ((float)(uint32_t)(d >> 32) > heavy && (uint32_t)(r >> 32) == 0u) {
+        if ((float)(uint32_t)(d >> 32) > heavy && (float)(uint32_t)(r >> 32) < light) {
             // pairs are a prefix of j (counts descend from the head, ascend from the tail), so slot j is dense
             pairs[2 * j] = ~(uint32_t)(d & 0xFFFFFFFFull);
             pairs[2 * j + 1] = ~(uint32_t)(r & 0xFFFFFFFFull);

@@ -181,3 +181,26 @@ def same_rows_up_to_ties(got_rows, ref_rows, ref_scores, tol: float = REL_TOL) -
             return False
         i = j
     return True
+
+
+def topk_matches_extended(got_rows, got_scores, ref_rows_ext, ref_scores_ext, k: int, tol: float = REL_TOL) -> str:
+    """Acceptance rule against a reference list that runs a few places PAST k (so that a tie across the cut is
+    visible): scores within tol, and at every rank either the reference's row or a row whose reference score ties
+    the reference's score at that rank within tol.  Returns "" when it holds, else what is wrong."""
+    got_rows = [int(r) for r in got_rows]
+    ref_rows_ext = [int(r) for r in ref_rows_ext]
+    ref_scores_ext = np.asarray(ref_scores_ext, dtype=np.float64)
+    n_ref = min(k, len(ref_rows_ext))
+    if len(got_rows) != n_ref:
+        return f"{len(got_rows)} rows, reference {n_ref}"
+    if len(set(got_rows)) != len(got_rows):
+        return "a row came back twice"
+    where = {r: i for i, r in enumerate(ref_rows_ext)}
+    for i, (r, s) in enumerate(zip(got_rows, np.asarray(got_scores, dtype=np.float64))):
+        if r not in where:
+            return f"rank {i}: row {r} is not among the reference's first {len(ref_rows_ext)}"
+        if abs(ref_scores_ext[where[r]] - ref_scores_ext[i]) > tol * abs(ref_scores_ext[i]) + ABS_TOL:
+            return f"rank {i}: row {r} (reference score {ref_scores_ext[where[r]]}) where the reference has {ref_rows_ext[i]} ({ref_scores_ext[i]})"
+        if abs(s - ref_scores_ext[where[r]]) > tol * abs(ref_scores_ext[where[r]]) + ABS_TOL:
+            return f"rank {i}: score {s} of row {r}, reference {ref_scores_ext[where[r]]}"
+    return ""

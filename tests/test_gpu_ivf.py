@@ -184,6 +184,7 @@ def test_batched_ivf_ranks_centroids_on_tensor_cores(n, dim, lists, clusters, ba
         got = st.search(qs, 10, all_docs=True, ivf=True, probes=probes)
         assert st.stats().kernel_launches - l0 == 4              # query norms, score GEMM, selection, ONE scan
         probed = st.debug_probes(batch, probes)
+        read_by_batch = st.stats().last_rows_read
         rows_read = 0
         for i in range(batch):
             mine = probed[i][probed[i] >= 0]
@@ -200,7 +201,7 @@ def test_batched_ivf_ranks_centroids_on_tensor_cores(n, dim, lists, clusters, ba
             if clear:
                 one = st.search(qs[i], 10, all_docs=True, ivf=True, probes=probes)
                 assert np.array_equal(one[2][0], got[2][i]) and np.array_equal(one[1][0], got[1][i])
-        assert st.stats().last_rows_read == rows_read
+        assert read_by_batch == rows_read
         # the same batch kept off the tensor cores: the fp32 centroid scan, 8 queries per pass, ONE probe scan
         simt = st.search(qs, 10, all_docs=True, ivf=True, probes=probes, no_tensor=True)
         probed_simt = st.debug_probes(batch, probes)
