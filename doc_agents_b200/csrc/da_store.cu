@@ -71,7 +71,7 @@ constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr size_t kRecTrailer = 16;      // bytes after a rank's record block in a multi-process store: its overflow flag
 
 struct ChunkInfo { uint32_t slot; int32_t shard; uint32_t row; };
-struct DocInfo { Id16 id; int32_t shard; };
+struct DocInfo { Id16 id; int32_t shard; uint32_t rows; };   // rows = embeddings resident for this document
 
 template <typename T>
 struct DevBuf {   // grow-only device buffer
@@ -900,7 +900,7 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
     auto it = st->doc_slot_of.find(did);
     if (it == st->doc_slot_of.end()) {
         slot = (uint32_t)st->docs.size();
-        st->docs.push_back(DocInfo{did, -1});
+        st->docs.push_back(DocInfo{did, -1, 0});
         st->doc_slot_of.emplace(did, slot);
     } else slot = it->second;
     for (size_t i = 0; i < n; i++) {
@@ -908,6 +908,7 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
         auto c = st->chunks.find(cid);
         if (c == st->chunks.end()) { st->chunks.emplace(cid, ChunkInfo{slot, -1, kNoRow}); continue; }
         if (c->second.slot == slot) continue;
+        if (c->second.row != kNoRow) { st->docs[c->second.slot].rows--; st->docs[slot].rows++; }
         c->second.slot = slot;
         if (c->second.row != kNoRow) {   // the chunk already has a vector: move its row to the new document
             Shard &s = st->shards[c->second.shard];
@@ -1066,7 +1067,10 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
         CU(cudaStreamSynchronize(sh.stream));
         sh.n_rows += pending[s];
     }
-    for (size_t i = 0; i < n; i++) { info[i]->shard = tgt_shard[i]; info[i]->row = tgt_row[i]; }
+    for (size_t i = 0; i < n; i++) {
+        if (info[i]->row == kNoRow) st->docs[info[i]->slot].rows++;          // a new embedding (an overwrite keeps its row)
+        info[i]->shard = tgt_shard[i]; info[i]->row = tgt_row[i];
+    }
     return DA_OK;
 }
 
@@ -1526,7 +1530,11 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
             da::synth_doc_id(p->seed_ids, d, id);
             const Id16 k = load_id(id);
             st->doc_slot_of.emplace(k, (uint32_t)(d - doc_lo));
-            st->docs.push_back(DocInfo{k, 0});
+            {
+                const uint64_t first = std::max<uint64_t>(p->row_lo, d * p->chunks_per_doc);
+                const uint64_t last = std::min<uint64_t>(p->row_lo + p->n_rows, (d + 1) * p->chunks_per_doc);
+                st->docs.push_back(DocInfo{k, 0, (uint32_t)(last - first)});
+            }
         }
     }
     for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
@@ -1615,6 +1623,18 @@ int da_store_debug_read_ivf(da_store *st, int32_t device_index, uint32_t *out_of
     if (out_offsets) CU(cudaMemcpy(out_offsets, s.ivf.offsets, (size_t)(L + 1) * 4, cudaMemcpyDeviceToHost));
     if (out_list_rows) CU(cudaMemcpy(out_list_rows, s.ivf.list_rows, (size_t)s.n_rows * 4, cudaMemcpyDeviceToHost));
     if (out_centroids) CU(cudaMemcpy(out_centroids, s.ivf.cent, (size_t)L * st->dim * 4, cudaMemcpyDeviceToHost));
+    return DA_OK;
+}
+
+int da_store_doc_rows(da_store *st, const uint8_t *doc_ids, size_t n_docs, uint32_t *out_rows)
+{
+    if (!st) return fail(DA_ERR_INVALID, "store is NULL");
+    if (n_docs && (!doc_ids || !out_rows)) return fail(DA_ERR_INVALID, "doc_ids/out_rows is NULL");
+    std::lock_guard<std::mutex> lock(st->mu);
+    for (size_t i = 0; i < n_docs; i++) {
+        auto it = st->doc_slot_of.find(load_id(doc_ids + 16 * i));
+        out_rows[i] = it == st->doc_slot_of.end() ? 0u : st->docs[it->second].rows;
+    }
     return DA_OK;
 }
 

@@ -205,6 +205,15 @@ class GpuStore:
             results.append(SearchResult(chunk, np.float32(out_scores[i]), summ))
         return results
 
+    def doc_rows(self, doc_ids) -> np.ndarray:
+        """Resident embeddings per document (0 = never given to this store): what a reader process checks before it
+        searches documents that another process embedded."""
+        d = np.ascontiguousarray(doc_ids, dtype=np.uint8).reshape(-1, 16) if not isinstance(doc_ids, (list, tuple)) \
+            else _ids_to_bytes(doc_ids)
+        out = np.zeros(d.shape[0], dtype=np.uint32)
+        _check(self._lib.da_store_doc_rows(self._h, _ptr(d), d.shape[0], out.ctypes.data if d.shape[0] else None))
+        return out
+
     # -- everything-exposed search on raw arrays -----------------------------------------
     def search(self, queries, k: int, doc_ids: np.ndarray | None = None, *, all_docs: bool = False,
                min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,

@@ -124,6 +124,12 @@ int da_store_bulk_load(da_store *st, const uint8_t *chunk_ids, const uint8_t *do
 int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *query,
                   int32_t dim, int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n);
 
+/* How many embeddings of each of n_docs documents are resident (0 = the store has never been given the document).
+ * No SQL counterpart; it is what lets a reader process notice that a document named by a request
+ * (document_ids is required: cmd/query/main.go:20-24) was embedded by ANOTHER process (the analysis agent:
+ * docker-compose.yml:87-128) and load it from Postgres before searching.  Host-side lookup, no GPU work. */
+int da_store_doc_rows(da_store *st, const uint8_t *doc_ids, size_t n_docs, uint32_t *out_rows);
+
 /* Flags of da_search_params. */
 #define DA_SEARCH_ALL_DOCS      0x1u  /* ignore doc_ids: every document is requested (bench roofline runs) */
 #define DA_SEARCH_READ_ALL_ROWS 0x2u  /* doc mask as a predicate: read every row even if its document is

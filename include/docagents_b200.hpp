@@ -95,9 +95,24 @@ public:
         check(da_store_save_embeddings(h_, ids.data(), vecs.data(), embs.size(), (int32_t)dim));
     }
 
-    // Store.TopK (store.go:66; postgres.go:218-285).  An empty result is the reference's nil slice.
+    // Resident embeddings per document (0 = never given to this store): the reader-side check of the Go decorator
+    // (integration/gpustore.go: ensureResident) before it searches documents another process embedded.
+    std::vector<uint32_t> DocRows(const std::vector<UUID> &docIDs)
+    {
+        std::vector<uint8_t> docs(docIDs.size() * 16);
+        for (size_t i = 0; i < docIDs.size(); i++) memcpy(&docs[16 * i], docIDs[i].data(), 16);
+        std::vector<uint32_t> out(docIDs.size());
+        check(da_store_doc_rows(h_, docs.data(), docIDs.size(), out.data()));
+        return out;
+    }
+
+    // Store.TopK (store.go:66; postgres.go:218-285).  An empty result is the reference's nil slice.  An empty
+    // query vector is an error (the reference sends '[]' to pgvector, which rejects it); an empty document list
+    // matches nothing (document_id = ANY('{}'), postgres.go:239).
     std::vector<SearchResult> TopK(const std::vector<UUID> &docIDs, const Vector &vector, int k)
     {
+        if (vector.empty()) throw StoreError(DA_ERR_DIM, "vector must have at least 1 dimension");
+        if (docIDs.empty()) return {};
         std::vector<uint8_t> docs(docIDs.size() * 16);
         for (size_t i = 0; i < docIDs.size(); i++) memcpy(&docs[16 * i], docIDs[i].data(), 16);
         const int kk = k > 0 ? k : 1;

@@ -11,7 +11,8 @@
 #include <cstdlib>
 
 extern "C" {
-struct orc_synth { uint64_t seed_data, seed_centroid, seed_query, seed_ids; uint32_t chunks_per_doc, n_clusters; int32_t cmul, nmul; };
+struct orc_synth { uint64_t seed_data, seed_centroid, seed_query, seed_ids; uint32_t chunks_per_doc, n_clusters; int32_t cmul, nmul;
+                   int32_t smul; uint32_t super_group; };
 void orc_gen_rows(const orc_synth *, uint64_t, uint64_t, int, float *);
 void orc_gen_query(const orc_synth *, uint64_t, uint32_t, int, float *);
 void orc_chunk_id(const orc_synth *, uint64_t, uint8_t *);
@@ -30,7 +31,7 @@ using namespace docagents;
 
 int main()
 {
-    const orc_synth S{0xD0C5EED, 0xC0FFEE, 0xBEEF, 0x1D5EED, 200, 1024, 2, 1};
+    const orc_synth S{0xD0C5EED, 0xC0FFEE, 0xBEEF, 0x1D5EED, 200, 1024, 2, 1, 0, 0};
     const int n = 200, dim = 3072;                          // BASELINE configs[0]
     std::vector<float> mat((size_t)n * dim), q(dim);
     orc_gen_rows(&S, 0, n, dim, mat.data());
@@ -50,6 +51,9 @@ int main()
 
     st.SaveEmbeddings({});                                   // empty slice: no-op, no error
     EXPECT(st.TopK({doc}, q, 5).empty());                    // nothing stored: nil slice, no error
+    // what the Go decorator asks before it searches: a document this process was never given has no rows
+    // (it was embedded by the analysis agent, another process) and is loaded from Postgres first
+    EXPECT(st.DocRows({doc, other}) == (std::vector<uint32_t>{0, 0}));
 
     std::vector<Embedding> embs(n);
     for (int i = 0; i < n; i++) {
@@ -58,6 +62,8 @@ int main()
         embs[i].Model = "text-embedding-3-large";
     }
     st.SaveEmbeddings(embs);                                 // once, with all chunks of the document
+
+    EXPECT(st.DocRows({other, doc, doc}) == (std::vector<uint32_t>{0, (uint32_t)n, (uint32_t)n}));
 
     uint32_t o_rows[20]; float o_scores[20]; double o_dist[20];
     const int on = orc_topk(mat.data(), n, dim, nullptr, nullptr, q.data(), 5, 0.7, 0, 1, o_rows, o_scores, o_dist);
@@ -76,7 +82,14 @@ int main()
     EXPECT(st.TopK({}, q, 5).empty());                       // ANY('{}')
     EXPECT(st.TopK({other, doc, doc}, q, 20).size() == 20);  // API cap 20, duplicate ids harmless
 
+    EXPECT(st.TopK({doc}, q, 0).empty());                    // LIMIT 0
     bool threw = false;
+    try { st.TopK({doc}, Vector{}, 5); } catch (const StoreError &e) { threw = e.code == DA_ERR_DIM; }
+    EXPECT(threw);                                           // the reference sends '[]', which pgvector rejects: an error, not nil
+    threw = false;
+    try { st.TopK({doc}, q, -1); } catch (const StoreError &e) { threw = e.code == DA_ERR_INVALID; }
+    EXPECT(threw);                                           // LIMIT must not be negative
+    threw = false;
     try { st.TopK({doc}, Vector(q.begin(), q.begin() + 1536), 5); } catch (const StoreError &e) { threw = e.code == DA_ERR_DIM; }
     EXPECT(threw);                                           // dimension mismatch -> error (-> HTTP 500)
     threw = false;
@@ -92,6 +105,7 @@ int main()
     st.SaveEmbeddings({up});
     res = st.TopK({doc}, q, 5);
     EXPECT(res.size() == 5 && res[0].ChunkID == chunks[o_rows[1]].ID);
+    EXPECT(st.DocRows({doc})[0] == (uint32_t)n);             // an overwrite adds no row
     printf("contract_test ok\n");
     return 0;
 }
