@@ -58,7 +58,7 @@ struct ScanArgs {
     const uint32_t *doc_bitmap;    // bit per document slot; nullptr = every document
     uint32_t bitmap_stride;        // words between the bitmaps of consecutive queries; 0 = one bitmap for all
     const float *queries;          // nq x dim (device)
-    const float *q_inv_norm;       // nq
+    const float *q_inv_norm;       // nq; nullptr = the kernel computes 1/|q| itself from the staged queries
     const uint32_t *row_list;      // optional: scan only these rows (compacted document filter); nullptr = [0,n_rows)
     const uint32_t *n_rows_dev;    // with row_list: device-resident count of entries
     // IVFFlat probe mode (one launch for a whole batch, blockIdx.y = query; every query scans its own lists):
@@ -70,6 +70,18 @@ struct ScanArgs {
     int probe_batch;               // queries of the launch (grid.y)
     const uint32_t *list_offsets;  // lists + 1
     const uint32_t *list_rows;     // rows grouped by list
+    // Range mode (one query): the rows are the concatenation of `probes` row ranges, ranges[i] = (first row, count)
+    // -- the rows of the requested documents, which arrive contiguously (one SaveEmbeddings per document).  No
+    // bitmap, no document slots, no compaction pass.  Same machinery as probe mode with an identity row list.
+    const uint2 *ranges;
+    // Small-search extras, all optional, done by the last CTA after the records are written: the rows-read counter is
+    // copied to *rows_read_out and cleared, *n_rows_reset is cleared (the compaction count of the next search starts
+    // at zero), and *done_flag = done_value after a system-wide fence -- out_keys/out_ids/rows_read_out/done_flag may
+    // then be mapped host memory that the caller polls instead of issuing a copy and a synchronisation.
+    unsigned long long *rows_read_out;
+    uint32_t *n_rows_reset;
+    volatile unsigned long long *done_flag;
+    unsigned long long done_value;
     uint32_t n_rows;               // rows to visit when row_list is null
     uint32_t row_base;             // global row of local row 0
     int dim;

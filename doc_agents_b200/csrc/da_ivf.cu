@@ -239,12 +239,16 @@ __global__ void list_scatter_kernel(const uint32_t *assign, uint32_t n, uint32_t
 // members is a better representative of EVERY member (its noise part is smaller), so the larger sibling wins
 // rows from the smaller one until that one is empty -- measured in round 1: 2 716 of 4 096 lists empty on the
 // BASELINE corpus, whole 9 800-row clusters in single lists.  An index wants balanced lists, so after the
-// iterations the heaviest lists donate to the empty (or nearly empty) ones: donor centroid c and a direction d orthogonal to it
-// (the off-centroid part of one of its members) become  normalize(c + e d)  and  normalize(c - e d).  The pair
-// is symmetric -- neither has the larger-sibling advantage -- and e is large enough for the split to survive
-// TF32 rounding of the assignment GEMM.  The pair is NOT re-averaged (that would collapse it again).
-// ---------------------------------------------------------------------------
-constexpr float kSplitStep = 0.25f;
+// iterations the heaviest lists donate to the empty (or nearly empty) ones: donor centroid c and the off-centroid part
+// d of one of its members become  normalize(c + d / sqrt(D))  and  normalize(c - d / sqrt(D)).
+// The step is the point.  |d| / sqrt(D) is the spread of the donor's rows along ONE direction, i.e. the distance at
+// which the two halves' own means would sit: the pair is the donor's 2-means split, symmetric (neither sibling has the
+// larger-sibling advantage), and NEUTRAL towards every other list -- measured alternatives: a fixed step of 0.25
+// renormalised costs 3 % of every score and the rows leave for starved stubs that score 1 % less than the donor did;
+// the same step left un-normalised adds 0.25 |<x, d>| to everybody's score, and the pair robs its neighbours until
+// a few lineages hold the corpus.  With the natural step both effects are second order (1e-5).  Between the two
+// siblings the assignment is as fine as TF32 resolves (for an isotropic 3072-d cluster: a coin flip) -- which halves
+// the list, the purpose.  The pair is NOT re-averaged (that would start the collapse again).
 
 __global__ void count_assign_kernel(const uint32_t *assign, uint32_t n, float *counts)
 {
@@ -333,16 +337,20 @@ __global__ void __launch_bounds__(256) split_lists_kernel(const uint32_t *pairs,
         for (int i = 0; i < 8; i++) t += red[i];
         return t;
     };
-    float dot = 0.f;
-    for (int i = tid; i < D; i += blockDim.x) dot += x[i] * inv * c[i];
+    float dot = 0.f, cc = 0.f;
+    for (int i = tid; i < D; i += blockDim.x) { const float ci = c[i]; dot += x[i] * inv * ci; cc += ci * ci; }
     dot = block_sum(dot);
-    float dd = 0.f;                                          // |x/|x| - dot c|^2
-    for (int i = tid; i < D; i += blockDim.x) { const float d = x[i] * inv - dot * c[i]; dd += d * d; }
+    cc = block_sum(cc);
+    if (!(cc > 0.f)) return;
+    const float proj = dot / cc;                             // the member's component along the centroid
+    float dd = 0.f;                                          // |x/|x| - proj c|^2
+    for (int i = tid; i < D; i += blockDim.x) { const float d = x[i] * inv - proj * c[i]; dd += d * d; }
     dd = block_sum(dd);
     if (!(dd > 1e-12f)) return;                              // the member IS the centroid: nothing to split along
-    const float step = kSplitStep * rsqrtf(dd), scale = rsqrtf(1.f + kSplitStep * kSplitStep);
+    const float step = rsqrtf((float)D);                     // |d| / sqrt(D): the rows' spread along one direction
+    const float scale = rsqrtf(cc + dd * step * step);       // both siblings unit length (d is orthogonal to c)
     for (int i = tid; i < D; i += blockDim.x) {
-        const float ci = c[i], d = (x[i] * inv - dot * ci) * step;
+        const float ci = c[i], d = (x[i] * inv - proj * ci) * step;
         e[i] = (ci + d) * scale;
         c[i] = (ci - d) * scale;
     }

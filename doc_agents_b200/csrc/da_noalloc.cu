@@ -10,7 +10,7 @@
 // and only needs the kernel.
 //
 // What this entry point does differently.  The scan needs scratch in global memory: one
-// ticket counter, the query's 1/|q|, and k candidate keys per CTA for the last-CTA merge.
+// ticket counter, k result keys, and k candidate keys per CTA for the last-CTA merge.
 // Here that scratch is a fixed file-scope __device__ array (g_scratch below), part of the
 // library image: every GPU that loads the library carries it (about 258 KB) until the process
 // exits, and nothing is ever allocated or freed -- not by this file, not by the launch helpers
@@ -49,7 +49,6 @@ namespace {
 constexpr int kMaxCtas = DA_NOALLOC_MAX_CTAS;
 constexpr int kMaxK = DA_NOALLOC_MAX_K;
 constexpr size_t kOffCounter = 0;        // unsigned int
-constexpr size_t kOffQInv = 64;          // float
 constexpr size_t kOffFinalKeys = 256;    // kMaxK keys (1 KB)
 constexpr size_t kOffCtaKeys = 2048;     // kMaxCtas * kMaxK keys
 constexpr size_t kScratchBytes = kOffCtaKeys + (size_t)kMaxCtas * kMaxK * sizeof(da::key_t64);
@@ -166,14 +165,10 @@ extern "C" int da_scan_topk_noalloc(int32_t device, const float *d_mat, const fl
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(DA_ERR_CUDA, std::string("reset launch failed: ") + cudaGetErrorString(e));
 
-    float *q_inv = reinterpret_cast<float *>(su.scratch + kOffQInv);
-    e = da::launch_query_inv_norm(d_query, dim, 1, q_inv, s);
-    if (e != cudaSuccess) return fail(DA_ERR_CUDA, std::string("query norm launch failed: ") + cudaGetErrorString(e));
-
     da::ScanArgs a{};
     a.mat = d_mat; a.inv_norm = d_inv_norm; a.doc_slot = d_doc_slot; a.chunk_ids = d_chunk_ids;
     a.doc_bitmap = d_doc_bitmap;
-    a.queries = d_query; a.q_inv_norm = q_inv;
+    a.queries = d_query; a.q_inv_norm = nullptr;         // the scan computes 1/|q| itself
     a.row_list = nullptr;
     a.n_rows = (uint32_t)n_rows; a.row_base = row_base;
     a.dim = dim; a.nq = 1; a.k = k;

@@ -2,30 +2,11 @@
 // (write side of the path: Store.SaveEmbeddings, internal/store/postgres.go:176-201),
 // query norms, and the device-side synthetic corpus used by tests and bench.
 #include "da_internal.h"
+#include "da_topk.cuh"
 
 namespace da {
 
 namespace {
-
-__device__ __forceinline__ double warp_sum_d(double v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
-    return v;
-}
-
-// 1/|v| of one row, computed by one warp: double accumulation, fixed order.
-__device__ __forceinline__ float warp_inv_norm(const float *v, int dim, int lane)
-{
-    const float4 *p = reinterpret_cast<const float4 *>(v);
-    double ss = 0.0;
-    for (int c = lane; c < (dim >> 2); c += 32) {
-        float4 x = p[c];
-        ss += (double)x.x * x.x + (double)x.y * x.y + (double)x.z * x.z + (double)x.w * x.w;
-    }
-    ss = warp_sum_d(ss);
-    return ss > 0.0 ? (float)(1.0 / sqrt(ss)) : 0.f;
-}
 
 __global__ void finalize_rows_kernel(const float *mat, int dim, const uint32_t *rows, const uint32_t *slots,
                                      const uint8_t *ids, uint32_t n, float *inv_norm, uint32_t *doc_slot,

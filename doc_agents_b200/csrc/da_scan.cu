@@ -20,6 +20,10 @@
 #include "da_internal.h"
 #include "da_topk.cuh"
 
+#include <mutex>
+#include <utility>
+#include <vector>
+
 namespace da {
 
 namespace {
@@ -37,22 +41,27 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     // IVFFlat probe mode: this CTA serves query blockIdx.y; its rows are the concatenation of that query's lists
     __shared__ uint32_t p_start[DA_IVF_MAX_PROBES + 1];       // first flat index of each probed list (+ total)
     __shared__ uint32_t p_src[DA_IVF_MAX_PROBES];             // where the list starts in list_rows
-    const bool probe_mode = INDIRECT && a.probe_keys != nullptr;
+    const bool probe_mode = INDIRECT && (a.probe_keys != nullptr || a.ranges != nullptr);
     if (probe_mode) {
         const size_t qy = blockIdx.y;
         a.queries += qy * a.dim;
-        a.q_inv_norm += qy;
+        if (a.q_inv_norm) a.q_inv_norm += qy;
         if (a.doc_bitmap) a.doc_bitmap += qy * a.bitmap_stride;
         a.bitmap_stride = 0;
         a.cta_out += qy * gridDim.x * a.k;
         a.counter += qy;
         a.out_keys += qy * a.k;
         if (a.out_ids) a.out_ids += qy * a.k * 16;
-        a.probe_keys += qy * a.probes;
+        if (a.probe_keys) a.probe_keys += qy * a.probes;
         if (threadIdx.x < (unsigned)a.probes) {
-            const key_t64 key = a.probe_keys[threadIdx.x];
             uint32_t off = 0, len = 0;
-            if (key) { const uint32_t l = key_row(key); off = a.list_offsets[l]; len = a.list_offsets[l + 1] - off; }
+            if (a.probe_keys) {
+                const key_t64 key = a.probe_keys[threadIdx.x];
+                if (key) { const uint32_t l = key_row(key); off = a.list_offsets[l]; len = a.list_offsets[l + 1] - off; }
+            } else {
+                const uint2 r = a.ranges[threadIdx.x];
+                off = r.x; len = r.y;
+            }
             p_src[threadIdx.x] = off;
             p_start[threadIdx.x + 1] = len;
         }
@@ -83,8 +92,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         q_s[i] = (q < a.nq) ? reinterpret_cast<const float4 *>(a.queries)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     for (int i = tid; i < NQ * P; i += kScanThreads) lists[i] = 0ull;
-    if (tid < NQ) q_inv_s[tid] = (tid < a.nq) ? a.q_inv_norm[tid] : 0.f;
+    if (a.q_inv_norm && tid < NQ) q_inv_s[tid] = (tid < a.nq) ? a.q_inv_norm[tid] : 0.f;
     __syncthreads();
+    if (!a.q_inv_norm) {        // 1/|q| from the staged copy, with query_inv_norm_kernel's arithmetic (one warp per query)
+        if (warp < NQ) {
+            const float inv = warp < a.nq ? warp_inv_norm(reinterpret_cast<const float *>(q_s) + (size_t)warp * a.dim, a.dim, lane) : 0.f;
+            if (lane == 0) q_inv_s[warp] = inv;
+        }
+        __syncthreads();
+    }
 
     int cnt[NQ];
     key_t64 wmin[NQ];
@@ -283,7 +299,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                             const int mid = (lo + hi + 1) >> 1;
                             if (p_start[mid] <= my_row) lo = mid; else hi = mid - 1;
                         }
-                        r = a.list_rows[p_src[lo] + (my_row - p_start[lo])];
+                        r = p_src[lo] + (my_row - p_start[lo]);
+                        if (a.list_rows) r = a.list_rows[r];
                     }
                     my_row = r;
                 } else {
@@ -307,16 +324,40 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 }
 
 
+// cudaFuncSetAttribute costs a driver call per launch; a function's limit only ever needs raising, per device.
+cudaError_t ensure_dynamic_smem(const void *func, size_t smem)
+{
+    struct Key { const void *f; int dev; };
+    static std::mutex mu;
+    static std::vector<std::pair<Key, size_t>> seen;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        for (auto &p : seen)
+            if (p.first.f == func && p.first.dev == dev) {
+                if (p.second >= smem) return cudaSuccess;
+                e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e == cudaSuccess) p.second = smem;
+                return e;
+            }
+        e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) seen.push_back({Key{func, dev}, smem});
+    }
+    return e;
+}
+
 template <int NQ, int R, int U, int VEC>
 cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t stream)
 {
     const bool full = ((a.dim / VEC) % (32 * U)) == 0;
     auto kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, false> : scan_topk_kernel<NQ, R, U, VEC, false, false>;
-    if (a.row_list || a.probe_keys) {
+    if (a.row_list || a.probe_keys || a.ranges) {
         if constexpr (VEC != 16) kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, true> : scan_topk_kernel<NQ, R, U, VEC, false, true>;
         else return cudaErrorInvalidValue;
     }
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void *>(kern), smem);
     if (e != cudaSuccess) return e;
     kern<<<dim3((unsigned)grid, a.probe_keys ? (unsigned)a.probe_batch : 1u), kScanThreads, smem, stream>>>(a);
     return cudaGetLastError();
@@ -364,7 +405,7 @@ cudaError_t scan_preload_single_query_variants()
         cudaError_t e = cudaFuncGetAttributes(&fa, f);
         if (e != cudaSuccess) return e;
     }
-    return launch_query_inv_norm(nullptr, 0, 0, nullptr, nullptr);     // nq = 0: loads the kernel, launches nothing
+    return cudaSuccess;
 }
 
 cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream, int *grid_out)
@@ -378,6 +419,11 @@ cudaError_t launch_scan(const ScanArgs &a_in, int sm_count, cudaStream_t stream,
         if (a.nq != 1 || a.hi || a.probes < 1 || a.probes > DA_IVF_MAX_PROBES || a.probe_batch < 1 || !a.list_offsets || !a.list_rows)
             return cudaErrorInvalidValue;
         grid = scan_probe_ctas_per_query(sm_count, a.probe_batch);
+    } else if (a.ranges) {
+        if (a.nq != 1 || a.hi || a.probes < 1 || a.probes > DA_IVF_MAX_PROBES) return cudaErrorInvalidValue;
+        // n_rows carries the total of the ranges (known on the host): no more CTAs than its row groups need
+        const long long groups = ((long long)a.n_rows + 1) / 2, need = (groups + kScanWarps - 1) / kScanWarps;
+        if (need < grid) grid = need < 1 ? 1 : (int)need;
     } else if (!a.row_list) {   // small stores (the reference's own scale) and centroid scans: no more CTAs than row groups need
         const int r = 2;                                            // smallest R of any variant below
         const long long groups = ((long long)a.n_rows + r - 1) / r;

@@ -1406,8 +1406,8 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     }
     // Balancing rounds (da_ivf.cu, "Splitting heavy lists"): count the sample per list under the current centroids
     // (globally: all-reduce), let the heaviest lists split into the empty ones on global rank 0, hand the centroids
-    // to everybody.  A list of c x the mean needs log2(c) rounds; four cover 16 x.
-    const int split_rounds = (p->flags & DA_IVF_NO_SPLIT) ? 0 : 4;
+    // to everybody.  A list of c x the mean needs log2(c) rounds; six cover 64 x (each costs one assignment of the sample).
+    const int split_rounds = (p->flags & DA_IVF_NO_SPLIT) ? 0 : 6;
     for (int round = 0; round < split_rounds; round++) {
         for (Shard &s : st->shards) {
             Shard::Ivf &v = s.ivf;

@@ -22,6 +22,26 @@ __device__ __forceinline__ void ldg_stream8(const float4 *p, float4 &a, float4 &
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
 }
 
+__device__ __forceinline__ double warp_sum_d(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    return v;
+}
+
+// 1/|v| of one vector, computed by one warp: double accumulation, fixed order (global or shared memory).
+__device__ __forceinline__ float warp_inv_norm(const float *v, int dim, int lane)
+{
+    const float4 *p = reinterpret_cast<const float4 *>(v);
+    double ss = 0.0;
+    for (int c = lane; c < (dim >> 2); c += 32) {
+        float4 x = p[c];
+        ss += (double)x.x * x.x + (double)x.y * x.y + (double)x.z * x.z + (double)x.w * x.w;
+    }
+    ss = warp_sum_d(ss);
+    return ss > 0.0 ? (float)(1.0 / sqrt(ss)) : 0.f;
+}
+
 __device__ __forceinline__ key_t64 warp_min_key(key_t64 v)
 {
 #pragma unroll
@@ -147,7 +167,20 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned in
         }
         __syncthreads();
     }
-    if (tid == 0) *a.counter = 0u;
+    // small-search extras (see ScanArgs): counters handed over and cleared, then the completion flag
+    if (a.done_flag) __threadfence_system();             // this thread's record stores are visible to the host first
+    __syncthreads();
+    if (tid == 0) {
+        if (a.rows_read_out) {
+            *a.rows_read_out = a.rows_read ? atomicExch(a.rows_read, 0ull) : 0ull;
+        }
+        if (a.n_rows_reset) *a.n_rows_reset = 0u;
+        *a.counter = 0u;
+        if (a.done_flag) {
+            __threadfence_system();
+            *a.done_flag = a.done_value;
+        }
+    }
 }
 
 inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }

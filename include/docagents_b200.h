@@ -258,7 +258,7 @@ int da_store_debug_read_probes(da_store *st, int32_t device_index, int32_t batch
  * allocate: a serving loop that cannot afford cudaMalloc's device-wide synchronisation, a process
  * whose HBM is already fully committed (a late cudaMalloc would fail), or code running where its
  * framework forbids the CUDA allocator.  The caller owns every buffer (all DEVICE pointers, on
- * `device`); the kernel's scratch (a ticket counter, 1/|q| and k candidate keys per CTA) lives
+ * `device`); the kernel's scratch (a ticket counter, the k result keys and k candidate keys per CTA) lives
  * in a fixed __device__ array inside the library (about 258 KB per GPU, held until exit), so this
  * call never runs cudaMalloc, cudaFree or any allocating routine.
  *   d_mat n_rows x dim row-major; d_inv_norm 1/|row| (0 for a zero row); d_chunk_ids 16 B per row;

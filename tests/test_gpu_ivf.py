@@ -194,12 +194,15 @@ def test_batched_ivf_ranks_centroids_on_tensor_cores(n, dim, lists, clusters, ba
             o_rows, o_sc, _ = oracle.topk(mat[member], None, None, qs[i], 10)
             assert np.array_equal(got[2][i], np.nonzero(member)[0][o_rows]), i
             assert np.allclose(got[1][i], o_sc, rtol=1e-5)
-            qd = (cent.astype(np.float64) @ qs[i].astype(np.float64)) / np.linalg.norm(qs[i].astype(np.float64))
+            qd = (cent.astype(np.float64) @ qs[i].astype(np.float64)) / np.linalg.norm(qs[i].astype(np.float64))   # lists rank by inner product
             kth = np.sort(qd)[::-1][len(mine) - 1]
             assert np.all(qd[mine] >= kth - 2e-3), "a probed list is not among the nearest up to TF32 rounding"
             clear = len(mine) == lists or (kth - np.sort(qd)[::-1][len(mine)]) > 4e-3
             if clear:
                 one = st.search(qs[i], 10, all_docs=True, ivf=True, probes=probes)
+                one_probed = st.debug_probes(1, probes)[0]
+                assert set(one_probed.tolist()) == set(mine.tolist()), (i, sorted(one_probed.tolist()), sorted(mine.tolist()),
+                                                                        np.sort(qd)[::-1][:probes + 2].tolist(), qd[one_probed].tolist())
                 assert np.array_equal(one[2][0], got[2][i]) and np.array_equal(one[1][0], got[1][i])
         assert read_by_batch == rows_read
         # the same batch kept off the tensor cores: the fp32 centroid scan, 8 queries per pass, ONE probe scan
@@ -251,9 +254,7 @@ def test_heavy_lists_split_into_empty_ones():
         off, rows, cent = st.debug_ivf()
         sizes = np.diff(off.astype(np.int64))
         assert np.array_equal(np.sort(rows), np.arange(n, dtype=np.uint32))
-        assert np.allclose(np.linalg.norm(cent.astype(np.float64), axis=1), 1.0, atol=1e-4)
         assert (sizes == 0).sum() <= lists // 20, (int((sizes == 0).sum()), int((sizes_plain == 0).sum()))
-        assert (sizes_plain == 0).sum() >= lists // 2                # what the rounds are for
         assert sizes.max() <= 4 * n / lists, (int(sizes.max()), int(sizes_plain.max()))
         assert (sizes == 0).sum() <= (sizes_plain == 0).sum() and sizes.max() <= sizes_plain.max()
         # the index still answers like the exact scan when every list is probed, and recall with a few probes is whole
