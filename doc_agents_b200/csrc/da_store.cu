@@ -19,10 +19,16 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <atomic>
+#include <memory>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
+
+#include <immintrin.h>
 
 namespace {
 
@@ -71,7 +77,25 @@ constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr size_t kRecTrailer = 16;      // bytes after a rank's record block in a multi-process store: its overflow flag
 
 struct ChunkInfo { uint32_t slot; int32_t shard; uint32_t row; };
-struct DocInfo { Id16 id; int32_t shard; uint32_t rows; };   // rows = embeddings resident for this document
+// rows = embeddings resident for this document.  `ranges` = where they are (first local row, count) on the document's
+// shard: one SaveEmbeddings call carries all chunks of one document (cmd/analysis/main.go:98-106), so a document is
+// one run of rows, and a filtered search can name its rows by a handful of ranges instead of testing every row of
+// the store.  `fragmented`: the ranges are not kept (too many pieces, a chunk moved between documents, rows spread
+// over several shards) and the document is found through the per-row document slots.
+constexpr size_t kMaxDocRanges = 8;
+struct DocInfo {
+    Id16 id; int32_t shard; uint32_t rows;
+    bool fragmented = false;
+    std::vector<std::pair<uint32_t, uint32_t>> ranges;
+    void add_row(uint32_t row)
+    {
+        if (fragmented) return;
+        if (!ranges.empty() && ranges.back().first + ranges.back().second == row) { ranges.back().second++; return; }
+        if (ranges.size() >= kMaxDocRanges) { fragmented = true; ranges.clear(); ranges.shrink_to_fit(); return; }
+        ranges.emplace_back(row, 1u);
+    }
+    void fragment() { fragmented = true; ranges.clear(); ranges.shrink_to_fit(); }
+};
 
 template <typename T>
 struct DevBuf {   // grow-only device buffer
@@ -180,10 +204,28 @@ void free_ivf(Shard &s)
     v = Shard::Ivf();
 }
 
+// One small search in flight: its own stream, request block (query + row ranges, one host-to-device copy), scan
+// scratch, and a result block in MAPPED host memory that the scan's last CTA writes directly, followed by a
+// completion word the caller polls -- no device-to-host copy, no stream synchronisation.  Concurrent TopK calls
+// (one goroutine per /api/query: cmd/query/main.go:34) each take a slot, so they overlap instead of queueing.
+struct Slot {
+    cudaStream_t stream = nullptr;
+    uint8_t *h_req = nullptr, *d_req = nullptr;          // [dim floats][kMaxRanges x (first row, count)]
+    uint8_t *h_out = nullptr, *d_out = nullptr;          // mapped: [k ids of 16 B][k keys][rows read][completion word]
+    da::key_t64 *d_cta = nullptr;
+    unsigned int *d_counter = nullptr;
+    unsigned long long *d_rows_read = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;            // resident timing only
+    unsigned long long ticket = 0;
+};
+constexpr int kMaxRanges = DA_IVF_MAX_PROBES;            // the scan's range table
+constexpr int kMaxSlots = 8;
+constexpr size_t kSlotOutBytes = (size_t)DA_MAX_K * 24 + 16;
+
 }  // namespace
 
 struct da_store {
-    std::mutex mu;
+    std::shared_mutex mu;          // searches of the small-search path share it; everything else takes it alone
     int dim = 0;
     float min_sim = DA_DEFAULT_MIN_SIMILARITY;
     int world = 1, rank = 0, total_ranks = 1;
@@ -213,6 +255,13 @@ struct da_store {
     bool split16 = false;          // split-plane resident format (DA_STORE_SPLIT16)
     bool q8 = false;               // int8 sidecar next to the fp32 rows (DA_STORE_Q8_SIDECAR)
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
+    // small-search path (single shard, single process): slots and the statistics they update
+    std::mutex slot_mu;
+    std::condition_variable slot_cv;
+    std::vector<std::unique_ptr<Slot>> slots;
+    std::vector<Slot *> free_slots;
+    std::mutex stats_mu;
+    uint64_t fast_searches = 0;
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
 
@@ -243,6 +292,66 @@ void free_shard(Shard &s)
     if (s.ev_done) cudaEventDestroy(s.ev_done);
     if (s.stream) cudaStreamDestroy(s.stream);
     s = Shard();
+}
+
+void free_slot(Slot &sl)
+{
+    if (sl.stream) cudaStreamSynchronize(sl.stream);
+    cudaFree(sl.d_req); cudaFree(sl.d_cta); cudaFree(sl.d_counter); cudaFree(sl.d_rows_read);
+    if (sl.h_req) cudaFreeHost(sl.h_req);
+    if (sl.h_out) cudaFreeHost(sl.h_out);
+    if (sl.ev0) cudaEventDestroy(sl.ev0);
+    if (sl.ev1) cudaEventDestroy(sl.ev1);
+    if (sl.stream) cudaStreamDestroy(sl.stream);
+    sl = Slot();
+}
+
+// Called with the shard's device current.
+int make_slot(da_store *st, Slot &sl)
+{
+    const Shard &s = st->shards[0];
+    const size_t req = (size_t)st->dim * 4 + (size_t)kMaxRanges * 8;
+    CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
+    CU(cudaMallocHost((void **)&sl.h_req, req));
+    CU(cudaMalloc((void **)&sl.d_req, req));
+    CU(cudaHostAlloc((void **)&sl.h_out, kSlotOutBytes, cudaHostAllocMapped));
+    CU(cudaHostGetDevicePointer((void **)&sl.d_out, sl.h_out, 0));
+    memset(sl.h_out, 0, kSlotOutBytes);
+    CU(cudaMalloc((void **)&sl.d_cta, (size_t)da::scan_grid_for(s.sm_count) * DA_MAX_K * sizeof(da::key_t64)));
+    CU(cudaMalloc((void **)&sl.d_counter, sizeof(unsigned int)));
+    CU(cudaMalloc((void **)&sl.d_rows_read, sizeof(unsigned long long)));
+    CU(cudaMemsetAsync(sl.d_counter, 0, sizeof(unsigned int), sl.stream));
+    CU(cudaMemsetAsync(sl.d_rows_read, 0, sizeof(unsigned long long), sl.stream));
+    CU(cudaEventCreate(&sl.ev0)); CU(cudaEventCreate(&sl.ev1));
+    CU(cudaStreamSynchronize(sl.stream));
+    return DA_OK;
+}
+
+// A free slot, a new one while fewer than kMaxSlots exist, else the next one to be released.
+Slot *acquire_slot(da_store *st, int *rc)
+{
+    std::unique_lock<std::mutex> lk(st->slot_mu);
+    for (;;) {
+        if (!st->free_slots.empty()) {
+            Slot *sl = st->free_slots.back();
+            st->free_slots.pop_back();
+            return sl;
+        }
+        if ((int)st->slots.size() < kMaxSlots) {
+            std::unique_ptr<Slot> sl(new Slot());
+            *rc = make_slot(st, *sl);
+            if (*rc != DA_OK) { free_slot(*sl); return nullptr; }
+            st->slots.push_back(std::move(sl));
+            return st->slots.back().get();
+        }
+        st->slot_cv.wait(lk);
+    }
+}
+
+void release_slot(da_store *st, Slot *sl)
+{
+    { std::lock_guard<std::mutex> lk(st->slot_mu); st->free_slots.push_back(sl); }
+    st->slot_cv.notify_one();
 }
 
 int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, bool q8)
@@ -538,8 +647,9 @@ int ivf_tc_min_batch()
     return env > 0 ? env : 8;
 }
 
-// Validate + stage the inputs of a search on every local shard.
-int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
+// What every search checks before anything is staged (the errors of the reference's statement: dimension mismatch,
+// negative LIMIT, NaN/Inf in the vector literal).
+int validate_search(const da_store *st, const da_search_params *p)
 {
     if (!p) return fail(DA_ERR_INVALID, "search params are NULL");
     if (p->struct_size != sizeof(da_search_params))
@@ -554,9 +664,28 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     if (ivf && st->ivf_lists == 0) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store (da_store_build_ivf)");
     const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
     if (!all_docs && p->n_docs && !p->doc_ids) return fail(DA_ERR_INVALID, "doc_ids is NULL with n_docs=%zu", p->n_docs);
+    // finite check on the raw bits: exponent all ones = Inf or NaN.  One branch-free pass (it vectorises), then the
+    // exact position only when something was found.
     const size_t nq_elems = (size_t)p->batch * st->dim;
-    for (size_t i = 0; i < nq_elems; i++)
-        if (!std::isfinite(p->queries[i])) return fail(DA_ERR_NONFINITE, "query element %zu is not finite", i);
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(p->queries);
+    uint32_t bad = 0;
+    for (size_t i = 0; i < nq_elems; i++) bad |= (uint32_t)((w[i] & 0x7F800000u) == 0x7F800000u);
+    if (bad)
+        for (size_t i = 0; i < nq_elems; i++)
+            if ((w[i] & 0x7F800000u) == 0x7F800000u) return fail(DA_ERR_NONFINITE, "query element %zu is not finite", i);
+    return DA_OK;
+}
+
+// Validate + stage the inputs of a search on every local shard.
+int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
+{
+    {
+        const int vrc = validate_search(st, p);
+        if (vrc != DA_OK) return vrc;
+    }
+    const bool ivf = (p->flags & DA_SEARCH_IVF) != 0;
+    const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
+    const size_t nq_elems = (size_t)p->batch * st->dim;
 
     pl.batch = p->batch; pl.k = p->k; pl.min_sim = p->min_similarity;
     pl.all_docs = all_docs; pl.read_all = (p->flags & DA_SEARCH_READ_ALL_ROWS) != 0;
@@ -778,6 +907,177 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     return DA_OK;
 }
 
+// ---------------------------------------------------------------------------
+// Small-search path: one query on a single-shard, single-process store -- the reference's own regime (one question,
+// 1..16 documents: cmd/query/main.go:20-24) and the headline single-query scan.  One host-to-device copy (query +
+// row ranges), ONE kernel (the scan computes 1/|q| itself and walks the requested documents' row ranges: no bitmap,
+// no document slots, no compaction pass), results written by the last CTA into mapped host memory and picked up by
+// polling a completion word.  Calls hold the store's lock SHARED and each uses its own slot, so they overlap.
+// ---------------------------------------------------------------------------
+struct FastPlan {
+    int k = 0;
+    float min_sim = 0.f;
+    bool ranged = false;        // false: every row of the shard (all documents requested)
+    int n_ranges = 0;
+    uint32_t total_rows = 0;    // rows the scan will read
+    bool nothing = false;       // no requested document holds a row: zero rows, as `= ANY('{}')`
+};
+
+bool fast_path_enabled()
+{
+    static const bool off = [] { const char *v = getenv("DA_NO_FAST_PATH"); return v && v[0] == '1'; }();
+    return !off;
+}
+
+// 1: eligible (fp and ranges filled), 0: not eligible (the general path answers), < 0: error.  Lock held (shared).
+int plan_fast(da_store *st, const da_search_params *p, FastPlan &fp, uint2 *ranges)
+{
+    if (!fast_path_enabled() || st->shards.size() != 1 || st->total_ranks != 1 || st->split16) return 0;
+    if (!p || p->struct_size != sizeof(da_search_params) || p->batch != 1 || p->doc_offsets) return 0;
+    if (p->flags & (DA_SEARCH_IVF | DA_SEARCH_READ_ALL_ROWS | DA_SEARCH_NO_COMPACT)) return 0;
+    const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
+    const bool q8_ok = st->q8 && !(p->flags & DA_SEARCH_NO_Q8);
+    if (all_docs && q8_ok) return 0;                       // the int8 sidecar scan reads a quarter of the bytes
+    const int vrc = validate_search(st, p);
+    if (vrc != DA_OK) return vrc;
+    const Shard &s = st->shards[0];
+    fp.k = p->k; fp.min_sim = p->min_similarity;
+    if (all_docs) {
+        fp.ranged = false; fp.total_rows = s.n_rows; fp.nothing = s.n_rows == 0;
+        return 1;
+    }
+    fp.ranged = true;
+    uint32_t seen_small[64];
+    size_t n_seen = 0, selected = 0;
+    std::vector<uint32_t> seen_big;
+    for (size_t i = 0; i < p->n_docs; i++) {
+        auto it = st->doc_slot_of.find(load_id(p->doc_ids + 16 * i));
+        if (it == st->doc_slot_of.end()) continue;          // unknown ids match nothing
+        const uint32_t slot = it->second;
+        bool dup = false;                                   // a repeated id is harmless (postgres.go:239)
+        for (size_t j = 0; j < n_seen && !dup; j++) dup = seen_small[j] == slot;
+        for (size_t j = 0; j < seen_big.size() && !dup; j++) dup = seen_big[j] == slot;
+        if (dup) continue;
+        if (n_seen < 64) seen_small[n_seen++] = slot; else seen_big.push_back(slot);
+        const DocInfo &d = st->docs[slot];
+        if (d.rows == 0) continue;
+        if (d.fragmented) return 0;
+        selected++;
+        for (const auto &r : d.ranges) {
+            if (fp.n_ranges == kMaxRanges) return 0;        // too many pieces for the range table: the bitmap paths
+            ranges[fp.n_ranges++] = make_uint2(r.first, r.second);
+            fp.total_rows += r.second;
+        }
+    }
+    if (q8_ok && selected * 4 >= st->docs.size() && selected > 0) return 0;   // most of the corpus: the sidecar scan pays
+    fp.nothing = fp.total_rows == 0;
+    return 1;
+}
+
+// Enqueue the H2D copy and the scan of one planned search on a slot.  `flag` = write the completion word.
+int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool upload, const float *query, const uint2 *ranges,
+                 bool flag, int *grid_out)
+{
+    Shard &s = st->shards[0];
+    const size_t qbytes = (size_t)st->dim * 4;
+    if (upload) {
+        memcpy(sl->h_req, query, qbytes);
+        if (fp.ranged) memcpy(sl->h_req + qbytes, ranges, (size_t)fp.n_ranges * 8);
+        CU(cudaMemcpyAsync(sl->d_req, sl->h_req, qbytes + (fp.ranged ? (size_t)fp.n_ranges * 8 : 0), cudaMemcpyHostToDevice, sl->stream));
+    }
+    da::ScanArgs a{};
+    a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
+    a.doc_bitmap = nullptr;
+    a.queries = reinterpret_cast<const float *>(sl->d_req); a.q_inv_norm = nullptr;
+    if (fp.ranged) { a.ranges = reinterpret_cast<const uint2 *>(sl->d_req + qbytes); a.probes = fp.n_ranges; a.probe_batch = 1; }
+    a.n_rows = fp.total_rows; a.row_base = s.row_base;
+    a.dim = st->dim; a.nq = 1; a.k = fp.k; a.min_sim = fp.min_sim; a.read_all = 0;
+    a.cta_out = sl->d_cta; a.counter = sl->d_counter;
+    a.out_ids = sl->d_out;
+    a.out_keys = reinterpret_cast<da::key_t64 *>(sl->d_out + (size_t)fp.k * 16);
+    a.rows_read = sl->d_rows_read;
+    a.rows_read_out = reinterpret_cast<unsigned long long *>(sl->d_out + kSlotOutBytes - 16);
+    if (flag) {
+        a.done_flag = reinterpret_cast<volatile unsigned long long *>(sl->d_out + kSlotOutBytes - 8);
+        a.done_value = sl->ticket;
+    }
+    CU(da::launch_scan(a, s.sm_count, sl->stream, grid_out));
+    return DA_OK;
+}
+
+// Wait for the completion word of the slot's current ticket.
+int wait_fast(Slot *sl)
+{
+    volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(sl->h_out + kSlotOutBytes - 8);
+    for (uint64_t spins = 1; *flag != sl->ticket; spins++) {
+        _mm_pause();
+        if ((spins & 0x3FFF) == 0) {               // now and then: did the stream fail, or finish without the word?
+            const cudaError_t q = cudaStreamQuery(sl->stream);
+            if (q == cudaSuccess) {
+                if (*flag == sl->ticket) break;
+                return fail(DA_ERR_CUDA, "the scan finished without delivering its result");
+            }
+            if (q != cudaErrorNotReady) return fail(DA_ERR_CUDA, "search failed on the device: %s", cudaGetErrorString(q));
+            if (spins > (1u << 20)) std::this_thread::yield();
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    return DA_OK;
+}
+
+// The whole small search.  Returns 1 when it answered, 0 when the general path must, < 0 on error.
+int search_fast(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids, float *out_scores, uint32_t *out_rows,
+                int32_t *out_n)
+{
+    std::shared_lock<std::shared_mutex> lock(st->mu);
+    FastPlan fp;
+    uint2 ranges[kMaxRanges];
+    const int pr = plan_fast(st, p, fp, ranges);
+    if (pr <= 0) return pr;
+    out_n[0] = 0;
+    if (fp.k == 0) return 1;
+    if (!out_chunk_ids || !out_scores) return fail(DA_ERR_INVALID, "output buffers are NULL");
+    const auto t0 = std::chrono::steady_clock::now();
+    uint64_t rows_read = 0;
+    int grid = 0;
+    if (!fp.nothing) {
+        Shard &s = st->shards[0];
+        CU(cudaSetDevice(s.device));
+        int rc = DA_OK;
+        Slot *sl = acquire_slot(st, &rc);
+        if (!sl) return rc;
+        sl->ticket++;
+        rc = enqueue_fast(st, sl, fp, true, p->queries, ranges, true, &grid);
+        if (rc == DA_OK) rc = wait_fast(sl);
+        if (rc != DA_OK) { cudaStreamSynchronize(sl->stream); release_slot(st, sl); return rc; }
+        const uint8_t *ids = sl->h_out;
+        const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(sl->h_out + (size_t)fp.k * 16);
+        int c = 0;
+        for (int i = 0; i < fp.k; i++) {
+            const da::key_t64 key = keys[i];
+            if (!key) break;
+            out_scores[c] = da::key_score(key);
+            if (out_rows) out_rows[c] = da::key_row(key);
+            memcpy(out_chunk_ids + (size_t)c * 16, ids + (size_t)i * 16, 16);
+            c++;
+        }
+        out_n[0] = c;
+        rows_read = *reinterpret_cast<const unsigned long long *>(sl->h_out + kSlotOutBytes - 16);
+        release_slot(st, sl);
+    }
+    const float ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    {
+        std::lock_guard<std::mutex> sl(st->stats_mu);
+        st->fast_searches++;
+        st->last_search_ms = ms; st->last_scan_ms = ms;         // host clock around copy + scan + pick-up on this path
+        st->last_rows_read = rows_read;
+        // the rows' vectors and 1/|row| (+ the range table); no document slots, no bitmap on this path
+        st->last_bytes = rows_read * ((uint64_t)st->dim * 4 + 4) + (uint64_t)fp.n_ranges * 8;
+        if (!fp.nothing) { st->launches++; st->scan_grid = grid; }
+    }
+    return 1;
+}
+
 }  // namespace
 
 namespace da {
@@ -886,6 +1186,8 @@ int da_store_create(const da_config *cfg, da_store **out)
 void da_store_destroy(da_store *st)
 {
     if (!st) return;
+    if (!st->shards.empty()) cudaSetDevice(st->shards[0].device);
+    for (auto &sl : st->slots) free_slot(*sl);
     for (Shard &s : st->shards) free_shard(s);
     delete st;
 }
@@ -894,13 +1196,13 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
 {
     if (!st || !doc_id) return fail(DA_ERR_INVALID, "store/doc_id is NULL");
     if (n && !chunk_ids) return fail(DA_ERR_INVALID, "chunk_ids is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     const Id16 did = load_id(doc_id);
     uint32_t slot;
     auto it = st->doc_slot_of.find(did);
     if (it == st->doc_slot_of.end()) {
         slot = (uint32_t)st->docs.size();
-        st->docs.push_back(DocInfo{did, -1, 0});
+        st->docs.push_back(DocInfo{did, -1, 0, false, {}});
         st->doc_slot_of.emplace(did, slot);
     } else slot = it->second;
     for (size_t i = 0; i < n; i++) {
@@ -908,7 +1210,10 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
         auto c = st->chunks.find(cid);
         if (c == st->chunks.end()) { st->chunks.emplace(cid, ChunkInfo{slot, -1, kNoRow}); continue; }
         if (c->second.slot == slot) continue;
-        if (c->second.row != kNoRow) { st->docs[c->second.slot].rows--; st->docs[slot].rows++; }
+        if (c->second.row != kNoRow) {
+            st->docs[c->second.slot].rows--; st->docs[slot].rows++;
+            st->docs[c->second.slot].fragment(); st->docs[slot].fragment();      // their rows are no longer whole runs
+        }
         c->second.slot = slot;
         if (c->second.row != kNoRow) {   // the chunk already has a vector: move its row to the new document
             Shard &s = st->shards[c->second.shard];
@@ -926,7 +1231,7 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
     if (n == 0) return DA_OK;                                   // postgres.go:177-179
     if (!chunk_ids || !vecs) return fail(DA_ERR_INVALID, "chunk_ids/vecs is NULL");
     if (dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, dim);
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
 
     // Validate everything before the store changes: the reference's statement is atomic.  Ids on the host,
     // vector elements on the device (staged, checked, and only then committed).
@@ -1068,7 +1373,10 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
         sh.n_rows += pending[s];
     }
     for (size_t i = 0; i < n; i++) {
-        if (info[i]->row == kNoRow) st->docs[info[i]->slot].rows++;          // a new embedding (an overwrite keeps its row)
+        if (info[i]->row == kNoRow) {                                        // a new embedding (an overwrite keeps its row)
+            st->docs[info[i]->slot].rows++;
+            st->docs[info[i]->slot].add_row(tgt_row[i]);
+        }
         info[i]->shard = tgt_shard[i]; info[i]->row = tgt_row[i];
     }
     return DA_OK;
@@ -1096,7 +1404,11 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
 {
     if (!st) return fail(DA_ERR_INVALID, "store is NULL");
     if (!out_n) return fail(DA_ERR_INVALID, "out_n is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    {
+        const int fr = search_fast(st, p, out_chunk_ids, out_scores, out_rows, out_n);     // one query, one shard: the short way
+        if (fr != 0) return fr < 0 ? fr : DA_OK;
+    }
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     Shard &s0 = st->shards[0];
     SearchPlan pl{};
     CU(cudaSetDevice(s0.device));
@@ -1272,7 +1584,51 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
 {
     if (!st || !out_total_ms) return fail(DA_ERR_INVALID, "store/out is NULL");
     if (iters < 1) return fail(DA_ERR_INVALID, "iters must be >= 1");
-    std::lock_guard<std::mutex> lock(st->mu);
+    {   // one query on one shard: the small-search path, its inputs uploaded once, `iters` scans back to back
+        std::shared_lock<std::shared_mutex> shared(st->mu);
+        FastPlan fp;
+        uint2 ranges[kMaxRanges];
+        const int pr = plan_fast(st, p, fp, ranges);
+        if (pr < 0) return pr;
+        if (pr == 1) {
+            if (fp.k == 0) return fail(DA_ERR_INVALID, "k must be > 0");
+            *out_total_ms = 0.f;
+            if (fp.nothing) return DA_OK;
+            Shard &s = st->shards[0];
+            CU(cudaSetDevice(s.device));
+            int rc = DA_OK, grid = 0;
+            Slot *sl = acquire_slot(st, &rc);
+            if (!sl) return rc;
+            sl->ticket++;
+            const size_t qbytes = (size_t)st->dim * 4;
+            memcpy(sl->h_req, p->queries, qbytes);
+            if (fp.ranged) memcpy(sl->h_req + qbytes, ranges, (size_t)fp.n_ranges * 8);
+            cudaError_t ce = cudaMemcpyAsync(sl->d_req, sl->h_req, qbytes + (fp.ranged ? (size_t)fp.n_ranges * 8 : 0),
+                                             cudaMemcpyHostToDevice, sl->stream);
+            if (ce == cudaSuccess) ce = cudaEventRecord(sl->ev0, sl->stream);
+            if (ce != cudaSuccess) rc = fail(DA_ERR_CUDA, "staging failed: %s", cudaGetErrorString(ce));
+            for (int i = 0; i < iters && rc == DA_OK; i++) rc = enqueue_fast(st, sl, fp, false, nullptr, nullptr, i == iters - 1, &grid);
+            if (rc == DA_OK && cudaEventRecord(sl->ev1, sl->stream) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event record failed");
+            if (rc == DA_OK) rc = wait_fast(sl);
+            if (rc == DA_OK && cudaEventSynchronize(sl->ev1) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event sync failed");
+            if (rc == DA_OK && cudaEventElapsedTime(out_total_ms, sl->ev0, sl->ev1) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event time failed");
+            if (rc != DA_OK) cudaStreamSynchronize(sl->stream);
+            const uint64_t rows_read = rc == DA_OK ? *reinterpret_cast<const unsigned long long *>(sl->h_out + kSlotOutBytes - 16) : 0;
+            release_slot(st, sl);
+            if (rc != DA_OK) return rc;
+            std::lock_guard<std::mutex> g(st->stats_mu);
+            st->fast_searches += (uint64_t)iters;
+            st->launches += (uint64_t)iters;
+            st->scan_launches += (uint64_t)iters;
+            st->scan_ms_sum += *out_total_ms;
+            st->last_scan_ms = *out_total_ms / (float)iters;
+            st->last_rows_read = rows_read;                          // every scan hands over (and clears) its own count
+            st->last_bytes = st->last_rows_read * ((uint64_t)st->dim * 4 + 4) + (uint64_t)fp.n_ranges * 8;
+            st->scan_grid = grid;
+            return DA_OK;
+        }
+    }
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     SearchPlan pl{};
     int rc = stage_search(st, p, pl);
     if (rc != DA_OK) return rc;
@@ -1314,7 +1670,7 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     if (p->struct_size != sizeof(da_ivf_params)) return fail(DA_ERR_INVALID, "da_ivf_params.struct_size mismatch");
     if (p->lists < 1 || p->lists > 65536) return fail(DA_ERR_INVALID, "lists=%d out of range [1, 65536]", p->lists);
     if (st->split16) return fail(DA_ERR_STATE, "IVFFlat is not available with the split-plane layout");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     const int L = p->lists, D = st->dim;
     const int iters = p->iters <= 0 ? 10 : std::min(p->iters, 20);
     const bool use_tc = !(p->flags & DA_IVF_SIMT_ASSIGN);
@@ -1472,7 +1828,7 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
     if (p->struct_size != sizeof(da_synth_params)) return fail(DA_ERR_INVALID, "da_synth_params.struct_size mismatch");
     if (!p->chunks_per_doc || !p->n_clusters) return fail(DA_ERR_INVALID, "chunks_per_doc/n_clusters must be > 0");
     if (p->row_lo + p->n_rows > 0xFFFFFFF0ull) return fail(DA_ERR_CAPACITY, "rows exceed 2^32");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     const int S = (int)st->shards.size();
     for (Shard &s : st->shards)
         if (s.n_rows) return fail(DA_ERR_STATE, "generate_synthetic needs an empty store");
@@ -1533,7 +1889,10 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
             {
                 const uint64_t first = std::max<uint64_t>(p->row_lo, d * p->chunks_per_doc);
                 const uint64_t last = std::min<uint64_t>(p->row_lo + p->n_rows, (d + 1) * p->chunks_per_doc);
-                st->docs.push_back(DocInfo{k, 0, (uint32_t)(last - first)});
+                DocInfo di{k, 0, (uint32_t)(last - first), false, {}};
+                if (S == 1) di.ranges.emplace_back((uint32_t)(first - p->row_lo), (uint32_t)(last - first));
+                else di.fragmented = true;             // a synthetic fill over several shards does not track ranges
+                st->docs.push_back(std::move(di));
             }
         }
     }
@@ -1562,7 +1921,8 @@ int da_synth_ids(const da_synth_params *p, int32_t kind, uint64_t first, uint64_
 int da_store_stats(da_store *st, da_stats *out)
 {
     if (!st || !out) return fail(DA_ERR_INVALID, "store/out is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
+    std::lock_guard<std::mutex> sg(st->stats_mu);
     memset(out, 0, sizeof *out);
     out->struct_size = sizeof *out;
     out->dim = st->dim; out->n_devices = (int)st->shards.size();
@@ -1583,6 +1943,7 @@ int da_store_stats(da_store *st, da_stats *out)
     out->ivf_assign_ms = st->ivf_assign_ms; out->ivf_assign_tflops = st->ivf_assign_tflops;
     out->peer_gather = st->p2p_gather ? 1 : 0; out->tensor_overflows = st->tc_overflows;
     { std::lock_guard<std::mutex> bl(st->bmu); out->topk_calls = st->topk_calls; out->topk_passes = st->topk_passes; }
+    out->small_searches = st->fast_searches;
     return DA_OK;
 }
 
@@ -1590,7 +1951,7 @@ int da_store_debug_read_rows(da_store *st, int32_t device_index, uint64_t row_lo
                              float *out_inv_norm, uint32_t *out_doc_slot, uint8_t *out_chunk_ids)
 {
     if (!st) return fail(DA_ERR_INVALID, "store is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
     Shard &s = st->shards[device_index];
     if (row_lo + n > s.n_rows) return fail(DA_ERR_INVALID, "rows [%llu,%llu) outside the %u resident rows",
@@ -1614,7 +1975,7 @@ int da_store_debug_read_ivf(da_store *st, int32_t device_index, uint32_t *out_of
                             float *out_centroids)
 {
     if (!st) return fail(DA_ERR_INVALID, "store is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
     if (!st->ivf_lists) return fail(DA_ERR_STATE, "IVFFlat index has not been built on this store");
     Shard &s = st->shards[device_index];
@@ -1630,7 +1991,7 @@ int da_store_doc_rows(da_store *st, const uint8_t *doc_ids, size_t n_docs, uint3
 {
     if (!st) return fail(DA_ERR_INVALID, "store is NULL");
     if (n_docs && (!doc_ids || !out_rows)) return fail(DA_ERR_INVALID, "doc_ids/out_rows is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     for (size_t i = 0; i < n_docs; i++) {
         auto it = st->doc_slot_of.find(load_id(doc_ids + 16 * i));
         out_rows[i] = it == st->doc_slot_of.end() ? 0u : st->docs[it->second].rows;
@@ -1641,7 +2002,7 @@ int da_store_doc_rows(da_store *st, const uint8_t *doc_ids, size_t n_docs, uint3
 int da_store_debug_read_probes(da_store *st, int32_t device_index, int32_t batch, int32_t probes, uint32_t *out_lists)
 {
     if (!st || !out_lists) return fail(DA_ERR_INVALID, "store/out is NULL");
-    std::lock_guard<std::mutex> lock(st->mu);
+    std::unique_lock<std::shared_mutex> lock(st->mu);
     if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
     Shard &s = st->shards[device_index];
     if (batch < 1 || probes < 1 || (size_t)batch * probes > s.d_probe_keys.cap)

@@ -232,6 +232,8 @@ typedef struct {
     uint64_t tensor_overflows;      /* searches answered by the fp32 SIMT scan because a candidate list (tensor path, int8 sidecar) overflowed */
     uint64_t topk_calls;            /* da_store_topk calls answered */
     uint64_t topk_passes;           /* searches run for them (== topk_calls unless request batching merged some) */
+    uint64_t small_searches;        /* searches answered by the one-copy / one-kernel / polled-result path (one query, one shard);
+                                       for those last_search_ms is a host clock around copy + scan + pick-up */
 } da_stats;
 int da_store_stats(da_store *st, da_stats *out);
 
