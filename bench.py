@@ -475,9 +475,7 @@ def main():
     clocks = sampler.stop()
     s_after = st.stats()
     ms_total = max_over_ranks(ms_total)
-    # kernels inside the timed region: the general path stages its queries (one query-norm kernel) before the clock starts
-    small_path = int(s_after.small_searches - s_before.small_searches) > 0
-    launches = int(s_after.kernel_launches - s_before.kernel_launches) - (0 if small_path else 1)
+    launches = int(s_after.last_bench_launches)      # this library's kernels inside the timed region (counted by the library)
     scan_launches = int(s_after.scan_launches - s_before.scan_launches)
     scan_ms = (s_after.scan_ms_sum - s_before.scan_ms_sum) / max(1, scan_launches)
     bytes_per_launch = int(s_after.last_bytes_algorithmic)

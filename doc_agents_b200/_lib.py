@@ -84,7 +84,8 @@ class da_stats(C.Structure):
                 ("scan_ms_sum", C.c_double), ("scan_launches", C.c_uint64),
                 ("ivf_build_ms", C.c_float), ("ivf_kmeans_ms", C.c_float), ("ivf_assign_ms", C.c_float),
                 ("ivf_assign_tflops", C.c_float), ("peer_gather", C.c_int32), ("tensor_overflows", C.c_uint64),
-                ("topk_calls", C.c_uint64), ("topk_passes", C.c_uint64), ("small_searches", C.c_uint64)]
+                ("topk_calls", C.c_uint64), ("topk_passes", C.c_uint64), ("small_searches", C.c_uint64),
+                ("last_bench_launches", C.c_uint64)]
 
 
 # Every symbol include/docagents_b200.h declares, with its signature.

@@ -210,7 +210,9 @@ void free_ivf(Shard &s)
 // (one goroutine per /api/query: cmd/query/main.go:34) each take a slot, so they overlap instead of queueing.
 struct Slot {
     cudaStream_t stream = nullptr;
-    uint8_t *h_req = nullptr, *d_req = nullptr;          // [dim floats][kMaxRanges x (first row, count)]
+    uint8_t *h_req = nullptr, *d_req = nullptr;          // [dim floats][kMaxRanges x (first row, count) | document bitmap]
+    size_t req_cap = 0;
+    da::key_t64 *d_probe_keys = nullptr;                 // IVFFlat: the lists the query probes
     uint8_t *h_out = nullptr, *d_out = nullptr;          // mapped: [k ids of 16 B][k keys][rows read][completion word]
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
@@ -262,6 +264,9 @@ struct da_store {
     std::vector<Slot *> free_slots;
     std::mutex stats_mu;
     uint64_t fast_searches = 0;
+    const unsigned long long *last_probe_keys = nullptr;   // device: where the last IVFFlat search left its probe lists
+    size_t last_probe_count = 0;
+    uint64_t bench_launches = 0;   // kernels launched inside the timed region of the last da_store_bench_resident
     float ivf_build_ms = 0, ivf_kmeans_ms = 0, ivf_assign_ms = 0, ivf_assign_tflops = 0;
 };
 
@@ -297,7 +302,7 @@ void free_shard(Shard &s)
 void free_slot(Slot &sl)
 {
     if (sl.stream) cudaStreamSynchronize(sl.stream);
-    cudaFree(sl.d_req); cudaFree(sl.d_cta); cudaFree(sl.d_counter); cudaFree(sl.d_rows_read);
+    cudaFree(sl.d_req); cudaFree(sl.d_cta); cudaFree(sl.d_counter); cudaFree(sl.d_rows_read); cudaFree(sl.d_probe_keys);
     if (sl.h_req) cudaFreeHost(sl.h_req);
     if (sl.h_out) cudaFreeHost(sl.h_out);
     if (sl.ev0) cudaEventDestroy(sl.ev0);
@@ -314,6 +319,8 @@ int make_slot(da_store *st, Slot &sl)
     CU(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
     CU(cudaMallocHost((void **)&sl.h_req, req));
     CU(cudaMalloc((void **)&sl.d_req, req));
+    sl.req_cap = req;
+    CU(cudaMalloc((void **)&sl.d_probe_keys, (size_t)DA_IVF_MAX_PROBES * sizeof(da::key_t64)));
     CU(cudaHostAlloc((void **)&sl.h_out, kSlotOutBytes, cudaHostAllocMapped));
     CU(cudaHostGetDevicePointer((void **)&sl.d_out, sl.h_out, 0));
     memset(sl.h_out, 0, kSlotOutBytes);
@@ -324,6 +331,21 @@ int make_slot(da_store *st, Slot &sl)
     CU(cudaMemsetAsync(sl.d_rows_read, 0, sizeof(unsigned long long), sl.stream));
     CU(cudaEventCreate(&sl.ev0)); CU(cudaEventCreate(&sl.ev1));
     CU(cudaStreamSynchronize(sl.stream));
+    return DA_OK;
+}
+
+// The request block grows with the store's document count (an IVFFlat search with a document filter carries a bitmap).
+int slot_reserve_request(Slot &sl, size_t bytes)
+{
+    if (bytes <= sl.req_cap) return DA_OK;
+    CU(cudaStreamSynchronize(sl.stream));
+    cudaFree(sl.d_req); sl.d_req = nullptr;
+    if (sl.h_req) cudaFreeHost(sl.h_req);
+    sl.h_req = nullptr; sl.req_cap = 0;
+    bytes += bytes / 2;
+    CU(cudaMallocHost((void **)&sl.h_req, bytes));
+    CU(cudaMalloc((void **)&sl.d_req, bytes));
+    sl.req_cap = bytes;
     return DA_OK;
 }
 
@@ -409,6 +431,7 @@ struct SearchPlan {
     size_t bitmap_words;
     bool ivf;
     int probes;
+    bool need_qinv;    // some kernel of the plan reads 1/|q| from memory (candidate paths); the plain scans compute it themselves
     bool ivf_tc;       // IVFFlat: rank the centroids for the whole batch with one tensor-core GEMM (batches of 8+)
     int ivf_ks;        // ... slices of the dimension of that GEMM
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
@@ -453,6 +476,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             const float ninf = -std::numeric_limits<float>::infinity();
             const int L = st->ivf_lists;
             da::key_t64 *probe_keys = reinterpret_cast<da::key_t64 *>(s.d_probe_keys.p);
+            if (first) { st->last_probe_keys = s.d_probe_keys.p; st->last_probe_count = (size_t)pl.batch * pl.probes; }
             if (pl.ivf_tc) {
                 CU(da::tc_launch_scores(s.d_queries.p, pl.batch, s.ivf.cent, L, dim, pl.ivf_ks, s.d_ivf_scores.p, s.stream));
                 CU(da::ivf_launch_select_probes(s.d_ivf_scores.p, pl.ivf_ks, pl.batch, L, pl.probes, probe_keys, s.stream));
@@ -462,7 +486,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 for (int q0 = 0; q0 < pl.batch; q0 += step) {
                     da::ScanArgs c{};
                     c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
-                    c.queries = s.d_queries.p + (size_t)q0 * dim; c.q_inv_norm = s.d_qinv.p + q0;
+                    c.queries = s.d_queries.p + (size_t)q0 * dim; c.q_inv_norm = nullptr;
                     c.n_rows = (uint32_t)L; c.row_base = 0;
                     c.dim = dim; c.nq = std::min(step, pl.batch - q0); c.k = pl.probes; c.min_sim = ninf;
                     c.cta_out = s.d_cta; c.counter = s.d_counter; c.out_keys = probe_keys + (size_t)q0 * pl.probes;
@@ -473,7 +497,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             da::ScanArgs a{};
             a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
             a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p; a.bitmap_stride = pl.bitmap_stride;
-            a.queries = s.d_queries.p; a.q_inv_norm = s.d_qinv.p;
+            a.queries = s.d_queries.p; a.q_inv_norm = nullptr;
             a.probe_keys = probe_keys; a.probes = pl.probes; a.probe_batch = pl.batch;
             a.list_offsets = s.ivf.offsets; a.list_rows = s.ivf.list_rows;
             a.n_rows = 0; a.row_base = s.row_base;
@@ -532,7 +556,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 da::ScanArgs a{};
                 a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
                 a.doc_bitmap = nullptr;                         // every listed row is requested
-                a.queries = s.d_queries.p + (size_t)q0 * dim; a.q_inv_norm = s.d_qinv.p + q0;
+                a.queries = s.d_queries.p + (size_t)q0 * dim; a.q_inv_norm = nullptr;
                 a.row_list = s.d_flt_rows.p; a.n_rows_dev = s.d_flt_n.p; a.n_rows = 0; a.row_base = s.row_base;
                 a.dim = dim; a.nq = std::min(step, pl.batch - q0); a.k = pl.k; a.min_sim = pl.min_sim; a.read_all = 0;
                 a.cta_out = s.d_cta; a.counter = s.d_counter;
@@ -554,7 +578,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             a.doc_bitmap = pl.all_docs ? nullptr : s.d_bitmap.p + (size_t)q0 * pl.bitmap_stride;
             a.bitmap_stride = pl.bitmap_stride;
             a.queries = s.d_queries.p + (size_t)q0 * dim;
-            a.q_inv_norm = s.d_qinv.p + q0;
+            a.q_inv_norm = pl.need_qinv ? s.d_qinv.p + q0 : nullptr;
             a.row_list = nullptr;
             a.n_rows = s.n_rows; a.row_base = s.row_base;
             a.dim = dim; a.nq = std::min(nq_max, pl.batch - q0); a.k = pl.k;
@@ -774,6 +798,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         pl.use_q8 = selected * 4 >= st->docs.size() && selected > 0;
     }
+    pl.need_qinv = pl.use_tc || pl.use_q8 || st->split16;
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
@@ -838,8 +863,10 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             memcpy(s.h_bitmap.p, bitmap.data(), bitmap.size() * 4);
             CU(cudaMemcpyAsync(s.d_bitmap.p, s.h_bitmap.p, bitmap.size() * 4, cudaMemcpyHostToDevice, s.stream));
         }
-        CU(da::launch_query_inv_norm(s.d_queries.p, st->dim, p->batch, s.d_qinv.p, s.stream));
-        st->launches++;
+        if (pl.need_qinv) {
+            CU(da::launch_query_inv_norm(s.d_queries.p, st->dim, p->batch, s.d_qinv.p, s.stream));
+            st->launches++;
+        }
         if (pl.tc_i8) {                       // the int8 contraction needs the queries as int8 with their scales and bounds
             CU(da::launch_q8_quantize_queries(s.d_queries.p, p->batch, st->dim, s.d_qinv.p, s.d_q8q.p, s.d_q8qf.p, s.d_q8qe.p, s.stream));
             st->launches++;
@@ -921,6 +948,9 @@ struct FastPlan {
     int n_ranges = 0;
     uint32_t total_rows = 0;    // rows the scan will read
     bool nothing = false;       // no requested document holds a row: zero rows, as `= ANY('{}')`
+    bool ivf = false;           // probe the IVFFlat lists: centroid scan (top `probes`), then the probe-mode scan
+    int probes = 0;
+    bool bitmap = false;        // IVFFlat with a document filter: bit per document slot, tested on the probed rows
 };
 
 bool fast_path_enabled()
@@ -934,14 +964,32 @@ int plan_fast(da_store *st, const da_search_params *p, FastPlan &fp, uint2 *rang
 {
     if (!fast_path_enabled() || st->shards.size() != 1 || st->total_ranks != 1 || st->split16) return 0;
     if (!p || p->struct_size != sizeof(da_search_params) || p->batch != 1 || p->doc_offsets) return 0;
-    if (p->flags & (DA_SEARCH_IVF | DA_SEARCH_READ_ALL_ROWS | DA_SEARCH_NO_COMPACT)) return 0;
+    if (p->flags & (DA_SEARCH_READ_ALL_ROWS | DA_SEARCH_NO_COMPACT)) return 0;
     const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
+    const bool ivf = (p->flags & DA_SEARCH_IVF) != 0;
     const bool q8_ok = st->q8 && !(p->flags & DA_SEARCH_NO_Q8);
-    if (all_docs && q8_ok) return 0;                       // the int8 sidecar scan reads a quarter of the bytes
+    if (all_docs && q8_ok && !ivf) return 0;               // the int8 sidecar scan reads a quarter of the bytes
     const int vrc = validate_search(st, p);
     if (vrc != DA_OK) return vrc;
     const Shard &s = st->shards[0];
     fp.k = p->k; fp.min_sim = p->min_similarity;
+    if (ivf) {
+        fp.ivf = true;
+        const int probes = p->ivf_probes > 0 ? p->ivf_probes : st->ivf_default_probes;
+        fp.probes = std::max(1, std::min(probes, std::min(st->ivf_lists, DA_IVF_MAX_PROBES)));
+        fp.bitmap = !all_docs;
+        fp.total_rows = 0;
+        fp.nothing = s.n_rows == 0;
+        if (fp.bitmap) {            // filters apply to the probed rows (pgvector filters after the index scan)
+            bool any = false;
+            for (size_t i = 0; i < p->n_docs && !any; i++) {
+                auto it = st->doc_slot_of.find(load_id(p->doc_ids + 16 * i));
+                any = it != st->doc_slot_of.end() && st->docs[it->second].rows > 0;
+            }
+            if (!any) fp.nothing = true;
+        }
+        return 1;
+    }
     if (all_docs) {
         fp.ranged = false; fp.total_rows = s.n_rows; fp.nothing = s.n_rows == 0;
         return 1;
@@ -974,25 +1022,64 @@ int plan_fast(da_store *st, const da_search_params *p, FastPlan &fp, uint2 *rang
     return 1;
 }
 
-// Enqueue the H2D copy and the scan of one planned search on a slot.  `flag` = write the completion word.
-int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool upload, const float *query, const uint2 *ranges,
-                 bool flag, int *grid_out)
+// Bytes of the request block: the query, then the range table or (IVFFlat with a filter) the document bitmap.
+size_t fast_request_bytes(const da_store *st, const FastPlan &fp)
+{
+    const size_t qbytes = (size_t)st->dim * 4;
+    if (fp.ivf) return qbytes + (fp.bitmap ? ((st->docs.size() + 31) / 32 + 1) * 4 : 0);
+    return qbytes + (fp.ranged ? (size_t)fp.n_ranges * 8 : 0);
+}
+
+// Fill the slot's pinned request block and queue its one host-to-device copy.
+int upload_fast(da_store *st, Slot *sl, const FastPlan &fp, const da_search_params *p, const uint2 *ranges)
+{
+    const size_t qbytes = (size_t)st->dim * 4, bytes = fast_request_bytes(st, fp);
+    const int rc = slot_reserve_request(*sl, bytes);
+    if (rc != DA_OK) return rc;
+    memcpy(sl->h_req, p->queries, qbytes);
+    if (fp.ivf && fp.bitmap) {
+        uint32_t *bm = reinterpret_cast<uint32_t *>(sl->h_req + qbytes);
+        memset(bm, 0, bytes - qbytes);
+        for (size_t i = 0; i < p->n_docs; i++) {
+            auto it = st->doc_slot_of.find(load_id(p->doc_ids + 16 * i));
+            if (it != st->doc_slot_of.end()) bm[it->second >> 5] |= 1u << (it->second & 31);
+        }
+    } else if (fp.ranged) {
+        memcpy(sl->h_req + qbytes, ranges, (size_t)fp.n_ranges * 8);
+    }
+    CU(cudaMemcpyAsync(sl->d_req, sl->h_req, bytes, cudaMemcpyHostToDevice, sl->stream));
+    return DA_OK;
+}
+
+// Queue the kernels of one planned search on a slot whose request block is (being) uploaded: ONE scan, or for
+// IVFFlat the centroid scan and the probe-mode scan.  `flag` = the last kernel writes the completion word.
+int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool flag, int *grid_out, int *launches)
 {
     Shard &s = st->shards[0];
     const size_t qbytes = (size_t)st->dim * 4;
-    if (upload) {
-        memcpy(sl->h_req, query, qbytes);
-        if (fp.ranged) memcpy(sl->h_req + qbytes, ranges, (size_t)fp.n_ranges * 8);
-        CU(cudaMemcpyAsync(sl->d_req, sl->h_req, qbytes + (fp.ranged ? (size_t)fp.n_ranges * 8 : 0), cudaMemcpyHostToDevice, sl->stream));
-    }
     da::ScanArgs a{};
     a.mat = s.mat; a.inv_norm = s.inv_norm; a.doc_slot = s.doc_slot; a.chunk_ids = s.chunk_ids;
     a.doc_bitmap = nullptr;
     a.queries = reinterpret_cast<const float *>(sl->d_req); a.q_inv_norm = nullptr;
-    if (fp.ranged) { a.ranges = reinterpret_cast<const uint2 *>(sl->d_req + qbytes); a.probes = fp.n_ranges; a.probe_batch = 1; }
     a.n_rows = fp.total_rows; a.row_base = s.row_base;
     a.dim = st->dim; a.nq = 1; a.k = fp.k; a.min_sim = fp.min_sim; a.read_all = 0;
     a.cta_out = sl->d_cta; a.counter = sl->d_counter;
+    if (fp.ivf) {
+        da::ScanArgs c{};
+        c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
+        c.queries = a.queries; c.q_inv_norm = nullptr;
+        c.n_rows = (uint32_t)st->ivf_lists; c.row_base = 0;
+        c.dim = st->dim; c.nq = 1; c.k = fp.probes; c.min_sim = -std::numeric_limits<float>::infinity();
+        c.cta_out = sl->d_cta; c.counter = sl->d_counter; c.out_keys = sl->d_probe_keys;
+        CU(da::launch_scan(c, s.sm_count, sl->stream, nullptr));
+        (*launches)++;
+        a.probe_keys = sl->d_probe_keys; a.probes = fp.probes; a.probe_batch = 1;
+        a.list_offsets = s.ivf.offsets; a.list_rows = s.ivf.list_rows;
+        a.n_rows = 0;
+        if (fp.bitmap) a.doc_bitmap = reinterpret_cast<const uint32_t *>(sl->d_req + qbytes);
+    } else if (fp.ranged) {
+        a.ranges = reinterpret_cast<const uint2 *>(sl->d_req + qbytes); a.probes = fp.n_ranges; a.probe_batch = 1;
+    }
     a.out_ids = sl->d_out;
     a.out_keys = reinterpret_cast<da::key_t64 *>(sl->d_out + (size_t)fp.k * 16);
     a.rows_read = sl->d_rows_read;
@@ -1002,7 +1089,17 @@ int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool upload, const 
         a.done_value = sl->ticket;
     }
     CU(da::launch_scan(a, s.sm_count, sl->stream, grid_out));
+    (*launches)++;
     return DA_OK;
+}
+
+// Algorithmic bytes of one small search that read `rows_read` rows.
+uint64_t fast_bytes(const da_store *st, const FastPlan &fp, uint64_t rows_read)
+{
+    const uint64_t dim4 = (uint64_t)st->dim * 4;
+    if (fp.ivf)     // the centroid matrix, then the probed rows: vector, 1/|row|, row number (+ document slot with a filter)
+        return (uint64_t)st->ivf_lists * (dim4 + 4) + rows_read * (dim4 + (fp.bitmap ? 12 : 8));
+    return rows_read * (dim4 + 4) + (uint64_t)fp.n_ranges * 8;      // no document slots, no bitmap on the range path
 }
 
 // Wait for the completion word of the slot's current ticket.
@@ -1039,7 +1136,8 @@ int search_fast(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids,
     if (!out_chunk_ids || !out_scores) return fail(DA_ERR_INVALID, "output buffers are NULL");
     const auto t0 = std::chrono::steady_clock::now();
     uint64_t rows_read = 0;
-    int grid = 0;
+    int grid = 0, launches = 0;
+    const unsigned long long *probe_src = nullptr;
     if (!fp.nothing) {
         Shard &s = st->shards[0];
         CU(cudaSetDevice(s.device));
@@ -1047,7 +1145,8 @@ int search_fast(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids,
         Slot *sl = acquire_slot(st, &rc);
         if (!sl) return rc;
         sl->ticket++;
-        rc = enqueue_fast(st, sl, fp, true, p->queries, ranges, true, &grid);
+        rc = upload_fast(st, sl, fp, p, ranges);
+        if (rc == DA_OK) rc = enqueue_fast(st, sl, fp, true, &grid, &launches);
         if (rc == DA_OK) rc = wait_fast(sl);
         if (rc != DA_OK) { cudaStreamSynchronize(sl->stream); release_slot(st, sl); return rc; }
         const uint8_t *ids = sl->h_out;
@@ -1063,6 +1162,7 @@ int search_fast(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids,
         }
         out_n[0] = c;
         rows_read = *reinterpret_cast<const unsigned long long *>(sl->h_out + kSlotOutBytes - 16);
+        probe_src = sl->d_probe_keys;
         release_slot(st, sl);
     }
     const float ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
@@ -1071,9 +1171,9 @@ int search_fast(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids,
         st->fast_searches++;
         st->last_search_ms = ms; st->last_scan_ms = ms;         // host clock around copy + scan + pick-up on this path
         st->last_rows_read = rows_read;
-        // the rows' vectors and 1/|row| (+ the range table); no document slots, no bitmap on this path
-        st->last_bytes = rows_read * ((uint64_t)st->dim * 4 + 4) + (uint64_t)fp.n_ranges * 8;
-        if (!fp.nothing) { st->launches++; st->scan_grid = grid; }
+        st->last_bytes = fast_bytes(st, fp, rows_read);
+        if (!fp.nothing) { st->launches += (uint64_t)launches; st->scan_grid = grid; }
+        if (fp.ivf && !fp.nothing) { st->last_probe_keys = probe_src; st->last_probe_count = (size_t)fp.probes; }
     }
     return 1;
 }
@@ -1600,14 +1700,10 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
             Slot *sl = acquire_slot(st, &rc);
             if (!sl) return rc;
             sl->ticket++;
-            const size_t qbytes = (size_t)st->dim * 4;
-            memcpy(sl->h_req, p->queries, qbytes);
-            if (fp.ranged) memcpy(sl->h_req + qbytes, ranges, (size_t)fp.n_ranges * 8);
-            cudaError_t ce = cudaMemcpyAsync(sl->d_req, sl->h_req, qbytes + (fp.ranged ? (size_t)fp.n_ranges * 8 : 0),
-                                             cudaMemcpyHostToDevice, sl->stream);
-            if (ce == cudaSuccess) ce = cudaEventRecord(sl->ev0, sl->stream);
-            if (ce != cudaSuccess) rc = fail(DA_ERR_CUDA, "staging failed: %s", cudaGetErrorString(ce));
-            for (int i = 0; i < iters && rc == DA_OK; i++) rc = enqueue_fast(st, sl, fp, false, nullptr, nullptr, i == iters - 1, &grid);
+            int launches = 0;
+            rc = upload_fast(st, sl, fp, p, ranges);
+            if (rc == DA_OK && cudaEventRecord(sl->ev0, sl->stream) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event record failed");
+            for (int i = 0; i < iters && rc == DA_OK; i++) rc = enqueue_fast(st, sl, fp, i == iters - 1, &grid, &launches);
             if (rc == DA_OK && cudaEventRecord(sl->ev1, sl->stream) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event record failed");
             if (rc == DA_OK) rc = wait_fast(sl);
             if (rc == DA_OK && cudaEventSynchronize(sl->ev1) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event sync failed");
@@ -1618,13 +1714,14 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
             if (rc != DA_OK) return rc;
             std::lock_guard<std::mutex> g(st->stats_mu);
             st->fast_searches += (uint64_t)iters;
-            st->launches += (uint64_t)iters;
+            st->launches += (uint64_t)launches;
             st->scan_launches += (uint64_t)iters;
             st->scan_ms_sum += *out_total_ms;
             st->last_scan_ms = *out_total_ms / (float)iters;
             st->last_rows_read = rows_read;                          // every scan hands over (and clears) its own count
-            st->last_bytes = st->last_rows_read * ((uint64_t)st->dim * 4 + 4) + (uint64_t)fp.n_ranges * 8;
+            st->last_bytes = fast_bytes(st, fp, st->last_rows_read);
             st->scan_grid = grid;
+            st->bench_launches = (uint64_t)launches;
             return DA_OK;
         }
     }
@@ -1642,10 +1739,12 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
         s0.ev_pool.push_back(e);
     }
     CU(cudaEventRecord(s0.ev_all0, s0.stream));
+    const uint64_t launches_before = st->launches;
     for (int i = 0; i < iters; i++) {
         rc = enqueue_search(st, pl, s0.ev_pool[2 * i], s0.ev_pool[2 * i + 1]);
         if (rc != DA_OK) return rc;
     }
+    st->bench_launches = st->launches - launches_before;
     CU(cudaSetDevice(s0.device));
     CU(cudaEventRecord(s0.ev_all1, s0.stream));
     rc = enqueue_stats_readback(st);
@@ -1944,6 +2043,7 @@ int da_store_stats(da_store *st, da_stats *out)
     out->peer_gather = st->p2p_gather ? 1 : 0; out->tensor_overflows = st->tc_overflows;
     { std::lock_guard<std::mutex> bl(st->bmu); out->topk_calls = st->topk_calls; out->topk_passes = st->topk_passes; }
     out->small_searches = st->fast_searches;
+    out->last_bench_launches = st->bench_launches;
     return DA_OK;
 }
 
@@ -2005,11 +2105,14 @@ int da_store_debug_read_probes(da_store *st, int32_t device_index, int32_t batch
     std::unique_lock<std::shared_mutex> lock(st->mu);
     if (device_index < 0 || device_index >= (int)st->shards.size()) return fail(DA_ERR_INVALID, "device_index out of range");
     Shard &s = st->shards[device_index];
-    if (batch < 1 || probes < 1 || (size_t)batch * probes > s.d_probe_keys.cap)
+    const unsigned long long *src = device_index == 0 ? st->last_probe_keys : s.d_probe_keys.p;
+    const size_t have = device_index == 0 ? st->last_probe_count : s.d_probe_keys.cap;
+    if (batch < 1 || probes < 1 || !src || (size_t)batch * probes > have)
         return fail(DA_ERR_INVALID, "no IVFFlat search of that shape has run on this shard");
     std::vector<unsigned long long> keys((size_t)batch * probes);
     CU(cudaSetDevice(s.device));
-    CU(cudaMemcpy(keys.data(), s.d_probe_keys.p, keys.size() * 8, cudaMemcpyDeviceToHost));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(keys.data(), src, keys.size() * 8, cudaMemcpyDeviceToHost));
     for (size_t i = 0; i < keys.size(); i++) out_lists[i] = keys[i] ? da::key_row(keys[i]) : 0xFFFFFFFFu;
     return DA_OK;
 }

@@ -234,6 +234,7 @@ typedef struct {
     uint64_t topk_passes;           /* searches run for them (== topk_calls unless request batching merged some) */
     uint64_t small_searches;        /* searches answered by the one-copy / one-kernel / polled-result path (one query, one shard);
                                        for those last_search_ms is a host clock around copy + scan + pick-up */
+    uint64_t last_bench_launches;   /* kernels of this library launched inside the timed region of the last da_store_bench_resident */
 } da_stats;
 int da_store_stats(da_store *st, da_stats *out);
 
