@@ -98,6 +98,8 @@ SIGNATURES = {
     "da_store_bulk_load": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int32]),
     "da_store_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int32, C.c_int32,
                                 C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]),
+    "da_store_export": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "da_store_attach": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
     "da_store_doc_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "da_store_search": (C.c_int, [C.c_void_p, C.POINTER(da_search_params), C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p]),

@@ -17,7 +17,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <cerrno>
 #include <cstring>
+#include <new>
 #include <limits>
 #include <atomic>
 #include <memory>
@@ -28,7 +30,12 @@
 #include <unordered_map>
 #include <vector>
 
+#include <fcntl.h>
 #include <immintrin.h>
+#include <pthread.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 namespace {
 
@@ -94,6 +101,13 @@ struct DocInfo {
         if (ranges.size() >= kMaxDocRanges) { fragmented = true; ranges.clear(); ranges.shrink_to_fit(); return; }
         ranges.emplace_back(row, 1u);
     }
+    void add_run(uint32_t first, uint32_t count)
+    {
+        if (fragmented || count == 0) return;
+        if (!ranges.empty() && ranges.back().first + ranges.back().second == first) { ranges.back().second += count; return; }
+        if (ranges.size() >= kMaxDocRanges) { fragment(); return; }
+        ranges.emplace_back(first, count);
+    }
     void fragment() { fragmented = true; ranges.clear(); ranges.shrink_to_fit(); }
 };
 
@@ -128,6 +142,7 @@ struct PinBuf {   // grow-only pinned host buffer
 
 struct Shard {
     int device = 0, sm_count = 148;
+    bool ipc_mapped = false;                    // mat / inv_norm / doc_slot / chunk_ids are another process's memory (da_store_attach)
     uint64_t cap_rows = 0;
     uint32_t n_rows = 0, row_base = 0;
     float *mat = nullptr, *inv_norm = nullptr;
@@ -204,6 +219,44 @@ void free_ivf(Shard &s)
     v = Shard::Ivf();
 }
 
+// ---------------------------------------------------------------------------
+// Sharing one device store between processes.  The writer of the reference (analysis agent,
+// cmd/analysis/main.go:106) and its reader (query agent, cmd/query/main.go:101) are different processes
+// (docker-compose.yml:87-128).  The writer exports its store: CUDA IPC handles of the four resident arrays plus,
+// in POSIX shared memory, a log of what it has stored (documents, runs of rows) and a process-shared rwlock.  A
+// reader attaches: it maps the SAME HBM, replays the log into its own id maps and row ranges, and before every
+// search replays what was appended since -- so a document saved by the writer is found by the reader's next TopK.
+// ---------------------------------------------------------------------------
+constexpr uint64_t kShmMagic = 0x4441495043763031ull;          // "DAIPCv01"
+enum : uint32_t { kRecDoc = 1, kRecRows = 2, kRecFragment = 3 };
+struct ShmRecord {                 // 32 bytes
+    uint32_t type, slot, first, count;
+    uint8_t id[16];                // kRecDoc: the document id of `slot`
+};
+struct ShmHeader {
+    uint64_t magic;
+    uint32_t version, dim;
+    uint64_t capacity_rows;
+    float min_sim;
+    uint32_t row_base;
+    char device_bus_id[32];        // the writer's GPU: a reader must open the handles on the same one
+    cudaIpcMemHandle_t h_mat, h_inv, h_slot, h_ids;
+    pthread_rwlock_t lock;         // writer: while rows or log change; readers: while a search runs
+    uint64_t max_records;
+    std::atomic<uint64_t> n_records;   // published with release order after the records and the rows are in place
+    std::atomic<uint64_t> n_rows;
+    std::atomic<uint32_t> overflow;    // the log ran out of room: readers can no longer follow (export again with a larger store)
+};
+struct Shared {
+    ShmHeader *hdr = nullptr;
+    ShmRecord *rec = nullptr;
+    size_t bytes = 0;
+    std::string name;
+    bool owner = false;            // the writer created it (and unlinks it)
+    uint64_t pending = 0;          // writer: records written, published at the end of the operation
+    std::atomic<uint64_t> replayed{0};   // reader: records already applied to its maps
+};
+
 // One small search in flight: its own stream, request block (query + row ranges, one host-to-device copy), scan
 // scratch, and a result block in MAPPED host memory that the scan's last CTA writes directly, followed by a
 // completion word the caller polls -- no device-to-host copy, no stream synchronisation.  Concurrent TopK calls
@@ -264,6 +317,8 @@ struct da_store {
     std::vector<Slot *> free_slots;
     std::mutex stats_mu;
     uint64_t fast_searches = 0;
+    Shared shm;                    // exported (writer) or attached (reader) state; hdr == nullptr: a private store
+    bool attached = false;         // reader of another process's store: read-only, device arrays are IPC mappings
     const unsigned long long *last_probe_keys = nullptr;   // device: where the last IVFFlat search left its probe lists
     size_t last_probe_count = 0;
     uint64_t bench_launches = 0;   // kernels launched inside the timed region of the last da_store_bench_resident
@@ -278,6 +333,10 @@ void free_shard(Shard &s)
     free_ivf(s);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
+    if (s.ipc_mapped) {
+        cudaIpcCloseMemHandle(s.mat); cudaIpcCloseMemHandle(s.inv_norm); cudaIpcCloseMemHandle(s.doc_slot); cudaIpcCloseMemHandle(s.chunk_ids);
+        s.mat = nullptr; s.inv_norm = nullptr; s.doc_slot = nullptr; s.chunk_ids = nullptr;
+    }
     cudaFree(s.mat); cudaFree(s.hi); cudaFree(s.lo); cudaFree(s.q8); cudaFree(s.q8_factor); cudaFree(s.q8_err); cudaFree(s.q8_errmax); cudaFree(s.inv_norm); cudaFree(s.doc_slot); cudaFree(s.chunk_ids);
     cudaFree(s.d_cta); cudaFree(s.d_counter); cudaFree(s.d_rows_read);
     s.d_queries.release(); s.d_qinv.release(); s.d_bitmap.release();
@@ -297,6 +356,87 @@ void free_shard(Shard &s)
     if (s.ev_done) cudaEventDestroy(s.ev_done);
     if (s.stream) cudaStreamDestroy(s.stream);
     s = Shard();
+}
+
+// ---- shared-store plumbing (see "Sharing one device store between processes") ----
+struct ShmWriteGuard {      // the exporting process takes the lock alone while rows or the log change
+    ShmHeader *h;
+    explicit ShmWriteGuard(da_store *st) : h(st->shm.hdr && st->shm.owner ? st->shm.hdr : nullptr) { if (h) pthread_rwlock_wrlock(&h->lock); }
+    ~ShmWriteGuard() { if (h) pthread_rwlock_unlock(&h->lock); }
+};
+struct ShmReadGuard {       // an attached process holds it shared while it replays the log and searches
+    ShmHeader *h;
+    explicit ShmReadGuard(da_store *st) : h(st->attached && st->shm.hdr ? st->shm.hdr : nullptr) { if (h) pthread_rwlock_rdlock(&h->lock); }
+    ~ShmReadGuard() { if (h) pthread_rwlock_unlock(&h->lock); }
+};
+
+// Writer: one more record (kept private until shm_publish).  A full log is remembered; readers then fail loudly.
+void shm_append(da_store *st, uint32_t type, uint32_t slot, uint32_t first, uint32_t count, const Id16 *id = nullptr)
+{
+    Shared &sh = st->shm;
+    if (!sh.hdr || !sh.owner) return;
+    if (sh.pending >= sh.hdr->max_records) { sh.hdr->overflow.store(1u, std::memory_order_release); return; }
+    ShmRecord &r = sh.rec[sh.pending++];
+    r.type = type; r.slot = slot; r.first = first; r.count = count;
+    if (id) memcpy(r.id, id, 16); else memset(r.id, 0, 16);
+}
+
+// Writer: make everything appended so far (and the rows it describes, already complete on the device) visible.
+void shm_publish(da_store *st)
+{
+    Shared &sh = st->shm;
+    if (!sh.hdr || !sh.owner) return;
+    sh.hdr->n_rows.store(st->shards[0].n_rows, std::memory_order_release);
+    sh.hdr->n_records.store(sh.pending, std::memory_order_release);
+}
+
+// Reader: apply the records appended since the last look.  Called with st->mu held alone.
+int shm_replay(da_store *st)
+{
+    Shared &sh = st->shm;
+    if (sh.hdr->overflow.load(std::memory_order_acquire))
+        return fail(DA_ERR_STATE, "the exporting process's log is full; this reader can no longer follow it");
+    const uint64_t n = sh.hdr->n_records.load(std::memory_order_acquire);
+    for (uint64_t i = sh.replayed.load(std::memory_order_relaxed); i < n; i++) {
+        const ShmRecord &r = sh.rec[i];
+        if (r.type == kRecDoc) {
+            if (r.slot != st->docs.size()) return fail(DA_ERR_STATE, "shared log out of order (document slot %u)", r.slot);
+            const Id16 id = load_id(r.id);
+            st->docs.push_back(DocInfo{id, 0, 0, false, {}});
+            st->doc_slot_of.emplace(id, r.slot);
+        } else if (r.slot >= st->docs.size()) {
+            return fail(DA_ERR_STATE, "shared log names an unknown document slot %u", r.slot);
+        } else if (r.type == kRecRows) {
+            st->docs[r.slot].rows += r.count;
+            st->docs[r.slot].add_run(r.first, r.count);
+        } else if (r.type == kRecFragment) {
+            st->docs[r.slot].fragment();
+            st->docs[r.slot].rows = r.count;
+        }
+    }
+    sh.replayed.store(n, std::memory_order_release);
+    st->shards[0].n_rows = (uint32_t)sh.hdr->n_rows.load(std::memory_order_acquire);
+    return DA_OK;
+}
+
+// Reader: before a search.  Cheap when nothing was appended.
+int shm_refresh(da_store *st)
+{
+    if (!st->attached) return DA_OK;
+    if (st->shm.hdr->n_records.load(std::memory_order_acquire) == st->shm.replayed.load(std::memory_order_acquire) &&
+        !st->shm.hdr->overflow.load(std::memory_order_acquire))
+        return DA_OK;
+    std::unique_lock<std::shared_mutex> lock(st->mu);
+    return shm_replay(st);
+}
+
+void shm_close(da_store *st)
+{
+    Shared &sh = st->shm;
+    if (!sh.hdr) return;
+    munmap(sh.hdr, sh.bytes);
+    if (sh.owner) shm_unlink(sh.name.c_str());
+    sh.hdr = nullptr; sh.rec = nullptr;
 }
 
 void free_slot(Slot &sl)
@@ -376,10 +516,11 @@ void release_slot(da_store *st, Slot *sl)
     st->slot_cv.notify_one();
 }
 
-int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, bool q8)
+int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, bool q8, bool attach_only = false)
 {
     s.device = device;
     s.cap_rows = cap_rows;
+    s.ipc_mapped = attach_only;
     CU(cudaSetDevice(device));
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
@@ -388,15 +529,17 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, b
     s.sm_count = prop.multiProcessorCount;
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
-    const uint64_t need = cap_rows * ((uint64_t)dim * 4 + 4 + 4 + 16 + (q8 ? (uint64_t)dim + 8 : 0));
-    if (need + (512ull << 20) > free_b)
+    const uint64_t need = attach_only ? 0 : cap_rows * ((uint64_t)dim * 4 + 4 + 4 + 16 + (q8 ? (uint64_t)dim + 8 : 0));
+    if (!attach_only && need + (512ull << 20) > free_b)
         return fail(DA_ERR_CAPACITY, "capacity_rows=%llu x dim=%d needs %.2f GB on device %d, %.2f GB free (no CPU fallback)",
                     (unsigned long long)cap_rows, dim, need / 1e9, device, free_b / 1e9);
     CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&s.ev_scan0)); CU(cudaEventCreate(&s.ev_scan1));
     CU(cudaEventCreate(&s.ev_all0)); CU(cudaEventCreate(&s.ev_all1));
     CU(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
-    if (split16) {
+    if (attach_only) {
+        // the resident arrays come from the exporting process (cudaIpcOpenMemHandle, by the caller)
+    } else if (split16) {
         CU(cudaMalloc((void **)&s.hi, cap_rows * (uint64_t)dim * 2));
         CU(cudaMalloc((void **)&s.lo, cap_rows * (uint64_t)dim * 2));
     } else {
@@ -409,9 +552,11 @@ int init_shard(Shard &s, int device, int dim, uint64_t cap_rows, bool split16, b
         CU(cudaMalloc((void **)&s.q8_errmax, 4));
         CU(cudaMemset(s.q8_errmax, 0, 4));
     }
-    CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
-    CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
-    CU(cudaMalloc((void **)&s.chunk_ids, cap_rows * 16));
+    if (!attach_only) {
+        CU(cudaMalloc((void **)&s.inv_norm, cap_rows * 4));
+        CU(cudaMalloc((void **)&s.doc_slot, cap_rows * 4));
+        CU(cudaMalloc((void **)&s.chunk_ids, cap_rows * 16));
+    }
     const size_t cta_keys = (size_t)da::scan_grid_for(s.sm_count) * da::kMaxNQ * DA_MAX_K;
     CU(cudaMalloc((void **)&s.d_cta, cta_keys * sizeof(da::key_t64)));
     CU(cudaMalloc((void **)&s.d_counter, sizeof(unsigned int)));
@@ -1289,6 +1434,7 @@ void da_store_destroy(da_store *st)
     if (!st->shards.empty()) cudaSetDevice(st->shards[0].device);
     for (auto &sl : st->slots) free_slot(*sl);
     for (Shard &s : st->shards) free_shard(s);
+    shm_close(st);
     delete st;
 }
 
@@ -1296,7 +1442,9 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
 {
     if (!st || !doc_id) return fail(DA_ERR_INVALID, "store/doc_id is NULL");
     if (n && !chunk_ids) return fail(DA_ERR_INVALID, "chunk_ids is NULL");
+    if (st->attached) return fail(DA_ERR_STATE, "an attached store is read-only: chunks are announced in the exporting process");
     std::unique_lock<std::shared_mutex> lock(st->mu);
+    ShmWriteGuard shared_writer(st);
     const Id16 did = load_id(doc_id);
     uint32_t slot;
     auto it = st->doc_slot_of.find(did);
@@ -1304,6 +1452,7 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
         slot = (uint32_t)st->docs.size();
         st->docs.push_back(DocInfo{did, -1, 0, false, {}});
         st->doc_slot_of.emplace(did, slot);
+        shm_append(st, kRecDoc, slot, 0, 0, &did);
     } else slot = it->second;
     for (size_t i = 0; i < n; i++) {
         const Id16 cid = load_id(chunk_ids + 16 * i);
@@ -1313,6 +1462,8 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
         if (c->second.row != kNoRow) {
             st->docs[c->second.slot].rows--; st->docs[slot].rows++;
             st->docs[c->second.slot].fragment(); st->docs[slot].fragment();      // their rows are no longer whole runs
+            shm_append(st, kRecFragment, c->second.slot, 0, st->docs[c->second.slot].rows);
+            shm_append(st, kRecFragment, slot, 0, st->docs[slot].rows);
         }
         c->second.slot = slot;
         if (c->second.row != kNoRow) {   // the chunk already has a vector: move its row to the new document
@@ -1322,6 +1473,7 @@ int da_store_save_chunks(da_store *st, const uint8_t doc_id[16], const uint8_t *
             CU(cudaStreamSynchronize(s.stream));
         }
     }
+    shm_publish(st);
     return DA_OK;
 }
 
@@ -1331,7 +1483,9 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
     if (n == 0) return DA_OK;                                   // postgres.go:177-179
     if (!chunk_ids || !vecs) return fail(DA_ERR_INVALID, "chunk_ids/vecs is NULL");
     if (dim != st->dim) return fail(DA_ERR_DIM, "expected %d dimensions, not %d", st->dim, dim);
+    if (st->attached) return fail(DA_ERR_STATE, "an attached store is read-only: embeddings are saved in the exporting process");
     std::unique_lock<std::shared_mutex> lock(st->mu);
+    ShmWriteGuard shared_writer(st);
 
     // Validate everything before the store changes: the reference's statement is atomic.  Ids on the host,
     // vector elements on the device (staged, checked, and only then committed).
@@ -1472,13 +1626,22 @@ int da_store_save_embeddings(da_store *st, const uint8_t *chunk_ids, const float
         CU(cudaStreamSynchronize(sh.stream));
         sh.n_rows += pending[s];
     }
+    uint32_t run_slot = 0, run_first = 0, run_count = 0;
     for (size_t i = 0; i < n; i++) {
         if (info[i]->row == kNoRow) {                                        // a new embedding (an overwrite keeps its row)
             st->docs[info[i]->slot].rows++;
             st->docs[info[i]->slot].add_row(tgt_row[i]);
+            // shared log: runs of new rows of one document (one record per document in the usual call)
+            if (run_count && run_slot == info[i]->slot && run_first + run_count == tgt_row[i]) run_count++;
+            else {
+                if (run_count) shm_append(st, kRecRows, run_slot, run_first, run_count);
+                run_slot = info[i]->slot; run_first = tgt_row[i]; run_count = 1;
+            }
         }
         info[i]->shard = tgt_shard[i]; info[i]->row = tgt_row[i];
     }
+    if (run_count) shm_append(st, kRecRows, run_slot, run_first, run_count);
+    shm_publish(st);
     return DA_OK;
 }
 
@@ -1504,6 +1667,11 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
 {
     if (!st) return fail(DA_ERR_INVALID, "store is NULL");
     if (!out_n) return fail(DA_ERR_INVALID, "out_n is NULL");
+    ShmReadGuard shared_reader(st);                // an attached store: the exporting process is not mid-write while we look
+    {
+        const int rr = shm_refresh(st);            // ... and what it has saved since our last search becomes visible
+        if (rr != DA_OK) return rr;
+    }
     {
         const int fr = search_fast(st, p, out_chunk_ids, out_scores, out_rows, out_n);     // one query, one shard: the short way
         if (fr != 0) return fr < 0 ? fr : DA_OK;
@@ -1684,6 +1852,11 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
 {
     if (!st || !out_total_ms) return fail(DA_ERR_INVALID, "store/out is NULL");
     if (iters < 1) return fail(DA_ERR_INVALID, "iters must be >= 1");
+    ShmReadGuard shared_reader(st);
+    {
+        const int rr = shm_refresh(st);
+        if (rr != DA_OK) return rr;
+    }
     {   // one query on one shard: the small-search path, its inputs uploaded once, `iters` scans back to back
         std::shared_lock<std::shared_mutex> shared(st->mu);
         FastPlan fp;
@@ -1769,6 +1942,7 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     if (p->struct_size != sizeof(da_ivf_params)) return fail(DA_ERR_INVALID, "da_ivf_params.struct_size mismatch");
     if (p->lists < 1 || p->lists > 65536) return fail(DA_ERR_INVALID, "lists=%d out of range [1, 65536]", p->lists);
     if (st->split16) return fail(DA_ERR_STATE, "IVFFlat is not available with the split-plane layout");
+    if (st->attached) return fail(DA_ERR_STATE, "an attached store is read-only: build the index in the exporting process");
     std::unique_lock<std::shared_mutex> lock(st->mu);
     const int L = p->lists, D = st->dim;
     const int iters = p->iters <= 0 ? 10 : std::min(p->iters, 20);
@@ -1927,7 +2101,9 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
     if (p->struct_size != sizeof(da_synth_params)) return fail(DA_ERR_INVALID, "da_synth_params.struct_size mismatch");
     if (!p->chunks_per_doc || !p->n_clusters) return fail(DA_ERR_INVALID, "chunks_per_doc/n_clusters must be > 0");
     if (p->row_lo + p->n_rows > 0xFFFFFFF0ull) return fail(DA_ERR_CAPACITY, "rows exceed 2^32");
+    if (st->attached) return fail(DA_ERR_STATE, "an attached store is read-only");
     std::unique_lock<std::shared_mutex> lock(st->mu);
+    ShmWriteGuard shared_writer(st);
     const int S = (int)st->shards.size();
     for (Shard &s : st->shards)
         if (s.n_rows) return fail(DA_ERR_STATE, "generate_synthetic needs an empty store");
@@ -1991,11 +2167,14 @@ int da_store_generate_synthetic(da_store *st, const da_synth_params *p)
                 DocInfo di{k, 0, (uint32_t)(last - first), false, {}};
                 if (S == 1) di.ranges.emplace_back((uint32_t)(first - p->row_lo), (uint32_t)(last - first));
                 else di.fragmented = true;             // a synthetic fill over several shards does not track ranges
+                shm_append(st, kRecDoc, (uint32_t)st->docs.size(), 0, 0, &k);
+                if (S == 1) shm_append(st, kRecRows, (uint32_t)st->docs.size(), di.ranges[0].first, di.ranges[0].second);
                 st->docs.push_back(std::move(di));
             }
         }
     }
     for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+    shm_publish(st);
     return DA_OK;
 }
 
@@ -2020,6 +2199,11 @@ int da_synth_ids(const da_synth_params *p, int32_t kind, uint64_t first, uint64_
 int da_store_stats(da_store *st, da_stats *out)
 {
     if (!st || !out) return fail(DA_ERR_INVALID, "store/out is NULL");
+    {
+        ShmReadGuard shared_reader(st);
+        const int rr = shm_refresh(st);
+        if (rr != DA_OK) return rr;
+    }
     std::unique_lock<std::shared_mutex> lock(st->mu);
     std::lock_guard<std::mutex> sg(st->stats_mu);
     memset(out, 0, sizeof *out);
@@ -2091,11 +2275,117 @@ int da_store_doc_rows(da_store *st, const uint8_t *doc_ids, size_t n_docs, uint3
 {
     if (!st) return fail(DA_ERR_INVALID, "store is NULL");
     if (n_docs && (!doc_ids || !out_rows)) return fail(DA_ERR_INVALID, "doc_ids/out_rows is NULL");
+    ShmReadGuard shared_reader(st);
+    {
+        const int rr = shm_refresh(st);
+        if (rr != DA_OK) return rr;
+    }
     std::unique_lock<std::shared_mutex> lock(st->mu);
     for (size_t i = 0; i < n_docs; i++) {
         auto it = st->doc_slot_of.find(load_id(doc_ids + 16 * i));
         out_rows[i] = it == st->doc_slot_of.end() ? 0u : st->docs[it->second].rows;
     }
+    return DA_OK;
+}
+
+int da_store_export(da_store *st, const char *shm_name)
+{
+    if (!st || !shm_name || shm_name[0] != '/') return fail(DA_ERR_INVALID, "store is NULL or the name does not start with '/'");
+    std::unique_lock<std::shared_mutex> lock(st->mu);
+    if (st->attached || st->shm.hdr) return fail(DA_ERR_STATE, "this store is already shared");
+    if (st->shards.size() != 1 || st->total_ranks != 1 || st->split16)
+        return fail(DA_ERR_STATE, "only a single-GPU store in the default fp32 layout can be exported");
+    Shard &s = st->shards[0];
+    CU(cudaSetDevice(s.device));
+    // one record per document plus one per run of rows in the usual flow; room for a sixteenth of the rows, at least 64 Ki
+    const uint64_t max_records = std::max<uint64_t>(65536, s.cap_rows / 16 + 2 * (uint64_t)st->docs.size() + 8 * kMaxDocRanges);
+    const size_t bytes = sizeof(ShmHeader) + (size_t)max_records * sizeof(ShmRecord);
+    shm_unlink(shm_name);
+    const int fd = shm_open(shm_name, O_CREAT | O_EXCL | O_RDWR, 0600);
+    if (fd < 0) return fail(DA_ERR_STATE, "shm_open(%s) failed: %s", shm_name, strerror(errno));
+    if (ftruncate(fd, (off_t)bytes) != 0) { close(fd); shm_unlink(shm_name); return fail(DA_ERR_STATE, "ftruncate failed: %s", strerror(errno)); }
+    void *mem = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (mem == MAP_FAILED) { shm_unlink(shm_name); return fail(DA_ERR_STATE, "mmap failed: %s", strerror(errno)); }
+    ShmHeader *h = new (mem) ShmHeader();
+    h->version = 1; h->dim = (uint32_t)st->dim; h->capacity_rows = s.cap_rows; h->min_sim = st->min_sim; h->row_base = s.row_base;
+    h->max_records = max_records;
+    h->n_records.store(0); h->n_rows.store(0); h->overflow.store(0);
+    cudaError_t ce = cudaDeviceGetPCIBusId(h->device_bus_id, (int)sizeof h->device_bus_id, s.device);
+    if (ce == cudaSuccess) ce = cudaIpcGetMemHandle(&h->h_mat, s.mat);
+    if (ce == cudaSuccess) ce = cudaIpcGetMemHandle(&h->h_inv, s.inv_norm);
+    if (ce == cudaSuccess) ce = cudaIpcGetMemHandle(&h->h_slot, s.doc_slot);
+    if (ce == cudaSuccess) ce = cudaIpcGetMemHandle(&h->h_ids, s.chunk_ids);
+    pthread_rwlockattr_t at;
+    pthread_rwlockattr_init(&at);
+    pthread_rwlockattr_setpshared(&at, PTHREAD_PROCESS_SHARED);
+    pthread_rwlockattr_setkind_np(&at, PTHREAD_RWLOCK_PREFER_WRITER_NONRECURSIVE_NP);     // searches must not starve the writer
+    const int lrc = pthread_rwlock_init(&h->lock, &at);
+    pthread_rwlockattr_destroy(&at);
+    if (ce != cudaSuccess || lrc != 0) {
+        munmap(mem, bytes); shm_unlink(shm_name);
+        return fail(DA_ERR_CUDA, "export failed: %s", ce != cudaSuccess ? cudaGetErrorString(ce) : strerror(lrc));
+    }
+    st->shm.hdr = h; st->shm.rec = reinterpret_cast<ShmRecord *>(h + 1); st->shm.bytes = bytes;
+    st->shm.name = shm_name; st->shm.owner = true; st->shm.pending = 0;
+    // what the store already holds, as the same records a reader replays
+    for (uint32_t slot = 0; slot < st->docs.size(); slot++) {
+        const DocInfo &d = st->docs[slot];
+        shm_append(st, kRecDoc, slot, 0, 0, &d.id);
+        if (d.fragmented) shm_append(st, kRecFragment, slot, 0, d.rows);
+        else for (const auto &r : d.ranges) shm_append(st, kRecRows, slot, r.first, r.second);
+    }
+    CU(cudaStreamSynchronize(s.stream));
+    h->magic = kShmMagic;                      // last: a reader that sees the magic sees a complete header
+    shm_publish(st);
+    return DA_OK;
+}
+
+int da_store_attach(const char *shm_name, da_store **out)
+{
+    if (!shm_name || !out) return fail(DA_ERR_INVALID, "name/out is NULL");
+    *out = nullptr;
+    const int fd = shm_open(shm_name, O_RDWR, 0600);
+    if (fd < 0) return fail(DA_ERR_STATE, "shm_open(%s) failed: %s (has the other process exported its store?)", shm_name, strerror(errno));
+    struct stat sb;
+    if (fstat(fd, &sb) != 0 || (size_t)sb.st_size < sizeof(ShmHeader)) { close(fd); return fail(DA_ERR_STATE, "%s is not an exported store", shm_name); }
+    void *mem = mmap(nullptr, (size_t)sb.st_size, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (mem == MAP_FAILED) return fail(DA_ERR_STATE, "mmap failed: %s", strerror(errno));
+    ShmHeader *h = static_cast<ShmHeader *>(mem);
+    if (h->magic != kShmMagic || h->version != 1 ||
+        (size_t)sb.st_size < sizeof(ShmHeader) + (size_t)h->max_records * sizeof(ShmRecord)) {
+        munmap(mem, (size_t)sb.st_size);
+        return fail(DA_ERR_STATE, "%s is not an exported store of this library version", shm_name);
+    }
+    int device = -1;
+    if (cudaDeviceGetByPCIBusId(&device, h->device_bus_id) != cudaSuccess || device < 0) {
+        munmap(mem, (size_t)sb.st_size);
+        return fail(DA_ERR_CUDA, "the exporting process's GPU (%s) is not visible to this process", h->device_bus_id);
+    }
+    da_store *st = new da_store();
+    st->dim = (int)h->dim; st->min_sim = h->min_sim;
+    st->attached = true;
+    st->shm.hdr = h; st->shm.rec = reinterpret_cast<ShmRecord *>(h + 1); st->shm.bytes = (size_t)sb.st_size;
+    st->shm.name = shm_name; st->shm.owner = false;
+    st->shards.resize(1);
+    Shard &s = st->shards[0];
+    int rc = init_shard(s, device, st->dim, h->capacity_rows, false, false, true);
+    if (rc == DA_OK) {
+        s.row_base = h->row_base;
+        cudaError_t ce = cudaIpcOpenMemHandle((void **)&s.mat, h->h_mat, cudaIpcMemLazyEnablePeerAccess);
+        if (ce == cudaSuccess) ce = cudaIpcOpenMemHandle((void **)&s.inv_norm, h->h_inv, cudaIpcMemLazyEnablePeerAccess);
+        if (ce == cudaSuccess) ce = cudaIpcOpenMemHandle((void **)&s.doc_slot, h->h_slot, cudaIpcMemLazyEnablePeerAccess);
+        if (ce == cudaSuccess) ce = cudaIpcOpenMemHandle((void **)&s.chunk_ids, h->h_ids, cudaIpcMemLazyEnablePeerAccess);
+        if (ce != cudaSuccess) rc = fail(DA_ERR_CUDA, "cudaIpcOpenMemHandle failed: %s (attach from a process other than the exporter)", cudaGetErrorString(ce));
+    }
+    if (rc == DA_OK) {
+        pthread_rwlock_rdlock(&h->lock);
+        rc = shm_replay(st);
+        pthread_rwlock_unlock(&h->lock);
+    }
+    if (rc != DA_OK) { da_store_destroy(st); return rc; }
+    *out = st;
     return DA_OK;
 }
 

@@ -109,6 +109,24 @@ class GpuStore:
         self._chunks: dict[uuid.UUID, Chunk] = {}
         self._summaries: dict[uuid.UUID, Summary] = {}
 
+    # -- one store, two processes (writer = analysis agent, reader = query agent) -------
+    def export(self, shm_name: str) -> None:
+        """Publish this store under a POSIX shared-memory name so that another process can attach to it."""
+        _check(self._lib.da_store_export(self._h, shm_name.encode()))
+
+    @classmethod
+    def attach(cls, shm_name: str) -> "GpuStore":
+        """Read-only view, in THIS process, of the store another process exported: same HBM, kept current."""
+        self = cls.__new__(cls)
+        self._lib = L.load()
+        self._h = C.c_void_p()
+        _check(self._lib.da_store_attach(shm_name.encode(), C.byref(self._h)))
+        s = self.stats()
+        self.dim = s.dim
+        self.min_similarity = L.DA_DEFAULT_MIN_SIMILARITY
+        self._chunks, self._summaries = {}, {}
+        return self
+
     # -- lifecycle ---------------------------------------------------------------------
     def close(self) -> None:
         if getattr(self, "_h", None) and self._h.value:

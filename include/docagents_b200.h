@@ -124,6 +124,20 @@ int da_store_bulk_load(da_store *st, const uint8_t *chunk_ids, const uint8_t *do
 int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const float *query,
                   int32_t dim, int32_t k, uint8_t *out_chunk_ids, float *out_scores, int32_t *out_n);
 
+/* One device store, two processes.  In the reference the writer and the reader of this path are
+ * different processes: the analysis agent calls SaveEmbeddings (cmd/analysis/main.go:106), the query agent calls
+ * TopK (cmd/query/main.go:101), both against one Postgres (docker-compose.yml:87-128).  Here both name one store:
+ *   da_store_export   the process that owns the store (single GPU, default fp32 layout) publishes it under a POSIX
+ *                     shared-memory name ("/docagents-gpu0"): CUDA IPC handles of the resident arrays, a log of the
+ *                     documents and row runs it holds, a process-shared lock.  It keeps saving as before.
+ *   da_store_attach   another process on the same GPU maps the same HBM read-only.  Every search first replays what
+ *                     the exporter has appended since, so a document saved there is found by the next TopK here.
+ *                     Saving, index building and synthetic fills are refused (DA_ERR_STATE) on an attached store.
+ * A search in the attached process and a save in the exporter exclude each other (the shared lock), so a reader never
+ * sees a half-written upsert.  Destroying the exporter's store removes the name; attached stores must be destroyed first. */
+int da_store_export(da_store *st, const char *shm_name);
+int da_store_attach(const char *shm_name, da_store **out);
+
 /* How many embeddings of each of n_docs documents are resident (0 = the store has never been given the document).
  * No SQL counterpart; it is what lets a reader process notice that a document named by a request
  * (document_ids is required: cmd/query/main.go:20-24) was embedded by ANOTHER process (the analysis agent:

@@ -48,8 +48,9 @@ import (
 // each requested document (da_store_doc_rows) and loads the documents it has never seen.
 type GPUStore struct {
 	*PostgresStore
-	h   *C.da_store
-	dim int
+	h        *C.da_store
+	dim      int
+	readOnly bool // attached to another process's store: saves go to Postgres only, the writer's process feeds the device
 
 	mu    sync.Mutex
 	stale map[uuid.UUID]struct{} // documents whose device copy may be behind Postgres (a device upsert failed)
@@ -63,6 +64,11 @@ type GPUOptions struct {
 	Int8Sidecar   bool    // GPU_INT8_SIDECAR: keep an int8 copy of every row (25 % more HBM, ~3.6x queries/s, same answers)
 	BatchWindowUs uint32  // GPU_BATCH_WINDOW_US: merge TopK calls that arrive within this window into one pass (0 = off)
 	Preload       bool    // GPU_PRELOAD: stream embeddings JOIN chunks into the device store at start
+	// One device store for both agents (same GPU, two processes): the analysis agent creates the store and exports
+	// it under SharedName (da_store_export); the query agent sets Attach and maps the same HBM read-only
+	// (da_store_attach) -- every TopK there first replays what the writer has saved since.
+	SharedName string // GPU_SHARED_NAME, e.g. "/docagents-gpu0"; empty = a private store
+	Attach     bool   // GPU_ATTACH: this process only reads the store exported under SharedName
 }
 
 // call runs one C entry point and, if it failed, fetches its message.  da_last_error() is
@@ -96,9 +102,25 @@ func NewGPU(ctx context.Context, pg *PostgresStore, o GPUOptions) (*GPUStore, er
 		cfg.flags |= C.DA_STORE_Q8_SIDECAR
 	}
 	cfg.batch_window_us = C.uint32_t(o.BatchWindowUs)
-	s := &GPUStore{PostgresStore: pg, dim: o.Dim, stale: map[uuid.UUID]struct{}{}}
+	s := &GPUStore{PostgresStore: pg, dim: o.Dim, stale: map[uuid.UUID]struct{}{}, readOnly: o.Attach}
+	if o.Attach {
+		name := C.CString(o.SharedName)
+		defer C.free(unsafe.Pointer(name))
+		if err := call(func() C.int { return C.da_store_attach(name, &s.h) }); err != nil {
+			return nil, err
+		}
+		return s, nil // the exporting process loads and saves; this one follows its log
+	}
 	if err := call(func() C.int { return C.da_store_create(&cfg, &s.h) }); err != nil {
 		return nil, err
+	}
+	if o.SharedName != "" {
+		name := C.CString(o.SharedName)
+		defer C.free(unsafe.Pointer(name))
+		if err := call(func() C.int { return C.da_store_export(s.h, name) }); err != nil {
+			s.Close()
+			return nil, err
+		}
 	}
 	if o.Preload {
 		if err := s.load(ctx, nil); err != nil { // every document
@@ -183,7 +205,7 @@ func (s *GPUStore) load(ctx context.Context, docIDs []uuid.UUID) error {
 // needs chunk -> document.
 func (s *GPUStore) SaveChunks(ctx context.Context, docID uuid.UUID, chunks []Chunk) ([]Chunk, error) {
 	out, err := s.PostgresStore.SaveChunks(ctx, docID, chunks)
-	if err != nil || len(out) == 0 {
+	if err != nil || len(out) == 0 || s.readOnly {
 		return out, err
 	}
 	ids := make([]byte, 16*len(out))
@@ -214,6 +236,9 @@ func (s *GPUStore) SaveEmbeddings(ctx context.Context, embs []Embedding) error {
 	}
 	if err := s.PostgresStore.SaveEmbeddings(ctx, embs); err != nil {
 		return err
+	}
+	if s.readOnly {
+		return nil
 	}
 	dim := len(embs[0].Vector)
 	ids := make([]byte, 16*len(embs))
@@ -312,6 +337,13 @@ func (s *GPUStore) ensureResident(ctx context.Context, docIDs []uuid.UUID) (map[
 	s.mu.Unlock()
 	if len(want) == 0 {
 		return nil, nil
+	}
+	if s.readOnly { // only the exporting process can load: answer these from Postgres until it has them
+		bad := make(map[uuid.UUID]struct{}, len(want))
+		for _, d := range want {
+			bad[d] = struct{}{}
+		}
+		return bad, nil
 	}
 	if err := s.load(ctx, want); err != nil {
 		bad := make(map[uuid.UUID]struct{}, len(want))

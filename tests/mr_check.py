@@ -75,7 +75,7 @@ def main():
         exact = st.search(qs[i], k, all_docs=True)
         ivf_all = st.search(qs[i], k, all_docs=True, ivf=True, probes=24)
         assert np.array_equal(exact[2][0], ivf_all[2][0]) and np.array_equal(exact[0][0], ivf_all[0][0])
-        ivf_some = st.search(qs[i], k, all_docs=True, ivf=True, probes=4)
+        ivf_some = st.search(qs[i], k, all_docs=True, ivf=True, probes=8)
         assert len(np.intersect1d(ivf_some[2][0], exact[2][0])) >= k - 1
     # an unknown document everywhere => nil on every rank, collective still matched
     assert len(st.search(qs[0], k, doc_ids=oracle.doc_ids(S, 10_000, 1))[2][0]) == 0

@@ -71,7 +71,8 @@ def test_ivf_on_two_shards_shares_centroids_and_probes_exactly():
             exact = two.search(q, K, all_docs=True)
             full = two.search(q, K, all_docs=True, ivf=True, probes=32)
             assert np.array_equal(exact[2][0], full[2][0]) and np.array_equal(exact[0][0], full[0][0])
-            some = two.search(q, K, all_docs=True, ivf=True, probes=4)
+            # (balanced lists: a cluster holds about four of the 32 lists, sometimes five or six)
+            some = two.search(q, K, all_docs=True, ivf=True, probes=8)
             assert len(np.intersect1d(some[2][0], exact[2][0])) >= K - 1
 
 
