@@ -48,6 +48,23 @@ constexpr int kScanThreads = 512;
 constexpr int kScanWarps = kScanThreads / 32;
 constexpr int kMaxNQ = 8;          // queries served by one pass of the SIMT scan
 
+// Cross-GPU exchange fused into the scan (one process per GPU): every rank's last CTA stores its records into its
+// slot of EVERY rank's exchange buffer (plain stores through CUDA IPC mappings over NVLink), announces them on
+// each rank's arrival counter, waits until its own counter shows all ranks, and merges -- no collective kernel,
+// no merge kernel, no host round trip.  Buffer layout per rank: [counter parity 0][counter parity 1] (128 B apart)
+// then data[parity][rank] of slot_bytes each, from byte 256.  Searches alternate parity; counters only grow.
+constexpr int kXchgMaxRanks = 8;
+struct XchgArgs {
+    unsigned char *peer[kXchgMaxRanks];     // every rank's buffer as mapped in THIS process (peer[rank] = own)
+    int n_ranks, rank;                      // n_ranks <= 1: no exchange
+    uint32_t slot_bytes;
+    uint32_t parity;
+    unsigned long long target;              // own counter value that means "all ranks delivered"
+    key_t64 *final_keys;                    // merged result of this rank: nq x k keys, nq x k x 16 ids
+    uint8_t *final_ids;
+    uint32_t *timeout_flag;                 // set to 1 if a peer did not deliver within the bound (then the result is invalid)
+};
+
 struct ScanArgs {
     const float *mat;              // n_rows x dim, row-major, 16-byte aligned rows (nullptr in split-plane stores)
     const uint16_t *hi;            // split-plane stores: upper 16 bits of every element, n_rows x dim (dim % 16 == 0)
@@ -82,6 +99,7 @@ struct ScanArgs {
     uint32_t *n_rows_reset;
     volatile unsigned long long *done_flag;
     unsigned long long done_value;
+    XchgArgs xg;
     uint32_t n_rows;               // rows to visit when row_list is null
     uint32_t row_base;             // global row of local row 0
     int dim;

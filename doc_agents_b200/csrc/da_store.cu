@@ -81,6 +81,7 @@ struct Id16Hash {
 inline Id16 load_id(const uint8_t *p) { Id16 k; memcpy(&k, p, 16); return k; }
 
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+constexpr uint32_t kXchgSlotBytes = da::kMaxNQ * DA_MAX_K * 24;      // one rank's records of one pass (<= 8 queries, k <= 128)
 constexpr size_t kRecTrailer = 16;      // bytes after a rank's record block in a multi-process store: its overflow flag
 
 struct ChunkInfo { uint32_t slot; int32_t shard; uint32_t row; };
@@ -159,6 +160,9 @@ struct Shard {
     std::vector<cudaEvent_t> ev_pool;   // extra pairs for per-launch timing inside a bench loop
     cudaEvent_t ev_done = nullptr;      // peer-gather mode: this shard's records have been written
     ncclComm_t comm = nullptr;
+    // fused cross-GPU exchange (one process per GPU): own buffer, every rank's buffer as mapped here (CUDA IPC)
+    unsigned char *xg_buf = nullptr;
+    unsigned char *xg_peer[da::kXchgMaxRanks] = {};
     // search state
     DevBuf<float> d_queries, d_qinv;
     DevBuf<uint32_t> d_bitmap;
@@ -310,6 +314,8 @@ struct da_store {
     bool split16 = false;          // split-plane resident format (DA_STORE_SPLIT16)
     bool q8 = false;               // int8 sidecar next to the fp32 rows (DA_STORE_Q8_SIDECAR)
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
+    bool xg_ok = false;            // one process per GPU, every peer's exchange buffer mapped: the scan exchanges and merges itself
+    uint64_t xg_seq = 0;           // fused searches so far (the same on every rank: searches are collective)
     // small-search path (single shard, single process): slots and the statistics they update
     std::mutex slot_mu;
     std::condition_variable slot_cv;
@@ -331,6 +337,9 @@ void free_shard(Shard &s)
 {
     cudaSetDevice(s.device);
     free_ivf(s);
+    for (int r = 0; r < da::kXchgMaxRanks; r++)
+        if (s.xg_peer[r] && s.xg_peer[r] != s.xg_buf) cudaIpcCloseMemHandle(s.xg_peer[r]);
+    cudaFree(s.xg_buf);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
     if (s.ipc_mapped) {
@@ -576,6 +585,7 @@ struct SearchPlan {
     size_t bitmap_words;
     bool ivf;
     int probes;
+    bool fused_xchg;   // several processes: the scan's last CTA exchanges the records with the other GPUs and merges (no collective)
     bool need_qinv;    // some kernel of the plan reads 1/|q| from memory (candidate paths); the plain scans compute it themselves
     bool ivf_tc;       // IVFFlat: rank the centroids for the whole batch with one tensor-core GEMM (batches of 8+)
     int ivf_ks;        // ... slices of the dimension of that GEMM
@@ -607,7 +617,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             CU(cudaStreamWaitEvent(s.stream, st->shards[0].ev_done, 0));
         uint8_t *out_ids = rec_base;
         da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(rec_base + (size_t)pl.batch * pl.k * 16);
-        if (s.n_rows == 0 || pl.none_requested) {   // an empty shard, or no known document requested: an empty record block
+        if ((s.n_rows == 0 || pl.none_requested) && !pl.fused_xchg) {   // an empty shard, or no known document requested: an empty record block
             CU(cudaMemsetAsync(rec_base, 0, rec_bytes, s.stream));
             CU(cudaEventRecord(first && e1 ? e1 : s.ev_scan1, s.stream));
             if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
@@ -732,6 +742,23 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             a.out_keys = out_keys + (size_t)q0 * pl.k;
             a.out_ids = out_ids + (size_t)q0 * pl.k * 16;
             a.rows_read = s.d_rows_read;
+            if (pl.fused_xchg) {
+                // the records go to this rank's slot of its own exchange buffer; the last CTA copies them into every
+                // other rank's buffer, waits for theirs, and writes the merged answer to d_final
+                da::XchgArgs &x = a.xg;
+                const int N = st->total_ranks;
+                for (int r = 0; r < N; r++) x.peer[r] = s.xg_peer[r];
+                x.n_ranks = N; x.rank = st->rank; x.slot_bytes = kXchgSlotBytes;
+                x.parity = (uint32_t)(st->xg_seq & 1);
+                x.target = (unsigned long long)N * (st->xg_seq / 2 + 1);
+                unsigned char *slot = s.xg_buf + 256 + ((size_t)x.parity * N + st->rank) * kXchgSlotBytes;
+                a.out_ids = slot;
+                a.out_keys = reinterpret_cast<da::key_t64 *>(slot + (size_t)a.nq * pl.k * 16);
+                x.final_ids = s.d_final.p;
+                x.final_keys = reinterpret_cast<da::key_t64 *>(s.d_final.p + (size_t)pl.batch * pl.k * 16);
+                x.timeout_flag = reinterpret_cast<uint32_t *>(s.d_final.p + rec_bytes + 4);
+                st->xg_seq++;
+            }
             if (st->split16) {             // scan the upper plane for candidates, then the exact finish from both planes
                 a.mat = nullptr; a.hi = s.hi; a.approx = s.d_approx.p;
                 a.min_sim = pl.min_sim - da::kSplitEps;
@@ -767,7 +794,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
     }
     st->scan_launches++;        // one timed unit per search: scan_ms_sum and last_bytes both cover ALL passes of a search
-    if (st->total_ranks > 1) {
+    if (st->total_ranks > 1 && !pl.fused_xchg) {
         Shard &s0 = st->shards[0];
         if (st->p2p_gather) {
             CU(cudaSetDevice(s0.device));
@@ -814,6 +841,46 @@ int ivf_tc_min_batch()
 {
     static const int env = [] { const char *v = getenv("DA_IVF_TC_MIN_BATCH"); return v ? atoi(v) : 0; }();
     return env > 0 ? env : 8;
+}
+
+// One process per GPU: give every rank a mapping of every rank's exchange buffer (CUDA IPC handles travel through
+// the NCCL communicator that exists anyway).  All ranks agree on the outcome; without it searches keep the
+// all-gather + merge kernels.
+int setup_fused_exchange(da_store *st)
+{
+    Shard &s = st->shards[0];
+    const int N = st->total_ranks, me = st->rank;
+    if (N < 2 || N > da::kXchgMaxRanks || st->shards.size() != 1) return DA_OK;
+    if (const char *v = getenv("DA_DISABLE_FUSED_EXCHANGE")) if (v[0] == '1') return DA_OK;
+    CU(cudaSetDevice(s.device));
+    const size_t bytes = 256 + (size_t)2 * N * kXchgSlotBytes;
+    CU(cudaMalloc((void **)&s.xg_buf, bytes));
+    CU(cudaMemsetAsync(s.xg_buf, 0, bytes, s.stream));
+    cudaIpcMemHandle_t mine;
+    CU(cudaIpcGetMemHandle(&mine, s.xg_buf));
+    unsigned char *d_handles = nullptr;
+    int *d_ok = nullptr;
+    CU(cudaMalloc((void **)&d_handles, (size_t)N * sizeof mine));
+    CU(cudaMalloc((void **)&d_ok, sizeof(int)));
+    CU(cudaMemcpyAsync(d_handles + (size_t)me * sizeof mine, &mine, sizeof mine, cudaMemcpyHostToDevice, s.stream));
+    NC(ncclAllGather(d_handles + (size_t)me * sizeof mine, d_handles, sizeof mine, ncclChar, s.comm, s.stream));
+    std::vector<cudaIpcMemHandle_t> all(N);
+    CU(cudaMemcpyAsync(all.data(), d_handles, (size_t)N * sizeof mine, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaStreamSynchronize(s.stream));
+    int ok = 1;
+    for (int r = 0; r < N; r++) {
+        if (r == me) { s.xg_peer[r] = s.xg_buf; continue; }
+        void *p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+        s.xg_peer[r] = static_cast<unsigned char *>(p);
+    }
+    CU(cudaMemcpyAsync(d_ok, &ok, sizeof ok, cudaMemcpyHostToDevice, s.stream));
+    NC(ncclAllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, s.comm, s.stream));
+    CU(cudaMemcpyAsync(&ok, d_ok, sizeof ok, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaStreamSynchronize(s.stream));
+    cudaFree(d_handles); cudaFree(d_ok);
+    st->xg_ok = ok == 1;
+    return DA_OK;
 }
 
 // What every search checks before anything is staged (the errors of the reference's statement: dimension mismatch,
@@ -944,6 +1011,12 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         pl.use_q8 = selected * 4 >= st->docs.size() && selected > 0;
     }
     pl.need_qinv = pl.use_tc || pl.use_q8 || st->split16;
+    // The scan exchanges and merges across GPUs itself when every rank is certain to run the same plan: that must
+    // follow from the call's arguments and the store's configuration alone (every document requested, one SIMT
+    // pass, no candidate path), never from what a rank happens to hold.
+    pl.fused_xchg = st->xg_ok && all_docs && !ivf && !st->split16 && p->batch <= da::scan_pick_nq(st->dim, pl.k, p->batch) &&
+                    (p->batch < tc_min_batch(st) || (p->flags & DA_SEARCH_NO_TENSOR)) && (!st->q8 || (p->flags & DA_SEARCH_NO_Q8)) &&
+                    !pl.use_tc && !pl.use_q8;
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
@@ -998,6 +1071,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         CU(s.d_out.ensure(rec_bytes + trailer)); CU(s.h_result.ensure(rec_bytes + trailer));
         if (st->total_ranks > 1) { CU(s.d_gather.ensure((rec_bytes + trailer) * st->total_ranks)); CU(s.d_final.ensure(rec_bytes + trailer)); }
         if (trailer) {
+            CU(cudaMemsetAsync(s.d_final.p + rec_bytes, 0, trailer, s.stream));     // flags: overflow (merge kernel), exchange timeout
             CU(cudaMemsetAsync(s.d_out.p + rec_bytes, 0, trailer, s.stream));
             if (!s.d_overflow.p) { CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1)); CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream)); *s.h_overflow.p = 0; }
         }
@@ -1423,6 +1497,10 @@ int da_store_create(const da_config *cfg, da_store **out)
             if (r != ncclSuccess) rc = fail(DA_ERR_NCCL, "ncclCommInitRank failed: %s", ncclGetErrorString(r));
         }
         if (rc != DA_OK) { da_store_destroy(st); return rc; }
+        if (world > 1 && cfg->n_devices == 1) {
+            rc = setup_fused_exchange(st);
+            if (rc != DA_OK) { da_store_destroy(st); return rc; }
+        }
     }
     *out = st;
     return DA_OK;
@@ -1699,6 +1777,8 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         if (rc != DA_OK) return rc;
         for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
         bool overflow = false;
+        if (trailer && *reinterpret_cast<const uint32_t *>(s0.h_result.p + rec_bytes + 4) != 0)
+            return fail(DA_ERR_STATE, "a rank did not deliver its candidates within 4 s (searches on a multi-process store are collective)");
         if (trailer)         // several processes: the OR of every rank's flag, the same word on every rank
             overflow = *reinterpret_cast<const uint32_t *>(s0.h_result.p + rec_bytes) != 0;
         else if (pl.use_tc || pl.use_q8 || st->split16)
@@ -2224,7 +2304,7 @@ int da_store_stats(da_store *st, da_stats *out)
     out->scan_ms_sum = st->scan_ms_sum; out->scan_launches = st->scan_launches;
     out->ivf_build_ms = st->ivf_build_ms; out->ivf_kmeans_ms = st->ivf_kmeans_ms;
     out->ivf_assign_ms = st->ivf_assign_ms; out->ivf_assign_tflops = st->ivf_assign_tflops;
-    out->peer_gather = st->p2p_gather ? 1 : 0; out->tensor_overflows = st->tc_overflows;
+    out->peer_gather = st->p2p_gather ? 1 : st->xg_ok ? 2 : 0; out->tensor_overflows = st->tc_overflows;
     { std::lock_guard<std::mutex> bl(st->bmu); out->topk_calls = st->topk_calls; out->topk_passes = st->topk_passes; }
     out->small_searches = st->fast_searches;
     out->last_bench_launches = st->bench_launches;

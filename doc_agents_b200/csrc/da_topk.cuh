@@ -167,6 +167,66 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned in
         }
         __syncthreads();
     }
+    // ---- exchange with the other GPUs (see XchgArgs): a.out_keys / a.out_ids ARE this rank's slot in its own buffer
+    if (a.xg.n_ranks > 1) {
+        const XchgArgs &x = a.xg;
+        const size_t data0 = 256 + (size_t)x.parity * x.n_ranks * x.slot_bytes;
+        const uint32_t rec16 = (uint32_t)(((size_t)a.nq * K * 24 + 15) / 16);       // 16-byte words of one record block
+        __syncthreads();
+        const uint4 *mine = reinterpret_cast<const uint4 *>(x.peer[x.rank] + data0 + (size_t)x.rank * x.slot_bytes);
+        for (int r = 0; r < x.n_ranks; r++) {
+            if (r == x.rank) continue;
+            uint4 *dst = reinterpret_cast<uint4 *>(x.peer[r] + data0 + (size_t)x.rank * x.slot_bytes);
+            for (uint32_t i = tid; i < rec16; i += kScanThreads) dst[i] = mine[i];
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            for (int r = 0; r < x.n_ranks; r++)
+                atomicAdd_system(reinterpret_cast<unsigned long long *>(x.peer[r] + (size_t)x.parity * 128), 1ull);
+            volatile unsigned long long *own = reinterpret_cast<volatile unsigned long long *>(x.peer[x.rank] + (size_t)x.parity * 128);
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while (*own < x.target) {
+                __nanosleep(64);
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 4000000000ull) { *x.timeout_flag = 1u; break; }      // 4 s: a peer never launched; do not hang the GPU
+            }
+            __threadfence_system();
+        }
+        __syncthreads();
+        // merge n_ranks x K keys per query (n_ranks * K <= P: the CTA's own list area is wide enough)
+        const unsigned char *base = x.peer[x.rank] + data0;
+        const size_t keys_off = (size_t)a.nq * K * 16;
+        for (int q = 0; q < a.nq; q++) {
+            key_t64 *mb = lists + (size_t)q * P;
+            for (int i = tid; i < P; i += kScanThreads) {
+                key_t64 v = 0ull;
+                if (i < x.n_ranks * K) {
+                    const int r = i / K, j = i % K;
+                    v = __ldcv(reinterpret_cast<const key_t64 *>(base + (size_t)r * x.slot_bytes + keys_off) + (size_t)q * K + j);
+                }
+                mb[i] = v;
+            }
+            cta_bitonic_desc(mb, P);
+            for (int i = tid; i < K; i += kScanThreads) {
+                const key_t64 key = mb[i];
+                uint4 id = make_uint4(0, 0, 0, 0);
+                if (key) {            // keys are unique across ranks (global rows): find the owner's id
+                    for (int r = 0; r < x.n_ranks; r++) {
+                        const key_t64 *kb = reinterpret_cast<const key_t64 *>(base + (size_t)r * x.slot_bytes + keys_off) + (size_t)q * K;
+                        const uint4 *ib = reinterpret_cast<const uint4 *>(base + (size_t)r * x.slot_bytes) + (size_t)q * K;
+                        for (int j = 0; j < K; j++)
+                            if (__ldcv(kb + j) == key) id = __ldcv(ib + j);
+                    }
+                }
+                x.final_keys[(size_t)q * K + i] = key;
+                reinterpret_cast<uint4 *>(x.final_ids)[(size_t)q * K + i] = id;
+            }
+            __syncthreads();
+        }
+    }
     // small-search extras (see ScanArgs): counters handed over and cleared, then the completion flag
     if (a.done_flag) __threadfence_system();             // this thread's record stores are visible to the host first
     __syncthreads();

@@ -242,7 +242,8 @@ typedef struct {
     float    ivf_kmeans_ms;         /* all k-means iterations (assignment GEMM + accumulate + finalize + all-reduce) */
     float    ivf_assign_ms;         /* final assignment GEMM over every resident row of shard 0 */
     float    ivf_assign_tflops;     /* 2 * rows * lists * dim / ivf_assign_ms */
-    int32_t  peer_gather;           /* 1: shards deliver their records into shard 0 over NVLink (no collective) */
+    int32_t  peer_gather;           /* 1: shards deliver their records into shard 0 over NVLink (no collective); 2: one process per
+                                       GPU and the scan's last CTA exchanges with every other GPU and merges (no collective, no merge kernel) */
     uint64_t tensor_overflows;      /* searches answered by the fp32 SIMT scan because a candidate list (tensor path, int8 sidecar) overflowed */
     uint64_t topk_calls;            /* da_store_topk calls answered */
     uint64_t topk_passes;           /* searches run for them (== topk_calls unless request batching merged some) */
