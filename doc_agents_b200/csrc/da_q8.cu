@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
     if (a.rows_read) {
         if (lane == 0 && my_rows_read) atomicAdd(a.rows_read, (unsigned long long)my_rows_read);
     }
-    scan_cta_epilogue(a, lists, &is_last_s, reinterpret_cast<key_t64 *>(smem_raw),
+    scan_cta_epilogue(a, scan_per_query(a), lists, &is_last_s, reinterpret_cast<key_t64 *>(smem_raw),
                       (int)(((size_t)NQ * a.dim + (size_t)NQ * P * sizeof(key_t64)) / sizeof(key_t64)));
 }
 

@@ -35,28 +35,29 @@ namespace {
 // the split-plane layout, where a 256-bit load brings 16 upper halves (truncated bf16) of a row of a.hi and every
 // row's approximate similarity is also stored to a.approx for the candidate pass (da_split.cu).
 template <int NQ, int R, int U, int VEC, bool FULL_TILES, bool INDIRECT>
-__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a_in)
+__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a)
 {
-    ScanArgs a = a_in;
-    // IVFFlat probe mode: this CTA serves query blockIdx.y; its rows are the concatenation of that query's lists
-    __shared__ uint32_t p_start[DA_IVF_MAX_PROBES + 1];       // first flat index of each probed list (+ total)
-    __shared__ uint32_t p_src[DA_IVF_MAX_PROBES];             // where the list starts in list_rows
+    ScanPerQuery pq = scan_per_query(a);
+    // IVFFlat probe mode / range mode: this CTA serves query blockIdx.y; its rows are the concatenation of that
+    // query's lists (or of the requested documents' row ranges)
+    __shared__ uint32_t p_start[DA_IVF_MAX_PROBES + 1];       // first flat index of each piece (+ total)
+    __shared__ uint32_t p_src[DA_IVF_MAX_PROBES];             // where the piece starts (in list_rows, or as a row number)
     const bool probe_mode = INDIRECT && (a.probe_keys != nullptr || a.ranges != nullptr);
     if (probe_mode) {
         const size_t qy = blockIdx.y;
-        a.queries += qy * a.dim;
-        if (a.q_inv_norm) a.q_inv_norm += qy;
-        if (a.doc_bitmap) a.doc_bitmap += qy * a.bitmap_stride;
-        a.bitmap_stride = 0;
-        a.cta_out += qy * gridDim.x * a.k;
-        a.counter += qy;
-        a.out_keys += qy * a.k;
-        if (a.out_ids) a.out_ids += qy * a.k * 16;
-        if (a.probe_keys) a.probe_keys += qy * a.probes;
+        pq.queries += qy * a.dim;
+        if (pq.q_inv_norm) pq.q_inv_norm += qy;
+        if (pq.doc_bitmap) pq.doc_bitmap += qy * a.bitmap_stride;
+        pq.bitmap_stride = 0;
+        pq.cta_out += qy * gridDim.x * a.k;
+        pq.counter += qy;
+        pq.out_keys += qy * a.k;
+        if (pq.out_ids) pq.out_ids += qy * a.k * 16;
+        if (pq.probe_keys) pq.probe_keys += qy * a.probes;
         if (threadIdx.x < (unsigned)a.probes) {
             uint32_t off = 0, len = 0;
-            if (a.probe_keys) {
-                const key_t64 key = a.probe_keys[threadIdx.x];
+            if (pq.probe_keys) {
+                const key_t64 key = pq.probe_keys[threadIdx.x];
                 if (key) { const uint32_t l = key_row(key); off = a.list_offsets[l]; len = a.list_offsets[l + 1] - off; }
             } else {
                 const uint2 r = a.ranges[threadIdx.x];
@@ -89,12 +90,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     // stage queries (rows beyond a.nq are zero so they never qualify) and clear the lists
     for (int i = tid; i < NQ * D4; i += kScanThreads) {
         int q = i / D4;
-        q_s[i] = (q < a.nq) ? reinterpret_cast<const float4 *>(a.queries)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        q_s[i] = (q < a.nq) ? reinterpret_cast<const float4 *>(pq.queries)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     for (int i = tid; i < NQ * P; i += kScanThreads) lists[i] = 0ull;
-    if (a.q_inv_norm && tid < NQ) q_inv_s[tid] = (tid < a.nq) ? a.q_inv_norm[tid] : 0.f;
+    if (pq.q_inv_norm && tid < NQ) q_inv_s[tid] = (tid < a.nq) ? pq.q_inv_norm[tid] : 0.f;
     __syncthreads();
-    if (!a.q_inv_norm) {        // 1/|q| from the staged copy, with query_inv_norm_kernel's arithmetic (one warp per query)
+    if (!pq.q_inv_norm) {        // 1/|q| from the staged copy, with query_inv_norm_kernel's arithmetic (one warp per query)
         if (warp < NQ) {
             const float inv = warp < a.nq ? warp_inv_norm(reinterpret_cast<const float *>(q_s) + (size_t)warp * a.dim, a.dim, lane) : 0.f;
             if (lane == 0) q_inv_s[warp] = inv;
@@ -118,15 +119,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         my_inv = 0.f;
         if (valid) {
             my_inv = a.inv_norm[my_row];
-            if (a.doc_bitmap) {
+            if (pq.doc_bitmap) {
                 const uint32_t slot = a.doc_slot[my_row];
-                if (a.bitmap_stride == 0) {
-                    want_bits = ((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u) ? 0xFFFFFFFFu : 0u;
+                if (pq.bitmap_stride == 0) {
+                    want_bits = ((pq.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u) ? 0xFFFFFFFFu : 0u;
                 } else {
 #pragma unroll
                     for (int q = 0; q < NQ; q++)
                         if (q < a.nq)
-                            want_bits |= ((a.doc_bitmap[(size_t)q * a.bitmap_stride + (slot >> 5)] >> (slot & 31)) & 1u) << q;
+                            want_bits |= ((pq.doc_bitmap[(size_t)q * pq.bitmap_stride + (slot >> 5)] >> (slot & 31)) & 1u) << q;
                 }
             } else {
                 want_bits = 0xFFFFFFFFu;
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         }
     };
 
-    if (!INDIRECT && a.doc_bitmap && !a.read_all && n_rows >= 32768u) {
+    if (!INDIRECT && pq.doc_bitmap && !a.read_all && n_rows >= 32768u) {
         // Document filter with rows skipped: the filter itself is the work when few rows qualify (the reference's
         // own case: one to sixteen documents), so a warp looks at 32 rows per step -- one per lane -- and hands
         // only the groups that contain a requested row to the row loop.  (Small stores keep the plain loop: there the
@@ -319,7 +320,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         if (lane == 0 && tot) atomicAdd(a.rows_read, (unsigned long long)tot);
     }
 
-    scan_cta_epilogue(a, lists, &is_last_s, reinterpret_cast<key_t64 *>(smem_raw),
+    scan_cta_epilogue(a, pq, lists, &is_last_s, reinterpret_cast<key_t64 *>(smem_raw),
                       (int)(((size_t)NQ * D4 * sizeof(float4) + (size_t)NQ * P * sizeof(key_t64)) / sizeof(key_t64)));
 }
 

@@ -883,6 +883,52 @@ int setup_fused_exchange(da_store *st)
     return DA_OK;
 }
 
+// Queries: caller's buffer -> pinned staging (once, on the first shard) -> every local device.  A large batch (4 096
+// queries x 1 536 floats = 25 MB) is cut into slices: several threads copy slices into the pinned buffer while the
+// slices already there are on their way to the device, so the staging costs about one pass of the slower of the two
+// instead of their sum.
+int upload_queries(da_store *st, Shard &s, const float *queries, size_t n_elems)
+{
+    Shard &s0 = st->shards[0];
+    const size_t bytes = n_elems * sizeof(float);
+    if (&s != &s0) {        // the pinned copy already exists (shards are staged in order)
+        CU(cudaMemcpyAsync(s.d_queries.p, s0.h_queries.p, bytes, cudaMemcpyHostToDevice, s.stream));
+        return DA_OK;
+    }
+    constexpr size_t kSlice = 2u << 20;
+    if (bytes <= 2 * kSlice) {
+        memcpy(s0.h_queries.p, queries, bytes);
+        CU(cudaMemcpyAsync(s0.d_queries.p, s0.h_queries.p, bytes, cudaMemcpyHostToDevice, s0.stream));
+        return DA_OK;
+    }
+    const size_t n_slices = (bytes + kSlice - 1) / kSlice;
+    const int n_threads = (int)std::min<size_t>(4, n_slices);
+    std::atomic<size_t> next{0};
+    std::vector<std::atomic<int>> ready(n_slices);
+    for (auto &r : ready) r.store(0);
+    const char *src = reinterpret_cast<const char *>(queries);
+    char *pin = reinterpret_cast<char *>(s0.h_queries.p);
+    std::vector<std::thread> workers;
+    for (int t = 0; t < n_threads; t++)
+        workers.emplace_back([&] {
+            for (size_t i = next.fetch_add(1); i < n_slices; i = next.fetch_add(1)) {
+                const size_t off = i * kSlice, len = std::min(kSlice, bytes - off);
+                memcpy(pin + off, src + off, len);
+                ready[i].store(1, std::memory_order_release);
+            }
+        });
+    cudaError_t ce = cudaSuccess;
+    for (size_t i = 0; i < n_slices; i++) {
+        while (!ready[i].load(std::memory_order_acquire)) _mm_pause();
+        const size_t off = i * kSlice, len = std::min(kSlice, bytes - off);
+        if (ce == cudaSuccess)
+            ce = cudaMemcpyAsync(reinterpret_cast<char *>(s0.d_queries.p) + off, pin + off, len, cudaMemcpyHostToDevice, s0.stream);
+    }
+    for (auto &w : workers) w.join();
+    if (ce != cudaSuccess) return fail(DA_ERR_CUDA, "query upload failed: %s", cudaGetErrorString(ce));
+    return DA_OK;
+}
+
 // What every search checks before anything is staged (the errors of the reference's statement: dimension mismatch,
 // negative LIMIT, NaN/Inf in the vector literal).
 int validate_search(const da_store *st, const da_search_params *p)
@@ -1066,7 +1112,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             *s.h_overflow.p = 0;
         }
         CU(s.d_queries.ensure(nq_elems)); CU(s.d_qinv.ensure(p->batch));
-        CU(s.h_queries.ensure(nq_elems));
+        if (&s == &st->shards[0]) CU(s.h_queries.ensure(nq_elems));      // one pinned copy serves every local device
         const size_t trailer = st->world > 1 ? kRecTrailer : 0;
         CU(s.d_out.ensure(rec_bytes + trailer)); CU(s.h_result.ensure(rec_bytes + trailer));
         if (st->total_ranks > 1) { CU(s.d_gather.ensure((rec_bytes + trailer) * st->total_ranks)); CU(s.d_final.ensure(rec_bytes + trailer)); }
@@ -1075,8 +1121,10 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
             CU(cudaMemsetAsync(s.d_out.p + rec_bytes, 0, trailer, s.stream));
             if (!s.d_overflow.p) { CU(s.d_overflow.ensure(1)); CU(s.h_overflow.ensure(1)); CU(cudaMemsetAsync(s.d_overflow.p, 0, 4, s.stream)); *s.h_overflow.p = 0; }
         }
-        memcpy(s.h_queries.p, p->queries, nq_elems * sizeof(float));
-        CU(cudaMemcpyAsync(s.d_queries.p, s.h_queries.p, nq_elems * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+        {
+            int rc_up = upload_queries(st, s, p->queries, nq_elems);
+            if (rc_up != DA_OK) return rc_up;
+        }
         if (!all_docs) {
             CU(s.d_bitmap.ensure(bitmap.size())); CU(s.h_bitmap.ensure(bitmap.size()));
             memcpy(s.h_bitmap.p, bitmap.data(), bitmap.size() * 4);

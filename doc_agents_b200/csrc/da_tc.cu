@@ -20,6 +20,8 @@
 
 #include <cuda.h>
 
+#include <cstdlib>
+
 namespace da {
 
 namespace {
@@ -1026,9 +1028,14 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     const int m_units = (m_tiles + ncta - 1) / ncta;
     const double esz = i8 ? 1.0 : bf16 ? 2.0 : 4.0;
     const double tile_mb = (double)TC_BN * D * esz / 1e6, q_mb = (double)batch * D * esz / 1e6;
+    // DA_TC_L2_MB / DA_TC_GROUP: measurement knobs (the budget for the live set, or the group size itself)
+    static const double l2_budget_mb = [] { const char *v = getenv("DA_TC_L2_MB"); return v ? atof(v) : 90.0; }();
+    static const int group_env = [] { const char *v = getenv("DA_TC_GROUP"); return v ? atoi(v) : 0; }();
     int group = 1;
-    while (group < m_units && group < n_units && 2.0 * (n_units / group) * tile_mb + q_mb > 90.0) group++;   // two live row tiles per group (lockstep window)
+    while (group < m_units && group < n_units && 2.0 * (n_units / group) * tile_mb + q_mb > l2_budget_mb) group++;   // two live row tiles per group (lockstep window)
+    if (group_env > 0) group = group_env;
     if (group > m_units) group = m_units;
+    if (group > n_units) group = n_units;
     int n_groups = n_units / group;
     if ((uint32_t)n_groups > n_tiles) n_groups = (int)n_tiles;
     if (n_groups < 1) n_groups = 1;

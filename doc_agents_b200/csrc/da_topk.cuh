@@ -107,25 +107,44 @@ __device__ void cta_bitonic_desc(key_t64 *buf, int P)
     __syncthreads();
 }
 
+// The pieces of ScanArgs that probe mode re-bases per query (blockIdx.y).  Kept as a handful of scalars in registers:
+// a mutable copy of the whole argument struct would live in local memory and put a load in front of every use in
+// the row loop (measured: 5 % of the scan's bandwidth).
+struct ScanPerQuery {
+    const float *queries;
+    const float *q_inv_norm;
+    const uint32_t *doc_bitmap;
+    uint32_t bitmap_stride;
+    key_t64 *cta_out;
+    unsigned int *counter;
+    key_t64 *out_keys;
+    uint8_t *out_ids;
+    const key_t64 *probe_keys;
+};
+__device__ __forceinline__ ScanPerQuery scan_per_query(const ScanArgs &a)
+{
+    return ScanPerQuery{a.queries, a.q_inv_norm, a.doc_bitmap, a.bitmap_stride, a.cta_out, a.counter, a.out_keys, a.out_ids, a.probe_keys};
+}
+
 // Tail of the scan kernels: the k best keys of this CTA per query go to global scratch; the last CTA to arrive
 // merges gridDim.x * k keys per query, writes a.out_keys and (if a.out_ids) gathers the chunk ids.
 // `lists` = a.nq x a.P keys in shared memory, filled by the warps (unused slots 0); blockDim.x = kScanThreads.
 // `mbuf` / `mbuf_keys`: the kernel's whole dynamic shared memory (queries + lists; both are dead once the CTA's keys
 // are in global scratch), which lets the merge sort up to 8x more keys per round than one list holds -- the merge
 // is the floor of small searches (a 3 200-row filtered search spent 30 of its 47 us in 7 rounds of 256 keys).
-__device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned int *is_last_s, key_t64 *mbuf, int mbuf_keys)
+__device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key_t64 *lists, unsigned int *is_last_s, key_t64 *mbuf, int mbuf_keys)
 {
     const int tid = threadIdx.x, K = a.k, P = a.P;
     // ---- CTA epilogue: k best of this CTA per query -> global scratch
     for (int q = 0; q < a.nq; q++) {
         cta_bitonic_desc(lists + (size_t)q * P, P);
         for (int i = tid; i < K; i += kScanThreads)
-            a.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
+            pq.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
     }
     __threadfence();
     __syncthreads();
     if (tid == 0) {
-        unsigned int t = atomicAdd(a.counter, 1u);
+        unsigned int t = atomicAdd(pq.counter, 1u);
         *is_last_s = (t == gridDim.x - 1);
     }
     __syncthreads();
@@ -149,7 +168,7 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned in
                 key_t64 v = 0ull;
                 if (j < total) {
                     uint32_t cta = j / K, idx = j % K;
-                    v = __ldcg(&a.cta_out[((size_t)cta * a.nq + q) * K + idx]);
+                    v = __ldcg(&pq.cta_out[((size_t)cta * a.nq + q) * K + idx]);
                 }
                 buf[K + i] = v;
             }
@@ -158,16 +177,16 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned in
         }
         for (int i = tid; i < K; i += kScanThreads) {
             key_t64 key = buf[i];
-            a.out_keys[(size_t)q * K + i] = key;
-            if (a.out_ids) {
+            pq.out_keys[(size_t)q * K + i] = key;
+            if (pq.out_ids) {
                 uint4 id = make_uint4(0, 0, 0, 0);
                 if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
-                reinterpret_cast<uint4 *>(a.out_ids)[(size_t)q * K + i] = id;
+                reinterpret_cast<uint4 *>(pq.out_ids)[(size_t)q * K + i] = id;
             }
         }
         __syncthreads();
     }
-    // ---- exchange with the other GPUs (see XchgArgs): a.out_keys / a.out_ids ARE this rank's slot in its own buffer
+    // ---- exchange with the other GPUs (see XchgArgs): pq.out_keys / pq.out_ids ARE this rank's slot in its own buffer
     if (a.xg.n_ranks > 1) {
         const XchgArgs &x = a.xg;
         const size_t data0 = 256 + (size_t)x.parity * x.n_ranks * x.slot_bytes;
@@ -235,7 +254,7 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, key_t64 *lists, unsigned in
             *a.rows_read_out = a.rows_read ? atomicExch(a.rows_read, 0ull) : 0ull;
         }
         if (a.n_rows_reset) *a.n_rows_reset = 0u;
-        *a.counter = 0u;
+        *pq.counter = 0u;
         if (a.done_flag) {
             __threadfence_system();
             *a.done_flag = a.done_value;

@@ -104,3 +104,40 @@ def test_int8_sidecar_store_on_two_shards_equals_fp32_single_shard():
                 for i in range(batch):
                     assert np.array_equal(a[2][i], b[2][i]) and np.array_equal(a[0][i], b[0][i])
                     assert np.array_equal(a[1][i].view(np.uint32), b[1][i].view(np.uint32))
+
+
+def test_upsert_loaded_shards_answer_like_one_shard_up_to_exact_ties():
+    """A store filled by SaveEmbeddings places every new document on the emptiest shard, so a row's global number
+    (shard x capacity + local row) depends on the device count.  Scores and the set of rows never do; the ORDER among
+    rows whose scores are exactly equal follows the global number (ties are unordered in the
+    reference's SQL too).  Duplicate vectors are planted in different documents to make such ties."""
+    dim, k, per, n_docs = 256, 12, 50, 8
+    rng = np.random.default_rng(21)
+    q = oracle.normalize(rng.standard_normal(dim).astype(np.float32))
+    vecs = np.stack([oracle.normalize((0.9 * q + 0.03 * rng.standard_normal(dim)).astype(np.float32)) for _ in range(n_docs * per)])
+    for d in range(1, n_docs):                       # the best row of document 0 repeated in every other document
+        vecs[d * per + 3] = vecs[3]
+    chunk = oracle.chunk_ids(S, 0, n_docs * per)
+    docs = oracle.doc_ids(S, 0, n_docs)
+    answers = []
+    for devices in ((0,), (0, 1)):
+        with GpuStore(dim=dim, capacity_rows=1024, devices=devices, min_similarity=0.5) as st:
+            for d in range(n_docs):
+                st.save_chunks_raw(docs[d], chunk[d * per:(d + 1) * per])
+                st.save_embeddings_raw(chunk[d * per:(d + 1) * per], vecs[d * per:(d + 1) * per])
+            if len(devices) == 2:
+                assert list(st.stats().rows_per_device[:2]) == [n_docs * per // 2, n_docs * per // 2]
+            ids, sc, rows = st.search(q, k, docs)
+            answers.append(([bytes(i) for i in ids[0]], sc[0].copy()))
+    (ids1, sc1), (ids2, sc2) = answers
+    assert np.array_equal(sc1, sc2)                                  # the same scores, position by position
+    assert set(ids1) == set(ids2)                                    # the same rows
+    i = 0
+    while i < k:                                                     # the same order outside runs of exactly equal scores
+        j = i + 1
+        while j < k and sc1[j] == sc1[i]:
+            j += 1
+        assert set(ids1[i:j]) == set(ids2[i:j])
+        i = j
+    o_rows, o_sc, _ = oracle.topk(vecs, None, None, q, k, 0.5)
+    assert np.allclose(sc1, o_sc, rtol=1e-5) and set(ids1) == {bytes(chunk[r]) for r in o_rows} or sc1[-1] == sc1[-2]
