@@ -41,6 +41,14 @@ namespace {
 
 thread_local std::string g_err;
 
+// DA_TRACE_SEARCH=1: host-side phase times of the general search path on stderr (measurements only)
+bool trace_search()
+{
+    static const bool on = [] { const char *v = getenv("DA_TRACE_SEARCH"); return v && v[0] == '1'; }();
+    return on;
+}
+double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 int fail(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
 int fail(int code, const char *fmt, ...)
 {
@@ -82,6 +90,7 @@ inline Id16 load_id(const uint8_t *p) { Id16 k; memcpy(&k, p, 16); return k; }
 
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr uint32_t kXchgSlotBytes = da::kMaxNQ * DA_MAX_K * 24;      // one rank's records of one pass (<= 8 queries, k <= 128)
+constexpr size_t kCheckWhileCopying = 4u << 20;    // query batches above this many bytes are finite-checked while they are staged
 constexpr size_t kRecTrailer = 16;      // bytes after a rank's record block in a multi-process store: its overflow flag
 
 struct ChunkInfo { uint32_t slot; int32_t shard; uint32_t row; };
@@ -896,6 +905,7 @@ int upload_queries(da_store *st, Shard &s, const float *queries, size_t n_elems)
         return DA_OK;
     }
     constexpr size_t kSlice = 2u << 20;
+    static_assert(2 * kSlice == kCheckWhileCopying, "batches that skip validate_search's check must take the sliced path");
     if (bytes <= 2 * kSlice) {
         memcpy(s0.h_queries.p, queries, bytes);
         CU(cudaMemcpyAsync(s0.d_queries.p, s0.h_queries.p, bytes, cudaMemcpyHostToDevice, s0.stream));
@@ -904,6 +914,7 @@ int upload_queries(da_store *st, Shard &s, const float *queries, size_t n_elems)
     const size_t n_slices = (bytes + kSlice - 1) / kSlice;
     const int n_threads = (int)std::min<size_t>(4, n_slices);
     std::atomic<size_t> next{0};
+    std::atomic<int> any_bad{0};
     std::vector<std::atomic<int>> ready(n_slices);
     for (auto &r : ready) r.store(0);
     const char *src = reinterpret_cast<const char *>(queries);
@@ -914,6 +925,10 @@ int upload_queries(da_store *st, Shard &s, const float *queries, size_t n_elems)
             for (size_t i = next.fetch_add(1); i < n_slices; i = next.fetch_add(1)) {
                 const size_t off = i * kSlice, len = std::min(kSlice, bytes - off);
                 memcpy(pin + off, src + off, len);
+                const uint32_t *w = reinterpret_cast<const uint32_t *>(pin + off);      // NaN/Inf: exponent all ones
+                uint32_t bad = 0;
+                for (size_t j = 0; j < len / 4; j++) bad |= (uint32_t)((w[j] & 0x7F800000u) == 0x7F800000u);
+                if (bad) any_bad.store(1);
                 ready[i].store(1, std::memory_order_release);
             }
         });
@@ -926,6 +941,11 @@ int upload_queries(da_store *st, Shard &s, const float *queries, size_t n_elems)
     }
     for (auto &w : workers) w.join();
     if (ce != cudaSuccess) return fail(DA_ERR_CUDA, "query upload failed: %s", cudaGetErrorString(ce));
+    if (any_bad.load()) {               // nothing has been launched yet; the copies in flight are harmless
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(queries);
+        for (size_t i = 0; i < n_elems; i++)
+            if ((w[i] & 0x7F800000u) == 0x7F800000u) return fail(DA_ERR_NONFINITE, "query element %zu is not finite", i);
+    }
     return DA_OK;
 }
 
@@ -949,6 +969,7 @@ int validate_search(const da_store *st, const da_search_params *p)
     // finite check on the raw bits: exponent all ones = Inf or NaN.  One branch-free pass (it vectorises), then the
     // exact position only when something was found.
     const size_t nq_elems = (size_t)p->batch * st->dim;
+    if (nq_elems * 4 > kCheckWhileCopying) return DA_OK;       // a large batch is checked by the threads that copy it (upload_queries)
     const uint32_t *w = reinterpret_cast<const uint32_t *>(p->queries);
     uint32_t bad = 0;
     for (size_t i = 0; i < nq_elems; i++) bad |= (uint32_t)((w[i] & 0x7F800000u) == 0x7F800000u);
@@ -1807,7 +1828,10 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     SearchPlan pl{};
     CU(cudaSetDevice(s0.device));
     CU(cudaEventRecord(s0.ev_all0, s0.stream));
+    const double t_begin = now_ms();
     int rc = stage_search(st, p, pl);
+    const double t_staged = now_ms();
+    double t_waited = t_staged;
     if (rc != DA_OK) return rc;
     for (int q = 0; q < pl.batch; q++) out_n[q] = 0;
     if (pl.k == 0) return DA_OK;
@@ -1824,6 +1848,7 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         rc = enqueue_stats_readback(st);
         if (rc != DA_OK) return rc;
         for (Shard &s : st->shards) { CU(cudaSetDevice(s.device)); CU(cudaStreamSynchronize(s.stream)); }
+        t_waited = now_ms();
         bool overflow = false;
         if (trailer && *reinterpret_cast<const uint32_t *>(s0.h_result.p + rec_bytes + 4) != 0)
             return fail(DA_ERR_STATE, "a rank did not deliver its candidates within 4 s (searches on a multi-process store are collective)");
@@ -1854,18 +1879,33 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
     }
     const uint8_t *ids = s0.h_result.p;
     const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(s0.h_result.p + nk * 16);
-    for (int q = 0; q < pl.batch; q++) {
-        int c = 0;
-        for (int i = 0; i < pl.k; i++) {
-            const da::key_t64 key = keys[(size_t)q * pl.k + i];
-            if (!key) break;
-            out_scores[(size_t)q * pl.k + c] = da::key_score(key);
-            if (out_rows) out_rows[(size_t)q * pl.k + c] = da::key_row(key);
-            memcpy(out_chunk_ids + ((size_t)q * pl.k + c) * 16, ids + ((size_t)q * pl.k + i) * 16, 16);
-            c++;
+    // records are best first and zero-padded: a query's hits are a prefix of its k slots
+    auto unpack = [&](int q_lo, int q_hi) {
+        for (int q = q_lo; q < q_hi; q++) {
+            const da::key_t64 *kq = keys + (size_t)q * pl.k;
+            int c = 0;
+            while (c < pl.k && kq[c]) c++;
+            float *sc = out_scores + (size_t)q * pl.k;
+            for (int i = 0; i < c; i++) sc[i] = da::key_score(kq[i]);
+            if (out_rows) {
+                uint32_t *rw = out_rows + (size_t)q * pl.k;
+                for (int i = 0; i < c; i++) rw[i] = da::key_row(kq[i]);
+            }
+            memcpy(out_chunk_ids + (size_t)q * pl.k * 16, ids + (size_t)q * pl.k * 16, (size_t)c * 16);
+            out_n[q] = c;
         }
-        out_n[q] = c;
+    };
+    if (nk >= (1u << 16)) {             // a large batch: four threads share the queries
+        std::vector<std::thread> th;
+        const int per = (pl.batch + 3) / 4;
+        for (int t = 0; t < 4; t++) th.emplace_back(unpack, std::min(pl.batch, t * per), std::min(pl.batch, (t + 1) * per));
+        for (auto &t : th) t.join();
+    } else {
+        unpack(0, pl.batch);
     }
+    if (trace_search())
+        fprintf(stderr, "da_store_search trace: batch %d k %d: stage %.3f ms, enqueue+device+readback %.3f ms, unpack %.3f ms\n", pl.batch, pl.k,
+                t_staged - t_begin, t_waited - t_staged, now_ms() - t_waited);
     CU(cudaSetDevice(s0.device));
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, s0.ev_all0, s0.ev_all1));

@@ -1025,14 +1025,20 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     // 126 MB L2; otherwise every query tile pulls its row tile from HBM again.  Measured on cfg4 (4096 queries,
     // 1.25M x 1536 rows, free-running groups of 1/4/16/32 CTAs): 274/188/152/102 GB of DRAM reads for a 7.7 GB shard;
     // with the members of a group in lockstep (below): 44 GB at group 4, 22.7 GB at group 8 (profiles/README.md).
+    // The budget is 55 MB, not the 126 MB on the data sheet: the L2 is two halves of 63 MB and a line that both dies
+    // touch lives in both, so a live set that every SM shares sees about half of it (round 2 sweep: budget 90 MB ->
+    // group 4 -> 28.6 ms per configs[3] shard, 55 MB -> group 8 -> 26.3 ms).
     const int m_units = (m_tiles + ncta - 1) / ncta;
     const double esz = i8 ? 1.0 : bf16 ? 2.0 : 4.0;
     const double tile_mb = (double)TC_BN * D * esz / 1e6, q_mb = (double)batch * D * esz / 1e6;
     // DA_TC_L2_MB / DA_TC_GROUP: measurement knobs (the budget for the live set, or the group size itself)
-    static const double l2_budget_mb = [] { const char *v = getenv("DA_TC_L2_MB"); return v ? atof(v) : 90.0; }();
+    static const double l2_budget_mb = [] { const char *v = getenv("DA_TC_L2_MB"); return v ? atof(v) : 55.0; }();
     static const int group_env = [] { const char *v = getenv("DA_TC_GROUP"); return v ? atoi(v) : 0; }();
     int group = 1;
     while (group < m_units && group < n_units && 2.0 * (n_units / group) * tile_mb + q_mb > l2_budget_mb) group++;   // two live row tiles per group (lockstep window)
+    // the query tiles are dealt round-robin to the members: a group size that divides their number keeps the members level
+    // (measured on a configs[3] shard, CTA pairs, 16 tile pairs: group 4 / 8 / 12 / 16 = 28.6 / 26.3 / 34.6 / 26.6 ms)
+    while (group < m_units && m_units % group != 0) group++;
     if (group_env > 0) group = group_env;
     if (group > m_units) group = m_units;
     if (group > n_units) group = n_units;
