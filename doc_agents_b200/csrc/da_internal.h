@@ -177,7 +177,10 @@ size_t ivf_split_scratch_bytes(int L);
 cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, const float *mat, int D, const float *inv_norm,
                                    const uint32_t *sample, uint32_t n_sample, const uint32_t *assign, uint64_t seed,
                                    float *cent, cudaStream_t stream);
-// Batched query -> centroid ranking: partial[ks][batch][L] scores (da_tc.cu) -> out_keys[batch][probes]
+// Small batches: out[q][l] = <queries[q], cent[l]> in fp32 for nq <= 8 queries (one pass over the centroid matrix)
+cudaError_t ivf_launch_centroid_scores(const float *cent, int L, int D, const float *queries, int nq, float *out, int sm_count,
+                                       cudaStream_t stream);
+// Query -> centroid ranking: partial[ks][batch][L] scores (the GEMM of da_tc.cu, or ks = 1 from the kernel above) -> out_keys[batch][probes]
 constexpr int kIvfSelectMaxLists = 49152;          // the select kernel keeps a query's L scores in shared memory
 cudaError_t ivf_launch_select_probes(const float *partial, int ks, int batch, int L, int probes, key_t64 *out_keys,
                                      cudaStream_t stream);

@@ -357,6 +357,57 @@ __global__ void __launch_bounds__(256) split_lists_kernel(const uint32_t *pairs,
 }
 
 // ---------------------------------------------------------------------------
+// Query -> centroid scores for small batches (fewer than 8 queries; larger ones take the tensor-core GEMM of da_tc.cu):
+// out[q][l] = <queries[q], cent[l]>, fp32, one warp per centroid, up to NQ queries per pass staged in shared memory.
+// Nothing but the scores: the selection of the `probes` best lists is select_probes_kernel's, as for the GEMM.  (Round 2
+// first ranked the centroids with the fused top-k scan: its per-CTA sorts and last-CTA merge of 128 x 32 keys cost
+// 45-70 us for a matrix that streams in 7 -- measured, profiles/README.md.)  The centroid matrix is read with plain
+// loads so that it stays in L2 between queries (the row scans stream with evict-first).
+// ---------------------------------------------------------------------------
+template <int NQ>
+__global__ void __launch_bounds__(512) centroid_scores_kernel(const float *__restrict__ cent, int L, int D,
+                                                              const float *__restrict__ queries, int nq, float *__restrict__ out)
+{
+    extern __shared__ __align__(16) unsigned char cs_smem[];
+    float4 *q_s = reinterpret_cast<float4 *>(cs_smem);                 // NQ x D/4
+    const int D4 = D >> 2, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < NQ * D4; i += blockDim.x)
+        q_s[i] = (i / D4 < nq) ? reinterpret_cast<const float4 *>(queries)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+    for (int l = blockIdx.x * (blockDim.x >> 5) + warp; l < L; l += gridDim.x * (blockDim.x >> 5)) {
+        const float4 *row = reinterpret_cast<const float4 *>(cent) + (size_t)l * D4;
+        float acc[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; q++) acc[q] = 0.f;
+        for (int c0 = lane; c0 < D4; c0 += 32 * 8) {
+            float4 x[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int c = c0 + 32 * u;
+                x[u] = c < D4 ? __ldg(row + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int c = c0 + 32 * u < D4 ? c0 + 32 * u : 0;          // x is zero there
+#pragma unroll
+                for (int q = 0; q < NQ; q++) {
+                    const float4 w = q_s[q * D4 + c];
+                    acc[q] = fmaf(x[u].x, w.x, acc[q]); acc[q] = fmaf(x[u].y, w.y, acc[q]);
+                    acc[q] = fmaf(x[u].z, w.z, acc[q]); acc[q] = fmaf(x[u].w, w.w, acc[q]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < NQ; q++) {
+            float v = acc[q];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+            if (lane == 0 && q < nq) out[(size_t)q * L + l] = v;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
 // Batched query -> centroid ranking: the scores come from the tensor-core GEMM (da_tc.cu: queries x centroids^T,
 // ks partial sums over slices of the dimension), this kernel adds the partials in a fixed order and keeps each
 // query's `probes` best lists.  One CTA per query; the L scores sit in shared memory as order-preserving integers;
@@ -369,7 +420,7 @@ __global__ void __launch_bounds__(256) select_probes_kernel(const float *partial
     extern __shared__ uint32_t sc[];                         // L ordered scores
     __shared__ uint32_t hist[256];
     __shared__ uint32_t sel_prefix, sel_mask, sel_remaining;
-    __shared__ uint32_t scan_gt[257], scan_eq[257];
+    __shared__ uint32_t scan_gt[8], scan_eq[8];
     const int q = blockIdx.x, tid = threadIdx.x;
     for (int i = tid; i < L; i += blockDim.x) {
         float s = 0.f;
@@ -377,25 +428,50 @@ __global__ void __launch_bounds__(256) select_probes_kernel(const float *partial
         sc[i] = score_to_ordered(s);
     }
     const int want = probes < L ? probes : L;
+    const int lane = tid & 31, warp = tid >> 5;
     if (tid == 0) { sel_prefix = 0u; sel_mask = 0u; sel_remaining = (uint32_t)want; }
     for (int shift = 24; shift >= 0; shift -= 8) {
         hist[tid] = 0u;
         __syncthreads();
         const uint32_t prefix = sel_prefix, mask = sel_mask;
-        for (int i = tid; i < L; i += blockDim.x) {
-            const uint32_t v = sc[i];
-            if ((v & mask) == prefix) atomicAdd(&hist[(v >> shift) & 255u], 1u);
+        // scores of one query crowd into a few bins (the top byte is the same for almost all of them): lanes that
+        // hit the same bin are counted together, one shared-memory atomic per distinct bin and warp
+        for (int i0 = 0; i0 < L; i0 += blockDim.x) {
+            const int i = i0 + tid;
+            const uint32_t v = i < L ? sc[i] : 0u;
+            const bool in = i < L && (v & mask) == prefix;
+            const uint32_t bin = in ? ((v >> shift) & 255u) : 256u;
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, bin);
+            if (in && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (uint32_t)__popc(peers));
         }
         __syncthreads();
-        if (tid == 0) {
-            uint32_t rem = sel_remaining, b = 255u;
-            for (;; b--) {
-                if (hist[b] >= rem || b == 0u) break;
-                rem -= hist[b];
+        if (warp == 0) {
+            // which bin, counted from the top, holds the remaining-th value: lane l owns bins 255-8l .. 248-8l
+            uint32_t mine[8], tot = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) { mine[j] = hist[255 - 8 * lane - j]; tot += mine[j]; }
+            uint32_t incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= o) incl += t;
             }
-            sel_remaining = rem;
-            sel_prefix = prefix | (b << shift);
-            sel_mask = mask | (255u << shift);
+            const uint32_t rem = sel_remaining, before = incl - tot;      // values in the bins above this lane's
+            const bool here = before < rem && rem <= incl;
+            const uint32_t found = __ballot_sync(0xFFFFFFFFu, here);
+            if (found == 0u) {                       // fewer matching values than wanted (cannot happen: want <= L)
+                if (lane == 0) { sel_prefix = prefix; sel_mask = mask | (255u << shift); }
+            } else if (here) {
+                uint32_t r = rem - before, b = 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (b == 0u && r <= mine[j]) b = 0x100u | (uint32_t)(255 - 8 * lane - j);   // flag + bin
+                    else if (b == 0u) r -= mine[j];
+                }
+                sel_remaining = r;
+                sel_prefix = prefix | ((b & 255u) << shift);
+                sel_mask = mask | (255u << shift);
+            }
         }
         __syncthreads();
     }
@@ -404,15 +480,21 @@ __global__ void __launch_bounds__(256) select_probes_kernel(const float *partial
     const int i0 = tid * per, i1 = min(L, i0 + per);
     uint32_t gt = 0, eq = 0;
     for (int i = i0; i < i1; i++) { const uint32_t v = sc[i]; gt += v > T; eq += v == T; }
-    scan_gt[tid + 1] = gt; scan_eq[tid + 1] = eq;
-    __syncthreads();
-    if (tid == 0) {
-        scan_gt[0] = 0u; scan_eq[0] = 0u;
-        for (int t = 1; t <= (int)blockDim.x; t++) { scan_gt[t] += scan_gt[t - 1]; scan_eq[t] += scan_eq[t - 1]; }
+    // exclusive prefix over the threads (in thread order = list order): warp scans, then the warps' totals
+    uint32_t ig = gt, ie = eq;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t tg = __shfl_up_sync(0xFFFFFFFFu, ig, o), te = __shfl_up_sync(0xFFFFFFFFu, ie, o);
+        if (lane >= o) { ig += tg; ie += te; }
     }
+    if (lane == 31) { scan_gt[warp] = ig; scan_eq[warp] = ie; }
     __syncthreads();
-    const uint32_t n_gt = scan_gt[blockDim.x];
-    uint32_t pg = scan_gt[tid], pe = scan_eq[tid];
+    uint32_t base_g = 0, base_e = 0, n_gt = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) {
+        if (w < warp) { base_g += scan_gt[w]; base_e += scan_eq[w]; }
+        n_gt += scan_gt[w];
+    }
+    uint32_t pg = base_g + ig - gt, pe = base_e + ie - eq;
     key_t64 *out = out_keys + (size_t)q * probes;
     for (int i = i0; i < i1; i++) {
         const uint32_t v = sc[i];
@@ -505,6 +587,30 @@ cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, co
     if (e != cudaSuccess) return e;
     split_lists_kernel<<<L / 2, 256, 0, stream>>>(pairs, n_pairs, mat, D, inv_norm, sample, n_sample, assign, seed, cent);
     return cudaGetLastError();
+}
+
+template <int NQ>
+static cudaError_t launch_centroid_scores(const float *cent, int L, int D, const float *queries, int nq, float *out, int sm_count,
+                                          cudaStream_t stream)
+{
+    const size_t smem = (size_t)NQ * D * 4;
+    cudaError_t e = cudaFuncSetAttribute(centroid_scores_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int grid = (L + 15) / 16;
+    if (grid > sm_count) grid = sm_count;
+    centroid_scores_kernel<NQ><<<grid, 512, smem, stream>>>(cent, L, D, queries, nq, out);
+    return cudaGetLastError();
+}
+
+// out[q][l] for q < nq <= 8 (one pass)
+cudaError_t ivf_launch_centroid_scores(const float *cent, int L, int D, const float *queries, int nq, float *out, int sm_count,
+                                       cudaStream_t stream)
+{
+    if (nq < 1 || nq > 8 || (D & 3) || (size_t)8 * D * 4 > 200 * 1024) return cudaErrorInvalidValue;
+    if (nq <= 1) return launch_centroid_scores<1>(cent, L, D, queries, nq, out, sm_count, stream);
+    if (nq <= 2) return launch_centroid_scores<2>(cent, L, D, queries, nq, out, sm_count, stream);
+    if (nq <= 4) return launch_centroid_scores<4>(cent, L, D, queries, nq, out, sm_count, stream);
+    return launch_centroid_scores<8>(cent, L, D, queries, nq, out, sm_count, stream);
 }
 
 size_t ivf_select_smem_bytes(int L) { return (size_t)L * 4; }

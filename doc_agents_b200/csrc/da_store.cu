@@ -279,6 +279,7 @@ struct Slot {
     uint8_t *h_req = nullptr, *d_req = nullptr;          // [dim floats][kMaxRanges x (first row, count) | document bitmap]
     size_t req_cap = 0;
     da::key_t64 *d_probe_keys = nullptr;                 // IVFFlat: the lists the query probes
+    float *d_scores = nullptr; size_t scores_cap = 0;    // ... and its score against every centroid
     uint8_t *h_out = nullptr, *d_out = nullptr;          // mapped: [k ids of 16 B][k keys][rows read][completion word]
     da::key_t64 *d_cta = nullptr;
     unsigned int *d_counter = nullptr;
@@ -460,7 +461,7 @@ void shm_close(da_store *st)
 void free_slot(Slot &sl)
 {
     if (sl.stream) cudaStreamSynchronize(sl.stream);
-    cudaFree(sl.d_req); cudaFree(sl.d_cta); cudaFree(sl.d_counter); cudaFree(sl.d_rows_read); cudaFree(sl.d_probe_keys);
+    cudaFree(sl.d_req); cudaFree(sl.d_cta); cudaFree(sl.d_counter); cudaFree(sl.d_rows_read); cudaFree(sl.d_probe_keys); cudaFree(sl.d_scores);
     if (sl.h_req) cudaFreeHost(sl.h_req);
     if (sl.h_out) cudaFreeHost(sl.h_out);
     if (sl.ev0) cudaEventDestroy(sl.ev0);
@@ -596,6 +597,7 @@ struct SearchPlan {
     int probes;
     bool fused_xchg;   // several processes: the scan's last CTA exchanges the records with the other GPUs and merges (no collective)
     bool need_qinv;    // some kernel of the plan reads 1/|q| from memory (candidate paths); the plain scans compute it themselves
+    bool ivf_select;   // IVFFlat: fp32 centroid scores + the selection kernel (small batches; lists fit the selection kernel)
     bool ivf_tc;       // IVFFlat: rank the centroids for the whole batch with one tensor-core GEMM (batches of 8+)
     int ivf_ks;        // ... slices of the dimension of that GEMM
     bool use_tc;       // batched queries through the tcgen05 candidate kernel + exact re-score
@@ -645,7 +647,16 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
                 CU(da::tc_launch_scores(s.d_queries.p, pl.batch, s.ivf.cent, L, dim, pl.ivf_ks, s.d_ivf_scores.p, s.stream));
                 CU(da::ivf_launch_select_probes(s.d_ivf_scores.p, pl.ivf_ks, pl.batch, L, pl.probes, probe_keys, s.stream));
                 st->launches += 2;
-            } else {
+            } else if (pl.ivf_select) {
+                // fp32 scores of up to 8 queries per pass over the centroid matrix, then the same selection kernel
+                for (int q0 = 0; q0 < pl.batch; q0 += 8) {
+                    CU(da::ivf_launch_centroid_scores(s.ivf.cent, L, dim, s.d_queries.p + (size_t)q0 * dim, std::min(8, pl.batch - q0),
+                                                      s.d_ivf_scores.p + (size_t)q0 * L, s.sm_count, s.stream));
+                    st->launches++;
+                }
+                CU(da::ivf_launch_select_probes(s.d_ivf_scores.p, 1, pl.batch, L, pl.probes, probe_keys, s.stream));
+                st->launches++;
+            } else {            // more lists than the selection kernel holds in shared memory: the fused top-k scan ranks them
                 const int step = da::scan_pick_nq(dim, pl.probes, pl.batch);
                 for (int q0 = 0; q0 < pl.batch; q0 += step) {
                     da::ScanArgs c{};
@@ -1003,6 +1014,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         // which lists are probed; every returned score comes from the fp32 scan of the probed rows)
         pl.ivf_tc = p->batch >= ivf_tc_min_batch() && !(p->flags & DA_SEARCH_NO_TENSOR) && st->ivf_lists <= da::kIvfSelectMaxLists;
         pl.ivf_ks = pl.ivf_tc ? da::tc_scores_splits(p->batch, st->ivf_lists, st->dim, st->shards[0].sm_count) : 0;
+        pl.ivf_select = !pl.ivf_tc && st->ivf_lists <= da::kIvfSelectMaxLists && (size_t)8 * st->dim * 4 <= 200 * 1024;
     }
 
     // document filter -> bit per slot (document_id = ANY($2): postgres.go:239); unknown ids match nothing.
@@ -1096,6 +1108,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
                 CU(cudaMemsetAsync(s.d_ivf_counter.p, 0, s.d_ivf_counter.cap * sizeof(unsigned int), s.stream));
             }
             if (pl.ivf_tc) CU(s.d_ivf_scores.ensure((size_t)pl.ivf_ks * p->batch * st->ivf_lists));
+            if (pl.ivf_select) CU(s.d_ivf_scores.ensure((size_t)p->batch * st->ivf_lists));
         }
         if (pl.use_q8) {
             const size_t nq = (size_t)da::scan_pick_nq(st->dim, pl.k, p->batch);
@@ -1199,7 +1212,7 @@ int collect_stats(da_store *st, const SearchPlan &pl, int searches = 1)
     // bytes the algorithm must move: vectors of the rows read + inv_norm (4 B) of every row visited
     // + doc_slot (4 B) of every row visited when a document filter is present.
     if (pl.ivf) {  // centroid matrix once per pass of the ranking step + the probed rows (vector, inv_norm, doc slot if filtered, row number)
-        const int cstep = da::scan_pick_nq(st->dim, pl.probes, pl.batch);
+        const int cstep = pl.ivf_select ? 8 : da::scan_pick_nq(st->dim, pl.probes, pl.batch);
         const uint64_t cpasses = pl.ivf_tc ? 1 : (uint64_t)((pl.batch + cstep - 1) / cstep);
         st->last_bytes = cpasses * st->shards.size() * st->ivf_lists * ((uint64_t)st->dim * 4 + 4) +
                          rows_read * ((uint64_t)st->dim * 4 + (pl.all_docs ? 8 : 12));
@@ -1353,14 +1366,27 @@ int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool flag, int *gri
     a.dim = st->dim; a.nq = 1; a.k = fp.k; a.min_sim = fp.min_sim; a.read_all = 0;
     a.cta_out = sl->d_cta; a.counter = sl->d_counter;
     if (fp.ivf) {
-        da::ScanArgs c{};
-        c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
-        c.queries = a.queries; c.q_inv_norm = nullptr;
-        c.n_rows = (uint32_t)st->ivf_lists; c.row_base = 0;
-        c.dim = st->dim; c.nq = 1; c.k = fp.probes; c.min_sim = -std::numeric_limits<float>::infinity();
-        c.cta_out = sl->d_cta; c.counter = sl->d_counter; c.out_keys = sl->d_probe_keys;
-        CU(da::launch_scan(c, s.sm_count, sl->stream, nullptr));
-        (*launches)++;
+        const int L = st->ivf_lists;
+        if (L <= da::kIvfSelectMaxLists && (size_t)8 * st->dim * 4 <= 200 * 1024) {
+            if (sl->scores_cap < (size_t)L) {
+                CU(cudaStreamSynchronize(sl->stream));
+                cudaFree(sl->d_scores); sl->d_scores = nullptr; sl->scores_cap = 0;
+                CU(cudaMalloc((void **)&sl->d_scores, (size_t)L * sizeof(float)));
+                sl->scores_cap = (size_t)L;
+            }
+            CU(da::ivf_launch_centroid_scores(s.ivf.cent, L, st->dim, a.queries, 1, sl->d_scores, s.sm_count, sl->stream));
+            CU(da::ivf_launch_select_probes(sl->d_scores, 1, 1, L, fp.probes, sl->d_probe_keys, sl->stream));
+            (*launches) += 2;
+        } else {
+            da::ScanArgs c{};
+            c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;
+            c.queries = a.queries; c.q_inv_norm = nullptr;
+            c.n_rows = (uint32_t)L; c.row_base = 0;
+            c.dim = st->dim; c.nq = 1; c.k = fp.probes; c.min_sim = -std::numeric_limits<float>::infinity();
+            c.cta_out = sl->d_cta; c.counter = sl->d_counter; c.out_keys = sl->d_probe_keys;
+            CU(da::launch_scan(c, s.sm_count, sl->stream, nullptr));
+            (*launches)++;
+        }
         a.probe_keys = sl->d_probe_keys; a.probes = fp.probes; a.probe_batch = 1;
         a.list_offsets = s.ivf.offsets; a.list_rows = s.ivf.list_rows;
         a.n_rows = 0;

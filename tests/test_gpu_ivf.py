@@ -205,7 +205,7 @@ def test_batched_ivf_ranks_centroids_on_tensor_cores(n, dim, lists, clusters, ba
                                                                         np.sort(qd)[::-1][:probes + 2].tolist(), qd[one_probed].tolist())
                 assert np.array_equal(one[2][0], got[2][i]) and np.array_equal(one[1][0], got[1][i])
         assert read_by_batch == rows_read
-        # the same batch kept off the tensor cores: the fp32 centroid scan, 8 queries per pass, ONE probe scan
+        # the same batch kept off the tensor cores: fp32 centroid scores, 8 queries per pass, the same selection, ONE probe scan
         simt = st.search(qs, 10, all_docs=True, ivf=True, probes=probes, no_tensor=True)
         probed_simt = st.debug_probes(batch, probes)
         for i in range(batch):
