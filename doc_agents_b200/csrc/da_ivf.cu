@@ -414,13 +414,13 @@ __global__ void __launch_bounds__(512) centroid_scores_kernel(const float *__res
 // a 4 x 8-bit radix select finds the probes-th largest value exactly; lists above it, then the lowest-numbered
 // lists equal to it, are emitted in list order (deterministic).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) select_probes_kernel(const float *partial, int ks, int batch, int L, int probes,
+__global__ void __launch_bounds__(512) select_probes_kernel(const float *partial, int ks, int batch, int L, int probes,
                                                             key_t64 *out_keys)
 {
     extern __shared__ uint32_t sc[];                         // L ordered scores
     __shared__ uint32_t hist[256];
     __shared__ uint32_t sel_prefix, sel_mask, sel_remaining;
-    __shared__ uint32_t scan_gt[8], scan_eq[8];
+    __shared__ uint32_t scan_gt[16], scan_eq[16];
     const int q = blockIdx.x, tid = threadIdx.x;
     for (int i = tid; i < L; i += blockDim.x) {
         float s = 0.f;
@@ -431,7 +431,7 @@ __global__ void __launch_bounds__(256) select_probes_kernel(const float *partial
     const int lane = tid & 31, warp = tid >> 5;
     if (tid == 0) { sel_prefix = 0u; sel_mask = 0u; sel_remaining = (uint32_t)want; }
     for (int shift = 24; shift >= 0; shift -= 8) {
-        hist[tid] = 0u;
+        if (tid < 256) hist[tid] = 0u;
         __syncthreads();
         const uint32_t prefix = sel_prefix, mask = sel_mask;
         // scores of one query crowd into a few bins (the top byte is the same for almost all of them): lanes that
@@ -622,7 +622,7 @@ cudaError_t ivf_launch_select_probes(const float *partial, int ks, int batch, in
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(select_probes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    select_probes_kernel<<<batch, 256, smem, stream>>>(partial, ks, batch, L, probes, out_keys);
+    select_probes_kernel<<<batch, 512, smem, stream>>>(partial, ks, batch, L, probes, out_keys);
     return cudaGetLastError();
 }
 
