@@ -17,6 +17,8 @@
 #include "da_internal.h"
 #include "da_topk.cuh"
 
+#include <cstdlib>
+
 namespace da {
 
 namespace {
@@ -97,9 +99,14 @@ struct Q8Args {
 
 // Same frame as scan_topk_kernel (da_scan.cu): persistent CTAs, a warp takes R rows at a time, 256-bit streaming
 // loads (32 int8 each), per-warp bounded lists, CTA sort, last-CTA merge.
-template <int NQ, int R, int U>
+// QS > 0 (one query, dim <= 1024 * QS): the lane keeps the int8 query words of ITS column slots (lane, lane + 32, ...:
+// QS slots of 8 words) in registers for the whole scan.  The shared-memory form re-reads two 128-bit words of the query
+// per slot and row group, and with 8 dp4a per 32 bytes loaded the kernel was issue-bound on exactly those
+// (round 1: 81 % DRAM throughput where the fp32 scan reaches 92 %).
+template <int NQ, int R, int U, int QS>
 __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args qa)
 {
+    static_assert(QS == 0 || NQ == 1, "the register-resident query serves one query");
     const ScanArgs &a = qa.s;
     const int DV = a.dim >> 5;                  // lane slots (32 bytes) per row
     const int DW = a.dim >> 2;                  // 32-bit words per row
@@ -116,6 +123,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
     for (int i = tid; i < NQ * P; i += kScanThreads) lists[i] = 0ull;
     if (tid < NQ) { qf_s[tid] = tid < a.nq ? qa.qfactor[tid] : 0.f; qe_s[tid] = tid < a.nq ? qa.qerr[tid] : 0.f; }
     __syncthreads();
+    uint32_t qreg[QS > 0 ? QS : 1][8];
+    if constexpr (QS > 0) {
+#pragma unroll
+        for (int j = 0; j < QS; j++) {
+            const int c = j * 32 + lane;
+#pragma unroll
+            for (int w = 0; w < 8; w++) qreg[j][w] = c < DV ? q_s[c * 8 + w] : 0u;
+        }
+    }
 
     int cnt[NQ];
     key_t64 wmin[NQ];
@@ -168,6 +184,45 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
             for (int q = 0; q < NQ; q++) acc[r][q] = 0;
 
         const float4 *rp = reinterpret_cast<const float4 *>(qa.rows + (size_t)row0 * a.dim);
+        if constexpr (QS > 0) {
+#pragma unroll
+            for (int j0 = 0; j0 < QS; j0 += U) {
+                float4 v[R][U][2];
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+#pragma unroll
+                    for (int u = 0; u < U; u++) {
+                        const int c = (j0 + u) * 32 + lane;
+                        if (j0 + u < QS && ((load_mask >> r) & 1u) && c < DV) {
+                            ldg_stream8(rp + (size_t)r * (DW >> 2) + (size_t)c * 2, v[r][u][0], v[r][u][1]);
+                        } else {
+                            v[r][u][0] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            v[r][u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    if (j0 + u < QS) {
+                        const uint32_t *qw = qreg[j0 + u < QS ? j0 + u : 0];
+#pragma unroll
+                        for (int r = 0; r < R; r++) {
+                            const float4 x0 = v[r][u][0], x1 = v[r][u][1];
+                            int s = acc[r][0];
+                            s = __dp4a((int)__float_as_uint(x0.x), (int)qw[0], s);
+                            s = __dp4a((int)__float_as_uint(x0.y), (int)qw[1], s);
+                            s = __dp4a((int)__float_as_uint(x0.z), (int)qw[2], s);
+                            s = __dp4a((int)__float_as_uint(x0.w), (int)qw[3], s);
+                            s = __dp4a((int)__float_as_uint(x1.x), (int)qw[4], s);
+                            s = __dp4a((int)__float_as_uint(x1.y), (int)qw[5], s);
+                            s = __dp4a((int)__float_as_uint(x1.z), (int)qw[6], s);
+                            s = __dp4a((int)__float_as_uint(x1.w), (int)qw[7], s);
+                            acc[r][0] = s;
+                        }
+                    }
+                }
+            }
+        } else {
         for (int c0 = 0; c0 < DV; c0 += 32 * U) {
             float4 v[R][U][2];
 #pragma unroll
@@ -207,6 +262,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
                     }
                 }
             }
+        }
         }
 #pragma unroll
         for (int r = 0; r < R; r++)
@@ -260,10 +316,10 @@ __global__ void q8_collect_kernel(const float *upper, uint32_t n_rows, int k, co
     }
 }
 
-template <int NQ, int R, int U>
+template <int NQ, int R, int U, int QS = 0>
 cudaError_t q8_launch_one(const Q8Args &qa, int grid, size_t smem, cudaStream_t stream)
 {
-    auto kern = q8_scan_kernel<NQ, R, U>;
+    auto kern = q8_scan_kernel<NQ, R, U, QS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<grid, kScanThreads, smem, stream>>>(qa);
@@ -321,7 +377,25 @@ cudaError_t launch_q8_candidates(const ScanArgs &a_in, const int8_t *q8, const f
     cudaError_t e;
     switch (nqt) {
         // measured at 10M x 3072 (ms per search): (R,U) = (1,3) 6.28, (2,3) 4.96, (3,3) 4.55, (4,2) 4.55, (4,3) 4.52 with spills
-        case 1: e = q8_launch_one<1, 4, 2>(qa, grid, smem, stream); break;
+        case 1: {
+            // one query: its int8 words stay in registers when the row has at most 4 slots per lane (dim <= 4096)
+            static const int ru = [] { const char *v = getenv("DA_Q8_RU"); return v ? atoi(v) : 42; }();    // measurement knob: 42, 23, 43, 41, 81
+            static const bool smem_q = [] { const char *v = getenv("DA_Q8_SMEM_QUERY"); return v && v[0] == '1'; }();
+            const int qs = (a.dim / 32 + 31) / 32;
+            if (smem_q || qs > 4) { e = q8_launch_one<1, 4, 2>(qa, grid, smem, stream); break; }
+#define DA_Q8_QS(R_, U_)                                                                  \
+            (qs == 1 ? q8_launch_one<1, R_, U_, 1>(qa, grid, smem, stream)                   \
+             : qs == 2 ? q8_launch_one<1, R_, U_, 2>(qa, grid, smem, stream)                 \
+             : qs == 3 ? q8_launch_one<1, R_, U_, 3>(qa, grid, smem, stream)                 \
+                       : q8_launch_one<1, R_, U_, 4>(qa, grid, smem, stream))
+            if (ru == 23) e = DA_Q8_QS(2, 3);
+            else if (ru == 43) e = DA_Q8_QS(4, 3);
+            else if (ru == 41) e = DA_Q8_QS(4, 1);
+            else if (ru == 81) e = DA_Q8_QS(8, 1);
+            else e = DA_Q8_QS(4, 2);
+#undef DA_Q8_QS
+            break;
+        }
         // two queries: (2,3) 6.04 ms, (4,2) 4.89, (4,1) 5.05, (3,3) 4.91; four: (2,3) 8.58, (4,2) 6.93 (spills), (4,1) 6.49, (2,2) 8.15
         case 2: e = q8_launch_one<2, 4, 2>(qa, grid, smem, stream); break;
         case 4: e = q8_launch_one<4, 4, 1>(qa, grid, smem, stream); break;
