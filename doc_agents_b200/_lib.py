@@ -50,7 +50,7 @@ class da_config(C.Structure):
                 ("device_ids", C.c_int32 * DA_MAX_DEVICES), ("capacity_rows", C.c_uint64),
                 ("min_similarity", C.c_float), ("world_size", C.c_int32), ("rank", C.c_int32),
                 ("nccl_id", C.c_uint8 * DA_NCCL_ID_BYTES), ("flags", C.c_uint32),
-                ("batch_window_us", C.c_uint32), ("batch_max", C.c_uint32)]
+                ("batch_window_us", C.c_uint32), ("batch_max", C.c_uint32), ("min_similarity_f64", C.c_double)]
 
 
 class da_search_params(C.Structure):
@@ -58,7 +58,7 @@ class da_search_params(C.Structure):
                 ("doc_ids", C.c_void_p), ("n_docs", C.c_size_t),
                 ("queries", C.c_void_p), ("batch", C.c_int32), ("dim", C.c_int32),
                 ("k", C.c_int32), ("min_similarity", C.c_float), ("ivf_probes", C.c_int32),
-                ("doc_offsets", C.c_void_p)]
+                ("doc_offsets", C.c_void_p), ("min_similarity_f64", C.c_double)]
 
 
 class da_ivf_params(C.Structure):

@@ -960,6 +960,20 @@ int upload_queries(da_store *st, Shard &s, const float *queries, size_t n_elems)
     return DA_OK;
 }
 
+// The smallest float f with (double)f >= d: for a float score s, (double)s >= d holds exactly when s >= f, so the
+// kernels keep comparing in fp32 and still decide like Postgres' float8 comparison (postgres.go:240).
+float float_at_least(double d)
+{
+    if (std::isnan(d)) return std::numeric_limits<float>::quiet_NaN();
+    float f = (float)d;
+    if ((double)f < d) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+    return f;
+}
+float search_floor(const da_search_params *p)
+{
+    return p->min_similarity_f64 != 0.0 ? float_at_least(p->min_similarity_f64) : p->min_similarity;
+}
+
 // What every search checks before anything is staged (the errors of the reference's statement: dimension mismatch,
 // negative LIMIT, NaN/Inf in the vector literal).
 int validate_search(const da_store *st, const da_search_params *p)
@@ -1001,7 +1015,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
     const size_t nq_elems = (size_t)p->batch * st->dim;
 
-    pl.batch = p->batch; pl.k = p->k; pl.min_sim = p->min_similarity;
+    pl.batch = p->batch; pl.k = p->k; pl.min_sim = search_floor(p);
     pl.all_docs = all_docs; pl.read_all = (p->flags & DA_SEARCH_READ_ALL_ROWS) != 0;
     pl.bitmap_words = (st->docs.size() + 31) / 32 + 1;
     pl.ivf = ivf;
@@ -1273,7 +1287,7 @@ int plan_fast(da_store *st, const da_search_params *p, FastPlan &fp, uint2 *rang
     const int vrc = validate_search(st, p);
     if (vrc != DA_OK) return vrc;
     const Shard &s = st->shards[0];
-    fp.k = p->k; fp.min_sim = p->min_similarity;
+    fp.k = p->k; fp.min_sim = search_floor(p);
     if (ivf) {
         fp.ivf = true;
         const int probes = p->ivf_probes > 0 ? p->ivf_probes : st->ivf_default_probes;
@@ -1543,7 +1557,7 @@ int da_store_create(const da_config *cfg, da_store **out)
 
     da_store *st = new da_store();
     st->dim = cfg->dim;
-    st->min_sim = cfg->min_similarity;
+    st->min_sim = cfg->min_similarity_f64 != 0.0 ? float_at_least(cfg->min_similarity_f64) : cfg->min_similarity;
     st->world = world; st->rank = rank; st->total_ranks = (int)total;
     st->batch_window_us = cfg->batch_window_us;
     st->split16 = (cfg->flags & DA_STORE_SPLIT16) != 0;

@@ -92,6 +92,8 @@ class GpuStore:
             cfg.device_ids[i] = d
         cfg.capacity_rows = capacity_rows
         cfg.min_similarity = min_similarity
+        # the floor as the float8 it is in the reference's SQL (0.7 is not a float32): compared as (double)score >= floor
+        cfg.min_similarity_f64 = float(min_similarity) if math.isfinite(min_similarity) else 0.0
         cfg.world_size = world_size
         cfg.rank = rank
         cfg.batch_window_us = batch_window_us
@@ -236,12 +238,12 @@ class GpuStore:
     def search(self, queries, k: int, doc_ids: np.ndarray | None = None, *, all_docs: bool = False,
                min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
                probes: int = 0, no_tensor: bool = False, no_q8: bool = False,
-               no_compact: bool = False):
+               no_compact: bool = False, float32_floor: bool = False):
         """queries: dim or batch x dim.  doc_ids: one n x 16 array for the whole batch, or a list with one
         array per query.  Returns (chunk_ids[b][n,16], scores[b][n], rows[b][n])."""
         out_ids, out_scores, out_rows, out_n = self.search_arrays(
             queries, k, doc_ids, all_docs=all_docs, min_similarity=min_similarity, read_all_rows=read_all_rows,
-            ivf=ivf, probes=probes, no_tensor=no_tensor, no_q8=no_q8, no_compact=no_compact)
+            ivf=ivf, probes=probes, no_tensor=no_tensor, no_q8=no_q8, no_compact=no_compact, float32_floor=float32_floor)
         b = out_n.shape[0]
         return ([out_ids[i, :out_n[i]] for i in range(b)],
                 [out_scores[i, :out_n[i]] for i in range(b)],
@@ -250,14 +252,15 @@ class GpuStore:
     def search_arrays(self, queries, k: int, doc_ids=None, *, all_docs: bool = False,
                       min_similarity: float | None = None, read_all_rows: bool = False, ivf: bool = False,
                       probes: int = 0, no_tensor: bool = False, no_q8: bool = False,
-                      no_compact: bool = False):
+                      no_compact: bool = False, float32_floor: bool = False):
         """The C-ABI call as it is: (chunk_ids[b,k,16], scores[b,k], rows[b,k], n[b]); query i has n[i] hits,
         the rest of its k slots are zero.  No per-query Python objects (a batch of 4096 would spend longer
         building lists than searching)."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
-        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8, no_compact)
+        p, keep = self._params(q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor, no_q8, no_compact,
+                               float32_floor)
         b, kk = q.shape[0], max(int(k), 1)
         out_ids = np.zeros((b, kk, 16), dtype=np.uint8)
         out_scores = np.zeros((b, kk), dtype=np.float32)
@@ -269,7 +272,7 @@ class GpuStore:
         return out_ids, out_scores, out_rows, out_n
 
     def _params(self, q, k, doc_ids, all_docs, min_similarity, read_all_rows, ivf, probes, no_tensor=False, no_q8=False,
-                no_compact=False):
+                no_compact=False, float32_floor=False):
         p = L.da_search_params()
         p.struct_size = C.sizeof(L.da_search_params)
         p.flags = (L.DA_SEARCH_ALL_DOCS if all_docs else 0) | (L.DA_SEARCH_READ_ALL_ROWS if read_all_rows else 0) \
@@ -296,6 +299,7 @@ class GpuStore:
         p.k = int(k)
         ms = self.min_similarity if min_similarity is None else min_similarity
         p.min_similarity = -math.inf if ms is None else ms
+        p.min_similarity_f64 = float(ms) if (ms is not None and math.isfinite(ms) and not float32_floor) else 0.0
         p.ivf_probes = probes
         return p, (q, d, offs)
 

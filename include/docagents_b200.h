@@ -73,6 +73,11 @@ typedef struct {
      * its own document set. */
     uint32_t batch_window_us;
     uint32_t batch_max;
+    /* The floor as the float8 it is in the reference (`const minSimilarity = 0.7`, a float64 parameter compared with a
+     * float8 expression: postgres.go:223,240).  Non-zero: rows qualify iff (double)score >= min_similarity_f64 -- exactly
+     * Postgres' comparison -- and min_similarity above is ignored.  Zero: the float field is used as it is (note that
+     * (float)0.7 = 0.69999999 lets a row with that score in, which the SQL would leave out). */
+    double   min_similarity_f64;
 } da_config;
 
 /* da_config.flags */
@@ -170,6 +175,7 @@ typedef struct {
      * documents): query i asks for doc_ids[doc_offsets[i] .. doc_offsets[i+1]), doc_offsets has batch+1
      * entries and n_docs == doc_offsets[batch].  NULL: one set shared by the whole batch. */
     const uint64_t *doc_offsets;
+    double min_similarity_f64;   /* non-zero: the floor as a double, compared as (double)score >= it (see da_config); else min_similarity */
 } da_search_params;
 
 /* Outputs are batch x k (row-major); out_n is batch counts; out_rows (optional, may be NULL)

@@ -46,7 +46,7 @@ public:
         int dim = 3072;                            // vector(3072): postgres.go:84
         std::vector<int> devices{0};
         uint64_t capacity_rows = 1 << 16;
-        float min_similarity = DA_DEFAULT_MIN_SIMILARITY;   // 0.7: postgres.go:223
+        double min_similarity = 0.7;               // postgres.go:223, a float64 constant; compared as (double)score >= floor
         uint32_t batch_window_us = 0;
     };
 
@@ -58,7 +58,8 @@ public:
         cfg.n_devices = (int32_t)o.devices.size();
         for (size_t i = 0; i < o.devices.size() && i < DA_MAX_DEVICES; i++) cfg.device_ids[i] = o.devices[i];
         cfg.capacity_rows = o.capacity_rows;
-        cfg.min_similarity = o.min_similarity;
+        cfg.min_similarity = (float)o.min_similarity;
+        cfg.min_similarity_f64 = o.min_similarity;
         cfg.batch_window_us = o.batch_window_us;
         check(da_store_create(&cfg, &h_));
     }

@@ -60,7 +60,7 @@ type GPUOptions struct {
 	Dim           int     // GPU_DIM, default 3072 (vector(3072): postgres.go:84)
 	Devices       []int   // GPU_DEVICES
 	CapacityRows  uint64  // GPU_CAPACITY_ROWS, per device
-	MinSimilarity float32 // GPU_MIN_SIMILARITY, default 0.7 (postgres.go:223)
+	MinSimilarity float64 // GPU_MIN_SIMILARITY, default 0.7: a float64 like the reference's constant (postgres.go:223), compared as (double)score >= floor
 	Int8Sidecar   bool    // GPU_INT8_SIDECAR: keep an int8 copy of every row (25 % more HBM, ~3.6x queries/s, same answers)
 	BatchWindowUs uint32  // GPU_BATCH_WINDOW_US: merge TopK calls that arrive within this window into one pass (0 = off)
 	Preload       bool    // GPU_PRELOAD: stream embeddings JOIN chunks into the device store at start
@@ -98,6 +98,7 @@ func NewGPU(ctx context.Context, pg *PostgresStore, o GPUOptions) (*GPUStore, er
 	}
 	cfg.capacity_rows = C.uint64_t(o.CapacityRows)
 	cfg.min_similarity = C.float(o.MinSimilarity)
+	cfg.min_similarity_f64 = C.double(o.MinSimilarity)
 	if o.Int8Sidecar {
 		cfg.flags |= C.DA_STORE_Q8_SIDECAR
 	}

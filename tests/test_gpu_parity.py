@@ -356,3 +356,32 @@ def test_empty_store_answers_every_kind_of_search_with_nothing():
             ids, sc, rows = st.search(qs, 10, **kw)
             assert all(len(r) == 0 for r in rows)
         assert st.TopK([], q1, 5) is None
+
+
+def test_floor_is_compared_as_the_float8_it_is_in_the_reference():
+    """`const minSimilarity = 0.7` reaches Postgres as a float8 and is compared with a float8 expression
+    (postgres.go:223,240); 0.7 is not a float32: (float)0.7 = 0.69999999.  A row whose fp32 score is exactly that value is
+    OUT in the SQL.  The floor therefore travels as a double and rows qualify iff (double)score >= floor; the legacy
+    float field keeps the round-1 behaviour."""
+    dim = 4
+    below, above = np.float32(0.69999999), np.float32(0.70000005)
+    assert float(below) < 0.7 < float(above) and np.nextafter(below, np.float32(1)) == above
+    rows = np.zeros((3, dim), np.float32)
+    for i, a in enumerate((below, above, np.float32(0.9))):
+        rows[i, 0] = a
+        rows[i, 1] = np.float32(np.sqrt(1.0 - float(a) ** 2))
+    q = np.array([1, 0, 0, 0], np.float32)
+    chunk, docs = ids_for(3, 1)
+    with GpuStore(dim=dim, capacity_rows=16) as st:                      # store floor: the default 0.7, as a double
+        st.save_chunks_raw(docs[0], chunk)
+        st.save_embeddings_raw(chunk, rows)
+        _, inv, _, _ = st.debug_rows(0, 0, 3)
+        ids, sc, got = st.search(q, 5, docs[:1])
+        if np.all(inv == np.float32(1.0)):                               # the scores are then exactly the planted values
+            assert list(sc[0]) == [np.float32(0.9), above] and list(got[0]) == [2, 1]
+            legacy = st.search(q, 5, docs[:1], float32_floor=True)
+            assert list(legacy[2][0]) == [2, 1, 0]                       # (float)0.7 lets 0.69999999 in
+        o_rows, o_sc, _ = oracle.topk(rows, np.zeros(3, np.uint32), np.ones(1, np.uint8), q, 5, 0.7)
+        assert np.array_equal(got[0], o_rows) and np.allclose(sc[0], o_sc, rtol=REL_TOL)
+        res = st.TopK([uuid.UUID(bytes=docs[0].tobytes())], q, 5)        # the reference's call, the store's own floor
+        assert [r.Chunk.ID.bytes for r in res] == [chunk[r].tobytes() for r in o_rows]
