@@ -90,6 +90,7 @@ inline Id16 load_id(const uint8_t *p) { Id16 k; memcpy(&k, p, 16); return k; }
 
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr uint32_t kXchgSlotBytes = da::kMaxNQ * DA_MAX_K * 24;      // one rank's records of one pass (<= 8 queries, k <= 128)
+constexpr uint64_t kBatchWorthBytes = 256ull << 20;  // searches reading less than this skip the request-batching window (~35 us of HBM time)
 constexpr size_t kCheckWhileCopying = 4u << 20;    // query batches above this many bytes are finite-checked while they are staged
 constexpr size_t kRecTrailer = 16;      // bytes after a rank's record block in a multi-process store: its overflow flag
 
@@ -1991,6 +1992,29 @@ int da_store_topk(da_store *st, const uint8_t *doc_ids, size_t n_docs, const flo
             { std::lock_guard<std::mutex> lk(st->bmu); st->topk_calls++; }
             return fail(DA_ERR_NONFINITE, "query element %d is not finite", (int)i);
         }
+    // A search that reads little (the reference's own regime: a handful of documents) gains nothing from sharing a pass
+    // and would only pay the window: it takes the small-search path at once, on its own slot, concurrently with the
+    // others.  The window is for searches that stream a large part of the corpus, where one pass can serve them all.
+    {
+        da_search_params sp{};
+        sp.struct_size = sizeof sp;
+        sp.doc_ids = doc_ids; sp.n_docs = n_docs; sp.queries = query; sp.batch = 1; sp.dim = dim; sp.k = k;
+        sp.min_similarity = st->min_sim;
+        bool light = false;
+        {
+            ShmReadGuard shared_reader(st);
+            if (shm_refresh(st) == DA_OK) {
+                std::shared_lock<std::shared_mutex> shared(st->mu);
+                FastPlan fp;
+                uint2 ranges[kMaxRanges];
+                light = plan_fast(st, &sp, fp, ranges) == 1 && (uint64_t)fp.total_rows * (uint64_t)dim * 4 <= kBatchWorthBytes;
+            }
+        }
+        if (light) {
+            { std::lock_guard<std::mutex> lk(st->bmu); st->topk_calls++; st->topk_passes++; }
+            return topk_direct(st, doc_ids, n_docs, query, 1, dim, k, out_chunk_ids, out_scores, out_n);
+        }
+    }
     // Request batching: the first caller to find no leader becomes one, waits for the window (or a full
     // batch), then answers every queued call that asks for the same document set with one batched pass.
     da_store::Pending me{doc_ids, n_docs, query, k, out_chunk_ids, out_scores, out_n};

@@ -69,3 +69,17 @@ def test_concurrent_topk_calls_are_batched_and_results_unchanged(sidecar):
         assert batched.TopK([], qs[0], 5) is None
         sp = plain.stats()
         assert sp.topk_calls == sp.topk_passes == n_threads
+        # a search that reads little does not wait for the window (20 ms here): it goes at once, on its own slot
+        import time
+        few = docs_a[:3]
+        batched.TopK(few, qs[1], 5)
+        t0 = time.perf_counter()
+        light = batched.TopK(few, qs[1], 5)
+        dt = time.perf_counter() - t0
+        assert dt < 0.010, dt
+        ref = plain.TopK(few, qs[1], 5)
+        assert (light is None) == (ref is None)
+        if ref is not None:
+            assert [r.Chunk.ID for r in light] == [r.Chunk.ID for r in ref] and [r.Score for r in light] == [r.Score for r in ref]
+        s2 = batched.stats()
+        assert s2.topk_calls - s.topk_calls == s2.topk_passes - s.topk_passes
