@@ -290,7 +290,7 @@ struct Slot {
 };
 constexpr int kMaxRanges = DA_IVF_MAX_PROBES;            // the scan's range table
 constexpr int kMaxSlots = 8;
-constexpr size_t kSlotOutBytes = (size_t)DA_MAX_K * 24 + 16;
+constexpr size_t kSlotOutBytes = (size_t)DA_MAX_K * 24 + 32;    // records, then: exchange-timeout word, rows read, completion word
 
 }  // namespace
 
@@ -327,6 +327,7 @@ struct da_store {
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
     bool xg_ok = false;            // one process per GPU, every peer's exchange buffer mapped: the scan exchanges and merges itself
     uint64_t xg_seq = 0;           // fused searches so far (the same on every rank: searches are collective)
+    std::mutex xg_mu;              // small-search path on a multi-process store: one collective search at a time
     // small-search path (single shard, single process): slots and the statistics they update
     std::mutex slot_mu;
     std::condition_variable slot_cv;
@@ -1267,6 +1268,7 @@ struct FastPlan {
     bool ivf = false;           // probe the IVFFlat lists: centroid scan (top `probes`), then the probe-mode scan
     int probes = 0;
     bool bitmap = false;        // IVFFlat with a document filter: bit per document slot, tested on the probed rows
+    bool xchg = false;          // one process per GPU: the scan exchanges its records with the other ranks and merges (collective)
 };
 
 bool fast_path_enabled()
@@ -1278,12 +1280,17 @@ bool fast_path_enabled()
 // 1: eligible (fp and ranges filled), 0: not eligible (the general path answers), < 0: error.  Lock held (shared).
 int plan_fast(da_store *st, const da_search_params *p, FastPlan &fp, uint2 *ranges)
 {
-    if (!fast_path_enabled() || st->shards.size() != 1 || st->total_ranks != 1 || st->split16) return 0;
+    if (!fast_path_enabled() || st->shards.size() != 1 || st->split16) return 0;
     if (!p || p->struct_size != sizeof(da_search_params) || p->batch != 1 || p->doc_offsets) return 0;
     if (p->flags & (DA_SEARCH_READ_ALL_ROWS | DA_SEARCH_NO_COMPACT)) return 0;
     const bool all_docs = (p->flags & DA_SEARCH_ALL_DOCS) != 0;
     const bool ivf = (p->flags & DA_SEARCH_IVF) != 0;
     const bool q8_ok = st->q8 && !(p->flags & DA_SEARCH_NO_Q8);
+    if (st->total_ranks != 1) {
+        // several processes: only the search every rank is certain to plan the same way (see SearchPlan::fused_xchg)
+        if (!(st->xg_ok && all_docs && !ivf && !q8_ok)) return 0;
+        fp.xchg = true;
+    }
     if (all_docs && q8_ok && !ivf) return 0;               // the int8 sidecar scan reads a quarter of the bytes
     const int vrc = validate_search(st, p);
     if (vrc != DA_OK) return vrc;
@@ -1307,7 +1314,7 @@ int plan_fast(da_store *st, const da_search_params *p, FastPlan &fp, uint2 *rang
         return 1;
     }
     if (all_docs) {
-        fp.ranged = false; fp.total_rows = s.n_rows; fp.nothing = s.n_rows == 0;
+        fp.ranged = false; fp.total_rows = s.n_rows; fp.nothing = s.n_rows == 0 && !fp.xchg;    // a rank of a collective search always takes part
         return 1;
     }
     fp.ranged = true;
@@ -1411,6 +1418,20 @@ int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool flag, int *gri
     }
     a.out_ids = sl->d_out;
     a.out_keys = reinterpret_cast<da::key_t64 *>(sl->d_out + (size_t)fp.k * 16);
+    if (fp.xchg) {      // the records go to this rank's slot of its exchange buffer; the merged answer to the mapped block
+        da::XchgArgs &x = a.xg;
+        const int N = st->total_ranks;
+        for (int r = 0; r < N; r++) x.peer[r] = s.xg_peer[r];
+        x.n_ranks = N; x.rank = st->rank; x.slot_bytes = kXchgSlotBytes;
+        x.parity = (uint32_t)(st->xg_seq & 1);
+        x.target = (unsigned long long)N * (st->xg_seq / 2 + 1);
+        unsigned char *slot = s.xg_buf + 256 + ((size_t)x.parity * N + st->rank) * kXchgSlotBytes;
+        x.final_ids = a.out_ids; x.final_keys = a.out_keys;
+        a.out_ids = slot;
+        a.out_keys = reinterpret_cast<da::key_t64 *>(slot + (size_t)fp.k * 16);
+        x.timeout_flag = reinterpret_cast<uint32_t *>(sl->d_out + kSlotOutBytes - 24);
+        st->xg_seq++;
+    }
     a.rows_read = sl->d_rows_read;
     a.rows_read_out = reinterpret_cast<unsigned long long *>(sl->d_out + kSlotOutBytes - 16);
     if (flag) {
@@ -1471,12 +1492,17 @@ int search_fast(da_store *st, const da_search_params *p, uint8_t *out_chunk_ids,
         Shard &s = st->shards[0];
         CU(cudaSetDevice(s.device));
         int rc = DA_OK;
+        std::unique_lock<std::mutex> collective(st->xg_mu, std::defer_lock);
+        if (fp.xchg) collective.lock();                  // searches of a multi-process store are collective: one at a time, in call order
         Slot *sl = acquire_slot(st, &rc);
         if (!sl) return rc;
         sl->ticket++;
+        *reinterpret_cast<volatile uint32_t *>(sl->h_out + kSlotOutBytes - 24) = 0u;
         rc = upload_fast(st, sl, fp, p, ranges);
         if (rc == DA_OK) rc = enqueue_fast(st, sl, fp, true, &grid, &launches);
         if (rc == DA_OK) rc = wait_fast(sl);
+        if (rc == DA_OK && fp.xchg && *reinterpret_cast<volatile uint32_t *>(sl->h_out + kSlotOutBytes - 24) != 0u)
+            rc = fail(DA_ERR_STATE, "a rank did not deliver its candidates within 4 s (searches on a multi-process store are collective)");
         if (rc != DA_OK) { cudaStreamSynchronize(sl->stream); release_slot(st, sl); return rc; }
         const uint8_t *ids = sl->h_out;
         const da::key_t64 *keys = reinterpret_cast<const da::key_t64 *>(sl->h_out + (size_t)fp.k * 16);
@@ -2102,15 +2128,20 @@ int da_store_bench_resident(da_store *st, const da_search_params *p, int32_t ite
             Shard &s = st->shards[0];
             CU(cudaSetDevice(s.device));
             int rc = DA_OK, grid = 0;
+            std::unique_lock<std::mutex> collective(st->xg_mu, std::defer_lock);
+            if (fp.xchg) collective.lock();
             Slot *sl = acquire_slot(st, &rc);
             if (!sl) return rc;
             sl->ticket++;
+            *reinterpret_cast<volatile uint32_t *>(sl->h_out + kSlotOutBytes - 24) = 0u;
             int launches = 0;
             rc = upload_fast(st, sl, fp, p, ranges);
             if (rc == DA_OK && cudaEventRecord(sl->ev0, sl->stream) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event record failed");
             for (int i = 0; i < iters && rc == DA_OK; i++) rc = enqueue_fast(st, sl, fp, i == iters - 1, &grid, &launches);
             if (rc == DA_OK && cudaEventRecord(sl->ev1, sl->stream) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event record failed");
             if (rc == DA_OK) rc = wait_fast(sl);
+            if (rc == DA_OK && fp.xchg && *reinterpret_cast<volatile uint32_t *>(sl->h_out + kSlotOutBytes - 24) != 0u)
+                rc = fail(DA_ERR_STATE, "a rank did not deliver its candidates within 4 s (searches on a multi-process store are collective)");
             if (rc == DA_OK && cudaEventSynchronize(sl->ev1) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event sync failed");
             if (rc == DA_OK && cudaEventElapsedTime(out_total_ms, sl->ev0, sl->ev1) != cudaSuccess) rc = fail(DA_ERR_CUDA, "event time failed");
             if (rc != DA_OK) cudaStreamSynchronize(sl->stream);
