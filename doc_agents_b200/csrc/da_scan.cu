@@ -21,8 +21,6 @@
 #include "da_topk.cuh"
 
 #include <mutex>
-#include <utility>
-#include <vector>
 
 namespace da {
 
@@ -326,26 +324,27 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 
 
 // cudaFuncSetAttribute costs a driver call per launch; a function's limit only ever needs raising, per device.
+// The table is a fixed array: this is also on the path of da_scan_topk_noalloc, which must not allocate anything.
 cudaError_t ensure_dynamic_smem(const void *func, size_t smem)
 {
-    struct Key { const void *f; int dev; };
+    struct Entry { const void *f; int dev; size_t smem; };
+    constexpr int kEntries = 256;            // (scan variants) x (devices); beyond that the attribute is simply set every time
     static std::mutex mu;
-    static std::vector<std::pair<Key, size_t>> seen;
+    static Entry seen[kEntries];
+    static int n_seen = 0;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    {
-        std::lock_guard<std::mutex> lock(mu);
-        for (auto &p : seen)
-            if (p.first.f == func && p.first.dev == dev) {
-                if (p.second >= smem) return cudaSuccess;
-                e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-                if (e == cudaSuccess) p.second = smem;
-                return e;
-            }
-        e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) seen.push_back({Key{func, dev}, smem});
-    }
+    std::lock_guard<std::mutex> lock(mu);
+    for (int i = 0; i < n_seen; i++)
+        if (seen[i].f == func && seen[i].dev == dev) {
+            if (seen[i].smem >= smem) return cudaSuccess;
+            e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e == cudaSuccess) seen[i].smem = smem;
+            return e;
+        }
+    e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess && n_seen < kEntries) seen[n_seen++] = Entry{func, dev, smem};
     return e;
 }
 
