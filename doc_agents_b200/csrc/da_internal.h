@@ -176,7 +176,8 @@ cudaError_t ivf_launch_count(const uint32_t *assign, uint32_t n, float *counts, 
 size_t ivf_split_scratch_bytes(int L);
 cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, const float *mat, int D, const float *inv_norm,
                                    const uint32_t *sample, uint32_t n_sample, const uint32_t *assign, uint64_t seed,
-                                   float *cent, cudaStream_t stream);
+                                   float *cent, cudaStream_t stream, float heavy_x = 1.5f, float light_x = 0.25f);
+// (heavy_x, light_x: a donor holds more than heavy_x times the mean, a receiver less than light_x times)
 // Small batches: out[q][l] = <queries[q], cent[l]> in fp32 for nq <= 8 queries (one pass over the centroid matrix)
 cudaError_t ivf_launch_centroid_scores(const float *cent, int L, int D, const float *queries, int nq, float *out, int sm_count,
                                        cudaStream_t stream);

@@ -261,7 +261,7 @@ __global__ void count_assign_kernel(const uint32_t *assign, uint32_t n, float *c
 // rows around its seed, which simply join their next-nearest list).  pairs[2j] = donor, pairs[2j+1] = receiver;
 // *n_pairs = number of pairs.
 __global__ void __launch_bounds__(1024) plan_splits_kernel(const float *counts, int L, int P, unsigned long long *keys,
-                                                          uint32_t *pairs, uint32_t *n_pairs)
+                                                          uint32_t *pairs, uint32_t *n_pairs, float heavy_x, float light_x)
 {
     __shared__ float total_s;
     __shared__ uint32_t n_s;
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(1024) plan_splits_kernel(const float *counts, 
             }
         }
     __syncthreads();
-    const float heavy = 1.5f * total_s / (float)L, light = 0.25f * total_s / (float)L;
+    const float heavy = heavy_x * total_s / (float)L, light = light_x * total_s / (float)L;
     for (int j = tid; j < L / 2; j += blockDim.x) {
         const unsigned long long d = keys[j], r = keys[L - 1 - j];
         if ((float)(uint32_t)(d >> 32) > heavy && (float)(uint32_t)(r >> 32) < light) {
@@ -574,7 +574,7 @@ size_t ivf_split_scratch_bytes(int L)
 
 cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, const float *mat, int D, const float *inv_norm,
                                    const uint32_t *sample, uint32_t n_sample, const uint32_t *assign, uint64_t seed,
-                                   float *cent, cudaStream_t stream)
+                                   float *cent, cudaStream_t stream, float heavy_x, float light_x)
 {
     if (L < 2) return cudaSuccess;
     int P = 1;
@@ -582,7 +582,7 @@ cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, co
     unsigned long long *keys = static_cast<unsigned long long *>(scratch);
     uint32_t *pairs = reinterpret_cast<uint32_t *>(keys + P);
     uint32_t *n_pairs = pairs + (size_t)(L / 2) * 2;
-    plan_splits_kernel<<<1, 1024, 0, stream>>>(counts, L, P, keys, pairs, n_pairs);
+    plan_splits_kernel<<<1, 1024, 0, stream>>>(counts, L, P, keys, pairs, n_pairs, heavy_x, light_x);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     split_lists_kernel<<<L / 2, 256, 0, stream>>>(pairs, n_pairs, mat, D, inv_norm, sample, n_sample, assign, seed, cent);

@@ -2298,8 +2298,28 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
     }
     // Balancing rounds (da_ivf.cu, "Splitting heavy lists"): count the sample per list under the current centroids
     // (globally: all-reduce), let the heaviest lists split into the empty ones on global rank 0, hand the centroids
-    // to everybody.  A list of c x the mean needs log2(c) rounds; six cover 64 x (each costs one assignment of the sample).
-    const int split_rounds = (p->flags & DA_IVF_NO_SPLIT) ? 0 : 6;
+    // to everybody.  A list of c x the mean needs log2(c) rounds; eight cover 256 x (each costs one assignment of the sample).
+    static const int rounds_env = [] { const char *v = getenv("DA_IVF_SPLIT_ROUNDS"); return v ? atoi(v) : 8; }();
+    static const float split_heavy_late = [] { const char *v = getenv("DA_IVF_SPLIT_HEAVY_LATE"); return v ? (float)atof(v) : 1.5f; }();
+    static const float split_light_late = [] { const char *v = getenv("DA_IVF_SPLIT_LIGHT_LATE"); return v ? (float)atof(v) : 0.25f; }();
+    const int split_rounds = (p->flags & DA_IVF_NO_SPLIT) ? 0 : rounds_env;
+    // The rounds judge the lists on rows the centroids have NOT been averaged from.  On the training sample a starved
+    // stub looks alive: its centroid is the mean of its dozen sample members, each of which therefore scores highest with it,
+    // while every other row of the corpus prefers the big sibling -- measured: lists of 13 to 40 rows (their sample members,
+    // exactly) next to lists of 9 600, invisible to a count over the training sample.  So a second sample is drawn.
+    if (split_rounds > 0)
+        for (Shard &s : st->shards) {
+            Shard::Ivf &v = s.ivf;
+            CU(cudaSetDevice(s.device));
+            CU(da::ivf_launch_sample(s.n_rows, v.n_sample,
+                                     p->seed + 0x7A11DA7Eull + 0x51ED * (uint64_t)(&s - &st->shards[0] + 1 + st->rank * st->shards.size()),
+                                     v.sample, s.stream));
+            st->launches++;
+            if (use_tc) {
+                CU(da::tc_launch_gather_rows(s.mat, D, v.sample, v.n_sample, v.sample_mat, s.stream));
+                st->launches++;
+            }
+        }
     for (int round = 0; round < split_rounds; round++) {
         for (Shard &s : st->shards) {
             Shard::Ivf &v = s.ivf;
@@ -2320,8 +2340,23 @@ int da_store_build_ivf(da_store *st, const da_ivf_params *p)
             CU(cudaSetDevice(s0.device));
             CU(da::ivf_launch_split_round(s0.ivf.counts_f, L, s0.ivf.split_scratch, s0.mat, D, s0.inv_norm, s0.ivf.sample,
                                           s0.ivf.n_sample, s0.ivf.sample_assign, p->seed + 0xB5 * (uint64_t)(round + 1),
-                                          s0.ivf.cent, s0.stream));
+                                          s0.ivf.cent, s0.stream, round < split_rounds - 2 ? 1.5f : split_heavy_late,
+                                          round < split_rounds - 2 ? 0.25f : split_light_late));
             st->launches += 2;
+            if (getenv("DA_IVF_TRACE")) {           // measurements: what each balancing round saw and did
+                CU(cudaStreamSynchronize(s0.stream));
+                std::vector<float> cnt(L);
+                uint32_t n_pairs = 0;
+                CU(cudaMemcpy(cnt.data(), s0.ivf.counts_f, (size_t)L * 4, cudaMemcpyDeviceToHost));
+                int Pp = 1; while (Pp < L) Pp <<= 1;
+                CU(cudaMemcpy(&n_pairs, reinterpret_cast<const uint8_t *>(s0.ivf.split_scratch) + (size_t)Pp * 8 + (size_t)(L / 2) * 8, 4, cudaMemcpyDeviceToHost));
+                double tot = 0; for (float c : cnt) tot += c;
+                const double mean = tot / L;
+                int heavy = 0, light = 0, empty = 0; float mx = 0;
+                for (float c : cnt) { heavy += c > 1.5 * mean; light += c < 0.25 * mean; empty += c == 0; mx = std::max(mx, c); }
+                fprintf(stderr, "ivf balance round %d: sample mean %.1f max %.0f, lists > 1.5x mean %d, < 0.25x mean %d (empty %d), pairs split %u\n",
+                        round, mean, mx, heavy, light, empty, n_pairs);
+            }
         }
         if (st->total_ranks > 1) {
             NC(ncclGroupStart());
