@@ -284,27 +284,34 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             }
         }
     } else {
-        for (uint32_t g = blockIdx.x * kScanWarps + warp; g < n_groups; g += gstride) {
+        // The row number of lane r's row of a group: itself, or looked up (compacted filter list, IVFFlat lists, ranges).
+        auto resolve = [&](uint32_t flat, bool valid) -> uint32_t {
+            if (!INDIRECT) return flat;
+            if (!valid) return 0u;
+            if (!probe_mode) return a.row_list[flat];
+            int lo = 0, hi = a.probes - 1;             // which piece holds the flat index: last p with p_start[p] <= flat
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (p_start[mid] <= flat) lo = mid; else hi = mid - 1;
+            }
+            const uint32_t r = p_src[lo] + (flat - p_start[lo]);
+            return a.list_rows ? a.list_rows[r] : r;
+        };
+        // The look-up of the NEXT group is issued before the current group's rows are streamed, so its latency (a
+        // dependent load in front of every group: binary search, list entry, then the row) hides behind them.
+        uint32_t g = blockIdx.x * kScanWarps + warp;
+        uint32_t nxt_row = 0u;
+        if (g < n_groups) nxt_row = resolve(g * R + lane, lane < R && g * R + lane < n_rows);
+        for (; g < n_groups; g += gstride) {
             const uint32_t row0 = g * R;
             // lane r (< R) looks at row0 + r: document mask and 1/|row|
-            uint32_t my_row = row0 + lane;
-            const bool valid = (lane < R) && (my_row < n_rows);
+            const bool valid = (lane < R) && (row0 + lane < n_rows);
+            const uint32_t my_row = nxt_row;
             if (INDIRECT) {
-                if (probe_mode) {
-                    uint32_t r = 0u;
-                    if (valid) {                     // which list holds flat index my_row: last p with p_start[p] <= my_row
-                        int lo = 0, hi = a.probes - 1;
-                        while (lo < hi) {
-                            const int mid = (lo + hi + 1) >> 1;
-                            if (p_start[mid] <= my_row) lo = mid; else hi = mid - 1;
-                        }
-                        r = p_src[lo] + (my_row - p_start[lo]);
-                        if (a.list_rows) r = a.list_rows[r];
-                    }
-                    my_row = r;
-                } else {
-                    my_row = valid ? a.row_list[my_row] : 0u;
-                }
+                const uint32_t gn = g + gstride;
+                if (gn < n_groups) nxt_row = resolve(gn * R + lane, lane < R && gn * R + lane < n_rows);
+            } else {
+                nxt_row = row0 + gstride * R + lane;
             }
             uint32_t want_bits;
             float my_inv;
