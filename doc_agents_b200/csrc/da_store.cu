@@ -173,6 +173,7 @@ struct Shard {
     // fused cross-GPU exchange (one process per GPU): own buffer, every rank's buffer as mapped here (CUDA IPC)
     unsigned char *xg_buf = nullptr;
     unsigned char *xg_peer[da::kXchgMaxRanks] = {};
+    uint32_t *h_xg_timeout = nullptr, *d_xg_timeout = nullptr;   // in-process exchange: mapped word a kernel sets if a shard never delivered
     // search state
     DevBuf<float> d_queries, d_qinv;
     DevBuf<uint32_t> d_bitmap;
@@ -325,6 +326,7 @@ struct da_store {
     bool split16 = false;          // split-plane resident format (DA_STORE_SPLIT16)
     bool q8 = false;               // int8 sidecar next to the fp32 rows (DA_STORE_Q8_SIDECAR)
     bool p2p_gather = false;       // one process, several GPUs with peer access: records go straight to shard 0
+    bool xg_inproc = false;        // one process, several GPUs, all-pairs peer access: the same exchange between this store's own shards
     bool xg_ok = false;            // one process per GPU, every peer's exchange buffer mapped: the scan exchanges and merges itself
     uint64_t xg_seq = 0;           // fused searches so far (the same on every rank: searches are collective)
     std::mutex xg_mu;              // small-search path on a multi-process store: one collective search at a time
@@ -349,9 +351,11 @@ void free_shard(Shard &s)
 {
     cudaSetDevice(s.device);
     free_ivf(s);
-    for (int r = 0; r < da::kXchgMaxRanks; r++)
-        if (s.xg_peer[r] && s.xg_peer[r] != s.xg_buf) cudaIpcCloseMemHandle(s.xg_peer[r]);
+    if (!s.h_xg_timeout)            // (in-process: the peers' buffers are the other shards' own allocations, nothing to close)
+        for (int r = 0; r < da::kXchgMaxRanks; r++)
+            if (s.xg_peer[r] && s.xg_peer[r] != s.xg_buf) cudaIpcCloseMemHandle(s.xg_peer[r]);
     cudaFree(s.xg_buf);
+    if (s.h_xg_timeout) cudaFreeHost(s.h_xg_timeout);
     if (s.comm) ncclCommDestroy(s.comm);
     if (s.stream) cudaStreamSynchronize(s.stream);
     if (s.ipc_mapped) {
@@ -626,7 +630,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         // NVLink -- compute and "all-to-one gather" are the same kernel, no collective is launched.
         const size_t shard_index = (size_t)(&s - &st->shards[0]);
         uint8_t *rec_base = st->p2p_gather ? st->shards[0].d_gather.p + shard_index * rec_bytes : s.d_out.p;
-        if (st->p2p_gather && !first)      // block `shard_index` is free again once shard 0 merged the previous search
+        if (st->p2p_gather && !first && !pl.fused_xchg)      // block `shard_index` is free again once shard 0 merged the previous search
             CU(cudaStreamWaitEvent(s.stream, st->shards[0].ev_done, 0));
         uint8_t *out_ids = rec_base;
         da::key_t64 *out_keys = reinterpret_cast<da::key_t64 *>(rec_base + (size_t)pl.batch * pl.k * 16);
@@ -765,21 +769,21 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             a.out_ids = out_ids + (size_t)q0 * pl.k * 16;
             a.rows_read = s.d_rows_read;
             if (pl.fused_xchg) {
-                // the records go to this rank's slot of its own exchange buffer; the last CTA copies them into every
-                // other rank's buffer, waits for theirs, and writes the merged answer to d_final
+                // the records go to this rank's (or shard's) slot of its own exchange buffer; the last CTA copies them into
+                // every other buffer, waits for the others' records, and writes the merged answer to d_final
                 da::XchgArgs &x = a.xg;
-                const int N = st->total_ranks;
+                const int N = st->xg_inproc ? (int)st->shards.size() : st->total_ranks;
+                const int me = st->xg_inproc ? (int)shard_index : st->rank;
                 for (int r = 0; r < N; r++) x.peer[r] = s.xg_peer[r];
-                x.n_ranks = N; x.rank = st->rank; x.slot_bytes = kXchgSlotBytes;
+                x.n_ranks = N; x.rank = me; x.slot_bytes = kXchgSlotBytes;
                 x.parity = (uint32_t)(st->xg_seq & 1);
                 x.target = (unsigned long long)N * (st->xg_seq / 2 + 1);
-                unsigned char *slot = s.xg_buf + 256 + ((size_t)x.parity * N + st->rank) * kXchgSlotBytes;
+                unsigned char *slot = s.xg_buf + 256 + ((size_t)x.parity * N + me) * kXchgSlotBytes;
                 a.out_ids = slot;
                 a.out_keys = reinterpret_cast<da::key_t64 *>(slot + (size_t)a.nq * pl.k * 16);
                 x.final_ids = s.d_final.p;
                 x.final_keys = reinterpret_cast<da::key_t64 *>(s.d_final.p + (size_t)pl.batch * pl.k * 16);
-                x.timeout_flag = reinterpret_cast<uint32_t *>(s.d_final.p + rec_bytes + 4);
-                st->xg_seq++;
+                x.timeout_flag = st->xg_inproc ? s.d_xg_timeout : reinterpret_cast<uint32_t *>(s.d_final.p + rec_bytes + 4);
             }
             if (st->split16) {             // scan the upper plane for candidates, then the exact finish from both planes
                 a.mat = nullptr; a.hi = s.hi; a.approx = s.d_approx.p;
@@ -816,6 +820,7 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
         if (st->p2p_gather && !first) CU(cudaEventRecord(s.ev_done, s.stream));
     }
     st->scan_launches++;        // one timed unit per search: scan_ms_sum and last_bytes both cover ALL passes of a search
+    if (pl.fused_xchg) st->xg_seq++;                  // one exchange per search, the same number on every rank / shard
     if (st->total_ranks > 1 && !pl.fused_xchg) {
         Shard &s0 = st->shards[0];
         if (st->p2p_gather) {
@@ -863,6 +868,42 @@ int ivf_tc_min_batch()
 {
     static const int env = [] { const char *v = getenv("DA_IVF_TC_MIN_BATCH"); return v ? atoi(v) : 0; }();
     return env > 0 ? env : 8;
+}
+
+// One process driving several GPUs (the Go query agent on an 8 x B200 box): with peer access between every pair of
+// its devices the shards exchange exactly as ranks of a multi-process store do -- every shard's last CTA stores its
+// records into every shard's buffer, the merged answer is taken from the first shard.
+int setup_inprocess_exchange(da_store *st)
+{
+    const int N = (int)st->shards.size();
+    if (N < 2 || N > da::kXchgMaxRanks || st->world != 1) return DA_OK;
+    if (const char *v = getenv("DA_DISABLE_FUSED_EXCHANGE")) if (v[0] == '1') return DA_OK;
+    for (int i = 0; i < N; i++)
+        for (int j = 0; j < N; j++) {
+            if (i == j) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, st->shards[i].device, st->shards[j].device) != cudaSuccess || !can) return DA_OK;
+        }
+    const size_t bytes = 256 + (size_t)2 * N * kXchgSlotBytes;
+    for (int i = 0; i < N; i++) {
+        Shard &s = st->shards[i];
+        CU(cudaSetDevice(s.device));
+        for (int j = 0; j < N; j++) {
+            if (i == j) continue;
+            cudaError_t e = cudaDeviceEnablePeerAccess(st->shards[j].device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+            if (e != cudaSuccess) { cudaGetLastError(); return DA_OK; }
+        }
+        CU(cudaMalloc((void **)&s.xg_buf, bytes));
+        CU(cudaMemset(s.xg_buf, 0, bytes));
+        CU(cudaHostAlloc((void **)&s.h_xg_timeout, 64, cudaHostAllocMapped | cudaHostAllocPortable));
+        memset(s.h_xg_timeout, 0, 64);
+        CU(cudaHostGetDevicePointer((void **)&s.d_xg_timeout, s.h_xg_timeout, 0));
+    }
+    for (int i = 0; i < N; i++)
+        for (int j = 0; j < N; j++) st->shards[i].xg_peer[j] = st->shards[j].xg_buf;
+    st->xg_inproc = true;
+    return DA_OK;
 }
 
 // One process per GPU: give every rank a mapping of every rank's exchange buffer (CUDA IPC handles travel through
@@ -1112,6 +1153,11 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
     pl.fused_xchg = st->xg_ok && all_docs && !ivf && !st->split16 && p->batch <= da::scan_pick_nq(st->dim, pl.k, p->batch) &&
                     (p->batch < tc_min_batch(st) || (p->flags & DA_SEARCH_NO_TENSOR)) && (!st->q8 || (p->flags & DA_SEARCH_NO_Q8)) &&
                     !pl.use_tc && !pl.use_q8;
+    // One process: its shards share this very plan, so any search answered by one plain scan pass per shard qualifies
+    // (document filters included; the compacted-list and candidate paths keep the gather into the first shard).
+    if (st->xg_inproc && !ivf && !st->split16 && !pl.use_tc && !pl.use_q8 && !pl.compact && !pl.none_requested &&
+        p->batch <= da::scan_pick_nq(st->dim, pl.k, p->batch))
+        pl.fused_xchg = true;
     const size_t rec_bytes = (size_t)pl.batch * pl.k * 24;
     for (Shard &s : st->shards) {
         CU(cudaSetDevice(s.device));
@@ -1611,6 +1657,10 @@ int da_store_create(const da_config *cfg, da_store **out)
             ok = (e == cudaSuccess);
         }
         st->p2p_gather = ok;
+        if (ok) {
+            int rc = setup_inprocess_exchange(st);
+            if (rc != DA_OK) { da_store_destroy(st); return rc; }
+        }
     }
     if (total > 1) {
         int rc = DA_OK;
@@ -1919,6 +1969,12 @@ int da_store_search(da_store *st, const da_search_params *p, uint8_t *out_chunk_
         bool overflow = false;
         if (trailer && *reinterpret_cast<const uint32_t *>(s0.h_result.p + rec_bytes + 4) != 0)
             return fail(DA_ERR_STATE, "a rank did not deliver its candidates within 4 s (searches on a multi-process store are collective)");
+        if (st->xg_inproc)
+            for (Shard &s : st->shards)
+                if (*reinterpret_cast<volatile uint32_t *>(s.h_xg_timeout) != 0u) {
+                    *reinterpret_cast<volatile uint32_t *>(s.h_xg_timeout) = 0u;
+                    return fail(DA_ERR_STATE, "a shard did not deliver its candidates within 4 s");
+                }
         if (trailer)         // several processes: the OR of every rank's flag, the same word on every rank
             overflow = *reinterpret_cast<const uint32_t *>(s0.h_result.p + rec_bytes) != 0;
         else if (pl.use_tc || pl.use_q8 || st->split16)
