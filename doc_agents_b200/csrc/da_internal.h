@@ -100,6 +100,11 @@ struct ScanArgs {
     volatile unsigned long long *done_flag;
     unsigned long long done_value;
     XchgArgs xg;
+    // Optional: after the final keys of query q are known the last CTA writes gate_out[q] = ordered(max(gate_floor,
+    // score of the k-th key)) -- or ordered(gate_floor) while fewer than k rows qualified (int8 sidecar: the gate of
+    // the candidate re-score, which round 1 computed in a kernel of its own).
+    uint32_t *gate_out;
+    float gate_floor;
     uint32_t n_rows;               // rows to visit when row_list is null
     uint32_t row_base;             // global row of local row 0
     int dim;
@@ -278,6 +283,9 @@ cudaError_t launch_q8_quantize_queries(const float *queries, int nq, int dim, co
 cudaError_t launch_q8_candidates(const ScanArgs &a, const int8_t *q8, const float *factor, const float *err,
                                  int8_t *q8_queries, float *qfactor, float *qerr, key_t64 *cand, uint32_t cap,
                                  uint32_t *cand_count, uint32_t *gate_ordered, uint32_t *overflow, int sm_count,
-                                 cudaStream_t stream, int *grid_out);
+                                 cudaStream_t stream, int *grid_out, int *launches_out = nullptr);
+// true: a search with this floor takes the one-kernel form (the scan quantises the queries itself, appends its
+// candidates and leaves the gate); then a.q_inv_norm may be null and launch_rescore_select may be given q_inv = nullptr
+bool q8_one_kernel_form(float min_sim);
 
 }  // namespace da

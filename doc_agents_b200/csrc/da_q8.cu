@@ -95,6 +95,16 @@ struct Q8Args {
     const int8_t *queries;      // nq x dim
     const float *qfactor;       // per query: scale / |q|
     const float *qerr;          // per query: e_q
+    // One-kernel form (searches with a similarity floor): the CTA quantises the fp32 queries itself (raw_queries; the
+    // three fields above are then unused), every wanted row whose upper end reaches `floor` is appended to the query's
+    // candidate list right away (instead of writing an upper end per row for a collect pass), and the last CTA leaves
+    // the gate max(floor, k-th best lower end) for the re-score (ScanArgs::gate_out).
+    const float *raw_queries;   // nq x dim fp32, or nullptr for the two-pass form
+    key_t64 *cand;              // [nq][cap]: ordered(upper end) << 32 | local row
+    uint32_t cap;
+    uint32_t *cand_count;       // [nq], zeroed by the caller
+    uint32_t *overflow;
+    float floor;
 };
 
 // Same frame as scan_topk_kernel (da_scan.cu): persistent CTAs, a warp takes R rows at a time, 256-bit streaming
@@ -118,10 +128,24 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int K = a.k, P = a.P;
-    for (int i = tid; i < NQ * DW; i += kScanThreads)
-        q_s[i] = (i / DW < a.nq) ? reinterpret_cast<const uint32_t *>(qa.queries)[i] : 0u;
+    if (qa.raw_queries) {
+        // each CTA quantises the queries for itself: one warp per query, q8_quantize_queries_kernel's arithmetic
+        if (warp < NQ) {
+            if (warp < a.nq) {
+                const float *qf = qa.raw_queries + (size_t)warp * a.dim;
+                const float inv = warp_inv_norm(qf, a.dim, lane);
+                q8_quantize_vector(qf, a.dim, inv, reinterpret_cast<int8_t *>(q_s) + (size_t)warp * a.dim, &qf_s[warp], &qe_s[warp], lane);
+            } else {
+                for (int i = lane; i < DW; i += 32) q_s[warp * DW + i] = 0u;
+                if (lane == 0) { qf_s[warp] = 0.f; qe_s[warp] = 0.f; }
+            }
+        }
+    } else {
+        for (int i = tid; i < NQ * DW; i += kScanThreads)
+            q_s[i] = (i / DW < a.nq) ? reinterpret_cast<const uint32_t *>(qa.queries)[i] : 0u;
+        if (tid < NQ) { qf_s[tid] = tid < a.nq ? qa.qfactor[tid] : 0.f; qe_s[tid] = tid < a.nq ? qa.qerr[tid] : 0.f; }
+    }
     for (int i = tid; i < NQ * P; i += kScanThreads) lists[i] = 0ull;
-    if (tid < NQ) { qf_s[tid] = tid < a.nq ? qa.qfactor[tid] : 0.f; qe_s[tid] = tid < a.nq ? qa.qerr[tid] : 0.f; }
     __syncthreads();
     uint32_t qreg[QS > 0 ? QS : 1][8];
     if constexpr (QS > 0) {
@@ -171,7 +195,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
         const uint32_t want_mask = __ballot_sync(0xFFFFFFFFu, want_bits != 0u);
         const uint32_t load_mask = a.read_all ? valid_mask : want_mask;
         if (load_mask == 0) {                                   // skipped rows still need an (impossible) upper end
-            if (valid)
+            if (valid && !qa.cand)
                 for (int q = 0; q < a.nq; q++) a.approx[(size_t)q * n_rows + my_row] = -3.0e38f;
             continue;
         }
@@ -282,7 +306,16 @@ __global__ void __launch_bounds__(kScanThreads, 1) q8_scan_kernel(const Q8Args q
                 const bool wanted = (wb >> q) & 1u;
                 const float approx = (float)acc[r][q] * f * qf_s[q];
                 const float E = ex + qe_s[q] + ex * qe_s[q] + kQ8Margin;
-                if (lane == 0) a.approx[(size_t)q * n_rows + row] = wanted ? fminf(1.f, approx + E) : -3.0e38f;
+                const float upper = fminf(1.f, approx + E);
+                if (qa.cand) {
+                    if (wanted && upper >= qa.floor && lane == 0) {
+                        const uint32_t pos = atomicAdd(qa.cand_count + q, 1u);
+                        if (pos < qa.cap) qa.cand[(size_t)q * qa.cap + pos] = ((key_t64)score_to_ordered(upper) << 32) | (key_t64)row;
+                        else *qa.overflow = 1u;
+                    }
+                } else if (lane == 0) {
+                    a.approx[(size_t)q * n_rows + row] = wanted ? upper : -3.0e38f;
+                }
                 if (!wanted) continue;
                 const key_t64 key = make_key(fmaxf(-1.f, approx - E), a.row_base + row);
                 warp_list_insert(lists + (size_t)q * P + warp * K, K, cnt[q], wmin[q], key, lane);
@@ -350,23 +383,43 @@ cudaError_t launch_q8_quantize_queries(const float *queries, int nq, int dim, co
 // Queries -> int8 (+ factor, error), the int8 scan, the candidate pass.  Leaves the candidates in `cand` /
 // `cand_count` / `gate_ordered` for launch_rescore_select (da_scan.cu).  `a` as for launch_scan, with a.approx set
 // (nq x n_rows floats) and a.out_keys pointing at nq x k scratch keys.
+// A floor of 0.5 or more bounds the candidate set from the first row on (only rows near the query can reach it), so the
+// scan can append candidates as it goes; without one the bound must come from the global k-th best lower end, which
+// exists only after the scan: those searches keep the two-pass form (upper ends per row, then a collect pass).
+bool q8_one_kernel_form(float min_sim)
+{
+    static const bool off = [] { const char *v = getenv("DA_Q8_TWO_PASS"); return v && v[0] == '1'; }();
+    return !off && min_sim >= 0.5f;
+}
+
 cudaError_t launch_q8_candidates(const ScanArgs &a_in, const int8_t *q8, const float *factor, const float *err,
                                  int8_t *q8_queries, float *qfactor, float *qerr, key_t64 *cand, uint32_t cap,
                                  uint32_t *cand_count, uint32_t *gate_ordered, uint32_t *overflow, int sm_count,
-                                 cudaStream_t stream, int *grid_out)
+                                 cudaStream_t stream, int *grid_out, int *launches_out)
 {
     Q8Args qa{};
     qa.s = a_in;
     ScanArgs &a = qa.s;
-    if ((a.dim % 32) || a.nq < 1 || a.nq > kMaxNQ || !a.approx || a.row_list) return cudaErrorInvalidValue;
+    const bool one_kernel = q8_one_kernel_form(a.min_sim);
+    if ((a.dim % 32) || a.nq < 1 || a.nq > kMaxNQ || (!one_kernel && !a.approx) || a.row_list) return cudaErrorInvalidValue;
     const int nqt = a.nq <= 1 ? 1 : a.nq <= 2 ? 2 : a.nq <= 4 ? 4 : 8;
     int P = next_pow2(kScanWarps * a.k);
     if (P < 2 * a.k) P = next_pow2(2 * a.k);
     a.P = P;
     const size_t smem = (size_t)nqt * a.dim + (size_t)nqt * P * sizeof(key_t64);
     if (smem > 220 * 1024) return cudaErrorInvalidValue;
-    q8_quantize_queries_kernel<<<(a.nq * 32 + 255) / 256, 256, 0, stream>>>(a.queries, a.nq, a.dim, a.q_inv_norm, q8_queries,
-                                                                            qfactor, qerr);
+    int launches = 0;
+    if (one_kernel) {
+        cudaError_t e0 = cudaMemsetAsync(cand_count, 0, (size_t)a.nq * 4, stream);
+        if (e0 != cudaSuccess) return e0;
+        qa.raw_queries = a.queries;
+        qa.cand = cand; qa.cap = cap; qa.cand_count = cand_count; qa.overflow = overflow; qa.floor = a.min_sim;
+        a.gate_out = gate_ordered; a.gate_floor = a.min_sim;
+    } else {
+        q8_quantize_queries_kernel<<<(a.nq * 32 + 255) / 256, 256, 0, stream>>>(a.queries, a.nq, a.dim, a.q_inv_norm, q8_queries,
+                                                                                qfactor, qerr);
+        launches++;
+    }
     qa.rows = q8; qa.factor = factor; qa.err = err;
     qa.queries = q8_queries; qa.qfactor = qfactor; qa.qerr = qerr;
     a.out_ids = nullptr;
@@ -402,6 +455,9 @@ cudaError_t launch_q8_candidates(const ScanArgs &a_in, const int8_t *q8, const f
         default: e = q8_launch_one<8, 4, 1>(qa, grid, smem, stream); break;
     }
     if (e != cudaSuccess) return e;
+    launches++;
+    if (launches_out) *launches_out = launches + (one_kernel ? 0 : 1);
+    if (one_kernel) return cudaSuccess;
     e = cudaMemsetAsync(cand_count, 0, (size_t)a.nq * 4, stream);
     if (e != cudaSuccess) return e;
     uint32_t bx = (a.n_rows + 1023) / 1024;

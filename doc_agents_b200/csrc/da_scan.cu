@@ -537,7 +537,18 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
     const int D4 = dim >> 2;
     const bool vec8 = (dim % 8) == 0 && (reinterpret_cast<uintptr_t>(mat) & 31) == 0;
     const float4 *qv = reinterpret_cast<const float4 *>(queries + (size_t)q * dim);
-    const float qi = q_inv[q];
+    float qi;
+    if (q_inv) {
+        qi = q_inv[q];
+    } else {            // no query-norm kernel ran: one warp computes it with that kernel's arithmetic
+        __shared__ float qi_s;
+        if (warp == 0) {
+            const float v = warp_inv_norm(queries + (size_t)q * dim, dim, lane);
+            if (lane == 0) qi_s = v;
+        }
+        __syncthreads();
+        qi = qi_s;
+    }
     const uint32_t gate = gate_ordered[q];
     // int8 sidecar: the gate is also a lower bound of the k-th best EXACT score, so exact scores below it are out
     const float exact_floor = gate_bounds_exact ? fmaxf(min_sim, ordered_to_score(gate)) : min_sim;
@@ -620,15 +631,50 @@ __global__ void __launch_bounds__(1024) select_candidates_kernel(const key_t64 *
     const int tid = threadIdx.x;
     const int n = (int)min(surv_count[q], (uint32_t)kSurvivorCap);
     const key_t64 *lst = surv + (size_t)q * kSurvivorCap;
-    for (int i = tid; i < k; i += blockDim.x) buf[i] = 0ull;
-    const int room = P - k;
-    int done = 0;
-    do {
+    constexpr int kPerThread = kSurvivorCap / 1024;              // 16 survivors per thread at most in the small-k form
+    if (k <= 16 && blockDim.x == 1024) {
+        // Small k (the reference's API caps top_k at 20; 10 in the BASELINE configs) and a CTA to itself: every thread
+        // keeps its survivors in registers and the CTA takes the maximum k times -- k rounds of a block-wide max
+        // instead of up to eight 2048-wide sorts (measured on the int8 path: 78 us -> ~10).  Keys are unique.
+        key_t64 mine[kPerThread];
+#pragma unroll
+        for (int j = 0; j < kPerThread; j++) { const int i = tid + j * 1024; mine[j] = i < n ? lst[i] : 0ull; }
+        key_t64 *warp_best = buf;                                // 32 keys
+        key_t64 *picked = buf + 32;                              // k keys
+        const int lane = tid & 31, warp = tid >> 5;
+        for (int r = 0; r < k; r++) {
+            key_t64 best = 0ull;
+#pragma unroll
+            for (int j = 0; j < kPerThread; j++) best = mine[j] > best ? mine[j] : best;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const key_t64 t = __shfl_xor_sync(0xFFFFFFFFu, best, o); best = t > best ? t : best; }
+            if (lane == 0) warp_best[warp] = best;
+            __syncthreads();
+            key_t64 top = warp_best[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const key_t64 t = __shfl_xor_sync(0xFFFFFFFFu, top, o); top = t > top ? t : top; }
+            if (tid == 0) picked[r] = top;
+            if (top) {
+#pragma unroll
+                for (int j = 0; j < kPerThread; j++) if (mine[j] == top) mine[j] = 0ull;
+            }
+            __syncthreads();
+        }
+        for (int i = tid; i < k; i += blockDim.x) buf[64 + i] = picked[i];
         __syncthreads();
-        for (int i = tid; i < room; i += blockDim.x) buf[k + i] = (done + i < n) ? lst[done + i] : 0ull;
-        cta_bitonic_desc(buf, P);
-        done += room;
-    } while (done < n);
+        for (int i = tid; i < k; i += blockDim.x) buf[i] = buf[64 + i];
+        __syncthreads();
+    } else {
+        for (int i = tid; i < k; i += blockDim.x) buf[i] = 0ull;
+        const int room = P - k;
+        int done = 0;
+        do {
+            __syncthreads();
+            for (int i = tid; i < room; i += blockDim.x) buf[k + i] = (done + i < n) ? lst[done + i] : 0ull;
+            cta_bitonic_desc(buf, P);
+            done += room;
+        } while (done < n);
+    }
     for (int i = tid; i < k; i += blockDim.x) {
         const key_t64 key = buf[i];
         out_keys[(size_t)q * k + i] = key;

@@ -794,13 +794,14 @@ int enqueue_search(da_store *st, const SearchPlan &pl, cudaEvent_t e0 = nullptr,
             if (pl.use_q8) {   // int8 sidecar: intervals for every row, candidates, exact re-score from the fp32 rows
                 const uint32_t cap = (uint32_t)std::min<uint64_t>(std::max<uint32_t>(s.n_rows, 1), 1u << 20);
                 a.approx = s.d_approx.p; a.out_keys = s.d_akeys.p; a.out_ids = nullptr;
+                int q8_launches = 0;
                 CU(da::launch_q8_candidates(a, s.q8, s.q8_factor, s.q8_err, s.d_q8q.p, s.d_q8qf.p, s.d_q8qe.p, s.d_cand.p, cap,
-                                            s.d_cand_count.p, s.d_gate.p, s.d_overflow.p, s.sm_count, s.stream, &grid));
+                                            s.d_cand_count.p, s.d_gate.p, s.d_overflow.p, s.sm_count, s.stream, &grid, &q8_launches));
                 CU(da::launch_rescore_select(s.d_cand.p, s.d_cand_count.p, (int)cap, s.d_gate.p, s.d_surv.p, s.d_surv_count.p,
                                              s.d_overflow.p, a.nq, s.mat, dim, s.inv_norm, a.queries, a.q_inv_norm, s.chunk_ids,
                                              s.row_base, pl.min_sim, pl.k, out_keys + (size_t)q0 * pl.k,
                                              out_ids + (size_t)q0 * pl.k * 16, s.stream, nullptr, nullptr, true));
-                st->launches += 5;
+                st->launches += (uint64_t)q8_launches + 2;
                 if (first) st->scan_grid = grid;
                 continue;
             }
@@ -1146,7 +1147,7 @@ int stage_search(da_store *st, const da_search_params *p, SearchPlan &pl)
         }
         pl.use_q8 = selected * 4 >= st->docs.size() && selected > 0;
     }
-    pl.need_qinv = pl.use_tc || pl.use_q8 || st->split16;
+    pl.need_qinv = pl.use_tc || (pl.use_q8 && !da::q8_one_kernel_form(pl.min_sim)) || st->split16;
     // The scan exchanges and merges across GPUs itself when every rank is certain to run the same plan: that must
     // follow from the call's arguments and the store's configuration alone (every document requested, one SIMT
     // pass, no candidate path), never from what a rank happens to hold.

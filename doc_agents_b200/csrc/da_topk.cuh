@@ -178,6 +178,8 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
         for (int i = tid; i < K; i += kScanThreads) {
             key_t64 key = buf[i];
             pq.out_keys[(size_t)q * K + i] = key;
+            if (a.gate_out && i == K - 1)
+                a.gate_out[q] = score_to_ordered(key ? fmaxf(a.gate_floor, key_score(key)) : a.gate_floor);
             if (pq.out_ids) {
                 uint4 id = make_uint4(0, 0, 0, 0);
                 if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
