@@ -187,6 +187,11 @@ cudaError_t ivf_launch_split_round(const float *counts, int L, void *scratch, co
 cudaError_t ivf_launch_centroid_scores(const float *cent, int L, int D, const float *queries, int nq, float *out, int sm_count,
                                        cudaStream_t stream);
 // Query -> centroid ranking: partial[ks][batch][L] scores (the GEMM of da_tc.cu, or ks = 1 from the kernel above) -> out_keys[batch][probes]
+// One query: scores + selection in one launch (`ticket`: a zeroed device word, left zero)
+cudaError_t ivf_launch_rank_one_query(const float *cent, int L, int D, const float *query, float *scores, int probes,
+                                      key_t64 *out_keys, unsigned int *ticket, int sm_count, cudaStream_t stream);
+// Raises a kernel's dynamic shared-memory limit once per (function, device) instead of per launch (da_scan.cu)
+cudaError_t ensure_dynamic_smem(const void *func, size_t smem);
 constexpr int kIvfSelectMaxLists = 49152;          // the select kernel keeps a query's L scores in shared memory
 cudaError_t ivf_launch_select_probes(const float *partial, int ks, int batch, int L, int probes, key_t64 *out_keys,
                                      cudaStream_t stream);

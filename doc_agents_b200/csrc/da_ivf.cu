@@ -8,9 +8,12 @@
 //     the score matrix is never written;
 //   - a list is an array of row numbers -- rows stay where they are in HBM (a 12 KB row is
 //     read contiguously anyway), so building or refreshing the index moves no vectors;
-//   - a query = the fused scan over the centroid matrix (top `probes`), an expansion of the
-//     chosen lists into one row list, and the fused scan again over that row list.
+//   - a query = score the centroids (fp32 here for small batches -- one launch with the selection for a single
+//     query --, the tcgen05 GEMM of da_tc.cu for batches), keep the `probes` best lists by an exact radix select, and
+//     ONE probe-mode launch of the fused scan (da_scan.cu) in which every query walks its own lists.
 #include "da_internal.h"
+
+#include <algorithm>
 
 namespace da {
 
@@ -414,22 +417,21 @@ __global__ void __launch_bounds__(512) centroid_scores_kernel(const float *__res
 // a 4 x 8-bit radix select finds the probes-th largest value exactly; lists above it, then the lowest-numbered
 // lists equal to it, are emitted in list order (deterministic).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(512) select_probes_kernel(const float *partial, int ks, int batch, int L, int probes,
-                                                            key_t64 *out_keys)
+__device__ void select_probes_cta(const float *partial, int ks, int batch, int q, int L, int probes, key_t64 *out_keys,
+                                  uint32_t *sc /* L words of shared memory */)
 {
-    extern __shared__ uint32_t sc[];                         // L ordered scores
     __shared__ uint32_t hist[256];
-    __shared__ uint32_t sel_prefix, sel_mask, sel_remaining;
+    __shared__ uint32_t sel_prefix, sel_mask, sel_remaining, sel_done;
     __shared__ uint32_t scan_gt[16], scan_eq[16];
-    const int q = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x;
     for (int i = tid; i < L; i += blockDim.x) {
         float s = 0.f;
-        for (int j = 0; j < ks; j++) s += partial[((size_t)j * batch + q) * L + i];
+        for (int j = 0; j < ks; j++) s += __ldcg(&partial[((size_t)j * batch + q) * L + i]);
         sc[i] = score_to_ordered(s);
     }
     const int want = probes < L ? probes : L;
     const int lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { sel_prefix = 0u; sel_mask = 0u; sel_remaining = (uint32_t)want; }
+    if (tid == 0) { sel_prefix = 0u; sel_mask = 0u; sel_remaining = (uint32_t)want; sel_done = 0u; }
     for (int shift = 24; shift >= 0; shift -= 8) {
         if (tid < 256) hist[tid] = 0u;
         __syncthreads();
@@ -471,9 +473,13 @@ __global__ void __launch_bounds__(512) select_probes_kernel(const float *partial
                 sel_remaining = r;
                 sel_prefix = prefix | ((b & 255u) << shift);
                 sel_mask = mask | (255u << shift);
+                // The whole bin is wanted (nearly always so after two passes: the bin then holds a single value): every
+                // value >= the bin's lowest possible one is selected, the lower digits need not be resolved.
+                if (r == hist[b & 255u]) sel_done = 1u;
             }
         }
         __syncthreads();
+        if (sel_done) break;
     }
     const uint32_t T = sel_prefix, take_eq = sel_remaining;     // the want-th largest value; how many of its equals to keep
     const int per = (L + (int)blockDim.x - 1) / (int)blockDim.x;
@@ -503,6 +509,57 @@ __global__ void __launch_bounds__(512) select_probes_kernel(const float *partial
         else if (v == T) { if (pe < take_eq) out[n_gt + pe] = key; pe++; }
     }
     for (int i = want + tid; i < probes; i += blockDim.x) out[i] = 0ull;
+}
+
+__global__ void __launch_bounds__(512) select_probes_kernel(const float *partial, int ks, int batch, int L, int probes,
+                                                            key_t64 *out_keys)
+{
+    extern __shared__ uint32_t sel_sc[];                     // L ordered scores
+    select_probes_cta(partial, ks, batch, (int)blockIdx.x, L, probes, out_keys, sel_sc);
+}
+
+// One query: scores and selection in ONE launch.  The CTAs score the centroids as centroid_scores_kernel does; the
+// last one to finish (ticket) ranks the L scores, which it finds in L2, in the shared memory the query no longer needs.
+// (As two kernels the selection paid a launch and a cold start: 13 us of a 44 us probes = 1 search.)
+__global__ void __launch_bounds__(512) rank_one_query_kernel(const float *__restrict__ cent, int L, int D, const float *__restrict__ query,
+                                                             float *scores, int probes, key_t64 *out_keys, unsigned int *ticket)
+{
+    extern __shared__ __align__(16) unsigned char rk_smem[];
+    __shared__ unsigned int rk_last;
+    float4 *q_s = reinterpret_cast<float4 *>(rk_smem);
+    const int D4 = D >> 2, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < D4; i += blockDim.x) q_s[i] = reinterpret_cast<const float4 *>(query)[i];
+    __syncthreads();
+    for (int l = blockIdx.x * (blockDim.x >> 5) + warp; l < L; l += gridDim.x * (blockDim.x >> 5)) {
+        const float4 *row = reinterpret_cast<const float4 *>(cent) + (size_t)l * D4;
+        float acc = 0.f;
+        for (int c0 = lane; c0 < D4; c0 += 32 * 8) {
+            float4 x[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int c = c0 + 32 * u;
+                x[u] = c < D4 ? __ldg(row + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int c = c0 + 32 * u < D4 ? c0 + 32 * u : 0;          // x is zero there
+                const float4 w = q_s[c];
+                acc = fmaf(x[u].x, w.x, acc); acc = fmaf(x[u].y, w.y, acc);
+                acc = fmaf(x[u].z, w.z, acc); acc = fmaf(x[u].w, w.w, acc);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+        if (lane == 0) scores[l] = acc;
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) rk_last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (!rk_last) return;
+    __threadfence();
+    select_probes_cta(scores, 1, 1, 0, L, probes, out_keys, reinterpret_cast<uint32_t *>(rk_smem));
+    if (tid == 0) *ticket = 0u;
 }
 
 }  // namespace
@@ -614,6 +671,21 @@ cudaError_t ivf_launch_centroid_scores(const float *cent, int L, int D, const fl
 }
 
 size_t ivf_select_smem_bytes(int L) { return (size_t)L * 4; }
+
+// One query: centroid scores + selection of the `probes` best lists in one launch (`ticket`: a zeroed word, left zero).
+cudaError_t ivf_launch_rank_one_query(const float *cent, int L, int D, const float *query, float *scores, int probes,
+                                      key_t64 *out_keys, unsigned int *ticket, int sm_count, cudaStream_t stream)
+{
+    if ((D & 3) || L < 1) return cudaErrorInvalidValue;
+    const size_t smem = std::max((size_t)D * 4, ivf_select_smem_bytes(L));
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void *>(rank_one_query_kernel), smem);
+    if (e != cudaSuccess) return e;
+    int grid = (L + 15) / 16;
+    if (grid > sm_count) grid = sm_count;
+    rank_one_query_kernel<<<grid, 512, smem, stream>>>(cent, L, D, query, scores, probes, out_keys, ticket);
+    return cudaGetLastError();
+}
 
 cudaError_t ivf_launch_select_probes(const float *partial, int ks, int batch, int L, int probes, key_t64 *out_keys,
                                      cudaStream_t stream)

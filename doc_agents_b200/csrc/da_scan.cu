@@ -35,6 +35,7 @@ namespace {
 template <int NQ, int R, int U, int VEC, bool FULL_TILES, bool INDIRECT>
 __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a)
 {
+    DA_TS(0);
     ScanPerQuery pq = scan_per_query(a);
     // IVFFlat probe mode / range mode: this CTA serves query blockIdx.y; its rows are the concatenation of that
     // query's lists (or of the requested documents' row ranges)
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     key_t64 wmin[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; q++) { cnt[q] = 0; wmin[q] = 0ull; }
+    DA_TS(1);
 
     const uint32_t n_rows = probe_mode ? p_start[a.probes] : INDIRECT ? *a.n_rows_dev : a.n_rows;
     const uint32_t n_groups = (n_rows + R - 1) / R;
@@ -330,6 +332,25 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 }
 
 
+template <int NQ, int R, int U, int VEC>
+cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t stream)
+{
+    const bool full = ((a.dim / VEC) % (32 * U)) == 0;
+    auto kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, false> : scan_topk_kernel<NQ, R, U, VEC, false, false>;
+    if (a.row_list || a.probe_keys || a.ranges) {
+        if constexpr (VEC != 16) kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, true> : scan_topk_kernel<NQ, R, U, VEC, false, true>;
+        else return cudaErrorInvalidValue;
+    }
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void *>(kern), smem);
+    if (e != cudaSuccess) return e;
+    kern<<<dim3((unsigned)grid, a.probe_keys ? (unsigned)a.probe_batch : 1u), kScanThreads, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+constexpr size_t kSmemBudget = 220 * 1024;
+
+}  // namespace
+
 // cudaFuncSetAttribute costs a driver call per launch; a function's limit only ever needs raising, per device.
 // The table is a fixed array: this is also on the path of da_scan_topk_noalloc, which must not allocate anything.
 cudaError_t ensure_dynamic_smem(const void *func, size_t smem)
@@ -354,25 +375,6 @@ cudaError_t ensure_dynamic_smem(const void *func, size_t smem)
     if (e == cudaSuccess && n_seen < kEntries) seen[n_seen++] = Entry{func, dev, smem};
     return e;
 }
-
-template <int NQ, int R, int U, int VEC>
-cudaError_t launch_one(const ScanArgs &a, int grid, size_t smem, cudaStream_t stream)
-{
-    const bool full = ((a.dim / VEC) % (32 * U)) == 0;
-    auto kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, false> : scan_topk_kernel<NQ, R, U, VEC, false, false>;
-    if (a.row_list || a.probe_keys || a.ranges) {
-        if constexpr (VEC != 16) kern = full ? scan_topk_kernel<NQ, R, U, VEC, true, true> : scan_topk_kernel<NQ, R, U, VEC, false, true>;
-        else return cudaErrorInvalidValue;
-    }
-    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void *>(kern), smem);
-    if (e != cudaSuccess) return e;
-    kern<<<dim3((unsigned)grid, a.probe_keys ? (unsigned)a.probe_batch : 1u), kScanThreads, smem, stream>>>(a);
-    return cudaGetLastError();
-}
-
-constexpr size_t kSmemBudget = 220 * 1024;
-
-}  // namespace
 
 size_t scan_smem_bytes(int dim, int nq_tmpl, int k, int *P_out)
 {

@@ -1443,9 +1443,9 @@ int enqueue_fast(da_store *st, Slot *sl, const FastPlan &fp, bool flag, int *gri
                 CU(cudaMalloc((void **)&sl->d_scores, (size_t)L * sizeof(float)));
                 sl->scores_cap = (size_t)L;
             }
-            CU(da::ivf_launch_centroid_scores(s.ivf.cent, L, st->dim, a.queries, 1, sl->d_scores, s.sm_count, sl->stream));
-            CU(da::ivf_launch_select_probes(sl->d_scores, 1, 1, L, fp.probes, sl->d_probe_keys, sl->stream));
-            (*launches) += 2;
+            CU(da::ivf_launch_rank_one_query(s.ivf.cent, L, st->dim, a.queries, sl->d_scores, fp.probes, sl->d_probe_keys, sl->d_counter,
+                                             s.sm_count, sl->stream));
+            (*launches)++;
         } else {
             da::ScanArgs c{};
             c.mat = s.ivf.cent; c.inv_norm = s.ivf.cent_inv;

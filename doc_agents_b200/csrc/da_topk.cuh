@@ -3,6 +3,9 @@
 #pragma once
 
 #include "da_internal.h"
+#ifdef DA_SCAN_TIMING
+#include <cstdio>
+#endif
 
 namespace da {
 namespace {
@@ -89,6 +92,13 @@ __device__ __forceinline__ void warp_list_insert(key_t64 *list, int K, int &cnt,
     wmin = st.wmin;
 }
 
+#ifdef DA_SCAN_TIMING
+__shared__ long long g_ts[16];
+#define DA_TS(i) do { if (threadIdx.x == 0) g_ts[i] = clock64(); } while (0)
+#else
+#define DA_TS(i) do { } while (0)
+#endif
+
 // In-place descending bitonic sort of P (power of two) keys in shared memory by the whole CTA.
 __device__ void cta_bitonic_desc(key_t64 *buf, int P)
 {
@@ -106,6 +116,39 @@ __device__ void cta_bitonic_desc(key_t64 *buf, int P)
     }
     __syncthreads();
 }
+
+// The K (<= 32) largest of the keys a warp holds in registers (PER per lane, 0 = empty slot; keys are unique), in
+// descending order: lane r returns the r-th largest (0 when fewer exist).  K rounds of two warp-wide integer maxima
+// (upper word, then lower word among the lanes that hold the winning upper word); the one lane that owned the winner
+// retires it.  No shared memory, no barrier: a round is ~100 cycles where a stage of the CTA-wide bitonic sort costs a
+// barrier, and a sort of 1 024 keys has 55 of them.
+template <int PER>
+__device__ __forceinline__ key_t64 warp_topk_rounds(key_t64 (&v)[PER], int K, int lane)
+{
+    key_t64 best = 0ull, mine = 0ull;
+#pragma unroll
+    for (int i = 0; i < PER; i++) best = v[i] > best ? v[i] : best;
+    for (int r = 0; r < K; r++) {
+        const uint32_t hi = (uint32_t)(best >> 32);
+        const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, hi);
+        if (mx == 0u) break;                                   // nothing left (uniform)
+        const uint32_t ml = __reduce_max_sync(0xFFFFFFFFu, hi == mx ? (uint32_t)best : 0u);
+        const key_t64 win = ((key_t64)mx << 32) | (key_t64)ml;
+        if (lane == r) mine = win;
+        if (best == win) {
+            best = 0ull;
+#pragma unroll
+            for (int i = 0; i < PER; i++) {
+                if (v[i] == win) v[i] = 0ull;
+                best = v[i] > best ? v[i] : best;
+            }
+        }
+    }
+    return mine;
+}
+
+constexpr int kSmallK = 16;             // top-k sizes whose merges run as warp tournaments (the reference asks for 5 and 10)
+constexpr int kTourneyPerLane = 5;      // level 1 of the last CTA's merge: 16 warps x 32 lanes x 5 keys
 
 // The pieces of ScanArgs that probe mode re-bases per query (blockIdx.y).  Kept as a handful of scalars in registers:
 // a mutable copy of the whole argument struct would live in local memory and put a load in front of every use in
@@ -135,11 +178,26 @@ __device__ __forceinline__ ScanPerQuery scan_per_query(const ScanArgs &a)
 __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key_t64 *lists, unsigned int *is_last_s, key_t64 *mbuf, int mbuf_keys)
 {
     const int tid = threadIdx.x, K = a.k, P = a.P;
+    DA_TS(3);
     // ---- CTA epilogue: k best of this CTA per query -> global scratch
-    for (int q = 0; q < a.nq; q++) {
-        cta_bitonic_desc(lists + (size_t)q * P, P);
-        for (int i = tid; i < K; i += kScanThreads)
-            pq.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
+    // Small k (the reference's 5 and 10): warp q ranks query q's kScanWarps x K keys in registers.  Otherwise: CTA-wide sorts.
+    const int lane = tid & 31, warp = tid >> 5;
+    const bool tourney = K <= kSmallK && P <= 256 && (uint32_t)gridDim.x * (uint32_t)K <= (uint32_t)(kScanWarps * 32 * kTourneyPerLane);
+    if (tourney) {
+        __syncthreads();                                 // every warp's list is complete
+        if (warp < a.nq) {
+            key_t64 v[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = lane + 32 * i < P ? lists[(size_t)warp * P + lane + 32 * i] : 0ull;
+            const key_t64 mine = warp_topk_rounds<8>(v, K, lane);
+            if (lane < K) pq.cta_out[((size_t)blockIdx.x * a.nq + warp) * K + lane] = mine;
+        }
+    } else {
+        for (int q = 0; q < a.nq; q++) {
+            cta_bitonic_desc(lists + (size_t)q * P, P);
+            for (int i = tid; i < K; i += kScanThreads)
+                pq.cta_out[((size_t)blockIdx.x * a.nq + q) * K + i] = lists[(size_t)q * P + i];
+        }
     }
     __threadfence();
     __syncthreads();
@@ -150,6 +208,7 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
     __syncthreads();
     if (!*is_last_s) return;
     __threadfence();
+    DA_TS(4);
 
     // ---- last CTA: merge gridDim.x * K keys per query, then write the records
     const uint32_t total = gridDim.x * (uint32_t)K;
@@ -157,6 +216,41 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
     while (MP * 2 <= mbuf_keys && (uint32_t)MP < total + (uint32_t)K) MP *= 2;
     key_t64 *buf = MP > P ? mbuf : lists;
     __syncthreads();
+    if (tourney) {
+        // level 1: the 16 warps share each query's gridDim.x * K keys (<= 5 per lane), winners into the dead list area
+        const uint32_t share = (total + kScanWarps - 1) / kScanWarps;
+        const uint32_t lo = (uint32_t)warp * share, hi = lo + share < total ? lo + share : total;
+        for (int q = 0; q < a.nq; q++) {
+            key_t64 v[kTourneyPerLane];
+#pragma unroll
+            for (int i = 0; i < kTourneyPerLane; i++) {
+                const uint32_t j = lo + (uint32_t)lane + 32u * i;
+                v[i] = j < hi ? __ldcg(&pq.cta_out[((size_t)(j / K) * a.nq + q) * K + j % K]) : 0ull;
+            }
+            const key_t64 mine = warp_topk_rounds<kTourneyPerLane>(v, K, lane);
+            if (lane < K) lists[(size_t)q * P + warp * K + lane] = mine;
+        }
+        __syncthreads();
+        // level 2: warp q ranks query q's 16 x K winners and writes the records
+        if (warp < a.nq) {
+            const int q = warp;
+            key_t64 v[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = lane + 32 * i < kScanWarps * K ? lists[(size_t)q * P + lane + 32 * i] : 0ull;
+            const key_t64 key = warp_topk_rounds<8>(v, K, lane);
+            if (lane < K) {
+                pq.out_keys[(size_t)q * K + lane] = key;
+                if (a.gate_out && lane == K - 1)
+                    a.gate_out[q] = score_to_ordered(key ? fmaxf(a.gate_floor, key_score(key)) : a.gate_floor);
+                if (pq.out_ids) {
+                    uint4 id = make_uint4(0, 0, 0, 0);
+                    if (key) id = reinterpret_cast<const uint4 *>(a.chunk_ids)[key_row(key) - a.row_base];
+                    reinterpret_cast<uint4 *>(pq.out_ids)[(size_t)q * K + lane] = id;
+                }
+            }
+        }
+        __syncthreads();
+    } else
     for (int q = 0; q < a.nq; q++) {
         for (int i = tid; i < K; i += kScanThreads) buf[i] = 0ull;
         uint32_t done = 0;
@@ -188,6 +282,7 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
         }
         __syncthreads();
     }
+    DA_TS(5);
     // ---- exchange with the other GPUs (see XchgArgs): pq.out_keys / pq.out_ids ARE this rank's slot in its own buffer
     if (a.xg.n_ranks > 1) {
         const XchgArgs &x = a.xg;
@@ -220,6 +315,34 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
         // merge n_ranks x K keys per query (n_ranks * K <= P: the CTA's own list area is wide enough)
         const unsigned char *base = x.peer[x.rank] + data0;
         const size_t keys_off = (size_t)a.nq * K * 16;
+        if (tourney) {
+            if (warp < a.nq) {                               // n_ranks x K <= 128 keys per query: warp q ranks query q's
+                const int q = warp;
+                key_t64 v[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int j = lane + 32 * i;
+                    v[i] = j < x.n_ranks * K
+                               ? __ldcv(reinterpret_cast<const key_t64 *>(base + (size_t)(j / K) * x.slot_bytes + keys_off) + (size_t)q * K + j % K)
+                               : 0ull;
+                }
+                const key_t64 key = warp_topk_rounds<4>(v, K, lane);
+                if (lane < K) {
+                    uint4 id = make_uint4(0, 0, 0, 0);
+                    if (key) {
+                        for (int r = 0; r < x.n_ranks; r++) {
+                            const key_t64 *kb = reinterpret_cast<const key_t64 *>(base + (size_t)r * x.slot_bytes + keys_off) + (size_t)q * K;
+                            const uint4 *ib = reinterpret_cast<const uint4 *>(base + (size_t)r * x.slot_bytes) + (size_t)q * K;
+                            for (int j = 0; j < K; j++)
+                                if (__ldcv(kb + j) == key) id = __ldcv(ib + j);
+                        }
+                    }
+                    x.final_keys[(size_t)q * K + lane] = key;
+                    reinterpret_cast<uint4 *>(x.final_ids)[(size_t)q * K + lane] = id;
+                }
+            }
+            __syncthreads();
+        } else
         for (int q = 0; q < a.nq; q++) {
             key_t64 *mb = lists + (size_t)q * P;
             for (int i = tid; i < P; i += kScanThreads) {
@@ -251,6 +374,12 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
     // small-search extras (see ScanArgs): counters handed over and cleared, then the completion flag
     if (a.done_flag) __threadfence_system();             // this thread's record stores are visible to the host first
     __syncthreads();
+    DA_TS(6);
+#ifdef DA_SCAN_TIMING
+    if (tid == 0 && blockIdx.y == 0)
+        printf("scan cta %d/%d: prologue %lld  loop %lld  cta-sort+ticket %lld  merge+ids %lld  fence %lld  (cycles)\n", (int)blockIdx.x, (int)gridDim.x,
+               g_ts[1] - g_ts[0], g_ts[3] - g_ts[1], g_ts[4] - g_ts[3], g_ts[5] - g_ts[4], g_ts[6] - g_ts[5]);
+#endif
     if (tid == 0) {
         if (a.rows_read_out) {
             *a.rows_read_out = a.rows_read ? atomicExch(a.rows_read, 0ull) : 0ull;
