@@ -59,6 +59,7 @@ WORKLOADS = {
     "cfg3_b64_split16": {"BATCH": 64, "SPLIT16": True},
     "cfg4_split16": {"DIM": 1536, "BATCH": 4096, "TOP_K": 100, "MIN_SIM": float("-inf"), "SPLIT16": True},
     "cfg3_b2": {"BATCH": 2},
+    "cfg3_b3": {"BATCH": 3},
     "cfg3_b4": {"BATCH": 4},
     "cfg3_b8": {"BATCH": 8},
     "cfg3_b64": {"BATCH": 64},
@@ -73,7 +74,7 @@ WORKLOADS = {
 def workload_name(n_gpus: int) -> str:
     flt = "all documents requested" if not FILTER_DOCS else \
         f"filtered to {FILTER_DOCS} doc IDs ({'mask as predicate, every row read' if READ_ALL else 'rows of other documents skipped'})"
-    tc_min = 16 if SPLIT16 else 12 if Q8 else 4          # tc_min_batch() in da_store.cu
+    tc_min = int(os.environ.get("DA_TC_MIN_BATCH", 0)) or (16 if SPLIT16 else 3)          # tc_min_batch() in da_store.cu
     path = "fused SIMT scan" if (BATCH < tc_min or NO_TENSOR or FILTER_DOCS) else "tcgen05 TF32 candidates + exact fp32 re-score"
     if SPLIT16:
         path = ("split-plane layout: scan of the upper 16-bit plane for candidates + exact fp32 re-score from both planes"

@@ -857,12 +857,11 @@ int tc_min_batch(const da_store *st)
 {
     static const int env = [] { const char *v = getenv("DA_TC_MIN_BATCH"); return v ? atoi(v) : 0; }();
     if (env > 0) return env;
-    // Measured at 10M x 3072 (ms per batch, fp32 SIMT scan vs tensor path): b=2 16.7 / 20.2, b=4 21.3 / 20.0,
-    // b=8 34.3 / 19.7 -- the SIMT scan pays 2*dim FMAs and dim shared-memory words per row and query, the tensor
-    // path reads the rows once whatever the batch.  The int8 sidecar scan serves 8 queries in 12.6 ms.
+    // Measured at 10M x 3072 (ms per batch, fp32 SIMT scan vs tensor path, rows as the M operand): b=2 16.7 / 17.2,
+    // b=3 21.0 / 17.3, b=4 20.9 / 17.3, b=8 34.3 / 17.2 -- the SIMT scan pays 2*dim FMAs and dim shared-memory words per
+    // row and query, the tensor path reads the rows once whatever the batch.  The int8 sidecar scan serves 8 queries in 12.6 ms.
     if (st->split16) return 16;
-    if (st->q8) return 3;          // int8 SIMT scan: 2 queries 4.9 ms, 4 queries 6.4; int8 tensor path: 5.2-5.8 ms for 4..16
-    return 4;
+    return 3;                      // (int8 SIMT scan: 2 queries 4.9 ms, 4 queries 6.4; int8 tensor path: 5.2-5.8 ms for 4..16)
 }
 
 int ivf_tc_min_batch()

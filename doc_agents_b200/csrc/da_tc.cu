@@ -823,6 +823,240 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     }
 }
 
+// ---------------------------------------------------------------------------
+// The same contraction for FEW queries (batch <= 64, BASELINE configs[2]'s b = 64), with the roles the other way round:
+// A = a tile of 128 corpus rows, B = the queries (N = 32 or 64 columns), accumulator = 128 lanes (rows) x N columns.
+// Why a second orientation: with a handful of queries the kernel above still multiplies a full 128-query tile (half
+// or more of it zero padding) against every row -- 128 tensor cycles per 8 KB of rows, a tensor pipe 40-75 % busy next
+// to a saturated HBM, SM clocks pulled to 1.36 GHz by the power cap, and a third of every 48 KB pipeline stage spent on
+// the query tile: 19.6 ms per pass at 10M x 3072 where the SIMT scan streams the same rows in 16.6.  Here an MMA costs
+// 128*N/256 cycles (16-32 per 4 KB of rows), a stage is 16 KB of rows + N x 128 B of queries, and 8-10 stages are in
+// flight.  Epilogue thread = one ROW: its N scores against the queries' gates (shared memory, broadcast reads).
+// Candidates are rare, so each takes its slot with its own atomicAdd; everything downstream (lists, histograms,
+// final gate, exact re-score, selection) is shared with the kernel above.
+// ---------------------------------------------------------------------------
+constexpr int TCR_MAX_N = 64;
+constexpr uint32_t TCR_SMEM_BUDGET = 200 * 1024;                 // pipeline stages
+constexpr uint32_t TCR_SMEM_BYTES = TCR_SMEM_BUDGET + 1024 + 256 + 2 * TCR_MAX_N * 4;
+
+// NCTA = 2: CTA pairs (tcgen05 cta_group::2, M = 256 rows): each CTA stages its own 128 rows and HALF of the queries, so the
+// query operand costs N/2 x 128 B of L2 traffic per 16 KB of rows -- at N = 64 the single-CTA form moves 1.5 bytes from L2
+// for every byte from HBM, which is what holds it at 19.7 ms when the power cap pulls the L2 clock down (N = 32: 17.6).
+template <int OP, int NCTA>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_rows_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
+                          const BatchArgs a, const int N /* 32 or 64 */)
+{
+    constexpr bool BF16 = OP == OP_BF16, I8 = OP == OP_I8;
+    const int q_rows = N / NCTA;                                  // rows of the query operand this CTA stages
+    const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)q_rows * 128u;
+    const int stages = (int)(TCR_SMEM_BUDGET / stage_bytes);
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = base + TCR_SMEM_BUDGET;
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * 12;          // up to 12 stages
+    const uint32_t bar_tfull = bars + 16 * 12, bar_tempty = bar_tfull + 16;
+    const uint32_t tmem_slot = bar_tempty + 16;
+    volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    float *thr_s = reinterpret_cast<float *>(smem_raw + (bars + 256 - smem_u32(smem_raw)));     // [TCR_MAX_N] gate / (1/|q|)
+    float *qinv_s = thr_s + TCR_MAX_N;                                                            // [TCR_MAX_N]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;        // 0 = leader of the pair
+    const int unit = (int)blockIdx.x / NCTA, n_units = (int)gridDim.x / NCTA;
+    const int n_tiles_total = (int)((a.n_rows + TC_BM * NCTA - 1) / (TC_BM * NCTA));      // tiles of 128 (256) rows
+    const int per_unit = (n_tiles_total + n_units - 1) / n_units;
+    const int t_begin = unit * per_unit;
+    const int t_end = min(n_tiles_total, t_begin + per_unit);
+    const int bk = I8 ? 4 * TC_BK : BF16 ? 2 * TC_BK : TC_BK;     // elements per 128-byte stage row
+    const int kb_count = (a.K + bk - 1) / bk;
+    const uint32_t tmem_cols = 2u * (uint32_t)N;                   // two accumulators: 64 or 128 columns
+    const uint32_t idesc = (I8 ? ((2u << 4) | (1u << 7) | (1u << 10)) : BF16 ? ((1u << 4) | (1u << 7) | (1u << 10)) : ((1u << 4) | (2u << 7) | (2u << 10))) |
+                           ((uint32_t)(N >> 3) << 17) | ((uint32_t)((NCTA * TC_BM) >> 4) << 24);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4 * NCTA); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kMmaWarp) {
+        if (NCTA == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    if (NCTA == 2) cluster_sync_all(); else __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot_ptr;
+    // barriers that live on the leader only: "stage full" (both CTAs' loads land on it) and "accumulator drained"
+    const uint32_t lead_full = NCTA == 2 ? mapa_rank(bar_full, 0) : bar_full;
+    const uint32_t lead_tempty = NCTA == 2 ? mapa_rank(bar_tempty, 0) : bar_tempty;
+
+    if (warp == kProdWarp) {
+        if (lane == 0) {
+            // (Issuing the stages in bursts of 2 / 4 / 8, so that consecutive 128-byte pieces of the same rows reach the
+            // memory controllers together, measured 17.6 / 18.1 / 21.2 ms against 17.6: depth in flight matters, not that.)
+            int stage = 0; uint32_t phase = 0;
+            for (int t = t_begin; t < t_end; t++) {
+                for (int kb = 0; kb < kb_count; kb++) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    const uint32_t sa = base + stage * stage_bytes, sb = sa + TC_A_BYTES;
+                    if (NCTA == 2) {
+                        if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * stage_bytes);
+                        tma_load_2d_pair(sa, &map_x, lead_full + 8 * stage, kb * bk, (t * 2 + rank) * TC_BM);
+                        tma_load_2d_pair(sb, &map_q, lead_full + 8 * stage, kb * bk, rank * q_rows);
+                    } else {
+                        mbar_expect_tx(bar_full + 8 * stage, stage_bytes);
+                        tma_load_2d(sa, &map_x, bar_full + 8 * stage, kb * bk, t * TC_BM);
+                        tma_load_2d(sb, &map_q, bar_full + 8 * stage, kb * bk, 0);
+                    }
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == kMmaWarp) {
+        if (lane == 0 && rank == 0) {
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = t_begin; t < t_end; t++, it++) {
+                const int as = it & 1;
+                const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+                mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + (uint32_t)as * (uint32_t)N;
+                for (int kb = 0; kb < kb_count; kb++) {
+                    mbar_wait(bar_full + 8 * stage, phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = base + stage * stage_bytes, sb = sa + TC_A_BYTES;
+                    const uint64_t da0 = smem_desc_sw128(sa), db0 = smem_desc_sw128(sb);
+#pragma unroll
+                    for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {     // 4 MMAs of 32 bytes of K each, any kind
+                        const uint64_t da_ = da0 + (uint64_t)(k * 2), db_ = db0 + (uint64_t)(k * 2);
+                        const uint32_t acc = (uint32_t)((kb | k) != 0);
+                        if (NCTA == 2) {
+                            if (I8) umma_i8_pair(tmem_d, da_, db_, idesc, acc);
+                            else if (BF16) umma_bf16_pair(tmem_d, da_, db_, idesc, acc);
+                            else umma_tf32_pair(tmem_d, da_, db_, idesc, acc);
+                        } else {
+                            if (I8) umma_i8(tmem_d, da_, db_, idesc, acc);
+                            else if (BF16) umma_bf16(tmem_d, da_, db_, idesc, acc);
+                            else umma_tf32(tmem_d, da_, db_, idesc, acc);
+                        }
+                    }
+                    if (NCTA == 2) umma_commit_pair(bar_empty + 8 * stage); else umma_commit(bar_empty + 8 * stage);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+                if (NCTA == 2) umma_commit_pair(bar_tfull + 8 * as); else umma_commit(bar_tfull + 8 * as);
+            }
+        }
+    } else {
+        // ===== epilogue warps 0..3: thread = row `rlocal` of every row tile; thread q < N also keeps query q's gate =====
+        const uint32_t quad = (uint32_t)warp & 3u;
+        const uint32_t rlocal = quad * 32u + (uint32_t)lane;
+        const bool per_query = a.doc_bitmap && a.bitmap_stride;
+        const bool my_query = rlocal < (uint32_t)N;
+        const bool q_valid = my_query && rlocal < (uint32_t)a.batch;
+        const float my_qinv = q_valid ? a.q_inv[rlocal] : 0.f;
+        const float my_eps = my_query ? batch_eps(a, rlocal) : 0.f;
+        // gate -> threshold on the un-normalised product (see the kernel above): acc * (1/|row|) >= gate / (1/|q|)
+        auto thr_of = [&](float gate) {
+            float thr = __int_as_float(0x7f800000);                 // an absent query (padding) takes nothing
+            if (q_valid) {
+                if (my_qinv > 0.f) { thr = gate / my_qinv; thr -= fabsf(thr) * 9.5367431640625e-7f; }
+                else if (gate <= 0.f) thr = -thr;                    // a zero query scores 0 everywhere
+            }
+            return thr;
+        };
+        if (my_query) { thr_s[rlocal] = thr_of(a.min_sim - my_eps); qinv_s[rlocal] = my_qinv; }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        int it = 0, visited = 0, next_refresh = 1;
+        for (int t = t_begin; t < t_end; t++, it++, visited++) {
+            const uint32_t row = (uint32_t)(t * NCTA + rank) * TC_BM + rlocal;
+            float inv = __int_as_float(0x7fc00000);                 // NaN: an absent, zero or filtered row passes no gate
+            uint32_t slot = 0;
+            if (row < a.n_rows) {
+                const float f = a.inv_norm[row];
+                if (f > 0.f) inv = f;
+                if (a.doc_bitmap) {
+                    slot = a.doc_slot[row];
+                    if (!per_query && !((a.doc_bitmap[slot >> 5] >> (slot & 31)) & 1u)) inv = __int_as_float(0x7fc00000);
+                }
+            }
+            if (visited == next_refresh) {                          // tighten the gates: often at first, then every 32 row tiles
+                next_refresh = visited < 8 ? visited + 1 : (visited < 32 ? visited + 4 : visited + 32);
+                asm volatile("bar.sync 1, 128;" ::: "memory");     // everybody has read the old thresholds
+                if (q_valid) {
+                    const float lb = hist_kth_lower_bound(a.hist + (size_t)rlocal * kHistWords, a.k);
+                    thr_s[rlocal] = thr_of(fmaxf(a.min_sim - my_eps, lb - 2.f * my_eps));
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            const int as = it & 1;
+            const uint32_t aphase = (uint32_t)(it >> 1) & 1;
+            mbar_wait(bar_tfull + 8 * as, aphase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)as * (uint32_t)N;
+            for (int c = 0; c < N / 32; c++) {
+                uint32_t r[32];
+                tmem_ld32(taddr + (uint32_t)c * 32u, r);
+                const float4 *t4 = reinterpret_cast<const float4 *>(thr_s + c * 32);
+                uint32_t pass = 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float4 th = t4[j];
+                    pass |= (acc_value<I8>(r[4 * j + 0]) * inv >= th.x ? 1u : 0u) << (4 * j + 0);
+                    pass |= (acc_value<I8>(r[4 * j + 1]) * inv >= th.y ? 1u : 0u) << (4 * j + 1);
+                    pass |= (acc_value<I8>(r[4 * j + 2]) * inv >= th.z ? 1u : 0u) << (4 * j + 2);
+                    pass |= (acc_value<I8>(r[4 * j + 3]) * inv >= th.w ? 1u : 0u) << (4 * j + 3);
+                }
+                if (pass) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        if (!((pass >> j) & 1u)) continue;
+                        const uint32_t q = (uint32_t)(c * 32 + j);
+                        if (per_query) {
+                            const uint32_t *qmask = a.doc_bitmap + (size_t)q * a.bitmap_stride;
+                            if (!((qmask[slot >> 5] >> (slot & 31)) & 1u)) continue;
+                        }
+                        const uint32_t pos = atomicAdd(a.cand_count + q, 1u);
+                        if (pos < (uint32_t)a.cap) {
+                            const float v = acc_value<I8>(r[j]) * inv * qinv_s[q];
+                            a.cand[(size_t)q * a.cap + pos] = ((unsigned long long)score_to_ordered(v) << 32) | (unsigned long long)row;
+                            uint32_t *hq = a.hist + (size_t)q * kHistWords;
+                            int hc, hf;
+                            hist_bins(fminf(1.f, fmaxf(-1.f, v)), hc, hf);
+                            atomicAdd(hq + 64 + hc * 64 + hf, 1u);
+                            atomicAdd(hq + hc, 1u);
+                        } else {
+                            *a.overflow = 1u;
+                        }
+                    }
+                }
+                __syncwarp();                                       // the next TMEM load is warp-wide
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                if (NCTA == 2) mbar_arrive_cluster(lead_tempty + 8 * as); else mbar_arrive(bar_tempty + 8 * as);
+            }
+        }
+    }
+
+    // a pair leaves together: the leader's MMAs read the other CTA's shared memory and write its TMEM
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncwarp();
+    if (NCTA == 2) cluster_sync_all(); else __syncthreads();
+    if (warp == kMmaWarp) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (NCTA == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+    }
+}
+
 // Final gate per query, read by the re-score kernel.
 __global__ void batch_final_gate_kernel(const uint32_t *hist, int batch, int k, const BatchArgs a, uint32_t *gate_ordered)
 {
@@ -966,6 +1200,70 @@ cudaError_t tc_launch_batch_candidates(const float *queries, int batch, const fl
     // scale/|q|, `eps` the rows' quantisation-error bound, i8->q_err the queries' own
     if (i8 && (bf16 || !i8->queries || !i8->rows || !i8->q_err)) return cudaErrorInvalidValue;
     if (batch > DA_TC_MAX_BATCH) return cudaErrorInvalidValue;
+    // Few queries: rows as the M operand, the queries as N = 32 or 64 columns (tc_rows_candidates_kernel);
+    // DA_TC_QUERY_TILES=1 keeps the query-tile form below for comparisons.
+    static const bool query_tiles_only = [] { const char *v = getenv("DA_TC_QUERY_TILES"); return v && v[0] == '1'; }();
+    if (batch <= TCR_MAX_N && !query_tiles_only) {
+        const int N = batch <= 32 ? 32 : 64;
+        // CTA pairs halve the query operand's L2 traffic (see the kernel); DA_TCR_PAIR = 0 never, 1 at N = 64 (default), 2 always
+        static const int pair_env = [] { const char *v = getenv("DA_TCR_PAIR"); return v ? atoi(v) : 1; }();
+        const int ncta = (pair_env == 2 || (pair_env == 1 && N == 64)) && sm_count >= 2 ? 2 : 1;
+        const uint32_t q_box = (uint32_t)(N / ncta);
+        CUtensorMap map_q, map_x;
+        bool ok;
+        if (i8) {
+            if ((reinterpret_cast<uintptr_t>(i8->rows) & 15) || (reinterpret_cast<uintptr_t>(i8->queries) & 15) || (D & 15)) return cudaErrorInvalidValue;
+            ok = make_map_i8(&map_q, i8->queries, (uint64_t)batch, (uint64_t)D, q_box) && make_map_i8(&map_x, i8->rows, (uint64_t)n_rows, (uint64_t)D, TC_BM);
+        } else if (bf16) {
+            if ((reinterpret_cast<uintptr_t>(x_hi) & 15) || (reinterpret_cast<uintptr_t>(q_hi) & 15) || (D & 7)) return cudaErrorInvalidValue;
+            ok = make_map_bf16(&map_q, q_hi, (uint64_t)batch, (uint64_t)D, q_box) && make_map_bf16(&map_x, x_hi, (uint64_t)n_rows, (uint64_t)D, TC_BM);
+        } else {
+            if ((reinterpret_cast<uintptr_t>(mat) & 15) || (reinterpret_cast<uintptr_t>(queries) & 15) || (D & 3)) return cudaErrorInvalidValue;
+            ok = make_map(&map_q, queries, (uint64_t)batch, (uint64_t)D, q_box) && make_map(&map_x, mat, (uint64_t)n_rows, (uint64_t)D, TC_BM);
+        }
+        if (!ok) return cudaErrorInvalidValue;
+        cudaError_t e = cudaMemsetAsync(cand_count, 0, (size_t)batch * 4, stream);
+        if (e != cudaSuccess) return e;
+        e = cudaMemsetAsync(hist, 0, tc_batch_hist_words(batch) * 4, stream);
+        if (e != cudaSuccess) return e;
+        BatchArgs a{};
+        a.n_rows = n_rows; a.K = D; a.batch = batch; a.k = k; a.cap = tc_batch_cap(k); a.group = 1;
+        a.min_sim = min_sim; a.eps = eps; a.q_err = i8 ? i8->q_err : nullptr;
+        a.inv_norm = inv_norm; a.doc_slot = doc_slot; a.doc_bitmap = doc_bitmap; a.bitmap_stride = bitmap_stride; a.q_inv = q_inv;
+        a.cand = cand; a.cand_count = cand_count; a.hist = hist; a.overflow = overflow; a.group_sync = group_sync;
+        const void *kernel = ncta == 2
+            ? (i8 ? (const void *)tc_rows_candidates_kernel<OP_I8, 2> : bf16 ? (const void *)tc_rows_candidates_kernel<OP_BF16, 2>
+                                                                              : (const void *)tc_rows_candidates_kernel<OP_TF32, 2>)
+            : (i8 ? (const void *)tc_rows_candidates_kernel<OP_I8, 1> : bf16 ? (const void *)tc_rows_candidates_kernel<OP_BF16, 1>
+                                                                              : (const void *)tc_rows_candidates_kernel<OP_TF32, 1>);
+        e = ensure_dynamic_smem(kernel, TCR_SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        cudaLaunchAttribute attrs[1];
+        cudaLaunchConfig_t cfg{};
+        cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = TCR_SMEM_BYTES; cfg.stream = stream;
+        cfg.attrs = attrs; cfg.numAttrs = 0;
+        int n_units = sm_count / ncta;
+        if (ncta == 2) {
+            attrs[0].id = cudaLaunchAttributeClusterDimension;
+            attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+            cfg.numAttrs = 1;
+            cfg.gridDim = dim3((unsigned)(2 * n_units));
+            int max_pairs = 0;
+            e = cudaOccupancyMaxActiveClusters(&max_pairs, kernel, &cfg);
+            if (e != cudaSuccess) return e;
+            if (max_pairs < 1) return cudaErrorLaunchOutOfResources;
+            if (n_units > max_pairs) n_units = max_pairs;
+        }
+        const uint32_t n_tiles = (n_rows + TC_BM * ncta - 1) / (TC_BM * ncta);
+        if ((uint32_t)n_units > n_tiles) n_units = n_tiles ? (int)n_tiles : 1;
+        cfg.gridDim = dim3((unsigned)(n_units * ncta));
+        int n_arg = N;
+        void *args[] = {(void *)&map_q, (void *)&map_x, (void *)&a, (void *)&n_arg};
+        e = cudaLaunchKernelExC(&cfg, kernel, args);
+        if (e != cudaSuccess) return e;
+        batch_final_gate_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(hist, batch, k, a, gate_ordered);
+        return cudaGetLastError();
+    }
     const int m_tiles = tc_batch_m_tiles(batch);
     // CTA pairs need two query tiles to work on; DA_TC_SINGLE_CTA=1 keeps the single-CTA form (for comparisons)
     static const bool single_only = [] { const char *v = getenv("DA_TC_SINGLE_CTA"); return v && v[0] == '1'; }();
