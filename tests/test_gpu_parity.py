@@ -225,6 +225,36 @@ def test_batched_queries_equal_single_queries(batch):
             assert np.allclose(sc_b[i], o_sc, rtol=REL_TOL)
 
 
+@pytest.mark.parametrize("k", [1, 2, 7, 15, 16, 17, 33])
+def test_top_k_on_both_sides_of_the_register_merge(k):
+    """k <= 16 is merged by warp tournaments in registers (CTA level, last CTA, cross-GPU), larger k by CTA-wide sorts
+    (da_topk.cuh): the same searches on both sides of the switch, through the bitmap scan, the range path, the SIMT batch
+    (2 and 8 queries per pass) and with more qualifying rows than k in every CTA -- all against the oracle."""
+    S = oracle.Synth(n_clusters=2)
+    n, dim = 40_000, 256                   # 148 CTAs x 16 warps each see a few rows
+    n_docs = n // S.chunks_per_doc
+    with GpuStore(dim=dim, capacity_rows=n) as st:
+        st.generate_synthetic(S, 0, n)
+        mat = oracle.gen_rows(S, 0, n, dim)
+        rd = oracle.row_docs(S, 0, n)
+        docs = oracle.doc_ids(S, 0, n_docs)
+        qs = np.stack([oracle.gen_query(S, 50 + i, i % 2, dim) for i in range(8)])
+        for floor in (0.7, -1.0):
+            for wanted in (None, list(range(0, n_docs, 3)), [4, 5, 11]):
+                allowed = None
+                kw = dict(all_docs=True) if wanted is None else dict(doc_ids=docs[wanted])
+                if wanted is not None:
+                    allowed = np.zeros(n_docs, np.uint8)
+                    allowed[wanted] = 1
+                for batch in (1, 2, 8):
+                    ids, sc, rows = st.search(qs[:batch], k, min_similarity=floor, no_tensor=True, **kw)
+                    for i in range(batch):
+                        o_rows, o_sc, _ = oracle.topk(mat, rd if wanted is not None else None, allowed, qs[i], k + 8, floor)
+                        why = topk_matches_extended(rows[i], sc[i], o_rows, o_sc, k)
+                        assert why == "", (k, floor, wanted and len(wanted), batch, i, why)
+                        assert np.array_equal(ids[i], oracle.chunk_ids(S, 0, n)[rows[i]])
+
+
 def _cluster_oracle(S, n_rows, dim, q, cluster, k, min_sim=0.7):
     """Oracle top-k over the documents of one cluster (the only rows that can rank: same-cluster cosine ~0.8 against
     ~0 across clusters).  Returns global rows and scores."""
