@@ -1,3 +1,5 @@
+# The 8-GPU validation of the round (run from the repo root on an 8-GPU box; outputs in gpurun_out/n8): bench at N = 8 / 4 / 2,
+# the int8, b = 64 and configs[3] workloads at N = 8, the CPU arm, the multi-GPU tests and the one-process 8-GPU bench.
 set -x
 O=gpurun_out/n8; mkdir -p $O
 run() { n=$1; shift; timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + RANDOM % 400)) bench.py --gpus $n "$@" 2> $O/err_$n.txt | tail -1; }

@@ -1,3 +1,4 @@
+# How the round-2 records under profiles/ were regenerated on one GPU (run from the repo root on the GPU box; outputs in gpurun_out/regen).
 set -x
 O=gpurun_out/regen; mkdir -p $O
 for w in cfg1 cfg2 cfg3_b3 cfg3_b8 cfg3_b64 cfg3_b1_q8 cfg3_b64_q8; do timeout 300 python bench.py --workload $w > $O/r2_bench_$w.json 2> $O/err_$w.txt; done

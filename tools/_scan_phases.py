@@ -1,3 +1,6 @@
+"""Phase times of the scan kernel's last CTA (prologue, row loop, CTA merge + ticket, last-CTA merge + ids, fence), printed by the
+kernel itself when the library is built with DA_NVCC_EXTRA=-DDA_SCAN_TIMING (clock64 stamps, da_topk.cuh): IVFFlat probe scans,
+a 16-document small search and full scans at 10M x 3072.  Measurement only."""
 import sys, os, numpy as np
 sys.path.insert(0, "/root/repo")
 from doc_agents_b200 import GpuStore, synth
