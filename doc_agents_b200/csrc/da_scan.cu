@@ -634,7 +634,7 @@ __global__ void __launch_bounds__(1024) select_candidates_kernel(const key_t64 *
     const int n = (int)min(surv_count[q], (uint32_t)kSurvivorCap);
     const key_t64 *lst = surv + (size_t)q * kSurvivorCap;
     constexpr int kPerThread = kSurvivorCap / 1024;              // 16 survivors per thread at most in the small-k form
-    if (k <= 16 && blockDim.x == 1024) {
+    if (k <= 20 && blockDim.x == 1024) {
         // Small k (the reference's API caps top_k at 20; 10 in the BASELINE configs) and a CTA to itself: every thread
         // keeps its survivors in registers and the CTA takes the maximum k times -- k rounds of a block-wide max
         // instead of up to eight 2048-wide sorts (measured on the int8 path: 78 us -> ~10).  Keys are unique.

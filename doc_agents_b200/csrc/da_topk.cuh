@@ -147,8 +147,47 @@ __device__ __forceinline__ key_t64 warp_topk_rounds(key_t64 (&v)[PER], int K, in
     return mine;
 }
 
-constexpr int kSmallK = 16;             // top-k sizes whose merges run as warp tournaments (the reference asks for 5 and 10)
-constexpr int kTourneyPerLane = 5;      // level 1 of the last CTA's merge: 16 warps x 32 lanes x 5 keys
+constexpr int kSmallK = 20;             // top-k sizes whose merges run as warp tournaments: the reference's API allows 1..20 (cmd/query/main.go:23)
+constexpr int kMidK = 16;               // up to here the narrow register arrays below do (measured: the wide ones cost k = 5 / 10 searches 0.8 us)
+// keys per lane:                          K <= 16 | K <= 20
+constexpr int kTourneyCtaPer = 8,  kTourneyCtaPerWide = 16;     // CTA level: kScanWarps x K <= P <= 256 | 512
+constexpr int kTourneyPerLane = 5, kTourneyPerLaneWide = 6;     // level 1 of the last CTA's merge: 16 warps x 32 lanes x 5 | 6 keys >= 148 CTAs x K
+constexpr int kTourneyL2Per = 8,   kTourneyL2PerWide = 10;      // level 2: kScanWarps x K <= 256 | 320 keys in one warp
+constexpr int kTourneyXgPer = 4,   kTourneyXgPerWide = 5;       // cross-GPU merge: kXchgMaxRanks x K <= 128 | 160 keys in one warp
+
+// The K best of src[0 .. count) (shared memory), one warp; lane r returns the r-th.
+template <int PER>
+__device__ __forceinline__ key_t64 tourney_smem(const key_t64 *src, int count, int K, int lane)
+{
+    key_t64 v[PER];
+#pragma unroll
+    for (int i = 0; i < PER; i++) v[i] = lane + 32 * i < count ? src[lane + 32 * i] : 0ull;
+    return warp_topk_rounds<PER>(v, K, lane);
+}
+// ... of the CTAs' keys [lo, hi) of query q in global scratch (flat index j = cta * K + i).
+template <int PER>
+__device__ __forceinline__ key_t64 tourney_cta_keys(const key_t64 *cta_out, uint32_t lo, uint32_t hi, int K, int nq, int q, int lane)
+{
+    key_t64 v[PER];
+#pragma unroll
+    for (int i = 0; i < PER; i++) {
+        const uint32_t j = lo + (uint32_t)lane + 32u * i;
+        v[i] = j < hi ? __ldcg(&cta_out[((size_t)(j / K) * nq + q) * K + j % K]) : 0ull;
+    }
+    return warp_topk_rounds<PER>(v, K, lane);
+}
+// ... of the ranks' keys of query q in this rank's exchange buffer.
+template <int PER>
+__device__ __forceinline__ key_t64 tourney_rank_keys(const unsigned char *base, size_t slot_bytes, size_t keys_off, int n_ranks, int K, int q, int lane)
+{
+    key_t64 v[PER];
+#pragma unroll
+    for (int i = 0; i < PER; i++) {
+        const int j = lane + 32 * i;
+        v[i] = j < n_ranks * K ? __ldcv(reinterpret_cast<const key_t64 *>(base + (size_t)(j / K) * slot_bytes + keys_off) + (size_t)q * K + j % K) : 0ull;
+    }
+    return warp_topk_rounds<PER>(v, K, lane);
+}
 
 // The pieces of ScanArgs that probe mode re-bases per query (blockIdx.y).  Kept as a handful of scalars in registers:
 // a mutable copy of the whole argument struct would live in local memory and put a load in front of every use in
@@ -182,14 +221,14 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
     // ---- CTA epilogue: k best of this CTA per query -> global scratch
     // Small k (the reference's 5 and 10): warp q ranks query q's kScanWarps x K keys in registers.  Otherwise: CTA-wide sorts.
     const int lane = tid & 31, warp = tid >> 5;
-    const bool tourney = K <= kSmallK && P <= 256 && (uint32_t)gridDim.x * (uint32_t)K <= (uint32_t)(kScanWarps * 32 * kTourneyPerLane);
+    const bool narrow = K <= kMidK;
+    const bool tourney = K <= kSmallK && P <= 32 * (narrow ? kTourneyCtaPer : kTourneyCtaPerWide) &&
+                         (uint32_t)gridDim.x * (uint32_t)K <= (uint32_t)(kScanWarps * 32 * (narrow ? kTourneyPerLane : kTourneyPerLaneWide));
     if (tourney) {
         __syncthreads();                                 // every warp's list is complete
         if (warp < a.nq) {
-            key_t64 v[8];
-#pragma unroll
-            for (int i = 0; i < 8; i++) v[i] = lane + 32 * i < P ? lists[(size_t)warp * P + lane + 32 * i] : 0ull;
-            const key_t64 mine = warp_topk_rounds<8>(v, K, lane);
+            const key_t64 mine = narrow ? tourney_smem<kTourneyCtaPer>(lists + (size_t)warp * P, P, K, lane)
+                                        : tourney_smem<kTourneyCtaPerWide>(lists + (size_t)warp * P, P, K, lane);
             if (lane < K) pq.cta_out[((size_t)blockIdx.x * a.nq + warp) * K + lane] = mine;
         }
     } else {
@@ -225,23 +264,16 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
         const uint32_t share = (total + kScanWarps - 1) / kScanWarps;
         const uint32_t lo = (uint32_t)warp * share, hi = lo + share < total ? lo + share : total;
         for (int q = 0; q < a.nq; q++) {
-            key_t64 v[kTourneyPerLane];
-#pragma unroll
-            for (int i = 0; i < kTourneyPerLane; i++) {
-                const uint32_t j = lo + (uint32_t)lane + 32u * i;
-                v[i] = j < hi ? __ldcg(&pq.cta_out[((size_t)(j / K) * a.nq + q) * K + j % K]) : 0ull;
-            }
-            const key_t64 mine = warp_topk_rounds<kTourneyPerLane>(v, K, lane);
+            const key_t64 mine = narrow ? tourney_cta_keys<kTourneyPerLane>(pq.cta_out, lo, hi, K, a.nq, q, lane)
+                                        : tourney_cta_keys<kTourneyPerLaneWide>(pq.cta_out, lo, hi, K, a.nq, q, lane);
             if (lane < K) lists[(size_t)q * P + warp * K + lane] = mine;
         }
         __syncthreads();
         // level 2: warp q ranks query q's 16 x K winners and writes the records
         if (warp < a.nq) {
             const int q = warp;
-            key_t64 v[8];
-#pragma unroll
-            for (int i = 0; i < 8; i++) v[i] = lane + 32 * i < kScanWarps * K ? lists[(size_t)q * P + lane + 32 * i] : 0ull;
-            const key_t64 key = warp_topk_rounds<8>(v, K, lane);
+            const key_t64 key = narrow ? tourney_smem<kTourneyL2Per>(lists + (size_t)q * P, kScanWarps * K, K, lane)
+                                       : tourney_smem<kTourneyL2PerWide>(lists + (size_t)q * P, kScanWarps * K, K, lane);
             if (lane < K) {
                 pq.out_keys[(size_t)q * K + lane] = key;
                 if (a.gate_out && lane == K - 1)
@@ -320,17 +352,10 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
         const unsigned char *base = x.peer[x.rank] + data0;
         const size_t keys_off = (size_t)a.nq * K * 16;
         if (tourney) {
-            if (warp < a.nq) {                               // n_ranks x K <= 128 keys per query: warp q ranks query q's
+            if (warp < a.nq) {                               // n_ranks x K <= 160 keys per query: warp q ranks query q's
                 const int q = warp;
-                key_t64 v[4];
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int j = lane + 32 * i;
-                    v[i] = j < x.n_ranks * K
-                               ? __ldcv(reinterpret_cast<const key_t64 *>(base + (size_t)(j / K) * x.slot_bytes + keys_off) + (size_t)q * K + j % K)
-                               : 0ull;
-                }
-                const key_t64 key = warp_topk_rounds<4>(v, K, lane);
+                const key_t64 key = narrow ? tourney_rank_keys<kTourneyXgPer>(base, x.slot_bytes, keys_off, x.n_ranks, K, q, lane)
+                                           : tourney_rank_keys<kTourneyXgPerWide>(base, x.slot_bytes, keys_off, x.n_ranks, K, q, lane);
                 if (lane < K) {
                     uint4 id = make_uint4(0, 0, 0, 0);
                     if (key) {

@@ -225,9 +225,9 @@ def test_batched_queries_equal_single_queries(batch):
             assert np.allclose(sc_b[i], o_sc, rtol=REL_TOL)
 
 
-@pytest.mark.parametrize("k", [1, 2, 7, 15, 16, 17, 33])
+@pytest.mark.parametrize("k", [1, 2, 7, 16, 17, 20, 21, 33])
 def test_top_k_on_both_sides_of_the_register_merge(k):
-    """k <= 16 is merged by warp tournaments in registers (CTA level, last CTA, cross-GPU), larger k by CTA-wide sorts
+    """k <= 20 (the reference's API range, cmd/query/main.go:23) is merged by warp tournaments in registers (CTA level, last CTA, cross-GPU), larger k by CTA-wide sorts
     (da_topk.cuh): the same searches on both sides of the switch, through the bitmap scan, the range path, the SIMT batch
     (2 and 8 queries per pass) and with more qualifying rows than k in every CTA -- all against the oracle."""
     S = oracle.Synth(n_clusters=2)
