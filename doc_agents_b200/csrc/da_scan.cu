@@ -104,8 +104,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 
     int cnt[NQ];
     key_t64 wmin[NQ];
+    uint32_t live_q = 0u;               // queries that can match at all: a zero query (1/|q| = 0) matches nothing, whatever the floor
 #pragma unroll
-    for (int q = 0; q < NQ; q++) { cnt[q] = 0; wmin[q] = 0ull; }
+    for (int q = 0; q < NQ; q++) { cnt[q] = 0; wmin[q] = 0ull; live_q |= (q_inv_s[q] > 0.f ? 1u : 0u) << q; }
     DA_TS(1);
 
     const uint32_t n_rows = probe_mode ? p_start[a.probes] : INDIRECT ? *a.n_rows_dev : a.n_rows;
@@ -132,6 +133,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             } else {
                 want_bits = 0xFFFFFFFFu;
             }
+            want_bits &= live_q;
         }
     };
 
@@ -551,6 +553,7 @@ __global__ void __launch_bounds__(256) rescore_candidates_kernel(const key_t64 *
         __syncthreads();
         qi = qi_s;
     }
+    if (!(qi > 0.f)) return;            // a zero query matches nothing (deviation 1): no survivors
     const uint32_t gate = gate_ordered[q];
     // int8 sidecar: the gate is also a lower bound of the k-th best EXACT score, so exact scores below it are out
     const float exact_floor = gate_bounds_exact ? fmaxf(min_sim, ordered_to_score(gate)) : min_sim;

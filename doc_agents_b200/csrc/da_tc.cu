@@ -710,13 +710,12 @@ tc_batch_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
                 const bool q_valid = q < (uint32_t)a.batch;
                 const float qinv = q_valid ? a.q_inv[q] : 0.f;
                 // gate on the un-normalised product: acc * (1/|row|) >= gate / (1/|q|), one multiply and one compare per
-                // row.  The factor of an unwanted row is NaN, which fails every comparison; a zero query scores 0
-                // everywhere; an absent query (padding of the last query tile) takes nothing.
+                // row.  The factor of an unwanted row is NaN, which fails every comparison; a zero query and an
+                // absent one (padding of the last query tile) take nothing.
                 const float gate = gate_s[mt * TC_BM + qlocal];
                 float thr = __int_as_float(0x7f800000);
                 if (q_valid) {
-                    if (qinv > 0.f) { thr = gate / qinv; thr -= fabsf(thr) * 9.5367431640625e-7f; }
-                    else if (gate <= 0.f) thr = -thr;
+                    if (qinv > 0.f) { thr = gate / qinv; thr -= fabsf(thr) * 9.5367431640625e-7f; }      // (a zero query takes nothing)
                 }
                 // per-query document sets are tested lazily, only for the few rows that pass the gate
                 const uint32_t *qmask = (per_query && q_valid) ? a.doc_bitmap + (size_t)q * a.bitmap_stride : nullptr;
@@ -966,8 +965,7 @@ tc_rows_candidates_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
         auto thr_of = [&](float gate) {
             float thr = __int_as_float(0x7f800000);                 // an absent query (padding) takes nothing
             if (q_valid) {
-                if (my_qinv > 0.f) { thr = gate / my_qinv; thr -= fabsf(thr) * 9.5367431640625e-7f; }
-                else if (gate <= 0.f) thr = -thr;                    // a zero query scores 0 everywhere
+                if (my_qinv > 0.f) { thr = gate / my_qinv; thr -= fabsf(thr) * 9.5367431640625e-7f; }      // (a zero query takes nothing)
             }
             return thr;
         };

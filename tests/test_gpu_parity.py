@@ -255,6 +255,56 @@ def test_top_k_on_both_sides_of_the_register_merge(k):
                         assert np.array_equal(ids[i], oracle.chunk_ids(S, 0, n)[rows[i]])
 
 
+def test_pgvectors_published_cosine_distance_answers_on_the_device():
+    """The eight answers of pgvector's own regression suite for cosine_distance (see tests/test_oracle.py for the provenance),
+    through the CUDA path: one stored row (padded to dim 4 with zeros, which changes no cosine), one query, no floor."""
+    from test_oracle import PGVECTOR_PUBLISHED
+    chunk = oracle.chunk_ids(S0, 0, 1)
+    docs = oracle.doc_ids(S0, 0, 1)
+    for a, b, want in PGVECTOR_PUBLISHED:
+        row = np.zeros((1, 4), np.float32); row[0, :len(a)] = a
+        q = np.zeros(4, np.float32); q[:len(b)] = b
+        with GpuStore(dim=4, capacity_rows=8) as st:
+            st.save_chunks_raw(docs[0], chunk)
+            st.save_embeddings_raw(chunk, row)
+            ids, sc, rows = st.search(q, 5, all_docs=True, min_similarity=-10.0)
+            if np.isnan(want) and abs(a[0]) < 1e30:
+                assert len(rows[0]) == 0                 # zero vector: NaN in pgvector, never a match here (DESIGN.md section 2, deviation 1)
+            elif np.isnan(want):
+                # [3e38] . [3e38]: pgvector's FLOAT accumulators overflow (inf / inf = NaN).  The device keeps norms in double and
+                # answers the true cosine, clamped: deviation 5 of DESIGN.md section 2 (norms outside float range: 19 orders of
+                # magnitude from any embedding, which openai.go:146-158 normalises to length 1).
+                assert len(rows[0]) == 1 and abs(float(sc[0][0]) - 1.0) <= REL_TOL
+            else:
+                assert len(rows[0]) == 1 and rows[0][0] == 0
+                # (the device multiplies by two rounded reciprocal norms: [1,1].[1,1] comes out as 0.99999994, inside the tolerance)
+                assert abs(float(sc[0][0]) - (1.0 - want)) <= REL_TOL * abs(1.0 - want) + ABS_TOL, (a, b, sc[0][0], want)
+                assert np.array_equal(ids[0][0], chunk[0])
+
+
+@pytest.mark.parametrize("sidecar", [False, True])
+def test_a_zero_query_matches_nothing_on_any_path_whatever_the_floor(sidecar):
+    """pgvector answers NaN for a zero vector; here such a query (like a zero row) matches nothing (DESIGN.md section 2,
+    deviation 1) -- also below a floor of 0, alone or inside a batch, on the SIMT scan, the tensor path and the int8 sidecar."""
+    S = oracle.Synth(n_clusters=2)
+    n, dim, k = 2000, 64, 7
+    with GpuStore(dim=dim, capacity_rows=n, q8_sidecar=sidecar) as st:
+        st.generate_synthetic(S, 0, n)
+        mat = oracle.gen_rows(S, 0, n, dim)
+        qs = np.stack([oracle.gen_query(S, i, i % 2, dim) for i in range(5)])
+        qs[2] = 0.0
+        for floor in (0.7, 0.5, -1.0):
+            for kw in (dict(), dict(no_tensor=True), dict(no_tensor=True, no_q8=True)):
+                ids, sc, rows = st.search(qs, k, all_docs=True, min_similarity=floor, **kw)
+                assert len(rows[2]) == 0, (floor, kw, rows[2], sc[2])
+                for i in (0, 1, 3, 4):
+                    o_rows, o_sc, _ = oracle.topk(mat, None, None, qs[i], k + 8, floor)
+                    assert topk_matches_extended(rows[i], sc[i], o_rows, o_sc, k) == "", (floor, kw, i)
+            alone = st.search(qs[2], k, all_docs=True, min_similarity=floor)
+            assert len(alone[2][0]) == 0
+            assert len(oracle.topk(mat, None, None, qs[2], k, floor)[0]) == 0
+
+
 def _cluster_oracle(S, n_rows, dim, q, cluster, k, min_sim=0.7):
     """Oracle top-k over the documents of one cluster (the only rows that can rank: same-cluster cosine ~0.8 against
     ~0 across clusters).  Returns global rows and scores."""

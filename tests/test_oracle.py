@@ -52,6 +52,40 @@ def test_fast_build_and_threads_agree(case):
             assert abs(full[a] - full[b]) <= REL_TOL * abs(full[b]) + ABS_TOL
 
 
+# pgvector's own regression suite for `cosine_distance` / `<=>` (test/sql/functions.sql with test/expected/functions.out in the
+# published repository -- the extension is not on this box and is not vendored by the reference, which only names the image
+# `ankane/pgvector`, untagged, in docker-compose.yml:3; restated here from the published file).  The only answers of the real
+# operator this repository can hold the oracle to: zero vector -> NaN, the clamp to [-1, 1] (1.1-scaled vectors give exactly
+# 0 and 2), and FLOAT accumulators (3e38 squared overflows to inf, inf/inf = NaN -- a double accumulator answers 0).
+PGVECTOR_PUBLISHED = [
+    ([1, 2], [2, 4], 0.0),
+    ([1, 2], [0, 0], float("nan")),
+    ([1, 1], [1, 1], 0.0),
+    ([1, 0], [0, 2], 1.0),
+    ([1, 1], [-1, -1], 2.0),
+    ([1, 1], [1.1, 1.1], 0.0),
+    ([1, 1], [-1.1, -1.1], 2.0),
+    ([3e38], [3e38], float("nan")),
+]
+
+
+@pytest.mark.parametrize("a,b,want", PGVECTOR_PUBLISHED)
+def test_cosine_distance_gives_pgvectors_published_answers(a, b, want):
+    a, b = np.asarray(a, np.float32), np.asarray(b, np.float32)
+    with np.errstate(over="ignore", invalid="ignore"):
+        got = [oracle.cosine_distance(a, b), float(oracle_np.cosine_distance(a, b))]
+    for g in got:
+        assert (np.isnan(g) and np.isnan(want)) or g == want, (a, b, got, want)
+    # through the TopK statement: a finite distance comes back as 1 - distance; a NaN distance never matches HERE (deliberate
+    # deviation (1) of DESIGN.md section 2 -- Postgres orders NaN above every number, so `NaN >= floor` holds there)
+    mat = np.zeros((1, 4), np.float32); mat[0, :len(a)] = a
+    q = np.zeros(4, np.float32); q[:len(b)] = b
+    rows, scores, _ = oracle.topk(mat, None, None, q, 5, -10.0)
+    assert len(rows) == (0 if np.isnan(want) else 1)
+    if not np.isnan(want):
+        assert scores[0] == np.float32(1.0 - want)
+
+
 def test_synthetic_known_answers():
     g = GOLDEN["synthetic"]
     S = oracle.Synth()
