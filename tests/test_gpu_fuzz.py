@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 import oracle
-from cases import ABS_TOL, REL_TOL, Case, check_against_oracle
+from cases import ABS_TOL, REL_TOL, Case, check_against_oracle, topk_matches_extended
 from doc_agents_b200 import GpuStore
 
 
@@ -121,3 +121,71 @@ def test_random_configurations_every_path_gives_the_same_answer(seed):
                     assert np.array_equal(a[0][i], b[0][i]), (info, batch, i)
             check_against_oracle(c, st.search(c.q, c.k, filt, min_similarity=c.min_sim)[2][0],
                                  st.search(c.q, c.k, filt, min_similarity=c.min_sim)[1][0])
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_write_sequences_match_a_model_of_the_tables(seed):
+    """The write side (SaveChunks / SaveEmbeddings: postgres.go:142-215) under random sequences -- documents saved in pieces and
+    interleaved, chunks re-embedded, chunks moved to another document, embeddings for a subset only -- against a Python model of
+    the two tables; after every few writes a search (one query: the range path or the bitmap paths; a batch: per-row document
+    slots) must equal the oracle over the model's current rows.  A row's number is the order of its chunk's first embedding."""
+    rng = np.random.default_rng(9000 + seed)
+    S0 = oracle.Synth()
+    dim, n_chunks, n_docs = 64, 500, 9
+    chunk = oracle.chunk_ids(S0, 0, n_chunks)
+    docs = oracle.doc_ids(S0, 0, n_docs + 2)
+    q = oracle.normalize(rng.standard_normal(dim).astype(np.float32))
+    doc_of = {}            # chunk index -> document index        (table chunks)
+    row_of = {}            # chunk index -> row                   (table embeddings, in order of first insert)
+    vec_of = {}
+    def new_vec():
+        v = (q * np.float32(rng.uniform(0.5, 1.0)) + np.float32(rng.uniform(0.02, 0.4) / np.sqrt(dim)) * rng.standard_normal(dim)).astype(np.float32)
+        return v if rng.random() < 0.5 else oracle.normalize(v)
+    with GpuStore(dim=dim, capacity_rows=n_chunks) as st:
+        for step in range(60):
+            op = rng.random()
+            if op < 0.35 or not doc_of:                                   # SaveChunks: a run of chunks for one document (new or moved)
+                d = int(rng.integers(0, n_docs))
+                start = int(rng.integers(0, n_chunks - 1))
+                idx = list(range(start, min(n_chunks, start + int(rng.integers(1, 40)))))
+                if rng.random() < 0.3:
+                    idx = [int(i) for i in rng.choice(n_chunks, size=int(rng.integers(1, 12)), replace=False)]
+                st.save_chunks_raw(docs[d], chunk[idx])
+                for i in idx:
+                    doc_of[i] = d
+            elif op < 0.8:                                                # SaveEmbeddings for chunks that exist
+                have = sorted(doc_of)
+                take = [int(i) for i in rng.choice(have, size=min(len(have), int(rng.integers(1, 50))), replace=False)]
+                if rng.random() < 0.5:
+                    take.sort()
+                vecs = np.stack([new_vec() for _ in take])
+                st.save_embeddings_raw(chunk[take], vecs)
+                for i, v in zip(take, vecs):
+                    if i not in row_of:
+                        row_of[i] = len(row_of)
+                    vec_of[i] = v
+            if step % 4 != 3 or not row_of:
+                continue
+            n = len(row_of)
+            by_row = sorted(row_of, key=row_of.get)
+            mat = np.stack([vec_of[i] for i in by_row])
+            row_doc = np.asarray([doc_of[i] for i in by_row], dtype=np.uint32)
+            assert st.stats().rows == n
+            k = int(rng.choice([1, 5, 10, 20, 40]))
+            floor = float(rng.choice([0.7, 0.9, -1.0]))
+            wanted = sorted(set(int(d) for d in rng.integers(0, n_docs + 2, size=int(rng.integers(1, 6)))))
+            allowed = np.zeros(n_docs + 2, np.uint8)
+            allowed[wanted] = 1
+            info = dict(seed=seed, step=step, n=n, k=k, floor=floor, wanted=wanted)
+            o_rows, o_sc, _ = oracle.topk(mat, row_doc, allowed, q, k + 8, floor)
+            for kw in (dict(), dict(no_compact=True), dict(read_all_rows=True)):
+                ids, sc, rows = st.search(q, k, docs[wanted], min_similarity=floor, **kw)
+                why = topk_matches_extended(rows[0], sc[0], o_rows, o_sc, k)
+                assert why == "", (info, kw, why)
+                assert np.array_equal(ids[0], chunk[[by_row[r] for r in rows[0]]]), (info, kw)
+            qs = np.stack([q, q * np.float32(3.0)])
+            b = st.search(qs, k, docs[wanted], min_similarity=floor)
+            for i in range(2):
+                assert topk_matches_extended(b[2][i], b[1][i], o_rows, o_sc, k) == "", (info, "batch", i)
+            counts = st.doc_rows(docs[: n_docs])
+            assert list(counts) == [int((row_doc == d).sum()) for d in range(n_docs)], info
