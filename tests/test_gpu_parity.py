@@ -282,6 +282,26 @@ def test_pgvectors_published_cosine_distance_answers_on_the_device():
                 assert np.array_equal(ids[0][0], chunk[0])
 
 
+def test_pgvectors_ivfflat_cosine_regression_on_the_device():
+    """test/sql/ivfflat_cosine.sql of pgvector (see tests/test_oracle.py): rows [0,0,0], [1,2,3], [1,1,1]; ORDER BY val <=> '[3,3,3]'
+    gives [1,1,1], [1,2,3] -- the zero vector is not in a cosine index.  Exact scan and IVFFlat (lists = 1) on the device."""
+    from test_oracle import PGVECTOR_IVFFLAT_COSINE as c
+    mat = np.zeros((3, 4), np.float32); mat[:, :3] = c["rows"]
+    q = np.zeros(4, np.float32); q[:3] = c["query"]
+    chunk = oracle.chunk_ids(S0, 0, 3)
+    docs = oracle.doc_ids(S0, 0, 1)
+    with GpuStore(dim=4, capacity_rows=8) as st:
+        st.save_chunks_raw(docs[0], chunk)
+        st.save_embeddings_raw(chunk, mat)
+        ids, sc, rows = st.search(q, 10, all_docs=True, min_similarity=-10.0)
+        assert [int(r) for r in rows[0]] == c["order"]
+        assert abs(float(sc[0][0]) - 1.0) <= REL_TOL and abs(float(sc[0][1]) - 6.0 / np.sqrt(42.0)) <= REL_TOL
+        assert np.array_equal(ids[0], chunk[c["order"]])
+        st.build_ivf(lists=1, iters=2, seed=1, default_probes=1)
+        ids2, sc2, rows2 = st.search(q, 10, all_docs=True, min_similarity=-10.0, ivf=True)
+        assert [int(r) for r in rows2[0]] == c["order"] and np.array_equal(sc2[0], sc[0])
+
+
 @pytest.mark.parametrize("sidecar", [False, True])
 def test_a_zero_query_matches_nothing_on_any_path_whatever_the_floor(sidecar):
     """pgvector answers NaN for a zero vector; here such a query (like a zero row) matches nothing (DESIGN.md section 2,

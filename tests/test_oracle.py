@@ -86,6 +86,27 @@ def test_cosine_distance_gives_pgvectors_published_answers(a, b, want):
         assert scores[0] == np.float32(1.0 - want)
 
 
+# pgvector's regression test of the index the reference creates (test/sql/ivfflat_cosine.sql, published repository; restated):
+#   INSERT INTO t (val) VALUES ('[0,0,0]'), ('[1,2,3]'), ('[1,1,1]'), (NULL);
+#   CREATE INDEX ON t USING ivfflat (val vector_cosine_ops) WITH (lists = 1);
+#   SELECT * FROM t ORDER BY val <=> '[3,3,3]';      ->  [1,1,1], [1,2,3]      (2 rows)
+# The zero vector is not indexed under vector_cosine_ops, so a search through the index (postgres.go:95-99) never returns it:
+# deviation (1) of DESIGN.md section 2 ("zero-norm rows never match") is what the reference's own index does.
+PGVECTOR_IVFFLAT_COSINE = dict(rows=[[0, 0, 0], [1, 2, 3], [1, 1, 1]], query=[3, 3, 3], order=[2, 1])
+
+
+def test_order_and_zero_row_as_in_pgvectors_ivfflat_cosine_regression():
+    c = PGVECTOR_IVFFLAT_COSINE
+    mat = np.zeros((3, 4), np.float32); mat[:, :3] = c["rows"]
+    q = np.zeros(4, np.float32); q[:3] = c["query"]
+    for f64 in (False, True):
+        rows, scores, _ = oracle.topk(mat, None, None, q, 10, -10.0, f64=f64)
+        assert [int(r) for r in rows] == c["order"]
+        assert scores[0] == np.float32(1.0) and abs(float(scores[1]) - 6.0 / np.sqrt(14.0 * 3.0)) < 1e-6
+    rn, _, _ = oracle_np.topk(mat, None, None, q, 10, -10.0, f64=True)
+    assert [int(r) for r in rn] == c["order"]
+
+
 def test_synthetic_known_answers():
     g = GOLDEN["synthetic"]
     S = oracle.Synth()
