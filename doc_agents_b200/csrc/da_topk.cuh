@@ -260,20 +260,27 @@ __device__ void scan_cta_epilogue(const ScanArgs &a, const ScanPerQuery &pq, key
     key_t64 *buf = MP > P ? mbuf : lists;
     __syncthreads();
     if (tourney) {
-        // level 1: the 16 warps share each query's gridDim.x * K keys (<= 5 per lane), winners into the dead list area
-        const uint32_t share = (total + kScanWarps - 1) / kScanWarps;
-        const uint32_t lo = (uint32_t)warp * share, hi = lo + share < total ? lo + share : total;
-        for (int q = 0; q < a.nq; q++) {
-            const key_t64 mine = narrow ? tourney_cta_keys<kTourneyPerLane>(pq.cta_out, lo, hi, K, a.nq, q, lane)
-                                        : tourney_cta_keys<kTourneyPerLaneWide>(pq.cta_out, lo, hi, K, a.nq, q, lane);
-            if (lane < K) lists[(size_t)q * P + warp * K + lane] = mine;
+        // A handful of CTAs (one or two documents of the reference: 200 chunks each): all their keys fit one warp's registers,
+        // so warp q ranks query q's straight from the scratch -- one level instead of two.
+        const bool one_level = total <= 32u * (uint32_t)(narrow ? kTourneyL2Per : kTourneyL2PerWide);
+        if (!one_level) {
+            // level 1: the 16 warps share each query's gridDim.x * K keys (<= 5 per lane), winners into the dead list area
+            const uint32_t share = (total + kScanWarps - 1) / kScanWarps;
+            const uint32_t lo = (uint32_t)warp * share, hi = lo + share < total ? lo + share : total;
+            for (int q = 0; q < a.nq; q++) {
+                const key_t64 mine = narrow ? tourney_cta_keys<kTourneyPerLane>(pq.cta_out, lo, hi, K, a.nq, q, lane)
+                                            : tourney_cta_keys<kTourneyPerLaneWide>(pq.cta_out, lo, hi, K, a.nq, q, lane);
+                if (lane < K) lists[(size_t)q * P + warp * K + lane] = mine;
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        // level 2: warp q ranks query q's 16 x K winners and writes the records
+        // level 2: warp q ranks query q's 16 x K winners (or, one level, every CTA's keys) and writes the records
         if (warp < a.nq) {
             const int q = warp;
-            const key_t64 key = narrow ? tourney_smem<kTourneyL2Per>(lists + (size_t)q * P, kScanWarps * K, K, lane)
-                                       : tourney_smem<kTourneyL2PerWide>(lists + (size_t)q * P, kScanWarps * K, K, lane);
+            const key_t64 key = one_level ? (narrow ? tourney_cta_keys<kTourneyL2Per>(pq.cta_out, 0u, total, K, a.nq, q, lane)
+                                                    : tourney_cta_keys<kTourneyL2PerWide>(pq.cta_out, 0u, total, K, a.nq, q, lane))
+                                          : (narrow ? tourney_smem<kTourneyL2Per>(lists + (size_t)q * P, kScanWarps * K, K, lane)
+                                                    : tourney_smem<kTourneyL2PerWide>(lists + (size_t)q * P, kScanWarps * K, K, lane));
             if (lane < K) {
                 pq.out_keys[(size_t)q * K + lane] = key;
                 if (a.gate_out && lane == K - 1)
